@@ -1,0 +1,175 @@
+// C ABI glue: exception -> status translation, thread-local error text, small host helpers.
+// Boundary declared in include/canopy.h; replaces the empty reference TU src/canopy.cpp.
+#include <cmath>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "plan.h"
+
+namespace {
+thread_local std::string g_last_error;
+
+template <class F>
+canopy_status guard(F&& f) {
+    try {
+        g_last_error.clear();
+        f();
+        return CANOPY_OK;
+    } catch (const canopy::Error& e) {
+        g_last_error = e.what();
+        return e.code;
+    } catch (const std::bad_alloc&) {
+        g_last_error = "out of host memory";
+        return CANOPY_E_OOM;
+    } catch (const std::exception& e) {
+        g_last_error = e.what();
+        return CANOPY_E_INVALID;
+    } catch (...) {
+        g_last_error = "unknown error";
+        return CANOPY_E_INVALID;
+    }
+}
+void require(bool ok, const char* what) {
+    if (!ok) throw canopy::Error(CANOPY_E_INVALID, what);
+}
+}  // namespace
+
+extern "C" {
+
+canopy_status canopy_plan_create(const canopy_graph_desc* desc, const canopy_plan_opts* opts, canopy_plan** out_plan) {
+    return guard([&] {
+        require(desc && out_plan, "canopy_plan_create: null argument");
+        *out_plan = nullptr;
+        canopy_plan_opts o{};
+        if (opts) o = *opts;
+        if (o.threshold_bits == 0) o.threshold_bits = 32;
+        auto* p = new canopy_plan();
+        try {
+            canopy::lower_graph(*desc, o, p->low);
+        } catch (...) { delete p; throw; }
+        *out_plan = p;
+    });
+}
+
+void canopy_plan_destroy(canopy_plan* plan) {
+    if (!plan) return;
+    for (auto* s : plan->dev) canopy::destroy_device_state(s);
+    delete plan;
+}
+
+canopy_status canopy_plan_info(const canopy_plan* plan, canopy_plan_stats* out) {
+    return guard([&] {
+        require(plan && out, "canopy_plan_info: null argument");
+        *out = plan->low.stats;
+    });
+}
+
+canopy_status canopy_plan_view_get(const canopy_plan* plan, canopy_plan_view* v) {
+    return guard([&] {
+        require(plan && v, "canopy_plan_view_get: null argument");
+        const canopy::Lowered& L = plan->low;
+        v->n_events = L.n_events(); v->n_gates = L.n_gates(); v->n_layers = L.n_layers();
+        v->n_tallies = (uint32_t)L.tally_kind.size(); v->n_edges = L.child.size();
+        v->event_orig = L.event_orig.data(); v->event_thr32 = L.event_thr32.data(); v->event_thr64 = L.event_thr64.data();
+        v->gate_child_off = L.gate_child_off.data(); v->gate_child = L.child.data();
+        v->gate_op = L.gate_op.data(); v->gate_flags = L.gate_flags.data();
+        v->gate_kmin = L.gate_kmin.data(); v->gate_kmax = L.gate_kmax.data();
+        v->layer_off = L.layer_off.data(); v->tally_kind = L.tally_kind.data(); v->tally_gate = L.tally_gate.data();
+    });
+}
+
+void canopy_mc_opts_default(canopy_mc_opts* o) {
+    if (!o) return;
+    std::memset(o, 0, sizeof *o);
+    o->overlap = 1;
+}
+
+canopy_status canopy_mc_run(canopy_plan* plan, const canopy_mc_opts* opts, uint64_t* tallies_host, canopy_mc_report* report) {
+    return guard([&] {
+        require(plan && opts, "canopy_mc_run: null argument");
+        require(tallies_host || plan->low.tally_kind.empty(), "canopy_mc_run: tallies_host is null");
+        canopy_mc_report dummy;
+        canopy::mc_run(plan, *opts, tallies_host, nullptr, report ? report : &dummy);
+    });
+}
+
+canopy_status canopy_mc_run_device(canopy_plan* plan, const canopy_mc_opts* opts, uint64_t* tallies_device, canopy_mc_report* report) {
+    return guard([&] {
+        require(plan && opts, "canopy_mc_run_device: null argument");
+        require(tallies_device || plan->low.tally_kind.empty(), "canopy_mc_run_device: tallies_device is null");
+        canopy::mc_run(plan, *opts, nullptr, tallies_device, report);
+    });
+}
+
+canopy_status canopy_mc_run_multi(canopy_plan* plan, const canopy_mc_opts* opts, const int32_t* devices, int32_t n_devices,
+                                  uint64_t* tallies_host, canopy_mc_report* report) {
+    return guard([&] {
+        require(plan && opts && devices && n_devices > 0, "canopy_mc_run_multi: bad argument");
+        require(tallies_host || plan->low.tally_kind.empty(), "canopy_mc_run_multi: tallies_host is null");
+        canopy::mc_run_multi(plan, *opts, devices, n_devices, tallies_host, report);
+    });
+}
+
+canopy_status canopy_mc_sample_words(canopy_plan* plan, const canopy_mc_opts* opts, uint64_t first_word, uint64_t n_words,
+                                     uint64_t* words_host) {
+    return guard([&] {
+        require(plan && opts && words_host, "canopy_mc_sample_words: null argument");
+        canopy::mc_sample_words(plan, *opts, first_word, n_words, words_host);
+    });
+}
+
+canopy_status canopy_shard_range(uint64_t sample_begin, uint64_t n_samples, int32_t rank, int32_t world,
+                                 uint64_t* out_begin, uint64_t* out_n) {
+    return guard([&] {
+        require(out_begin && out_n, "canopy_shard_range: null argument");
+        canopy::shard_range(sample_begin, n_samples, rank, world, out_begin, out_n);
+    });
+}
+
+canopy_status canopy_estimate_from_tally(uint64_t tally, uint64_t n_samples, canopy_estimate* out) {
+    return guard([&] {
+        require(out != nullptr, "canopy_estimate_from_tally: null argument");
+        require(n_samples > 0 && tally <= n_samples, "canopy_estimate_from_tally: need 0 <= tally <= n_samples, n_samples > 0");
+        const double n = (double)n_samples, p = (double)tally / n;
+        const double sigma = std::sqrt(p * (1.0 - p) / n);
+        out->p = p; out->sigma = sigma;
+        out->ci_lo = std::fmax(0.0, p - 1.959963984540054 * sigma);
+        out->ci_hi = std::fmin(1.0, p + 1.959963984540054 * sigma);
+    });
+}
+
+canopy_status canopy_microbench_int(int32_t device, int32_t kind, double* out_lane_ops_per_s, double* out_ms) {
+    return guard([&] {
+        require(out_lane_ops_per_s && out_ms && kind >= 0 && kind <= 3, "canopy_microbench_int: bad argument");
+        canopy::microbench_int(device, kind, out_lane_ops_per_s, out_ms);
+    });
+}
+
+const char* canopy_last_error(void) { return g_last_error.c_str(); }
+
+const char* canopy_status_string(canopy_status s) {
+    switch (s) {
+        case CANOPY_OK: return "ok";
+        case CANOPY_E_INVALID: return "invalid argument";
+        case CANOPY_E_VALIDITY: return "validity error";
+        case CANOPY_E_CYCLE: return "cycle error";
+        case CANOPY_E_UNSUPPORTED: return "unsupported";
+        case CANOPY_E_CUDA: return "CUDA error";
+        case CANOPY_E_NCCL: return "NCCL error";
+        case CANOPY_E_OOM: return "out of memory";
+        case CANOPY_E_DOMAIN: return "domain error";
+        case CANOPY_E_IO: return "I/O error";
+    }
+    return "unknown";
+}
+
+uint32_t canopy_version(void) { return (CANOPY_VERSION_MAJOR << 16) | CANOPY_VERSION_MINOR; }
+uint32_t canopy_spec_version(void) { return CANOPY_SPEC_VERSION; }
+
+}  // extern "C"
+
+namespace canopy {
+// shared by mef_xml.cpp
+void set_last_error(const std::string& m) { g_last_error = m; }
+}

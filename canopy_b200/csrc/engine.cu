@@ -1,0 +1,581 @@
+// Monte Carlo engine: kernels + per-device state + the batch loop.  sm_100a only, no CPU fallback.
+// See kernels.cuh for the kernel inventory and DESIGN.md for layout, spec and roofline accounting.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+
+namespace canopy {
+
+#define CUDA_CHECK(expr)                                                                              \
+    do {                                                                                              \
+        cudaError_t _e = (expr);                                                                      \
+        if (_e != cudaSuccess)                                                                        \
+            throw Error(CANOPY_E_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));           \
+    } while (0)
+
+// ================================================================================================
+// Sampler kernel.  One warp per (basic event, slab); lane r owns words 2r and 2r+1 of the row, i.e.
+// 128 consecutive samples = 32 Philox calls (SPEC v1: call index q = s >> 2, lane of the call = s & 3).
+// All 32 calls are independent, so ILP comes for free; the only memory traffic is one LDG of the
+// threshold per warp and one 16-byte store per lane (512 B per warp, fully coalesced).
+// ================================================================================================
+template <int BITS>
+__global__ void __launch_bounds__(256)
+sampler_kernel(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_orig,
+               const uint32_t* __restrict__ thr32, const uint64_t* __restrict__ thr64,
+               uint32_t n_ev, uint32_t n_nodes, uint64_t first_slab, PhiloxKeys K) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t ev = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (ev >= n_ev) return;
+    const uint32_t slab = blockIdx.y;
+    const uint32_t e = __ldg(ev_orig + ev);
+    const uint64_t w0 = (first_slab + slab) * kSlabWords + 2 * lane;  // first global word of this lane
+    uint32_t out[4];
+    if (BITS == 32) {
+        const uint32_t thr = __ldg(thr32 + ev);
+        const uint64_t q = w0 * 16;  // 16 calls per 64-sample word; q % 32 == 0 so q_hi is fixed below
+        const uint32_t q_lo = (uint32_t)q, q_hi = (uint32_t)(q >> 32);
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+            uint32_t bits = 0;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const uint4 r = philox4x32_10(q_lo + h * 8 + c, q_hi, e, 0u, K);
+                bits |= (uint32_t)(r.x < thr) << (4 * c);
+                bits |= (uint32_t)(r.y < thr) << (4 * c + 1);
+                bits |= (uint32_t)(r.z < thr) << (4 * c + 2);
+                bits |= (uint32_t)(r.w < thr) << (4 * c + 3);
+            }
+            out[h] = bits;
+        }
+    } else {
+        const uint64_t thr = __ldg(thr64 + ev);
+        const uint64_t q = w0 * 32;  // 32 calls per word, 2 samples per call
+        const uint32_t q_lo = (uint32_t)q, q_hi = (uint32_t)(q >> 32);
+#pragma unroll 1
+        for (int h = 0; h < 4; ++h) {
+            uint32_t bits = 0;
+#pragma unroll
+            for (int c = 0; c < 16; ++c) {
+                const uint4 r = philox4x32_10(q_lo + h * 16 + c, q_hi, e, 1u, K);
+                const uint64_t u0 = ((uint64_t)r.y << 32) | r.x, u1 = ((uint64_t)r.w << 32) | r.z;
+                bits |= (uint32_t)(u0 < thr) << (2 * c);
+                bits |= (uint32_t)(u1 < thr) << (2 * c + 1);
+            }
+            out[h] = bits;
+        }
+    }
+    uint4* row = vals + ((size_t)slab * n_nodes + ev) * kRowVec;
+    st_cg(row + lane, make_uint4(out[0], out[1], out[2], out[3]));
+}
+
+// ================================================================================================
+// Gate kernel (slab walker).
+// ================================================================================================
+__device__ __forceinline__ uint4 and4(uint4 a, uint4 b) { return make_uint4(a.x & b.x, a.y & b.y, a.z & b.z, a.w & b.w); }
+__device__ __forceinline__ uint4 or4(uint4 a, uint4 b) { return make_uint4(a.x | b.x, a.y | b.y, a.z | b.z, a.w | b.w); }
+__device__ __forceinline__ uint4 xor4(uint4 a, uint4 b) { return make_uint4(a.x ^ b.x, a.y ^ b.y, a.z ^ b.z, a.w ^ b.w); }
+__device__ __forceinline__ uint4 xors4(uint4 a, uint32_t m) { return make_uint4(a.x ^ m, a.y ^ m, a.z ^ m, a.w ^ m); }
+__device__ __forceinline__ uint4 andn4(uint4 a, uint4 b) { return make_uint4(a.x & ~b.x, a.y & ~b.y, a.z & ~b.z, a.w & ~b.w); }
+__device__ __forceinline__ uint4 splat4(uint32_t v) { return make_uint4(v, v, v, v); }
+
+// Load one child row segment (16 B for this lane), applying the edge complement (bit 31 of the code).
+__device__ __forceinline__ uint4 load_child(const uint4* __restrict__ base, uint32_t code, uint32_t lane, bool ok,
+                                            uint32_t identity) {
+    if (!ok) return splat4(identity);
+    const uint32_t row = code & 0x7FFFFFFFu;
+    const uint32_t m = (uint32_t)((int32_t)code >> 31);
+    return xors4(ld_cg(base + (size_t)row * kRowVec + lane), m);
+}
+
+template <int OP>  // kDevAnd / kDevOr / kDevXor
+__device__ __forceinline__ uint4 eval_simple(const uint4* __restrict__ base, const uint32_t* __restrict__ child,
+                                             uint32_t n, uint32_t lane) {
+    constexpr uint32_t ident = OP == kDevAnd ? 0xFFFFFFFFu : 0u;
+    uint4 acc = splat4(ident);
+    for (uint32_t j0 = 0; j0 < n; j0 += 32) {
+        const uint32_t cnt = min(32u, n - j0);
+        const uint32_t my = lane < cnt ? __ldg(child + j0 + lane) : 0u;
+        for (uint32_t j = 0; j < cnt; j += 8) {
+            uint4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const uint32_t code = __shfl_sync(0xFFFFFFFFu, my, (j + u) & 31);
+                v[u] = load_child(base, code, lane, j + u < cnt, ident);
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+                acc = OP == kDevAnd ? and4(acc, v[u]) : OP == kDevOr ? or4(acc, v[u]) : xor4(acc, v[u]);
+        }
+    }
+    return acc;
+}
+
+// count-in-range with a bit-sliced ripple counter of P planes (P bits hold counts < 2^P).
+// V is the per-lane vector: uint4 (one pass, 16 B per lane per child) for the common fan-ins, or
+// uint32_t (four passes, one 32-bit component each) for fan-in >= 512 where 16 planes x 4 registers
+// would not fit the register budget of the common path.
+__device__ __forceinline__ uint32_t and4(uint32_t a, uint32_t b) { return a & b; }
+__device__ __forceinline__ uint32_t or4(uint32_t a, uint32_t b) { return a | b; }
+__device__ __forceinline__ uint32_t xor4(uint32_t a, uint32_t b) { return a ^ b; }
+__device__ __forceinline__ uint32_t andn4(uint32_t a, uint32_t b) { return a & ~b; }
+template <class V> __device__ __forceinline__ V splat(uint32_t v);
+template <> __device__ __forceinline__ uint4 splat<uint4>(uint32_t v) { return splat4(v); }
+template <> __device__ __forceinline__ uint32_t splat<uint32_t>(uint32_t v) { return v; }
+
+__device__ __forceinline__ void load_child_v(uint4& out, const uint4* __restrict__ base, uint32_t code, uint32_t lane, bool ok, int) {
+    out = load_child(base, code, lane, ok, 0u);
+}
+__device__ __forceinline__ void load_child_v(uint32_t& out, const uint4* __restrict__ base, uint32_t code, uint32_t lane, bool ok, int comp) {
+    if (!ok) { out = 0u; return; }
+    const uint32_t row = code & 0x7FFFFFFFu, m = (uint32_t)((int32_t)code >> 31);
+    out = __ldcg(reinterpret_cast<const uint32_t*>(base + (size_t)row * kRowVec + lane) + comp) ^ m;
+}
+
+template <int P, class V>
+__device__ __forceinline__ V eval_range(const uint4* __restrict__ base, const uint32_t* __restrict__ child,
+                                        uint32_t n, uint32_t lo, uint32_t hi, uint32_t lane, int comp) {
+    V pl[P];
+#pragma unroll
+    for (int p = 0; p < P; ++p) pl[p] = splat<V>(0u);
+    for (uint32_t j0 = 0; j0 < n; j0 += 32) {
+        const uint32_t cnt = min(32u, n - j0);
+        const uint32_t my = lane < cnt ? __ldg(child + j0 + lane) : 0u;
+        for (uint32_t j = 0; j < cnt; j += 4) {
+            V v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const uint32_t code = __shfl_sync(0xFFFFFFFFu, my, (j + u) & 31);
+                load_child_v(v[u], base, code, lane, j + u < cnt, comp);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                V carry = v[u];
+#pragma unroll
+                for (int p = 0; p < P; ++p) {
+                    const V t = and4(pl[p], carry);
+                    pl[p] = xor4(pl[p], carry);
+                    carry = t;
+                }
+            }
+        }
+    }
+    // count >= lo  (MSB-first comparison against the uniform constant lo)
+    V gt = splat<V>(0u), eq = splat<V>(0xFFFFFFFFu);
+#pragma unroll
+    for (int p = P - 1; p >= 0; --p) {
+        if ((lo >> p) & 1u) eq = and4(eq, pl[p]);
+        else { gt = or4(gt, and4(eq, pl[p])); eq = andn4(eq, pl[p]); }
+    }
+    V res = or4(gt, eq);
+    if (hi < n) {  // count <= hi
+        V lt = splat<V>(0u); eq = splat<V>(0xFFFFFFFFu);
+#pragma unroll
+        for (int p = P - 1; p >= 0; --p) {
+            if ((hi >> p) & 1u) { lt = or4(lt, andn4(eq, pl[p])); eq = and4(eq, pl[p]); }
+            else eq = andn4(eq, pl[p]);
+        }
+        res = and4(res, or4(lt, eq));
+    }
+    return res;
+}
+
+__device__ __forceinline__ uint32_t valid_mask32(uint64_t s, uint64_t begin, uint64_t end) {
+    if (s + 32 <= begin || s >= end) return 0u;
+    uint32_t m = 0xFFFFFFFFu;
+    if (s < begin) m &= 0xFFFFFFFFu << (uint32_t)(begin - s);
+    if (s + 32 > end) m &= 0xFFFFFFFFu >> (uint32_t)(s + 32 - end);
+    return m;
+}
+
+constexpr int kGateThreads = 256;
+
+__global__ void __launch_bounds__(kGateThreads)
+gate_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const uint32_t* __restrict__ child,
+            const uint32_t* __restrict__ layer_off, uint32_t n_layers, uint32_t n_nodes, uint32_t n_ev,
+            unsigned long long* __restrict__ tallies, uint64_t first_slab, uint64_t begin, uint64_t end) {
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+    const uint32_t slab = blockIdx.x;
+    uint4* base = vals + (size_t)slab * n_nodes * kRowVec;
+    const uint64_t s0 = (first_slab + slab) * (uint64_t)kSlabSamples + lane * 128u;
+    const uint4 mask = make_uint4(valid_mask32(s0, begin, end), valid_mask32(s0 + 32, begin, end),
+                                  valid_mask32(s0 + 64, begin, end), valid_mask32(s0 + 96, begin, end));
+    for (uint32_t l = 0; l < n_layers; ++l) {
+        const uint32_t g_end = __ldg(layer_off + l + 1);
+        for (uint32_t g = __ldg(layer_off + l) + warp; g < g_end; g += n_warps) {
+            const uint4 rec = __ldg(grec + g);
+            const uint32_t* ch = child + rec.x;
+            const uint32_t n = rec.y, op = rec.z & 0xFFu, flags = rec.z >> 8;
+            uint4 r;
+            if (op == kDevAnd) r = eval_simple<kDevAnd>(base, ch, n, lane);
+            else if (op == kDevOr) r = eval_simple<kDevOr>(base, ch, n, lane);
+            else if (op == kDevXor) r = eval_simple<kDevXor>(base, ch, n, lane);
+            else {
+                const uint32_t lo = rec.w & 0xFFFFu, hi = rec.w >> 16;
+                if (n < 8) r = eval_range<3, uint4>(base, ch, n, lo, hi, lane, 0);
+                else if (n < 64) r = eval_range<6, uint4>(base, ch, n, lo, hi, lane, 0);
+                else if (n < 512) r = eval_range<9, uint4>(base, ch, n, lo, hi, lane, 0);
+                else {
+                    r.x = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 0);
+                    r.y = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 1);
+                    r.z = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 2);
+                    r.w = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 3);
+                }
+            }
+            if (flags & kFlagStore) st_cg(base + (size_t)(n_ev + g) * kRowVec + lane, r);
+            if (flags & kFlagTally) {
+                uint32_t c = __popc(r.x & mask.x) + __popc(r.y & mask.y) + __popc(r.z & mask.z) + __popc(r.w & mask.w);
+                c = __reduce_add_sync(0xFFFFFFFFu, c);
+                if (lane == 0 && c) atomicAdd(tallies + g, (unsigned long long)c);
+            }
+        }
+        __syncthreads();  // rows written in this layer are read by later layers of the same CTA only
+    }
+}
+
+__global__ void finalize_kernel(unsigned long long* __restrict__ out, const unsigned long long* __restrict__ gate_tallies,
+                                const uint8_t* __restrict__ kind, const uint32_t* __restrict__ gate, uint32_t n,
+                                unsigned long long n_samples) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint8_t k = kind[i];
+    unsigned long long v = 0;
+    if (k == kTallyTrue) v = n_samples;
+    else if (k == kTallyGate) v = gate_tallies[gate[i]];
+    else if (k == kTallyNotGate) v = n_samples - gate_tallies[gate[i]];
+    out[i] = v;
+}
+
+// Repack rows of one batch into [event][word] order for the sampler parity hook.
+__global__ void gather_words_kernel(const uint4* __restrict__ vals, uint32_t n_ev, uint32_t n_nodes, uint32_t n_slabs,
+                                    unsigned long long* __restrict__ out /* [n_ev][n_slabs*64] */) {
+    const uint32_t ev = blockIdx.x, slab = blockIdx.y, t = threadIdx.x;  // 64 threads: one word each
+    const unsigned long long* row = (const unsigned long long*)(vals + ((size_t)slab * n_nodes + ev) * kRowVec);
+    out[((size_t)ev * n_slabs + slab) * kSlabWords + t] = row[t];
+}
+
+// ================================================================================================
+// Integer-pipe microbenchmarks (roofline denominators for the sampler; MEASURED_PEAKS.json has none).
+// ================================================================================================
+template <int KIND>
+__global__ void __launch_bounds__(256) intpeak_kernel(uint32_t* out, uint32_t iters, uint32_t seed) {
+    uint32_t a[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a[i] = seed * (threadIdx.x + 1) + i * 0x9E3779B9u + blockIdx.x;
+    const uint32_t b = seed ^ 0x5bd1e995u, c = seed + 77u;
+    for (uint32_t it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int rep = 0; rep < 4; ++rep) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                if (KIND == 0) {  // LOP3 with a loop-carried dependency per chain
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(b), "r"(c + i));
+                } else if (KIND == 1) {  // IMAD.WIDE.U32: 32x32 -> 64, consume hi ^ lo through the next multiply
+                    uint32_t lo, hi;
+                    asm volatile("{ .reg .u64 t; mul.wide.u32 t, %2, %3; mov.b64 {%0, %1}, t; }" : "=r"(lo), "=r"(hi) : "r"(a[i]), "r"(kPhiloxM0));
+                    a[i] = hi ^ lo;  // +1 LOP3 on the other pipe; counted as one IMAD.WIDE
+                } else if (KIND == 3) {
+                    asm volatile("popc.b32 %0, %0;" : "+r"(a[i]));
+                }
+            }
+            if (KIND == 2) {  // two interleaved Philox rounds-chains: 4 x (2 IMAD.WIDE + 2 LOP3)
+                philox_round(a[0], a[1], a[2], a[3], b, c);
+                philox_round(a[4], a[5], a[6], a[7], c, b);
+                philox_round(a[0], a[1], a[2], a[3], c, b);
+                philox_round(a[4], a[5], a[6], a[7], b, c);
+            }
+        }
+    }
+    uint32_t x = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x ^= a[i];
+    if (x == 0x12345678u) out[blockIdx.x * blockDim.x + threadIdx.x] = x;  // keep the chains alive
+}
+
+void microbench_int(int device, int kind, double* lane_ops_per_s, double* ms_out) {
+    CUDA_CHECK(cudaSetDevice(device));
+    cudaDeviceProp prop; CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
+    const int blocks = prop.multiProcessorCount * 8, threads = 256;
+    const uint32_t iters = 2048;
+    uint32_t* d = nullptr; CUDA_CHECK(cudaMalloc(&d, (size_t)blocks * threads * 4));
+    cudaEvent_t e0, e1; CUDA_CHECK(cudaEventCreate(&e0)); CUDA_CHECK(cudaEventCreate(&e1));
+    auto launch = [&]() {
+        switch (kind) {
+            case 0: intpeak_kernel<0><<<blocks, threads>>>(d, iters, 12345u); break;
+            case 1: intpeak_kernel<1><<<blocks, threads>>>(d, iters, 12345u); break;
+            case 2: intpeak_kernel<2><<<blocks, threads>>>(d, iters, 12345u); break;
+            default: intpeak_kernel<3><<<blocks, threads>>>(d, iters, 12345u); break;
+        }
+    };
+    for (int w = 0; w < 3; ++w) launch();
+    CUDA_CHECK(cudaDeviceSynchronize());
+    const int reps = 5;
+    CUDA_CHECK(cudaEventRecord(e0));
+    for (int r = 0; r < reps; ++r) launch();
+    CUDA_CHECK(cudaEventRecord(e1));
+    CUDA_CHECK(cudaEventSynchronize(e1));
+    float ms = 0; CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+    ms /= reps;
+    // lane-instructions per launch: kinds 0,1,3: iters*4*8 ; kind 2: iters*4*4 rounds * 4 instr
+    const double per_thread = kind == 2 ? (double)iters * 4 * 4 * 4 : (double)iters * 4 * 8;
+    *lane_ops_per_s = per_thread * blocks * threads / (ms * 1e-3);
+    *ms_out = ms;
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+}
+
+// ================================================================================================
+// Per-device state
+// ================================================================================================
+struct DeviceState {
+    int device = -1;
+    int sm_count = 0;
+    uint32_t *ev_orig = nullptr, *thr32 = nullptr, *child = nullptr, *layer_off = nullptr, *tally_gate = nullptr;
+    uint64_t* thr64 = nullptr;
+    uint4* grec = nullptr;
+    uint8_t* tally_kind = nullptr;
+    unsigned long long* gate_tallies = nullptr;
+    unsigned long long* out_tallies = nullptr;   // used when the caller wants host output
+    unsigned long long* host_tallies = nullptr;  // pinned staging
+    uint4* vals[2] = {nullptr, nullptr};
+    size_t vals_slabs = 0;  // capacity of each buffer in slabs
+    int n_bufs = 0;
+    cudaStream_t main = nullptr, s_sample = nullptr, s_gate = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_t0 = nullptr, ev_t1 = nullptr;
+    cudaEvent_t ev_sampled[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
+    uint64_t h2d_bytes = 0;
+    std::mutex run_mu;  // one run at a time per device (the value buffers and streams are per-device scratch)
+};
+
+void destroy_device_state(DeviceState* s) {
+    if (!s) return;
+    cudaSetDevice(s->device);
+    cudaFree(s->ev_orig); cudaFree(s->thr32); cudaFree(s->thr64); cudaFree(s->child); cudaFree(s->layer_off);
+    cudaFree(s->tally_gate); cudaFree(s->grec); cudaFree(s->tally_kind); cudaFree(s->gate_tallies);
+    cudaFree(s->out_tallies); cudaFreeHost(s->host_tallies); cudaFree(s->vals[0]); cudaFree(s->vals[1]);
+    if (s->main) cudaStreamDestroy(s->main);
+    if (s->s_sample) cudaStreamDestroy(s->s_sample);
+    if (s->s_gate) cudaStreamDestroy(s->s_gate);
+    for (cudaEvent_t e : {s->ev_fork, s->ev_join, s->ev_t0, s->ev_t1, s->ev_sampled[0], s->ev_sampled[1],
+                          s->ev_consumed[0], s->ev_consumed[1]})
+        if (e) cudaEventDestroy(e);
+    delete s;
+}
+
+template <class T>
+static T* upload(const std::vector<T>& v, uint64_t& bytes) {
+    T* d = nullptr;
+    const size_t n = std::max<size_t>(v.size(), 1) * sizeof(T);
+    if (cudaMalloc(&d, n) != cudaSuccess) throw Error(CANOPY_E_OOM, "cudaMalloc failed for plan arrays");
+    if (!v.empty()) CUDA_CHECK(cudaMemcpy(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+    bytes += v.size() * sizeof(T);
+    return d;
+}
+
+static DeviceState* get_state(canopy_plan* plan, int device) {
+    for (DeviceState* s : plan->dev) if (s->device == device) { CUDA_CHECK(cudaSetDevice(device)); return s; }
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
+        throw Error(CANOPY_E_CUDA, "no CUDA device available: libcanopy has no CPU fallback");
+    if (device < 0 || device >= count) throw Error(CANOPY_E_INVALID, "device ordinal out of range");
+    cudaDeviceProp prop; CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        throw Error(CANOPY_E_CUDA, std::string("device '") + prop.name + "' is sm_" + std::to_string(prop.major) +
+                                       std::to_string(prop.minor) + "; libcanopy is built for sm_100a only");
+    CUDA_CHECK(cudaSetDevice(device));
+    const Lowered& L = plan->low;
+    DeviceState* s = new DeviceState();
+    s->device = device; s->sm_count = prop.multiProcessorCount;
+    try {
+        s->ev_orig = upload(L.event_orig, s->h2d_bytes);
+        s->thr32 = upload(L.event_thr32, s->h2d_bytes);
+        s->thr64 = upload(L.event_thr64, s->h2d_bytes);
+        s->child = upload(L.child, s->h2d_bytes);
+        s->layer_off = upload(L.layer_off.empty() ? std::vector<uint32_t>{0} : L.layer_off, s->h2d_bytes);
+        s->tally_gate = upload(L.tally_gate, s->h2d_bytes);
+        s->tally_kind = upload(L.tally_kind, s->h2d_bytes);
+        static_assert(sizeof(GateRec) == sizeof(uint4), "GateRec must be 16 bytes");
+        s->grec = reinterpret_cast<uint4*>(upload(L.gate_rec, s->h2d_bytes));
+        const size_t ng = std::max<size_t>(L.n_gates(), 1), nt = std::max<size_t>(L.tally_kind.size(), 1);
+        CUDA_CHECK(cudaMalloc(&s->gate_tallies, ng * 8));
+        CUDA_CHECK(cudaMalloc(&s->out_tallies, nt * 8));
+        CUDA_CHECK(cudaMallocHost(&s->host_tallies, nt * 8));
+        CUDA_CHECK(cudaStreamCreateWithFlags(&s->main, cudaStreamNonBlocking));
+        CUDA_CHECK(cudaStreamCreateWithFlags(&s->s_sample, cudaStreamNonBlocking));
+        CUDA_CHECK(cudaStreamCreateWithFlags(&s->s_gate, cudaStreamNonBlocking));
+        for (cudaEvent_t* e : {&s->ev_fork, &s->ev_join, &s->ev_sampled[0], &s->ev_sampled[1], &s->ev_consumed[0], &s->ev_consumed[1]})
+            CUDA_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+        CUDA_CHECK(cudaEventCreate(&s->ev_t0)); CUDA_CHECK(cudaEventCreate(&s->ev_t1));
+    } catch (...) { destroy_device_state(s); throw; }
+    plan->dev.push_back(s);
+    return s;
+}
+
+static void ensure_vals(DeviceState* s, const Lowered& L, size_t slabs, int n_bufs) {
+    if (s->vals_slabs >= slabs && s->n_bufs >= n_bufs) return;
+    for (int b = 0; b < 2; ++b) { cudaFree(s->vals[b]); s->vals[b] = nullptr; }
+    s->vals_slabs = 0; s->n_bufs = 0;
+    const size_t bytes = slabs * (size_t)L.n_nodes() * kRowBytes;
+    for (int b = 0; b < n_bufs; ++b)
+        if (cudaMalloc(&s->vals[b], std::max<size_t>(bytes, 16)) != cudaSuccess) {
+            cudaGetLastError();
+            throw Error(CANOPY_E_OOM, "cudaMalloc failed for the value buffer (" + std::to_string(bytes >> 20) + " MiB)");
+        }
+    s->vals_slabs = slabs; s->n_bufs = n_bufs;
+}
+
+static PhiloxKeys make_keys(uint64_t seed) {
+    PhiloxKeys K;
+    uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+    for (int r = 0; r < 10; ++r) { K.k0[r] = k0; K.k1[r] = k1; k0 += kPhiloxW0; k1 += kPhiloxW1; }
+    return K;
+}
+
+static void launch_sampler(const DeviceState* s, const Lowered& L, uint4* vals, uint64_t first_slab, uint32_t n_slabs,
+                           const PhiloxKeys& K, cudaStream_t st) {
+    if (L.n_events() == 0 || n_slabs == 0) return;
+    const dim3 grid((L.n_events() + 7) / 8, n_slabs), block(256);
+    if (L.opts.threshold_bits == 64)
+        sampler_kernel<64><<<grid, block, 0, st>>>(vals, s->ev_orig, s->thr32, s->thr64, L.n_events(), L.n_nodes(), first_slab, K);
+    else
+        sampler_kernel<32><<<grid, block, 0, st>>>(vals, s->ev_orig, s->thr32, s->thr64, L.n_events(), L.n_nodes(), first_slab, K);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+static void launch_gates(const DeviceState* s, const Lowered& L, uint4* vals, uint64_t first_slab, uint32_t n_slabs,
+                         uint64_t begin, uint64_t end, cudaStream_t st) {
+    if (L.n_gates() == 0 || n_slabs == 0) return;
+    gate_kernel<<<n_slabs, kGateThreads, 0, st>>>(vals, s->grec, s->child, s->layer_off, L.n_layers(), L.n_nodes(),
+                                                  L.n_events(), s->gate_tallies, first_slab, begin, end);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+static uint32_t pick_batch_slabs(const DeviceState* s, const Lowered& L, const canopy_mc_opts& o, uint64_t total_slabs, int n_bufs) {
+    uint64_t want = o.batch_slabs > 0 ? (uint64_t)o.batch_slabs : (uint64_t)s->sm_count * 4;
+    size_t free_b = 0, total_b = 0;
+    CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
+    free_b += s->vals_slabs * (size_t)L.n_nodes() * kRowBytes * s->n_bufs;  // what we would release on regrow
+    const size_t per_slab = (size_t)L.n_nodes() * kRowBytes;
+    const uint64_t fit = per_slab ? (uint64_t)((free_b / 2) / (per_slab * n_bufs)) : want;
+    if (fit == 0) throw Error(CANOPY_E_OOM, "one slab of node rows does not fit in device memory");
+    want = std::min(want, fit);
+    want = std::min<uint64_t>(want, 65535);
+    want = std::min(want, std::max<uint64_t>(total_slabs, 1));
+    return (uint32_t)want;
+}
+
+void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, uint64_t* tallies_dev, canopy_mc_report* rep) {
+    const Lowered& L = plan->low;
+    DeviceState* s = nullptr;
+    { std::lock_guard<std::mutex> lock(plan->mu); s = get_state(plan, o.device); }
+    std::lock_guard<std::mutex> run_lock(s->run_mu);
+    if (o.sample_begin + o.n_samples < o.sample_begin) throw Error(CANOPY_E_INVALID, "sample range overflows 64 bits");
+    const uint64_t begin = o.sample_begin, end = o.sample_begin + o.n_samples;
+    const uint64_t slab0 = begin / kSlabSamples;
+    const uint64_t total_slabs = o.n_samples ? (end - 1) / kSlabSamples - slab0 + 1 : 0;
+    const bool profile = o.profile != 0;
+    bool overlap = o.overlap != 0 && !profile;
+    cudaStream_t user = o.stream ? (cudaStream_t)o.stream : s->main;
+    const uint32_t n_tallies = (uint32_t)L.tally_kind.size();
+    unsigned long long* d_out = tallies_dev ? (unsigned long long*)tallies_dev : s->out_tallies;
+
+    uint32_t batch = 1; uint64_t n_batches = 0;
+    if (total_slabs && L.n_gates()) {
+        batch = pick_batch_slabs(s, L, o, total_slabs, overlap ? 2 : 1);
+        n_batches = (total_slabs + batch - 1) / batch;
+        if (n_batches < 2) overlap = false;
+        ensure_vals(s, L, batch, overlap ? 2 : 1);
+    }
+    const PhiloxKeys K = make_keys(o.seed);
+    canopy_mc_report R{};
+    R.slab_samples = kSlabSamples; R.batch_slabs = batch; R.n_batches = n_batches;
+
+    CUDA_CHECK(cudaEventRecord(s->ev_t0, user));
+    CUDA_CHECK(cudaMemsetAsync(s->gate_tallies, 0, std::max<size_t>(L.n_gates(), 1) * 8, user));
+    R.other_launches += 1;
+    std::vector<cudaEvent_t> pe;  // profile events: 4 per batch
+    if (!overlap) {
+        for (uint64_t b = 0; b < n_batches; ++b) {
+            const uint64_t fs = slab0 + b * batch;
+            const uint32_t ns = (uint32_t)std::min<uint64_t>(batch, total_slabs - b * batch);
+            if (profile) { cudaEvent_t e[3]; for (auto& x : e) { CUDA_CHECK(cudaEventCreate(&x)); pe.push_back(x); } CUDA_CHECK(cudaEventRecord(e[0], user)); }
+            launch_sampler(s, L, s->vals[0], fs, ns, K, user);
+            if (profile) CUDA_CHECK(cudaEventRecord(pe[pe.size() - 2], user));
+            launch_gates(s, L, s->vals[0], fs, ns, begin, end, user);
+            if (profile) CUDA_CHECK(cudaEventRecord(pe[pe.size() - 1], user));
+            R.sampler_launches += L.n_events() ? 1 : 0; R.gate_launches += 1;
+        }
+    } else {
+        // sampler of batch b+1 (integer-pipe bound) runs beside the gate walk of batch b (HBM bound)
+        CUDA_CHECK(cudaEventRecord(s->ev_fork, user));
+        CUDA_CHECK(cudaStreamWaitEvent(s->s_sample, s->ev_fork, 0));
+        CUDA_CHECK(cudaStreamWaitEvent(s->s_gate, s->ev_fork, 0));
+        for (uint64_t b = 0; b < n_batches; ++b) {
+            const int buf = (int)(b & 1);
+            const uint64_t fs = slab0 + b * batch;
+            const uint32_t ns = (uint32_t)std::min<uint64_t>(batch, total_slabs - b * batch);
+            if (b >= 2) CUDA_CHECK(cudaStreamWaitEvent(s->s_sample, s->ev_consumed[buf], 0));
+            launch_sampler(s, L, s->vals[buf], fs, ns, K, s->s_sample);
+            CUDA_CHECK(cudaEventRecord(s->ev_sampled[buf], s->s_sample));
+            CUDA_CHECK(cudaStreamWaitEvent(s->s_gate, s->ev_sampled[buf], 0));
+            launch_gates(s, L, s->vals[buf], fs, ns, begin, end, s->s_gate);
+            CUDA_CHECK(cudaEventRecord(s->ev_consumed[buf], s->s_gate));
+            R.sampler_launches += L.n_events() ? 1 : 0; R.gate_launches += 1;
+        }
+        CUDA_CHECK(cudaEventRecord(s->ev_join, s->s_gate));
+        CUDA_CHECK(cudaStreamWaitEvent(user, s->ev_join, 0));
+    }
+    if (n_tallies) {
+        finalize_kernel<<<(n_tallies + 255) / 256, 256, 0, user>>>(d_out, s->gate_tallies, s->tally_kind, s->tally_gate,
+                                                                  n_tallies, (unsigned long long)o.n_samples);
+        CUDA_CHECK(cudaGetLastError());
+        R.other_launches += 1;
+    }
+    CUDA_CHECK(cudaEventRecord(s->ev_t1, user));
+    if (tallies_host && n_tallies) {
+        CUDA_CHECK(cudaMemcpyAsync(s->host_tallies, d_out, (size_t)n_tallies * 8, cudaMemcpyDeviceToHost, user));
+        R.d2h_bytes = (uint64_t)n_tallies * 8;
+    }
+    if (tallies_host || rep || profile) {
+        CUDA_CHECK(cudaStreamSynchronize(user));
+        if (tallies_host && n_tallies) std::memcpy(tallies_host, s->host_tallies, (size_t)n_tallies * 8);
+        float ms = 0; CUDA_CHECK(cudaEventElapsedTime(&ms, s->ev_t0, s->ev_t1)); R.total_ms = ms;
+        for (size_t i = 0; i + 3 <= pe.size(); i += 3) {
+            float a = 0, b2 = 0;
+            CUDA_CHECK(cudaEventElapsedTime(&a, pe[i], pe[i + 1]));
+            CUDA_CHECK(cudaEventElapsedTime(&b2, pe[i + 1], pe[i + 2]));
+            R.sampler_ms += a; R.gate_ms += b2;
+        }
+    }
+    for (cudaEvent_t e : pe) cudaEventDestroy(e);
+    R.h2d_bytes = s->h2d_bytes;
+    if (rep) *rep = R;
+}
+
+void mc_sample_words(canopy_plan* plan, const canopy_mc_opts& o, uint64_t first_word, uint64_t n_words, uint64_t* words_host) {
+    const Lowered& L = plan->low;
+    DeviceState* s = nullptr;
+    { std::lock_guard<std::mutex> lock(plan->mu); s = get_state(plan, o.device); }
+    std::lock_guard<std::mutex> run_lock(s->run_mu);
+    if (first_word % kSlabWords || n_words % kSlabWords || n_words == 0)
+        throw Error(CANOPY_E_INVALID, "first_word and n_words must be multiples of 64 (one slab)");
+    if (L.n_events() == 0) return;
+    const uint64_t n_slabs = n_words / kSlabWords;
+    if (n_slabs > 65535) throw Error(CANOPY_E_INVALID, "too many words requested");
+    ensure_vals(s, L, n_slabs, 1);
+    const PhiloxKeys K = make_keys(o.seed);
+    launch_sampler(s, L, s->vals[0], first_word / kSlabWords, (uint32_t)n_slabs, K, s->main);
+    unsigned long long* d = nullptr;
+    const size_t bytes = (size_t)L.n_events() * n_words * 8;
+    if (cudaMalloc(&d, bytes) != cudaSuccess) throw Error(CANOPY_E_OOM, "cudaMalloc failed");
+    gather_words_kernel<<<dim3(L.n_events(), (uint32_t)n_slabs), kSlabWords, 0, s->main>>>(s->vals[0], L.n_events(), L.n_nodes(), (uint32_t)n_slabs, d);
+    cudaError_t e = cudaMemcpyAsync(words_host, d, bytes, cudaMemcpyDeviceToHost, s->main);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s->main);
+    cudaFree(d);
+    CUDA_CHECK(e);
+}
+
+}  // namespace canopy

@@ -1,0 +1,141 @@
+// Single-process multi-GPU run: contiguous Philox counter ranges per device, one host
+// thread per device, then ONE ncclAllReduce(ncclUint64, ncclSum) over the final tallies on NVLink.
+// The tallies buffer the engine finalises into is the buffer NCCL reduces in place on the same stream:
+// no staging copy and no host synchronisation sits between the last gate kernel and the collective.
+//
+// NCCL is bound lazily with dlopen("libnccl.so.2") so that libcanopy has no load-time dependency on it
+// (the torchrun path lets torch.distributed own the communicator and only needs canopy_mc_run_device).
+#include <dlfcn.h>
+#include <nccl.h>  // types only; no symbol is linked
+
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "plan.h"
+
+namespace canopy {
+namespace {
+
+struct NcclApi {
+    void* h = nullptr;
+    ncclResult_t (*CommInitAll)(ncclComm_t*, int, const int*) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+
+NcclApi& nccl() {
+    static NcclApi api;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        api.h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!api.h) api.h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (!api.h) return;
+        api.CommInitAll = (decltype(api.CommInitAll))dlsym(api.h, "ncclCommInitAll");
+        api.CommDestroy = (decltype(api.CommDestroy))dlsym(api.h, "ncclCommDestroy");
+        api.AllReduce = (decltype(api.AllReduce))dlsym(api.h, "ncclAllReduce");
+        api.GroupStart = (decltype(api.GroupStart))dlsym(api.h, "ncclGroupStart");
+        api.GroupEnd = (decltype(api.GroupEnd))dlsym(api.h, "ncclGroupEnd");
+        api.GetErrorString = (decltype(api.GetErrorString))dlsym(api.h, "ncclGetErrorString");
+    });
+    if (!api.h || !api.CommInitAll || !api.AllReduce || !api.CommDestroy || !api.GroupStart || !api.GroupEnd)
+        throw Error(CANOPY_E_NCCL, "libnccl.so.2 could not be loaded");
+    return api;
+}
+
+void nccl_check(ncclResult_t r, const char* what) {
+    if (r != ncclSuccess) {
+        NcclApi& a = nccl();
+        throw Error(CANOPY_E_NCCL, std::string(what) + ": " + (a.GetErrorString ? a.GetErrorString(r) : "nccl error"));
+    }
+}
+
+struct CommSet { std::vector<ncclComm_t> comms; };
+std::mutex g_comm_mu;
+std::map<std::vector<int>, CommSet> g_comms;  // communicators are cached per device list for the process lifetime
+
+CommSet& get_comms(const std::vector<int>& devs) {
+    std::lock_guard<std::mutex> lock(g_comm_mu);
+    auto it = g_comms.find(devs);
+    if (it != g_comms.end()) return it->second;
+    CommSet cs; cs.comms.resize(devs.size());
+    nccl_check(nccl().CommInitAll(cs.comms.data(), (int)devs.size(), devs.data()), "ncclCommInitAll");
+    return g_comms.emplace(devs, std::move(cs)).first->second;
+}
+
+#define CU(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) throw Error(CANOPY_E_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); } while (0)
+
+}  // namespace
+
+void mc_run_multi(canopy_plan* plan, const canopy_mc_opts& o, const int32_t* devices, int32_t n_devices,
+                  uint64_t* tallies_host, canopy_mc_report* rep) {
+    const size_t nt = plan->low.tally_kind.size();
+    std::vector<int> devs(devices, devices + n_devices);
+    if (n_devices == 1) {  // degenerate: no collective
+        canopy_mc_opts o1 = o; o1.device = devs[0];
+        mc_run(plan, o1, tallies_host, nullptr, rep);
+        return;
+    }
+    CommSet& cs = get_comms(devs);
+    std::vector<unsigned long long*> d_t(n_devices, nullptr);
+    std::vector<cudaStream_t> st(n_devices, nullptr);
+    std::vector<canopy_mc_report> reps(n_devices);
+    std::vector<std::string> errs(n_devices);
+    std::vector<canopy_status> codes(n_devices, CANOPY_OK);
+    std::vector<std::thread> th;
+    for (int i = 0; i < n_devices; ++i) {
+        th.emplace_back([&, i] {
+            try {
+                CU(cudaSetDevice(devs[i]));
+                CU(cudaMalloc(&d_t[i], std::max<size_t>(nt, 1) * 8));
+                CU(cudaStreamCreateWithFlags(&st[i], cudaStreamNonBlocking));
+                canopy_mc_opts oi = o;
+                oi.device = devs[i]; oi.stream = st[i];
+                shard_range(o.sample_begin, o.n_samples, i, n_devices, &oi.sample_begin, &oi.n_samples);
+                mc_run(plan, oi, nullptr, (uint64_t*)d_t[i], &reps[i]);
+            } catch (const Error& e) { codes[i] = e.code; errs[i] = e.what(); }
+        });
+    }
+    for (auto& t : th) t.join();
+    auto cleanup = [&] {
+        for (int i = 0; i < n_devices; ++i) {
+            cudaSetDevice(devs[i]);
+            if (st[i]) { cudaStreamSynchronize(st[i]); cudaStreamDestroy(st[i]); }
+            cudaFree(d_t[i]);
+        }
+    };
+    for (int i = 0; i < n_devices; ++i)
+        if (codes[i] != CANOPY_OK) { cleanup(); throw Error(codes[i], "device " + std::to_string(devs[i]) + ": " + errs[i]); }
+    try {
+        if (nt) {
+            nccl_check(nccl().GroupStart(), "ncclGroupStart");
+            for (int i = 0; i < n_devices; ++i)
+                nccl_check(nccl().AllReduce(d_t[i], d_t[i], nt, ncclUint64, ncclSum, cs.comms[i], st[i]), "ncclAllReduce");
+            nccl_check(nccl().GroupEnd(), "ncclGroupEnd");
+            CU(cudaSetDevice(devs[0]));
+            CU(cudaMemcpyAsync(tallies_host, d_t[0], nt * 8, cudaMemcpyDeviceToHost, st[0]));
+        }
+        for (int i = 0; i < n_devices; ++i) { CU(cudaSetDevice(devs[i])); CU(cudaStreamSynchronize(st[i])); }
+    } catch (...) { cleanup(); throw; }
+    cleanup();
+    if (rep) {
+        *rep = reps[0];
+        for (int i = 1; i < n_devices; ++i) {
+            rep->total_ms = std::max(rep->total_ms, reps[i].total_ms);
+            rep->sampler_launches += reps[i].sampler_launches; rep->gate_launches += reps[i].gate_launches;
+            rep->other_launches += reps[i].other_launches; rep->n_batches += reps[i].n_batches;
+            rep->h2d_bytes += reps[i].h2d_bytes;
+        }
+        rep->d2h_bytes = nt * 8;
+    }
+}
+
+}  // namespace canopy

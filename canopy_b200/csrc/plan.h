@@ -1,0 +1,89 @@
+// Internal structures of libcanopy: the lowered (device-ready) form of a MEF gate DAG.
+// Public boundary: include/canopy.h.  Nothing here is visible to callers.
+#pragma once
+#include <cstdint>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "canopy.h"
+
+namespace canopy {
+
+// Error carrying a status code; translated to canopy_status + thread-local message at the C boundary.
+// Mirrors the reference's exception hierarchy only by code (reference src/mef/openpsa/error.h:23-96).
+struct Error : std::runtime_error {
+    canopy_status code;
+    Error(canopy_status c, const std::string& m) : std::runtime_error(m), code(c) {}
+};
+
+// Device connectives after canonicalisation. Every MEF connective (event.h:143-157) lowers to one of
+// these plus edge complements: nand/nor/iff become a complemented reference to and/or/xor,
+// imply(a,b) = or(!a,b), not/null become aliases, atleast/cardinality become kRange[lo,hi].
+enum DevOp : uint8_t { kDevAnd = 0, kDevOr = 1, kDevXor = 2, kDevRange = 3 };
+enum GateFlags : uint8_t { kFlagInvert = 1, kFlagStore = 2, kFlagTally = 4 };
+enum TallyKind : uint8_t { kTallyFalse = 0, kTallyTrue = 1, kTallyGate = 2, kTallyNotGate = 3 };
+
+// Geometry of the value buffer. A slab is a tile of 4096 consecutive samples: 64 words of 64 samples;
+// one node row inside a slab is 64 words = 512 bytes = 32 lanes x 16 bytes, so one warp moves one row
+// with one 128-bit access per lane.
+constexpr uint32_t kSlabWords = 64;
+constexpr uint32_t kSlabSamples = kSlabWords * 64;   // 4096
+constexpr uint32_t kRowBytes = kSlabWords * 8;       // 512
+constexpr uint32_t kRowVec = 32;                     // uint4 per row
+
+struct GateRec {           // 16 bytes, loaded as one uint4 by the gate kernel
+    uint32_t child_off;    // into Lowered::child
+    uint32_t n_children;
+    uint32_t op_flags;     // op | flags << 8
+    uint32_t krange;       // lo | hi << 16   (kDevRange only)
+};
+
+struct Lowered {
+    canopy_plan_opts opts{};
+    canopy_plan_stats stats{};
+    // live basic events, ascending original index; device node id == position
+    std::vector<uint32_t> event_orig;
+    std::vector<uint32_t> event_thr32;
+    std::vector<uint64_t> event_thr64;
+    // live gates in layer order; device node id == n_events + position
+    std::vector<GateRec> gate_rec;
+    std::vector<uint32_t> gate_child_off;  // [n_gates+1] (same offsets as GateRec, kept for the view)
+    std::vector<uint32_t> child;           // device node id | complement << 31
+    std::vector<uint8_t> gate_op, gate_flags;
+    std::vector<uint16_t> gate_kmin, gate_kmax;
+    std::vector<uint32_t> layer_off;       // [n_layers+1]
+    // output mapping: user-visible tallies -> device gate tallies
+    std::vector<uint8_t> tally_kind;
+    std::vector<uint32_t> tally_gate;
+    uint32_t n_events() const { return (uint32_t)event_orig.size(); }
+    uint32_t n_gates() const { return (uint32_t)gate_rec.size(); }
+    uint32_t n_nodes() const { return n_events() + n_gates(); }
+    uint32_t n_layers() const { return layer_off.empty() ? 0 : (uint32_t)layer_off.size() - 1; }
+};
+
+void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lowered& out);
+
+struct DeviceState;  // engine.cu
+void destroy_device_state(DeviceState*);
+
+}  // namespace canopy
+
+struct canopy_plan {
+    canopy::Lowered low;
+    std::mutex mu;  // serialises runs on one plan (per-device scratch is owned by the plan)
+    std::vector<canopy::DeviceState*> dev;  // lazily created, one per CUDA ordinal used
+};
+
+namespace canopy {
+// engine.cu
+void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, uint64_t* tallies_dev,
+            canopy_mc_report* rep);
+void mc_sample_words(canopy_plan* plan, const canopy_mc_opts& o, uint64_t first_word, uint64_t n_words,
+                     uint64_t* words_host);
+void mc_run_multi(canopy_plan* plan, const canopy_mc_opts& o, const int32_t* devices, int32_t n_devices,
+                  uint64_t* tallies_host, canopy_mc_report* rep);
+void microbench_int(int device, int kind, double* lane_ops_per_s, double* ms);
+void shard_range(uint64_t begin, uint64_t n, int rank, int world, uint64_t* ob, uint64_t* on);
+}  // namespace canopy

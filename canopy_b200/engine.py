@@ -1,0 +1,229 @@
+"""Host-side mirror of the quantification interface, over the C ABI (include/canopy.h).
+
+Vocabulary follows the reference: `Settings` carries the Monte Carlo knobs of
+reference src/mef/openpsa/settings.h:118-187,324-327 (num_trials, seed, batch_size), widened to 64 bit;
+`Plan` is the lowered fault-tree DAG; `run()` returns tallies per top event / per gate.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import _lib
+from .graph import CGraphDesc, Graph
+
+
+class SettingsError(ValueError):
+    """reference src/mef/openpsa/error.h:66 (SettingsError)."""
+
+
+@dataclass
+class Settings:
+    """Monte Carlo subset of the reference Settings builder (settings.h:118-187)."""
+    num_trials: int = 1000      # settings.h:325 default 1e3
+    seed: int = 0               # settings.h:324
+    batch_size: int = 0         # slabs per batch here (settings.h:326 is 1 trial); 0 = engine default
+    sample_begin: int = 0       # first global sample index (restart / shard by counter range)
+    tally_all_gates: bool = False
+    threshold_bits: int = 32
+    overlap: bool = True
+    profile: bool = False
+
+    def validate(self):
+        if self.num_trials < 1:
+            raise SettingsError("The number of trials cannot be less than 1.")      # settings.h:129
+        if self.seed < 0:
+            raise SettingsError("The seed for PRNG cannot be negative.")            # settings.h:186
+        if self.batch_size < 0:
+            raise SettingsError("The batch size cannot be negative.")
+        if self.threshold_bits not in (32, 64):
+            raise SettingsError("threshold_bits must be 32 or 64")
+        return self
+
+
+@dataclass
+class Report:
+    total_ms: float
+    sampler_ms: float
+    gate_ms: float
+    sampler_launches: int
+    gate_launches: int
+    other_launches: int
+    n_batches: int
+    slab_samples: int
+    batch_slabs: int
+    h2d_bytes: int
+    d2h_bytes: int
+
+    @property
+    def launches(self) -> int:
+        return self.sampler_launches + self.gate_launches + self.other_launches
+
+
+def _report(r: _lib.CMcReport) -> Report:
+    return Report(r.total_ms, r.sampler_ms, r.gate_ms, r.sampler_launches, r.gate_launches, r.other_launches,
+                  r.n_batches, r.slab_samples, r.batch_slabs, r.h2d_bytes, r.d2h_bytes)
+
+
+def _arr(ptr, n, dtype):
+    if n == 0:
+        return np.zeros(0, dtype=dtype)
+    return np.ctypeslib.as_array(ptr, shape=(n,)).astype(dtype, copy=True)
+
+
+class Plan:
+    """Lowered DAG (host) + lazily created per-device state (owned by libcanopy)."""
+
+    def __init__(self, graph: Graph, tally_all_gates: bool = False, threshold_bits: int = 32):
+        self._h = C.c_void_p()
+        self.graph = graph
+        self.tally_all_gates = bool(tally_all_gates)
+        self.threshold_bits = threshold_bits
+        desc = graph.c_desc()
+        opts = _lib.CPlanOpts(tally_all_gates=int(tally_all_gates), threshold_bits=threshold_bits)
+        _lib.check(_lib.lib().canopy_plan_create(C.byref(desc), C.byref(opts), C.byref(self._h)))
+        st = _lib.CPlanStats()
+        _lib.check(_lib.lib().canopy_plan_info(self._h, C.byref(st)))
+        self.stats = {f: getattr(st, f) for f, _ in _lib.CPlanStats._fields_}
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            _lib.lib().canopy_plan_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    @property
+    def n_tallies(self) -> int:
+        return int(self.stats["n_tallies"])
+
+    def view(self) -> dict:
+        """Copies of the lowered arrays (for the host-logic tests)."""
+        v = _lib.CPlanView()
+        _lib.check(_lib.lib().canopy_plan_view_get(self._h, C.byref(v)))
+        return dict(
+            n_events=v.n_events, n_gates=v.n_gates, n_layers=v.n_layers, n_tallies=v.n_tallies, n_edges=v.n_edges,
+            event_orig=_arr(v.event_orig, v.n_events, np.uint32), event_thr32=_arr(v.event_thr32, v.n_events, np.uint32),
+            event_thr64=_arr(v.event_thr64, v.n_events, np.uint64),
+            gate_child_off=_arr(v.gate_child_off, v.n_gates + 1, np.uint32), gate_child=_arr(v.gate_child, v.n_edges, np.uint32),
+            gate_op=_arr(v.gate_op, v.n_gates, np.uint8), gate_flags=_arr(v.gate_flags, v.n_gates, np.uint8),
+            gate_kmin=_arr(v.gate_kmin, v.n_gates, np.uint16), gate_kmax=_arr(v.gate_kmax, v.n_gates, np.uint16),
+            layer_off=_arr(v.layer_off, v.n_layers + 1, np.uint32),
+            tally_kind=_arr(v.tally_kind, v.n_tallies, np.uint8), tally_gate=_arr(v.tally_gate, v.n_tallies, np.uint32))
+
+    def _opts(self, seed, sample_begin, n_samples, device, batch_slabs, stream, overlap, profile) -> _lib.CMcOpts:
+        o = _lib.CMcOpts()
+        _lib.lib().canopy_mc_opts_default(C.byref(o))
+        o.seed, o.sample_begin, o.n_samples = int(seed), int(sample_begin), int(n_samples)
+        o.device, o.batch_slabs = int(device), int(batch_slabs)
+        o.stream = stream
+        o.overlap, o.profile = int(bool(overlap)), int(bool(profile))
+        return o
+
+    def run(self, n_samples: int, seed: int = 0, sample_begin: int = 0, device: int = 0, batch_slabs: int = 0,
+            stream=None, overlap: bool = True, profile: bool = False):
+        """Tallies into a HOST buffer (h2d/d2h inside the call). Returns (uint64[n_tallies], Report)."""
+        o = self._opts(seed, sample_begin, n_samples, device, batch_slabs, stream, overlap, profile)
+        out = np.zeros(max(self.n_tallies, 1), dtype=np.uint64)
+        rep = _lib.CMcReport()
+        _lib.check(_lib.lib().canopy_mc_run(self._h, C.byref(o), out.ctypes.data_as(C.POINTER(C.c_uint64)), C.byref(rep)))
+        return out[: self.n_tallies], _report(rep)
+
+    def run_device(self, tallies_ptr: int, n_samples: int, seed: int = 0, sample_begin: int = 0, device: int = 0,
+                   batch_slabs: int = 0, stream=None, overlap: bool = True, profile: bool = False, want_report: bool = False):
+        """Tallies left in DEVICE memory at `tallies_ptr` (uint64[n_tallies]), ordered on `stream`.
+        With want_report=False nothing synchronises the host."""
+        o = self._opts(seed, sample_begin, n_samples, device, batch_slabs, stream, overlap, profile)
+        rep = _lib.CMcReport()
+        _lib.check(_lib.lib().canopy_mc_run_device(self._h, C.byref(o), C.c_void_p(tallies_ptr),
+                                                   C.byref(rep) if want_report else None))
+        return _report(rep) if want_report else None
+
+    def run_multi(self, devices, n_samples: int, seed: int = 0, sample_begin: int = 0, batch_slabs: int = 0,
+                  overlap: bool = True):
+        """Single-process multi-GPU with one NCCL all-reduce of the tallies (canopy_mc_run_multi)."""
+        o = self._opts(seed, sample_begin, n_samples, 0, batch_slabs, None, overlap, False)
+        devs = (C.c_int32 * len(devices))(*devices)
+        out = np.zeros(max(self.n_tallies, 1), dtype=np.uint64)
+        rep = _lib.CMcReport()
+        _lib.check(_lib.lib().canopy_mc_run_multi(self._h, C.byref(o), devs, len(devices),
+                                                  out.ctypes.data_as(C.POINTER(C.c_uint64)), C.byref(rep)))
+        return out[: self.n_tallies], _report(rep)
+
+    def sample_words(self, seed: int, first_word: int, n_words: int, device: int = 0) -> np.ndarray:
+        """Raw sampler output [n_events_live, n_words] (parity hook)."""
+        o = self._opts(seed, 0, 0, device, 0, None, False, False)
+        n_ev = int(self.stats["n_basic_live"])
+        out = np.zeros((max(n_ev, 1), n_words), dtype=np.uint64)
+        _lib.check(_lib.lib().canopy_mc_sample_words(self._h, C.byref(o), first_word, n_words,
+                                                     out.ctypes.data_as(C.POINTER(C.c_uint64))))
+        return out[:n_ev]
+
+
+def quantify(graph: Graph, settings: Settings, device: int = 0):
+    """One-call analysis: lower, run, estimate.  Returns dict(tallies, p, sigma, ci_lo, ci_hi, report, stats)."""
+    settings.validate()
+    with Plan(graph, settings.tally_all_gates, settings.threshold_bits) as plan:
+        t, rep = plan.run(settings.num_trials, settings.seed, settings.sample_begin, device, settings.batch_size,
+                          overlap=settings.overlap, profile=settings.profile)
+        est = [estimate(int(x), settings.num_trials) for x in t]
+        return dict(tallies=t, p=np.array([e[0] for e in est]), sigma=np.array([e[1] for e in est]),
+                    ci_lo=np.array([e[2] for e in est]), ci_hi=np.array([e[3] for e in est]), report=rep,
+                    stats=dict(plan.stats))
+
+
+def estimate(tally: int, n_samples: int):
+    e = _lib.CEstimate()
+    _lib.check(_lib.lib().canopy_estimate_from_tally(tally, n_samples, C.byref(e)))
+    return e.p, e.sigma, e.ci_lo, e.ci_hi
+
+
+def shard_range(sample_begin: int, n_samples: int, rank: int, world: int):
+    b, n = C.c_uint64(), C.c_uint64()
+    _lib.check(_lib.lib().canopy_shard_range(sample_begin, n_samples, rank, world, C.byref(b), C.byref(n)))
+    return int(b.value), int(n.value)
+
+
+def microbench_int(kind: int, device: int = 0):
+    ops, ms = C.c_double(), C.c_double()
+    _lib.check(_lib.lib().canopy_microbench_int(device, kind, C.byref(ops), C.byref(ms)))
+    return ops.value, ms.value
+
+
+def load_mef(paths=None, text: str | None = None) -> Graph:
+    """Open-PSA MEF XML -> Graph via the C++ loader in libcanopy (canopy_model_load_mef*)."""
+    h = C.c_void_p()
+    L = _lib.lib()
+    if text is not None:
+        _lib.check(L.canopy_model_load_mef_string(text.encode(), C.byref(h)))
+    else:
+        if isinstance(paths, (str, bytes)):
+            paths = [paths]
+        arr = (C.c_char_p * len(paths))(*[p.encode() if isinstance(p, str) else p for p in paths])
+        _lib.check(L.canopy_model_load_mef(arr, len(paths), C.byref(h)))
+    try:
+        d = CGraphDesc()
+        _lib.check(L.canopy_model_desc(h, C.byref(d)))
+        def cp(ptr, n, dt):
+            return np.ctypeslib.as_array(ptr, shape=(n,)).astype(dt, copy=True) if n else np.zeros(0, dtype=dt)
+        g = Graph(p=cp(d.p, d.n_basic, np.float64), op=cp(d.op, d.n_gates, np.uint8),
+                  kmin=cp(d.kmin, d.n_gates, np.uint16), kmax=cp(d.kmax, d.n_gates, np.uint16),
+                  child_off=cp(d.child_off, d.n_gates + 1, np.uint64), child=cp(d.child, d.n_edges, np.uint32),
+                  roots=cp(d.roots, d.n_roots, np.uint32),
+                  basic_names=[L.canopy_model_basic_name(h, i).decode() for i in range(d.n_basic)],
+                  gate_names=[L.canopy_model_gate_name(h, i).decode() for i in range(d.n_gates)])
+        return g
+    finally:
+        L.canopy_model_destroy(h)

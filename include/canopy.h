@@ -1,0 +1,247 @@
+/*
+ * canopy.h -- C ABI of the B200-native Monte Carlo quantification engine.
+ *
+ * Packaging contract kept from the reference (openpra-org/canopy):
+ *   - shared library target `canopy`              (reference src/CMakeLists.txt:9-12, CMakeLists.txt:21)
+ *   - installed public headers canopy.h / canopy-cpp.h   (reference CMakeLists.txt:60-68)
+ *   - export macros keyed on CANOPY_BUILD / CANOPY_SHARED (reference src/CMakeLists.txt:21-22)
+ * The reference header itself is an empty include guard (reference include/canopy.h:33-36)
+ * and the reference ships no quantification code, so every entry point below is a
+ * *designed* boundary; each one cites the reference type it consumes or stands in for.
+ *
+ * Conventions
+ *   - every function returns canopy_status and never throws across the boundary; the
+ *     reference signals errors with C++ exceptions (reference src/mef/openpsa/error.h:23-96),
+ *     which map to the status codes below; the message is available from
+ *     canopy_last_error() (thread-local).
+ *   - caller owns every array in a descriptor and every output buffer; the library owns
+ *     canopy_plan and all device memory.
+ *   - there is NO CPU fallback: canopy_mc_* fail with CANOPY_E_CUDA when no sm_100 device
+ *     is usable. Lowering (canopy_plan_*) is host-only and works without a GPU.
+ */
+#ifndef CANOPY_H
+#define CANOPY_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef CANOPY_SHARED
+#  if defined(_WIN32) && !defined(__MINGW32__)
+#    ifdef CANOPY_BUILD
+#      define CANOPY_API __declspec(dllexport)
+#    else
+#      define CANOPY_API __declspec(dllimport)
+#    endif
+#  else
+#    define CANOPY_API __attribute__((visibility("default")))
+#  endif
+#else
+#  define CANOPY_API
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CANOPY_VERSION_MAJOR 0
+#define CANOPY_VERSION_MINOR 1
+/* Version of the sampling specification (DESIGN.md "SPEC v1"). Tallies are a pure
+ * function of (spec version, graph, seed, sample range); bump invalidates goldens. */
+#define CANOPY_SPEC_VERSION 1
+
+typedef enum canopy_status {
+    CANOPY_OK = 0,
+    CANOPY_E_INVALID = 1,     /* null pointer, bad option, id out of range          (LogicError, error.h:55)      */
+    CANOPY_E_VALIDITY = 2,    /* connective arity / min / max rules violated         (ValidityError, error.h:76)   */
+    CANOPY_E_CYCLE = 3,       /* gate graph is not acyclic                           (CycleError, error.h:93)      */
+    CANOPY_E_UNSUPPORTED = 4, /* valid MEF construct this engine does not evaluate                                 */
+    CANOPY_E_CUDA = 5,        /* CUDA failure, no device, or device is not sm_100                                  */
+    CANOPY_E_NCCL = 6,        /* NCCL failure or libnccl.so.2 not loadable                                         */
+    CANOPY_E_OOM = 7,         /* host or device allocation failed                                                  */
+    CANOPY_E_DOMAIN = 8,      /* probability outside [0,1] or NaN                    (DomainError, error.h:98)     */
+    CANOPY_E_IO = 9           /* model file unreadable / malformed XML               (IOError, io/xml/error.h:34)  */
+} canopy_status;
+
+/* Same numeric values as `enum Connective` in reference src/mef/openpsa/event/event.h:143-157. */
+typedef enum canopy_connective {
+    CANOPY_AND = 0,
+    CANOPY_OR = 1,
+    CANOPY_ATLEAST = 2,      /* k-of-n, k = kmin                                   */
+    CANOPY_XOR = 3,          /* exactly 2 args                                     */
+    CANOPY_NOT = 4,          /* exactly 1 arg                                      */
+    CANOPY_NAND = 5,
+    CANOPY_NOR = 6,
+    CANOPY_NULL = 7,         /* pass-through, exactly 1 arg                        */
+    CANOPY_IFF = 8,          /* exactly 2 args                                     */
+    CANOPY_IMPLY = 9,        /* exactly 2 args, arg0 -> arg1                       */
+    CANOPY_CARDINALITY = 10  /* kmin <= (#true args) <= kmax                       */
+} canopy_connective;
+#define CANOPY_NUM_CONNECTIVES 11
+
+/* Child reference encoding (one uint32 per formula argument, reference
+ * src/mef/openpsa/event/formula.h:9-15 `Arg{complement, event}`):
+ *   bit 31     complement flag
+ *   bits 0-30  node id: [0, n_basic) basic event, [n_basic, n_basic+n_gates) gate,
+ *              or one of the two constants (HouseEvent::kFalse/kTrue, event.h:37-38). */
+#define CANOPY_CHILD_COMPLEMENT 0x80000000u
+#define CANOPY_CHILD_ID_MASK    0x7FFFFFFFu
+#define CANOPY_CONST_FALSE      0x7FFFFFFEu
+#define CANOPY_CONST_TRUE       0x7FFFFFFFu
+
+/* Flat, caller-owned description of a MEF gate DAG. This is what a walk over
+ * Model -> FaultTree::top_events() -> Gate::formula().args() (reference fault_tree.h:142,
+ * event/gate.h:45-48, event/formula.h:100) produces; house events are passed as the two
+ * constants. Read during the call only. */
+typedef struct canopy_graph_desc {
+    uint32_t n_basic;
+    uint32_t n_gates;
+    uint32_t n_roots;
+    uint32_t reserved0;
+    uint64_t n_edges;
+    const double*   p;          /* [n_basic]   BasicEvent::p() (event.h:93-96), must be in [0,1]           */
+    const uint8_t*  op;         /* [n_gates]   canopy_connective                                           */
+    const uint16_t* kmin;       /* [n_gates]   Formula::min_number (formula.h:145); ignored unless atleast/cardinality */
+    const uint16_t* kmax;       /* [n_gates]   Formula::max_number (formula.h:146); ignored unless cardinality         */
+    const uint64_t* child_off;  /* [n_gates+1] CSR offsets into child[]                                    */
+    const uint32_t* child;      /* [n_edges]   encoded as above, argument order preserved (matters for imply) */
+    const uint32_t* roots;      /* [n_roots]   node ids (gate or basic event) whose tallies are reported first */
+} canopy_graph_desc;
+
+typedef struct canopy_plan_opts {
+    int32_t tally_all_gates;   /* 0: tallies = [n_roots]; 1: tallies = [n_roots] ++ [n_gates] (descriptor order) */
+    int32_t threshold_bits;    /* 32 (SPEC v1 default) or 64 (two variates per Philox call)                      */
+    int32_t reserved[6];
+} canopy_plan_opts;
+
+/* Lowering statistics, reported before and after dead-code elimination / folding. */
+typedef struct canopy_plan_stats {
+    uint32_t n_basic_in, n_gates_in;
+    uint64_t n_edges_in;
+    uint32_t n_basic_live;     /* basic events that are actually sampled                         */
+    uint32_t n_gates_live;     /* device gates after alias/constant folding + DCE                */
+    uint64_t n_edges_live;     /* E: sum of fan-in over live gates                               */
+    uint32_t n_gates_stored;   /* G': live gates whose output word is consumed by a later layer  */
+    uint32_t n_gates_tallied;
+    uint32_t n_layers;
+    uint32_t max_fanin;
+    double   mean_fanin;
+    uint32_t n_tallies;        /* length of the tallies output array                             */
+    uint32_t n_const_nodes;    /* roots/gates folded to constants                                */
+    uint32_t n_alias_nodes;    /* gates folded to (possibly complemented) aliases                */
+    uint32_t spec_version;
+} canopy_plan_stats;
+
+typedef struct canopy_plan canopy_plan; /* opaque; immutable lowered graph + lazily created per-device state */
+
+/* Host lowering: validate (reference event.cpp:140-204 arity/min/max/nesting rules), fold constants
+ * and NOT/NULL aliases, eliminate dead nodes, levelise, emit CSR. No GPU needed. */
+CANOPY_API canopy_status canopy_plan_create(const canopy_graph_desc* desc, const canopy_plan_opts* opts,
+                                            canopy_plan** out_plan);
+CANOPY_API void          canopy_plan_destroy(canopy_plan* plan);
+CANOPY_API canopy_status canopy_plan_info(const canopy_plan* plan, canopy_plan_stats* out);
+
+/* Introspection of the lowered form (used by the host-logic tests; all pointers stay valid until
+ * canopy_plan_destroy). Device node ids: [0,n_basic_live) events, then gates in layer order. */
+typedef struct canopy_plan_view {
+    uint32_t n_events, n_gates, n_layers, n_tallies;
+    uint64_t n_edges;
+    const uint32_t* event_orig;   /* [n_events] original basic-event index (feeds the Philox counter)      */
+    const uint32_t* event_thr32;  /* [n_events] floor(p * 2^32)                                             */
+    const uint64_t* event_thr64;  /* [n_events] floor(p * 2^64) (valid when threshold_bits == 64)           */
+    const uint32_t* gate_child_off; /* [n_gates+1]                                                          */
+    const uint32_t* gate_child;   /* [n_edges] device node id | complement bit 31                           */
+    const uint8_t*  gate_op;      /* [n_gates] device op: 0 and, 1 or, 2 xor, 3 count-in-range              */
+    const uint8_t*  gate_flags;   /* [n_gates] bit0 invert output, bit1 store, bit2 tally                   */
+    const uint16_t* gate_kmin;    /* [n_gates]                                                              */
+    const uint16_t* gate_kmax;    /* [n_gates]                                                              */
+    const uint32_t* layer_off;    /* [n_layers+1] gate index ranges                                         */
+    const uint8_t*  tally_kind;   /* [n_tallies] 0 const-false, 1 const-true, 2 device gate, 3 complement of device gate */
+    const uint32_t* tally_gate;   /* [n_tallies] device gate index for kinds 2/3                            */
+} canopy_plan_view;
+CANOPY_API canopy_status canopy_plan_view_get(const canopy_plan* plan, canopy_plan_view* out);
+
+/* Mirrors the Monte Carlo fields of reference Settings (settings.h:118-151,178-187,324-327):
+ * num_trials -> n_samples, seed -> seed (both widened from int to 64 bit); batch_size -> batch_slabs
+ * (0 = engine default). sample_begin makes a run restartable / shardable by counter range. */
+typedef struct canopy_mc_opts {
+    uint64_t seed;
+    uint64_t sample_begin;
+    uint64_t n_samples;
+    int32_t  device;          /* CUDA ordinal                                                       */
+    int32_t  batch_slabs;     /* slabs (4096 samples each) per batch; 0 = default                   */
+    void*    stream;          /* cudaStream_t to order the run on; NULL = library-owned stream      */
+    int32_t  overlap;         /* 1 (default when 0 is passed via canopy_mc_opts_default): sampler of batch i+1 overlaps gates of batch i */
+    int32_t  profile;         /* 1: time sampler / gate kernels separately with CUDA events (serialises the two) */
+    int32_t  reserved[4];
+} canopy_mc_opts;
+CANOPY_API void canopy_mc_opts_default(canopy_mc_opts* opts);
+
+/* Per-run measurements taken with CUDA events on the run's streams. */
+typedef struct canopy_mc_report {
+    double   total_ms;          /* device time first launch -> last kernel done                     */
+    double   sampler_ms;        /* sum over batches (profile=1 only, else 0)                        */
+    double   gate_ms;           /* sum over batches (profile=1 only, else 0)                        */
+    uint64_t sampler_launches;
+    uint64_t gate_launches;
+    uint64_t other_launches;    /* tally clear etc.                                                 */
+    uint64_t n_batches;
+    uint64_t slab_samples;      /* samples per slab (4096)                                          */
+    uint64_t batch_slabs;
+    uint64_t h2d_bytes, d2h_bytes;
+} canopy_mc_report;
+
+/* Run S = n_samples trials of the whole DAG on one device; tallies[i] = number of samples in
+ * [sample_begin, sample_begin+n_samples) for which output i is true. Host output buffer. */
+CANOPY_API canopy_status canopy_mc_run(canopy_plan* plan, const canopy_mc_opts* opts,
+                                       uint64_t* tallies_host, canopy_mc_report* report);
+/* Same, but tallies are left in device memory (uint64[n_tallies], caller-allocated on opts->device),
+ * ordered on opts->stream: the buffer a collective (NCCL all-reduce) consumes with no host hop. */
+CANOPY_API canopy_status canopy_mc_run_device(canopy_plan* plan, const canopy_mc_opts* opts,
+                                              uint64_t* tallies_device, canopy_mc_report* report);
+/* Single-process multi-GPU: shards [sample_begin, +n_samples) into n_devices contiguous counter
+ * ranges, one host thread per device, then one ncclAllReduce(ncclUint64, ncclSum) over the tallies. */
+CANOPY_API canopy_status canopy_mc_run_multi(canopy_plan* plan, const canopy_mc_opts* opts,
+                                             const int32_t* devices, int32_t n_devices,
+                                             uint64_t* tallies_host, canopy_mc_report* report);
+
+/* Parity hook: run only the sampler kernel and return the packed words of the live basic events,
+ * words_host[e * n_words + w], e in canopy_plan_view.event_orig order, w = global word index
+ * first_word .. first_word+n_words-1 (sample s is bit s&63 of word s>>6). */
+CANOPY_API canopy_status canopy_mc_sample_words(canopy_plan* plan, const canopy_mc_opts* opts,
+                                                uint64_t first_word, uint64_t n_words,
+                                                uint64_t* words_host);
+
+/* Shard helper: contiguous, 4096-sample-aligned split of a sample range over `world`
+ * ranks; the union over ranks is exactly the input range for every world size. */
+CANOPY_API canopy_status canopy_shard_range(uint64_t sample_begin, uint64_t n_samples,
+                                            int32_t rank, int32_t world,
+                                            uint64_t* out_begin, uint64_t* out_n);
+
+/* Point estimate from a tally: p_hat = tally/n, sigma = sqrt(p(1-p)/n), 95% normal CI. */
+typedef struct canopy_estimate { double p, sigma, ci_lo, ci_hi; } canopy_estimate;
+CANOPY_API canopy_status canopy_estimate_from_tally(uint64_t tally, uint64_t n_samples, canopy_estimate* out);
+
+/* Integer-pipe microbenchmarks used for the sampler roofline (lane-instructions per second).
+ * kind: 0 LOP3, 1 IMAD.WIDE.U32, 2 Philox4x32-10 rounds (2 IMAD.WIDE + 2 LOP3 per round), 3 POPC */
+CANOPY_API canopy_status canopy_microbench_int(int32_t device, int32_t kind, double* out_lane_ops_per_s,
+                                               double* out_ms);
+
+/* Open-PSA MEF XML (fault-tree subset) -> flat graph. The returned model owns the arrays that
+ * canopy_model_desc() points to. Stands in for reference Initializer (initializer.h:65-70). */
+typedef struct canopy_model canopy_model;
+CANOPY_API canopy_status canopy_model_load_mef(const char* const* xml_paths, int32_t n_paths, canopy_model** out);
+CANOPY_API canopy_status canopy_model_load_mef_string(const char* xml_text, canopy_model** out);
+CANOPY_API canopy_status canopy_model_desc(const canopy_model* model, canopy_graph_desc* out);
+CANOPY_API const char*   canopy_model_basic_name(const canopy_model* model, uint32_t i);
+CANOPY_API const char*   canopy_model_gate_name(const canopy_model* model, uint32_t i);
+CANOPY_API void          canopy_model_destroy(canopy_model* model);
+
+CANOPY_API const char* canopy_last_error(void);   /* thread-local; valid until the next call on this thread */
+CANOPY_API const char* canopy_status_string(canopy_status s);
+CANOPY_API uint32_t    canopy_version(void);      /* major<<16 | minor */
+CANOPY_API uint32_t    canopy_spec_version(void);
+
+#ifdef __cplusplus
+} /* extern "C" */
+#endif
+#endif /* CANOPY_H */

@@ -1,0 +1,403 @@
+/*
+ * canopy_oracle.c -- CPU oracle for the bit-packed Monte Carlo hot path.  TEST INFRASTRUCTURE ONLY.
+ *
+ * PARITY UNPINNED: the reference (openpra-org/canopy) contains no implementation of this path, no
+ * tests and no golden vectors.  This oracle is therefore a restatement of
+ *   (a) the connective semantics of the Open-PSA MEF as constrained by the reference's own
+ *       validation rules (reference src/mef/openpsa/event/event.cpp:140-204, event/event.h:143-157,
+ *       event/formula.h:9-15), and
+ *   (b) this repository's written sampling spec ("SPEC v1"),
+ * pinned only by the published Philox4x32-10 known-answer vectors (Random123 kat_vectors) and by
+ * exact 2^B enumeration on small trees.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load
+ * this file's shared object.  Nothing under canopy_b200/ links or calls it.
+ *
+ * Three independent evaluators live here on purpose:
+ *   oracle_mc_scalar   one sample at a time, one `unsigned char` per node, recursion over the
+ *                      ORIGINAL descriptor (no lowering, no bit tricks)          -> parity checker
+ *   oracle_exact       sum over all 2^B basic-event states with the QUANTISED probabilities
+ *   oracle_mc_packed   64 samples per word, pthreads over sample blocks          -> timed CPU baseline
+ */
+#include <math.h>
+#include <pthread.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../include/canopy.h" /* descriptor struct + connective enum only */
+
+/* ------------------------------------------------------------------------------------------------
+ * Philox4x32-10 (Salmon et al., SC'11).  Constants as in Random123 / cuRAND
+ * (curand_philox4x32_x.h:88-91).  SPEC v1 section "RNG".
+ * ---------------------------------------------------------------------------------------------- */
+#define PHILOX_M0 0xD2511F53u
+#define PHILOX_M1 0xCD9E8D57u
+#define PHILOX_W0 0x9E3779B9u
+#define PHILOX_W1 0xBB67AE85u
+
+void oracle_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) {
+    uint32_t c0 = ctr[0], c1 = ctr[1], c2 = ctr[2], c3 = ctr[3];
+    uint32_t k0 = key[0], k1 = key[1];
+    for (int r = 0; r < 10; ++r) {
+        uint64_t p0 = (uint64_t)PHILOX_M0 * c0;
+        uint64_t p1 = (uint64_t)PHILOX_M1 * c2;
+        uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+        uint32_t n1 = (uint32_t)p1;
+        uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+        uint32_t n3 = (uint32_t)p0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += PHILOX_W0; k1 += PHILOX_W1;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * SPEC v1 "Threshold quantisation".  kind: 0 = always false (p <= 0), 1 = always true (p >= 1),
+ * 2 = sampled with thr = floor(p * 2^bits).  Returns -1 for NaN / out of [0,1].
+ * ---------------------------------------------------------------------------------------------- */
+int oracle_threshold(double p, int bits, uint64_t* thr) {
+    if (!(p >= 0.0) || !(p <= 1.0)) return -1;
+    if (p <= 0.0) { *thr = 0; return 0; }
+    if (p >= 1.0) { *thr = 0; return 1; }
+    if (bits == 32) *thr = (uint64_t)(p * 4294967296.0);              /* exact: scaling by 2^32 */
+    else            *thr = (uint64_t)(p * 18446744073709551616.0);    /* exact: scaling by 2^64, p < 1 */
+    return 2;
+}
+
+/* Quantised probability actually realised by the sampler for one event. */
+double oracle_quantised_p(double p, int bits) {
+    uint64_t thr; int k = oracle_threshold(p, bits, &thr);
+    if (k <= 0) return 0.0;
+    if (k == 1) return 1.0;
+    return bits == 32 ? (double)thr / 4294967296.0 : (double)thr / 18446744073709551616.0;
+}
+
+/* SPEC v1 "Counter mapping": one basic-event bit for (seed, original event index e, global sample s). */
+int oracle_sample_bit(uint64_t seed, uint32_t e, uint64_t s, int kind, uint64_t thr, int bits) {
+    if (kind == 0) return 0;
+    if (kind == 1) return 1;
+    uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
+    uint32_t ctr[4], out[4];
+    if (bits == 32) {
+        uint64_t q = s >> 2;
+        ctr[0] = (uint32_t)q; ctr[1] = (uint32_t)(q >> 32); ctr[2] = e; ctr[3] = 0;
+        oracle_philox4x32_10(ctr, key, out);
+        return out[s & 3] < (uint32_t)thr;
+    } else {
+        uint64_t q = s >> 1;
+        ctr[0] = (uint32_t)q; ctr[1] = (uint32_t)(q >> 32); ctr[2] = e; ctr[3] = 1;
+        oracle_philox4x32_10(ctr, key, out);
+        unsigned j = (unsigned)(s & 1) * 2;
+        uint64_t u = ((uint64_t)out[j + 1] << 32) | out[j];
+        return u < thr;
+    }
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * Connective semantics on plain ints (arity rules event.cpp:140-191).
+ * x[] are the child values AFTER the per-edge complement (formula.h:12-15).
+ * ---------------------------------------------------------------------------------------------- */
+static int eval_connective(int op, const unsigned char* x, uint32_t n, unsigned kmin, unsigned kmax) {
+    unsigned c = 0;
+    for (uint32_t i = 0; i < n; ++i) c += x[i] ? 1u : 0u;
+    switch (op) {
+        case CANOPY_AND:         return c == n;
+        case CANOPY_OR:          return c > 0;
+        case CANOPY_ATLEAST:     return c >= kmin;
+        case CANOPY_XOR:         return (x[0] != 0) != (x[1] != 0);
+        case CANOPY_NOT:         return !x[0];
+        case CANOPY_NAND:        return c != n;
+        case CANOPY_NOR:         return c == 0;
+        case CANOPY_NULL:        return x[0] != 0;
+        case CANOPY_IFF:         return (x[0] != 0) == (x[1] != 0);
+        case CANOPY_IMPLY:       return !x[0] || x[1];
+        case CANOPY_CARDINALITY: return c >= kmin && c <= kmax;
+        default:                 return 0;
+    }
+}
+
+/* Topological order of gates by DFS over the original descriptor.  Returns 0, or -3 on a cycle,
+ * -1 on a bad id.  order[] receives gate indices, children first. */
+static int topo_order(const canopy_graph_desc* d, uint32_t* order) {
+    uint32_t G = d->n_gates, B = d->n_basic;
+    unsigned char* mark = (unsigned char*)calloc(G ? G : 1, 1); /* 0 new, 1 on stack, 2 done */
+    uint32_t* stack = (uint32_t*)malloc(sizeof(uint32_t) * (G ? G : 1));
+    uint64_t* pos = (uint64_t*)malloc(sizeof(uint64_t) * (G ? G : 1));
+    uint32_t n_out = 0; int rc = 0;
+    for (uint32_t g0 = 0; g0 < G && rc == 0; ++g0) {
+        if (mark[g0]) continue;
+        uint32_t sp = 0; stack[sp] = g0; pos[sp] = d->child_off[g0]; mark[g0] = 1; sp = 1;
+        while (sp && rc == 0) {
+            uint32_t g = stack[sp - 1];
+            if (pos[sp - 1] == d->child_off[g + 1]) { mark[g] = 2; order[n_out++] = g; --sp; continue; }
+            uint32_t id = d->child[pos[sp - 1]++] & CANOPY_CHILD_ID_MASK;
+            if (id == CANOPY_CONST_FALSE || id == CANOPY_CONST_TRUE || id < B) continue;
+            if (id >= B + G) { rc = -1; break; }
+            uint32_t c = id - B;
+            if (mark[c] == 1) { rc = -3; break; }
+            if (mark[c] == 0) { mark[c] = 1; stack[sp] = c; pos[sp] = d->child_off[c]; ++sp; }
+        }
+    }
+    free(mark); free(stack); free(pos);
+    return rc;
+}
+
+static size_t n_tallies_of(const canopy_graph_desc* d, int tally_all) {
+    return (size_t)d->n_roots + (tally_all ? d->n_gates : 0);
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * Scalar Monte Carlo: tallies[i] = #{s in [begin, begin+n) : output_i(s)}.
+ * Outputs: roots in descriptor order, then (tally_all) every gate in descriptor order.
+ * ---------------------------------------------------------------------------------------------- */
+int oracle_mc_scalar(const canopy_graph_desc* d, uint64_t seed, uint64_t begin, uint64_t n,
+                     int tally_all, int bits, uint64_t* tallies) {
+    uint32_t B = d->n_basic, G = d->n_gates;
+    uint32_t* order = (uint32_t*)malloc(sizeof(uint32_t) * (G ? G : 1));
+    int rc = topo_order(d, order);
+    if (rc) { free(order); return rc; }
+    int* kind = (int*)malloc(sizeof(int) * (B ? B : 1));
+    uint64_t* thr = (uint64_t*)malloc(sizeof(uint64_t) * (B ? B : 1));
+    for (uint32_t e = 0; e < B; ++e) {
+        kind[e] = oracle_threshold(d->p[e], bits, &thr[e]);
+        if (kind[e] < 0) { free(order); free(kind); free(thr); return -8; }
+    }
+    /* which basic events are referenced at all (skip sampling the rest: they cannot matter) */
+    unsigned char* used = (unsigned char*)calloc(B ? B : 1, 1);
+    for (uint64_t i = 0; i < d->n_edges; ++i) { uint32_t id = d->child[i] & CANOPY_CHILD_ID_MASK; if (id < B) used[id] = 1; }
+    for (uint32_t r = 0; r < d->n_roots; ++r) if (d->roots[r] < B) used[d->roots[r]] = 1;
+    size_t nt = n_tallies_of(d, tally_all);
+    memset(tallies, 0, sizeof(uint64_t) * nt);
+    unsigned char* val = (unsigned char*)malloc((size_t)B + G + 1);
+    uint32_t maxf = 1;
+    for (uint32_t g = 0; g < G; ++g) { uint64_t f = d->child_off[g + 1] - d->child_off[g]; if (f > maxf) maxf = (uint32_t)f; }
+    unsigned char* x = (unsigned char*)malloc(maxf);
+    for (uint64_t s = begin; s < begin + n; ++s) {
+        for (uint32_t e = 0; e < B; ++e)
+            val[e] = used[e] ? (unsigned char)oracle_sample_bit(seed, e, s, kind[e], thr[e], bits) : 0;
+        for (uint32_t i = 0; i < G; ++i) {
+            uint32_t g = order[i];
+            uint64_t o = d->child_off[g]; uint32_t f = (uint32_t)(d->child_off[g + 1] - o);
+            for (uint32_t j = 0; j < f; ++j) {
+                uint32_t c = d->child[o + j]; uint32_t id = c & CANOPY_CHILD_ID_MASK;
+                unsigned char v = id == CANOPY_CONST_TRUE ? 1 : id == CANOPY_CONST_FALSE ? 0 : val[id];
+                x[j] = (c & CANOPY_CHILD_COMPLEMENT) ? !v : v;
+            }
+            val[B + g] = (unsigned char)eval_connective(d->op[g], x, f, d->kmin ? d->kmin[g] : 0, d->kmax ? d->kmax[g] : 0);
+        }
+        for (uint32_t r = 0; r < d->n_roots; ++r) tallies[r] += val[d->roots[r]];
+        if (tally_all) for (uint32_t g = 0; g < G; ++g) tallies[d->n_roots + g] += val[B + g];
+    }
+    free(order); free(kind); free(thr); free(used); free(val); free(x);
+    return 0;
+}
+
+/* Raw sampler words, same layout as canopy_mc_sample_words: words[i*n_words + w] for the events
+ * listed in event_ids[0..n_events). */
+int oracle_sample_words(const canopy_graph_desc* d, uint64_t seed, int bits, const uint32_t* event_ids,
+                        uint32_t n_events, uint64_t first_word, uint64_t n_words, uint64_t* words) {
+    for (uint32_t i = 0; i < n_events; ++i) {
+        uint32_t e = event_ids[i]; uint64_t thr; int kind = oracle_threshold(d->p[e], bits, &thr);
+        if (kind < 0) return -8;
+        for (uint64_t w = 0; w < n_words; ++w) {
+            uint64_t word = 0;
+            for (unsigned b = 0; b < 64; ++b)
+                word |= (uint64_t)oracle_sample_bit(seed, e, (first_word + w) * 64 + b, kind, thr, bits) << b;
+            words[(uint64_t)i * n_words + w] = word;
+        }
+    }
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * Exact probabilities by enumeration of all 2^B states (B <= 24), with the quantised p.
+ * probs[] has the same layout as tallies.
+ * ---------------------------------------------------------------------------------------------- */
+int oracle_exact(const canopy_graph_desc* d, int tally_all, int bits, double* probs) {
+    uint32_t B = d->n_basic, G = d->n_gates;
+    if (B > 24) return -4;
+    uint32_t* order = (uint32_t*)malloc(sizeof(uint32_t) * (G ? G : 1));
+    int rc = topo_order(d, order);
+    if (rc) { free(order); return rc; }
+    double* q = (double*)malloc(sizeof(double) * (B ? B : 1));
+    for (uint32_t e = 0; e < B; ++e) {
+        if (!(d->p[e] >= 0.0) || !(d->p[e] <= 1.0)) { free(order); free(q); return -8; }
+        q[e] = oracle_quantised_p(d->p[e], bits);
+    }
+    size_t nt = n_tallies_of(d, tally_all);
+    long double* acc = (long double*)calloc(nt ? nt : 1, sizeof(long double));
+    unsigned char* val = (unsigned char*)malloc((size_t)B + G + 1);
+    uint32_t maxf = 1;
+    for (uint32_t g = 0; g < G; ++g) { uint64_t f = d->child_off[g + 1] - d->child_off[g]; if (f > maxf) maxf = (uint32_t)f; }
+    unsigned char* x = (unsigned char*)malloc(maxf);
+    for (uint64_t st = 0; st < (1ull << B); ++st) {
+        long double w = 1.0L;
+        for (uint32_t e = 0; e < B; ++e) { val[e] = (st >> e) & 1; w *= val[e] ? (long double)q[e] : 1.0L - (long double)q[e]; }
+        if (w == 0.0L) continue;
+        for (uint32_t i = 0; i < G; ++i) {
+            uint32_t g = order[i];
+            uint64_t o = d->child_off[g]; uint32_t f = (uint32_t)(d->child_off[g + 1] - o);
+            for (uint32_t j = 0; j < f; ++j) {
+                uint32_t c = d->child[o + j]; uint32_t id = c & CANOPY_CHILD_ID_MASK;
+                unsigned char v = id == CANOPY_CONST_TRUE ? 1 : id == CANOPY_CONST_FALSE ? 0 : val[id];
+                x[j] = (c & CANOPY_CHILD_COMPLEMENT) ? !v : v;
+            }
+            val[B + g] = (unsigned char)eval_connective(d->op[g], x, f, d->kmin ? d->kmin[g] : 0, d->kmax ? d->kmax[g] : 0);
+        }
+        for (uint32_t r = 0; r < d->n_roots; ++r) if (val[d->roots[r]]) acc[r] += w;
+        if (tally_all) for (uint32_t g = 0; g < G; ++g) if (val[B + g]) acc[d->n_roots + g] += w;
+    }
+    for (size_t i = 0; i < nt; ++i) probs[i] = (double)acc[i];
+    free(order); free(q); free(acc); free(val); free(x);
+    return 0;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * Bit-packed multi-threaded CPU evaluator: the "port" timed as the CPU baseline.
+ * Work unit = one 64-sample word column of the whole DAG; threads take blocks of word columns.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+    const canopy_graph_desc* d;
+    const uint32_t* order;
+    const int* kind; const uint64_t* thr; const unsigned char* used;
+    uint64_t seed, begin, n; int tally_all, bits;
+    uint64_t first_word, n_words; /* global word range covering [begin, begin+n) */
+    int tid, nthreads;
+    uint64_t* tallies; /* private */
+} packed_job;
+
+static uint64_t packed_sample_word(uint64_t seed, uint32_t e, uint64_t w, int kind, uint64_t thr, int bits) {
+    if (kind == 0) return 0;
+    if (kind == 1) return ~0ull;
+    uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
+    uint32_t ctr[4], out[4];
+    uint64_t word = 0;
+    if (bits == 32) {
+        uint32_t t = (uint32_t)thr;
+        uint64_t q0 = w * 16;
+        for (unsigned c = 0; c < 16; ++c) {
+            uint64_t q = q0 + c;
+            ctr[0] = (uint32_t)q; ctr[1] = (uint32_t)(q >> 32); ctr[2] = e; ctr[3] = 0;
+            oracle_philox4x32_10(ctr, key, out);
+            uint64_t nib = (uint64_t)(out[0] < t) | ((uint64_t)(out[1] < t) << 1) | ((uint64_t)(out[2] < t) << 2) | ((uint64_t)(out[3] < t) << 3);
+            word |= nib << (4 * c);
+        }
+    } else {
+        uint64_t q0 = w * 32;
+        for (unsigned c = 0; c < 32; ++c) {
+            uint64_t q = q0 + c;
+            ctr[0] = (uint32_t)q; ctr[1] = (uint32_t)(q >> 32); ctr[2] = e; ctr[3] = 1;
+            oracle_philox4x32_10(ctr, key, out);
+            uint64_t u0 = ((uint64_t)out[1] << 32) | out[0], u1 = ((uint64_t)out[3] << 32) | out[2];
+            word |= ((uint64_t)(u0 < thr) | ((uint64_t)(u1 < thr) << 1)) << (2 * c);
+        }
+    }
+    return word;
+}
+
+/* count-in-range on 64 lanes with a ripple bit-sliced counter */
+static uint64_t packed_count_range(const uint64_t* x, uint32_t n, unsigned lo, unsigned hi) {
+    uint64_t plane[17]; memset(plane, 0, sizeof plane);
+    for (uint32_t i = 0; i < n; ++i) {
+        uint64_t carry = x[i];
+        for (int j = 0; j < 17 && carry; ++j) { uint64_t t = plane[j] & carry; plane[j] ^= carry; carry = t; }
+    }
+    /* ge_lo: count >= lo ; le_hi: count <= hi, both by MSB-first comparison against a constant */
+    uint64_t gt = 0, eq = ~0ull;
+    for (int j = 16; j >= 0; --j) { if ((lo >> j) & 1) eq &= plane[j]; else { gt |= eq & plane[j]; eq &= ~plane[j]; } }
+    uint64_t ge_lo = gt | eq;
+    uint64_t lt = 0; eq = ~0ull;
+    for (int j = 16; j >= 0; --j) { if ((hi >> j) & 1) { lt |= eq & ~plane[j]; eq &= plane[j]; } else eq &= ~plane[j]; }
+    uint64_t le_hi = lt | eq;
+    return ge_lo & le_hi;
+}
+
+static void* packed_worker(void* arg) {
+    packed_job* J = (packed_job*)arg;
+    const canopy_graph_desc* d = J->d;
+    uint32_t B = d->n_basic, G = d->n_gates;
+    uint64_t* val = (uint64_t*)malloc(sizeof(uint64_t) * ((size_t)B + G + 1));
+    uint32_t maxf = 1;
+    for (uint32_t g = 0; g < G; ++g) { uint64_t f = d->child_off[g + 1] - d->child_off[g]; if (f > maxf) maxf = (uint32_t)f; }
+    uint64_t* x = (uint64_t*)malloc(sizeof(uint64_t) * maxf);
+    uint64_t end = J->begin + J->n;
+    for (uint64_t wi = J->tid; wi < J->n_words; wi += J->nthreads) {
+        uint64_t w = J->first_word + wi;
+        uint64_t s0 = w * 64, mask = ~0ull;
+        if (s0 < J->begin) mask &= ~0ull << (J->begin - s0);
+        if (s0 + 64 > end) mask &= (end - s0 >= 64) ? ~0ull : ((1ull << (end - s0)) - 1);
+        for (uint32_t e = 0; e < B; ++e) val[e] = J->used[e] ? packed_sample_word(J->seed, e, w, J->kind[e], J->thr[e], J->bits) : 0;
+        for (uint32_t i = 0; i < G; ++i) {
+            uint32_t g = J->order[i];
+            uint64_t o = d->child_off[g]; uint32_t f = (uint32_t)(d->child_off[g + 1] - o);
+            for (uint32_t j = 0; j < f; ++j) {
+                uint32_t c = d->child[o + j]; uint32_t id = c & CANOPY_CHILD_ID_MASK;
+                uint64_t v = id == CANOPY_CONST_TRUE ? ~0ull : id == CANOPY_CONST_FALSE ? 0 : val[id];
+                x[j] = (c & CANOPY_CHILD_COMPLEMENT) ? ~v : v;
+            }
+            uint64_t r = 0;
+            switch (d->op[g]) {
+                case CANOPY_AND:  r = ~0ull; for (uint32_t j = 0; j < f; ++j) r &= x[j]; break;
+                case CANOPY_NAND: r = ~0ull; for (uint32_t j = 0; j < f; ++j) r &= x[j]; r = ~r; break;
+                case CANOPY_OR:   r = 0; for (uint32_t j = 0; j < f; ++j) r |= x[j]; break;
+                case CANOPY_NOR:  r = 0; for (uint32_t j = 0; j < f; ++j) r |= x[j]; r = ~r; break;
+                case CANOPY_XOR:  r = x[0] ^ x[1]; break;
+                case CANOPY_IFF:  r = ~(x[0] ^ x[1]); break;
+                case CANOPY_IMPLY: r = ~x[0] | x[1]; break;
+                case CANOPY_NOT:  r = ~x[0]; break;
+                case CANOPY_NULL: r = x[0]; break;
+                case CANOPY_ATLEAST: r = packed_count_range(x, f, d->kmin[g], 0xFFFFu); break;
+                case CANOPY_CARDINALITY: r = packed_count_range(x, f, d->kmin[g], d->kmax[g]); break;
+                default: r = 0;
+            }
+            val[B + g] = r;
+        }
+        for (uint32_t r = 0; r < d->n_roots; ++r) J->tallies[r] += (uint64_t)__builtin_popcountll(val[d->roots[r]] & mask);
+        if (J->tally_all) for (uint32_t g = 0; g < G; ++g) J->tallies[d->n_roots + g] += (uint64_t)__builtin_popcountll(val[B + g] & mask);
+    }
+    free(val); free(x);
+    return NULL;
+}
+
+int oracle_mc_packed(const canopy_graph_desc* d, uint64_t seed, uint64_t begin, uint64_t n,
+                     int tally_all, int bits, int nthreads, uint64_t* tallies) {
+    uint32_t B = d->n_basic, G = d->n_gates;
+    if (nthreads < 1) nthreads = 1;
+    uint32_t* order = (uint32_t*)malloc(sizeof(uint32_t) * (G ? G : 1));
+    int rc = topo_order(d, order);
+    if (rc) { free(order); return rc; }
+    int* kind = (int*)malloc(sizeof(int) * (B ? B : 1));
+    uint64_t* thr = (uint64_t*)malloc(sizeof(uint64_t) * (B ? B : 1));
+    for (uint32_t e = 0; e < B; ++e) {
+        kind[e] = oracle_threshold(d->p[e], bits, &thr[e]);
+        if (kind[e] < 0) { free(order); free(kind); free(thr); return -8; }
+    }
+    unsigned char* used = (unsigned char*)calloc(B ? B : 1, 1);
+    for (uint64_t i = 0; i < d->n_edges; ++i) { uint32_t id = d->child[i] & CANOPY_CHILD_ID_MASK; if (id < B) used[id] = 1; }
+    for (uint32_t r = 0; r < d->n_roots; ++r) if (d->roots[r] < B) used[d->roots[r]] = 1;
+    size_t nt = n_tallies_of(d, tally_all);
+    memset(tallies, 0, sizeof(uint64_t) * nt);
+    if (n == 0) { free(order); free(kind); free(thr); free(used); return 0; }
+    uint64_t first_word = begin / 64, last_word = (begin + n - 1) / 64;
+    packed_job* jobs = (packed_job*)calloc((size_t)nthreads, sizeof(packed_job));
+    pthread_t* th = (pthread_t*)malloc(sizeof(pthread_t) * (size_t)nthreads);
+    for (int t = 0; t < nthreads; ++t) {
+        packed_job* J = &jobs[t];
+        J->d = d; J->order = order; J->kind = kind; J->thr = thr; J->used = used;
+        J->seed = seed; J->begin = begin; J->n = n; J->tally_all = tally_all; J->bits = bits;
+        J->first_word = first_word; J->n_words = last_word - first_word + 1;
+        J->tid = t; J->nthreads = nthreads;
+        J->tallies = (uint64_t*)calloc(nt ? nt : 1, sizeof(uint64_t));
+        pthread_create(&th[t], NULL, packed_worker, J);
+    }
+    for (int t = 0; t < nthreads; ++t) {
+        pthread_join(th[t], NULL);
+        for (size_t i = 0; i < nt; ++i) tallies[i] += jobs[t].tallies[i];
+        free(jobs[t].tallies);
+    }
+    free(jobs); free(th); free(order); free(kind); free(thr); free(used);
+    return 0;
+}
+
+int oracle_spec_version(void) { return CANOPY_SPEC_VERSION; }

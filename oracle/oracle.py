@@ -1,0 +1,99 @@
+"""ctypes wrapper around oracle/liboracle.so.  TEST INFRASTRUCTURE ONLY (see canopy_oracle.c header).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this.
+PARITY UNPINNED: the reference ships no implementation, tests or golden vectors for this path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+def build(force: bool = False) -> str:
+    so = os.path.join(_HERE, "liboracle.so")
+    src = os.path.join(_HERE, "canopy_oracle.c")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-s"] + (["-B"] if force else []))
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        _LIB = C.CDLL(build())
+        L = _LIB
+        u32p, u64p, dblp = C.POINTER(C.c_uint32), C.POINTER(C.c_uint64), C.POINTER(C.c_double)
+        L.oracle_philox4x32_10.argtypes = [u32p, u32p, u32p]
+        L.oracle_threshold.argtypes = [C.c_double, C.c_int, u64p]
+        L.oracle_quantised_p.argtypes = [C.c_double, C.c_int]
+        L.oracle_quantised_p.restype = C.c_double
+        L.oracle_sample_bit.argtypes = [C.c_uint64, C.c_uint32, C.c_uint64, C.c_int, C.c_uint64, C.c_int]
+        L.oracle_mc_scalar.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int, C.c_int, u64p]
+        L.oracle_mc_packed.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, u64p]
+        L.oracle_exact.argtypes = [C.c_void_p, C.c_int, C.c_int, dblp]
+        L.oracle_sample_words.argtypes = [C.c_void_p, C.c_uint64, C.c_int, u32p, C.c_uint32, C.c_uint64, C.c_uint64, u64p]
+    return _LIB
+
+
+_RC = {-1: "bad node id", -3: "cycle", -4: "too many basic events for enumeration", -8: "probability out of domain"}
+
+
+def _check(rc):
+    if rc != 0:
+        raise ValueError(f"oracle: {_RC.get(rc, rc)}")
+
+
+def philox4x32_10(ctr, key):
+    c = (C.c_uint32 * 4)(*[int(x) & 0xFFFFFFFF for x in ctr])
+    k = (C.c_uint32 * 2)(*[int(x) & 0xFFFFFFFF for x in key])
+    o = (C.c_uint32 * 4)()
+    lib().oracle_philox4x32_10(c, k, o)
+    return [int(x) for x in o]
+
+
+def threshold(p: float, bits: int = 32):
+    t = C.c_uint64()
+    kind = lib().oracle_threshold(p, bits, C.byref(t))
+    return kind, int(t.value)
+
+
+def quantised_p(p: float, bits: int = 32) -> float:
+    return float(lib().oracle_quantised_p(p, bits))
+
+
+def mc_scalar(graph, seed: int, begin: int, n: int, tally_all: bool = False, bits: int = 32) -> np.ndarray:
+    d = graph.c_desc()
+    out = np.zeros(graph.n_tallies(tally_all), dtype=np.uint64)
+    _check(lib().oracle_mc_scalar(C.addressof(d), seed, begin, n, int(tally_all), bits,
+                                  out.ctypes.data_as(C.POINTER(C.c_uint64))))
+    return out
+
+
+def mc_packed(graph, seed: int, begin: int, n: int, tally_all: bool = False, bits: int = 32, nthreads: int = 1) -> np.ndarray:
+    d = graph.c_desc()
+    out = np.zeros(graph.n_tallies(tally_all), dtype=np.uint64)
+    _check(lib().oracle_mc_packed(C.addressof(d), seed, begin, n, int(tally_all), bits, nthreads,
+                                  out.ctypes.data_as(C.POINTER(C.c_uint64))))
+    return out
+
+
+def exact(graph, tally_all: bool = False, bits: int = 32) -> np.ndarray:
+    d = graph.c_desc()
+    out = np.zeros(graph.n_tallies(tally_all), dtype=np.float64)
+    _check(lib().oracle_exact(C.addressof(d), int(tally_all), bits, out.ctypes.data_as(C.POINTER(C.c_double))))
+    return out
+
+
+def sample_words(graph, seed: int, event_ids, first_word: int, n_words: int, bits: int = 32) -> np.ndarray:
+    d = graph.c_desc()
+    ev = np.ascontiguousarray(event_ids, dtype=np.uint32)
+    out = np.zeros((len(ev), n_words), dtype=np.uint64)
+    _check(lib().oracle_sample_words(C.addressof(d), seed, bits, ev.ctypes.data_as(C.POINTER(C.c_uint32)), len(ev),
+                                     first_word, n_words, out.ctypes.data_as(C.POINTER(C.c_uint64))))
+    return out
