@@ -2,6 +2,7 @@
 // See kernels.cuh for the kernel inventory and DESIGN.md for layout, spec and roofline accounting.
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -23,7 +24,15 @@ namespace canopy {
 // All 32 calls are independent, so ILP comes for free; the only memory traffic is one LDG of the
 // threshold per warp and one 16-byte store per lane (512 B per warp, fully coalesced).
 // ================================================================================================
-template <int BITS>
+// bits = 2*bits + (u < thr) in two instructions: `sub.cc (thr-1) - u` leaves the hardware carry set exactly
+// when u <= thr-1 (the subtraction is thr-1 + ~u + 1, carry = no borrow), and addc shifts it in.
+// thr >= 1 always holds: events whose threshold quantises to 0 are folded to constants by the lowering.
+__device__ __forceinline__ uint32_t shift_in_lt(uint32_t bits, uint32_t u, uint32_t thr_m1) {
+    asm("{ .reg .u32 t; sub.cc.u32 t, %2, %1; addc.u32 %0, %0, %0; }" : "+r"(bits) : "r"(u), "r"(thr_m1));
+    return bits;
+}
+
+template <int BITS, int PACK>
 __global__ void __launch_bounds__(256)
 sampler_kernel(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_orig,
                const uint32_t* __restrict__ thr32, const uint64_t* __restrict__ thr64,
@@ -41,14 +50,19 @@ sampler_kernel(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_orig,
         const uint32_t q_lo = (uint32_t)q, q_hi = (uint32_t)(q >> 32);
 #pragma unroll
         for (int h = 0; h < 4; ++h) {
+            // bits = 2*bits + (u < thr): the borrow of u - thr shifted in through the carry chain, two
+            // ALU instructions per sample. Samples are visited last-to-first so sample i lands on bit i.
             uint32_t bits = 0;
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
+            for (int c = 7; c >= 0; --c) {
                 const uint4 r = philox4x32_10(q_lo + h * 8 + c, q_hi, e, 0u, K);
-                bits |= (uint32_t)(r.x < thr) << (4 * c);
-                bits |= (uint32_t)(r.y < thr) << (4 * c + 1);
-                bits |= (uint32_t)(r.z < thr) << (4 * c + 2);
-                bits |= (uint32_t)(r.w < thr) << (4 * c + 3);
+                if (PACK == 0) {
+                    bits = (bits << 4) | (uint32_t)(r.x < thr) | ((uint32_t)(r.y < thr) << 1) |
+                           ((uint32_t)(r.z < thr) << 2) | ((uint32_t)(r.w < thr) << 3);
+                } else {
+                    bits = shift_in_lt(bits, r.w, thr - 1); bits = shift_in_lt(bits, r.z, thr - 1);
+                    bits = shift_in_lt(bits, r.y, thr - 1); bits = shift_in_lt(bits, r.x, thr - 1);
+                }
             }
             out[h] = bits;
         }
@@ -92,23 +106,27 @@ __device__ __forceinline__ uint4 load_child(const uint4* __restrict__ base, uint
     return xors4(ld_cg(base + (size_t)row * kRowVec + lane), m);
 }
 
+#ifndef CANOPY_SIMPLE_UNROLL
+#define CANOPY_SIMPLE_UNROLL 4
+#endif
+constexpr int kSimpleUnroll = CANOPY_SIMPLE_UNROLL;
 template <int OP>  // kDevAnd / kDevOr / kDevXor
 __device__ __forceinline__ uint4 eval_simple(const uint4* __restrict__ base, const uint32_t* __restrict__ child,
-                                             uint32_t n, uint32_t lane) {
+                                             uint32_t n, uint32_t lane, uint32_t first_ids) {
     constexpr uint32_t ident = OP == kDevAnd ? 0xFFFFFFFFu : 0u;
     uint4 acc = splat4(ident);
     for (uint32_t j0 = 0; j0 < n; j0 += 32) {
         const uint32_t cnt = min(32u, n - j0);
-        const uint32_t my = lane < cnt ? __ldg(child + j0 + lane) : 0u;
-        for (uint32_t j = 0; j < cnt; j += 8) {
-            uint4 v[8];
+        const uint32_t my = j0 == 0 ? first_ids : (lane < cnt ? __ldg(child + j0 + lane) : 0u);
+        for (uint32_t j = 0; j < cnt; j += kSimpleUnroll) {
+            uint4 v[kSimpleUnroll];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) {
+            for (int u = 0; u < kSimpleUnroll; ++u) {
                 const uint32_t code = __shfl_sync(0xFFFFFFFFu, my, (j + u) & 31);
                 v[u] = load_child(base, code, lane, j + u < cnt, ident);
             }
 #pragma unroll
-            for (int u = 0; u < 8; ++u)
+            for (int u = 0; u < kSimpleUnroll; ++u)
                 acc = OP == kDevAnd ? and4(acc, v[u]) : OP == kDevOr ? or4(acc, v[u]) : xor4(acc, v[u]);
         }
     }
@@ -123,7 +141,12 @@ __device__ __forceinline__ uint32_t and4(uint32_t a, uint32_t b) { return a & b;
 __device__ __forceinline__ uint32_t or4(uint32_t a, uint32_t b) { return a | b; }
 __device__ __forceinline__ uint32_t xor4(uint32_t a, uint32_t b) { return a ^ b; }
 __device__ __forceinline__ uint32_t andn4(uint32_t a, uint32_t b) { return a & ~b; }
+__device__ __forceinline__ uint2 and4(uint2 a, uint2 b) { return make_uint2(a.x & b.x, a.y & b.y); }
+__device__ __forceinline__ uint2 or4(uint2 a, uint2 b) { return make_uint2(a.x | b.x, a.y | b.y); }
+__device__ __forceinline__ uint2 xor4(uint2 a, uint2 b) { return make_uint2(a.x ^ b.x, a.y ^ b.y); }
+__device__ __forceinline__ uint2 andn4(uint2 a, uint2 b) { return make_uint2(a.x & ~b.x, a.y & ~b.y); }
 template <class V> __device__ __forceinline__ V splat(uint32_t v);
+template <> __device__ __forceinline__ uint2 splat<uint2>(uint32_t v) { return make_uint2(v, v); }
 template <> __device__ __forceinline__ uint4 splat<uint4>(uint32_t v) { return splat4(v); }
 template <> __device__ __forceinline__ uint32_t splat<uint32_t>(uint32_t v) { return v; }
 
@@ -136,24 +159,33 @@ __device__ __forceinline__ void load_child_v(uint32_t& out, const uint4* __restr
     out = __ldcg(reinterpret_cast<const uint32_t*>(base + (size_t)row * kRowVec + lane) + comp) ^ m;
 }
 
+__device__ __forceinline__ void load_child_v(uint2& out, const uint4* __restrict__ base, uint32_t code, uint32_t lane, bool ok, int comp) {
+    if (!ok) { out = make_uint2(0u, 0u); return; }
+    const uint32_t row = code & 0x7FFFFFFFu, m = (uint32_t)((int32_t)code >> 31);
+    const uint2 v = __ldcg(reinterpret_cast<const uint2*>(base + (size_t)row * kRowVec + lane) + comp);
+    out = make_uint2(v.x ^ m, v.y ^ m);
+}
+
 template <int P, class V>
 __device__ __forceinline__ V eval_range(const uint4* __restrict__ base, const uint32_t* __restrict__ child,
-                                        uint32_t n, uint32_t lo, uint32_t hi, uint32_t lane, int comp) {
+                                        uint32_t n, uint32_t lo, uint32_t hi, uint32_t lane, int comp,
+                                        uint32_t first_ids) {
     V pl[P];
 #pragma unroll
     for (int p = 0; p < P; ++p) pl[p] = splat<V>(0u);
     for (uint32_t j0 = 0; j0 < n; j0 += 32) {
         const uint32_t cnt = min(32u, n - j0);
-        const uint32_t my = lane < cnt ? __ldg(child + j0 + lane) : 0u;
-        for (uint32_t j = 0; j < cnt; j += 4) {
-            V v[4];
+        const uint32_t my = j0 == 0 ? first_ids : (lane < cnt ? __ldg(child + j0 + lane) : 0u);
+        constexpr int U = (P * (int)sizeof(V) > 64) ? 2 : 4;  // keep planes + loads inside the register budget
+        for (uint32_t j = 0; j < cnt; j += U) {
+            V v[U];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < U; ++u) {
                 const uint32_t code = __shfl_sync(0xFFFFFFFFu, my, (j + u) & 31);
                 load_child_v(v[u], base, code, lane, j + u < cnt, comp);
             }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < U; ++u) {
                 V carry = v[u];
 #pragma unroll
                 for (int p = 0; p < P; ++p) {
@@ -193,8 +225,12 @@ __device__ __forceinline__ uint32_t valid_mask32(uint64_t s, uint64_t begin, uin
 }
 
 constexpr int kGateThreads = 256;
+#ifndef CANOPY_GATE_MIN_BLOCKS
+#define CANOPY_GATE_MIN_BLOCKS 4
+#endif
+constexpr int kGateMinBlocks = CANOPY_GATE_MIN_BLOCKS;
 
-__global__ void __launch_bounds__(kGateThreads)
+__global__ void __launch_bounds__(kGateThreads, kGateMinBlocks)
 gate_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const uint32_t* __restrict__ child,
             const uint32_t* __restrict__ layer_off, uint32_t n_layers, uint32_t n_nodes, uint32_t n_ev,
             unsigned long long* __restrict__ tallies, uint64_t first_slab, uint64_t begin, uint64_t end) {
@@ -206,24 +242,41 @@ gate_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const uint
                                   valid_mask32(s0 + 64, begin, end), valid_mask32(s0 + 96, begin, end));
     for (uint32_t l = 0; l < n_layers; ++l) {
         const uint32_t g_end = __ldg(layer_off + l + 1);
-        for (uint32_t g = __ldg(layer_off + l) + warp; g < g_end; g += n_warps) {
-            const uint4 rec = __ldg(grec + g);
+        uint32_t g = __ldg(layer_off + l) + warp;
+        // Metadata pipeline: the record of gate g+2W and the first 32 child ids of gate g+W are requested
+        // before the child rows of gate g, so the record -> ids -> rows dependency never stalls the warp.
+        uint4 rec = make_uint4(0, 0, 0, 0), rec1 = rec;
+        uint32_t ids = 0;
+        if (g < g_end) {
+            rec = __ldg(grec + g);
+            if (g + n_warps < g_end) rec1 = __ldg(grec + g + n_warps);
+            if (lane < rec.y) ids = __ldg(child + rec.x + lane);
+        }
+        for (; g < g_end; g += n_warps) {
+            uint4 rec2 = make_uint4(0, 0, 0, 0);
+            uint32_t ids1 = 0;
+            if (g + 2 * n_warps < g_end) rec2 = __ldg(grec + g + 2 * n_warps);
+            if (g + n_warps < g_end && lane < rec1.y) ids1 = __ldg(child + rec1.x + lane);
             const uint32_t* ch = child + rec.x;
             const uint32_t n = rec.y, op = rec.z & 0xFFu, flags = rec.z >> 8;
             uint4 r;
-            if (op == kDevAnd) r = eval_simple<kDevAnd>(base, ch, n, lane);
-            else if (op == kDevOr) r = eval_simple<kDevOr>(base, ch, n, lane);
-            else if (op == kDevXor) r = eval_simple<kDevXor>(base, ch, n, lane);
+            if (op == kDevAnd) r = eval_simple<kDevAnd>(base, ch, n, lane, ids);
+            else if (op == kDevOr) r = eval_simple<kDevOr>(base, ch, n, lane, ids);
+            else if (op == kDevXor) r = eval_simple<kDevXor>(base, ch, n, lane, ids);
             else {
                 const uint32_t lo = rec.w & 0xFFFFu, hi = rec.w >> 16;
-                if (n < 8) r = eval_range<3, uint4>(base, ch, n, lo, hi, lane, 0);
-                else if (n < 64) r = eval_range<6, uint4>(base, ch, n, lo, hi, lane, 0);
-                else if (n < 512) r = eval_range<9, uint4>(base, ch, n, lo, hi, lane, 0);
+                if (n < 8) r = eval_range<3, uint4>(base, ch, n, lo, hi, lane, 0, ids);
+                else if (n < 64) r = eval_range<6, uint4>(base, ch, n, lo, hi, lane, 0, ids);
+                else if (n < 512) {  // 9 planes: two passes of 8 bytes per lane
+                    const uint2 a = eval_range<9, uint2>(base, ch, n, lo, hi, lane, 0, ids);
+                    const uint2 b = eval_range<9, uint2>(base, ch, n, lo, hi, lane, 1, ids);
+                    r = make_uint4(a.x, a.y, b.x, b.y);
+                }
                 else {
-                    r.x = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 0);
-                    r.y = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 1);
-                    r.z = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 2);
-                    r.w = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 3);
+                    r.x = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 0, ids);
+                    r.y = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 1, ids);
+                    r.z = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 2, ids);
+                    r.w = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 3, ids);
                 }
             }
             if (flags & kFlagStore) st_cg(base + (size_t)(n_ev + g) * kRowVec + lane, r);
@@ -232,6 +285,7 @@ gate_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const uint
                 c = __reduce_add_sync(0xFFFFFFFFu, c);
                 if (lane == 0 && c) atomicAdd(tallies + g, (unsigned long long)c);
             }
+            rec = rec1; rec1 = rec2; ids = ids1;
         }
         __syncthreads();  // rows written in this layer are read by later layers of the same CTA only
     }
@@ -438,10 +492,12 @@ static void launch_sampler(const DeviceState* s, const Lowered& L, uint4* vals, 
                            const PhiloxKeys& K, cudaStream_t st) {
     if (L.n_events() == 0 || n_slabs == 0) return;
     const dim3 grid((L.n_events() + 7) / 8, n_slabs), block(256);
-    if (L.opts.threshold_bits == 64)
-        sampler_kernel<64><<<grid, block, 0, st>>>(vals, s->ev_orig, s->thr32, s->thr64, L.n_events(), L.n_nodes(), first_slab, K);
-    else
-        sampler_kernel<32><<<grid, block, 0, st>>>(vals, s->ev_orig, s->thr32, s->thr64, L.n_events(), L.n_nodes(), first_slab, K);
+#define CANOPY_SAMPLER_ARGS vals, s->ev_orig, s->thr32, s->thr64, L.n_events(), L.n_nodes(), first_slab, K
+    static const int pack = getenv("CANOPY_SAMPLER_PACK") ? atoi(getenv("CANOPY_SAMPLER_PACK")) : 1;  // tuning knob
+    if (L.opts.threshold_bits == 64) sampler_kernel<64, 0><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
+    else if (pack == 0) sampler_kernel<32, 0><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
+    else sampler_kernel<32, 1><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
+#undef CANOPY_SAMPLER_ARGS
     CUDA_CHECK(cudaGetLastError());
 }
 
