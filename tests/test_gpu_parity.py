@@ -1,0 +1,108 @@
+"""GPU parity tests proper: the CUDA path through the C ABI against the oracle, bit-exact.
+Sizes are chosen so the oracle (multi-threaded packed port, itself checked against the scalar oracle on CPU)
+finishes in seconds; BASELINE-sized runs are covered by size-independent properties in test_gpu_properties.py."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from helpers import G, O, ROOT, random_graph
+from canopy_b200 import synth
+from canopy_b200.engine import Plan, load_mef
+
+pytestmark = pytest.mark.gpu
+CORES = len(os.sched_getaffinity(0))
+
+
+def _golden():
+    with open(os.path.join(ROOT, "tests", "golden", "golden_tallies.json")) as f:
+        return json.load(f)["cases"]
+
+
+@pytest.mark.parametrize("case", _golden(), ids=lambda c: c["name"])
+def test_golden_fixtures(case):
+    g = case["graph"]
+    graph = G.Graph(p=g["p"], op=g["op"], kmin=g["kmin"], kmax=g["kmax"], child_off=g["child_off"], child=g["child"],
+                    roots=g["roots"])
+    with Plan(graph, case["tally_all"], case["bits"]) as plan:
+        got, _ = plan.run(case["n"], seed=case["seed"], sample_begin=case["begin"])
+    assert np.array_equal(got, np.array(case["tallies"], dtype=np.uint64))
+
+
+def test_c1_mef_example_2pow20():
+    """BASELINE.json config 1: the small AND/OR MEF tree, 2^20 samples, GPU vs the CPU path."""
+    g = load_mef(os.path.join(ROOT, "examples", "c1_small_ft.xml"))
+    n = 1 << 20
+    with Plan(g, tally_all_gates=True) as plan:
+        got, _ = plan.run(n, seed=2024)
+    assert np.array_equal(got, O.mc_packed(g, 2024, 0, n, True, nthreads=CORES))
+
+
+@pytest.mark.parametrize("name,scale,n", [("c2", 0.1, 1 << 15), ("c3", 0.05, 1 << 15), ("c4", 0.02, 1 << 14)])
+def test_scaled_configs(name, scale, n):
+    g = synth.config_graph(name, scale)
+    tally_all = name == "c3"
+    with Plan(g, tally_all) as plan:
+        got, rep = plan.run(n, seed=77, sample_begin=4096 * 9 + 13)
+    assert np.array_equal(got, O.mc_packed(g, 77, 4096 * 9 + 13, n, tally_all, nthreads=CORES))
+    assert rep.gate_launches >= 1 and rep.sampler_launches >= 1
+
+
+def test_c2_full_graph_short_run():
+    g = synth.config_graph("c2")
+    n = 1 << 13
+    with Plan(g, tally_all_gates=True) as plan:
+        got, _ = plan.run(n, seed=5)
+    assert np.array_equal(got, O.mc_packed(g, 5, 0, n, True, nthreads=CORES))
+
+
+def test_sampler_words_every_live_event():
+    g = synth.config_graph("c2", 0.05)
+    with Plan(g) as plan:
+        v = plan.view()
+        got = plan.sample_words(seed=(1 << 63) + 12345, first_word=64 * 1000, n_words=64)
+    assert np.array_equal(got, O.sample_words(g, (1 << 63) + 12345, v["event_orig"], 64 * 1000, 64))
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_graphs_all_connectives(seed):
+    g = random_graph(100 + seed, n_basic=16, n_gates=48, max_fanin=9, n_roots=4)
+    with Plan(g, tally_all_gates=True) as plan:
+        got, _ = plan.run(20_000, seed=seed, sample_begin=1000 * seed + 7)
+    assert np.array_equal(got, O.mc_scalar(g, seed, 1000 * seed + 7, 20_000, True))
+
+
+@pytest.mark.parametrize("bits", [32, 64])
+def test_rare_events_and_threshold_width(bits):
+    """p down to 1e-9: 32-bit thresholds quantise to multiples of 2^-32, 64-bit ones resolve them."""
+    b = G.GraphBuilder()
+    e = [b.basic_event(p) for p in (1e-9, 3e-7, 1e-4, 0.02, 0.5, 2.0 ** -33)]
+    b.root(b.gate(G.OR, e))
+    b.root(b.gate(G.AND, [e[3], e[4]]))
+    g = b.build()
+    n = 1 << 17
+    with Plan(g, tally_all_gates=True, threshold_bits=bits) as plan:
+        got, _ = plan.run(n, seed=31337)
+    assert np.array_equal(got, O.mc_packed(g, 31337, 0, n, True, bits=bits, nthreads=CORES))
+
+
+@pytest.mark.parametrize("fanin,lo,hi", [(5, 2, 0), (40, 7, 0), (300, 30, 0), (300, 20, 40), (700, 95, 0), (700, 90, 100), (33, 0, 3)])
+def test_high_fanin_count_gates(fanin, lo, hi):
+    """k-of-n / cardinality across every bit-sliced counter width (3, 6, 9 and 16 planes)."""
+    b = G.GraphBuilder()
+    e = [b.basic_event(0.02 + 0.1 * ((i * 37) % 11) / 11) for i in range(fanin)]
+    args = [(x, i % 13 == 0) for i, x in enumerate(e)]
+    if hi:
+        b.root(b.gate(G.CARDINALITY, args, lo, hi))
+    else:
+        b.root(b.gate(G.ATLEAST, args, lo))
+    b.root(b.gate(G.OR, e[:fanin // 2] ))
+    b.root(b.gate(G.AND, [(x, True) for x in e]))
+    g = b.build()
+    n = 3 * 4096
+    with Plan(g) as plan:
+        got, _ = plan.run(n, seed=fanin)
+    want = O.mc_packed(g, fanin, 0, n, nthreads=CORES)
+    assert np.array_equal(got, want)
+    assert 0 < int(got[0]) < n          # the threshold sits inside the count distribution: the gate is exercised

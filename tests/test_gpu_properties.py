@@ -1,0 +1,126 @@
+"""Size-independent properties at BASELINE sizes, and the edge cases of the boundary.  GPU only."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import G, O, random_graph
+from canopy_b200 import _lib, synth
+from canopy_b200.engine import Plan, quantify, Settings
+
+pytestmark = pytest.mark.gpu
+CORES = len(os.sched_getaffinity(0))
+
+
+@pytest.fixture(scope="module")
+def c2_plan():
+    g = synth.config_graph("c2")
+    with Plan(g, tally_all_gates=True) as plan:
+        yield plan
+
+
+def test_c2_full_size_decomposition_and_batching_invariance(c2_plan):
+    """2^26 samples of config 2: tallies of [a,c) == [a,b) + [b,c); independent of batch size and of overlap."""
+    S = 1 << 26
+    whole, rep = c2_plan.run(S, seed=9)
+    cut = 4096 * 5000 + 1234
+    a, _ = c2_plan.run(cut, seed=9)
+    b, _ = c2_plan.run(S - cut, seed=9, sample_begin=cut)
+    assert np.array_equal(whole, a + b)
+    small_batches, rep2 = c2_plan.run(S, seed=9, batch_slabs=148, overlap=False)
+    assert np.array_equal(whole, small_batches) and rep2.n_batches > rep.n_batches
+    assert rep.n_batches * rep.batch_slabs * 4096 >= S
+    # statistical sanity of the top event against its own binomial error (no oracle at this size)
+    top = int(whole[0]); p = top / S
+    assert 0 < top < S and (p * (1 - p) / S) ** 0.5 < 1e-3
+
+
+def test_c2_prefix_matches_oracle_inside_a_long_run(c2_plan):
+    """The first 2^14 samples of a long run are the same samples as a short run (counter-based RNG)."""
+    n = 1 << 14
+    got, _ = c2_plan.run(n, seed=9)
+    assert np.array_equal(got, O.mc_packed(c2_plan.graph, 9, 0, n, True, nthreads=CORES))
+
+
+def test_complement_and_alias_identities():
+    b = G.GraphBuilder()
+    e = [b.basic_event(0.3), b.basic_event(0.6), b.basic_event(0.1)]
+    x = b.gate(G.AND, [e[0], e[1]])
+    for h in (x, b.gate(G.NOT, [x]), b.gate(G.NAND, [e[0], e[1]]), b.gate(G.NULL, [x]),
+              b.gate(G.OR, [e[2], e[0]]), b.gate(G.NOR, [e[2], e[0]])):
+        b.root(h)
+    n = 100_000
+    with Plan(b.build()) as plan:
+        t, _ = plan.run(n, seed=4, sample_begin=17)
+    t = [int(v) for v in t]
+    assert t[0] + t[1] == n and t[1] == t[2] and t[3] == t[0] and t[4] + t[5] == n
+
+
+@pytest.mark.parametrize("begin,n", [(0, 0), (0, 1), (63, 2), (4095, 2), (5, 4091), (4096 * 3, 4096), ((1 << 44) + 4097, 9000),
+                                     ((1 << 63) - 5000, 4999)])
+def test_ragged_ranges(begin, n):
+    g = random_graph(21, n_basic=10, n_gates=18)
+    with Plan(g, tally_all_gates=True) as plan:
+        got, _ = plan.run(n, seed=8, sample_begin=begin)
+    assert np.array_equal(got, O.mc_scalar(g, 8, begin, n, True))
+
+
+def test_constant_and_empty_outputs():
+    b = G.GraphBuilder()
+    e0, e1 = b.basic_event(0.0), b.basic_event(1.0)
+    b.root(b.gate(G.OR, [e0, G.GraphBuilder.constant(False)]))
+    b.root(b.gate(G.AND, [e1, G.GraphBuilder.constant(True)]))
+    b.root(e1)
+    with Plan(b.build()) as plan:
+        t, rep = plan.run(12345, seed=1)
+        assert [int(v) for v in t] == [0, 12345, 12345] and rep.gate_launches == 0
+    with Plan(G.from_lists([], [], [])) as plan:
+        t, _ = plan.run(1000)
+        assert len(t) == 0
+
+
+def test_device_output_on_torch_stream_matches_host_output():
+    g = synth.config_graph("c2", 0.1)
+    with Plan(g, tally_all_gates=True) as plan:
+        host, _ = plan.run(1 << 18, seed=3)
+        side = torch.cuda.Stream()
+        out = torch.zeros(plan.n_tallies, dtype=torch.int64, device="cuda")
+        with torch.cuda.stream(side):
+            plan.run_device(out.data_ptr(), 1 << 18, seed=3, stream=side.cuda_stream)   # no host sync inside
+            doubled = out * 2                                                         # ordered after the run on `side`
+        side.synchronize()
+    assert np.array_equal(out.cpu().numpy().astype(np.uint64), host)
+    assert np.array_equal(doubled.cpu().numpy().astype(np.uint64), host * 2)
+
+
+def test_run_multi_equals_single_device():
+    g = synth.config_graph("c2", 0.1)
+    n = 4096 * 37 + 5
+    devs = list(range(torch.cuda.device_count()))
+    with Plan(g, tally_all_gates=True) as plan:
+        one, _ = plan.run(n, seed=6, sample_begin=11)
+        multi, rep = plan.run_multi(devs, n, seed=6, sample_begin=11)      # NCCL all-reduce when len(devs) > 1
+        assert np.array_equal(one, multi)
+        two_way = plan.run(n // 2, seed=6, sample_begin=11)[0] + plan.run(n - n // 2, seed=6, sample_begin=11 + n // 2)[0]
+        assert np.array_equal(one, two_way)
+
+
+def test_quantify_front_end_and_three_sigma_vs_exact():
+    g = random_graph(60, n_basic=10, n_gates=16, n_roots=2, extreme_p=False)
+    res = quantify(g, Settings(num_trials=1 << 20, seed=12, tally_all_gates=True))
+    exact = O.exact(g, True)
+    sigma = np.sqrt(np.maximum(exact * (1 - exact), 1e-12) / (1 << 20))
+    assert np.all(np.abs(res["p"] - exact) <= 4 * sigma + 1e-9)
+    assert np.all(res["ci_lo"] <= res["p"]) and np.all(res["p"] <= res["ci_hi"])
+
+
+def test_bad_run_arguments():
+    with Plan(random_graph(2)) as plan:
+        with pytest.raises(_lib.CanopyError) as ei:
+            plan.run(100, device=99)
+        assert ei.value.status == _lib.E_INVALID
+        with pytest.raises(_lib.CanopyError):
+            plan.run(1 << 20, sample_begin=(1 << 64) - 10)
+        with pytest.raises(_lib.CanopyError):
+            plan.sample_words(1, 3, 64)
