@@ -169,7 +169,8 @@ typedef struct canopy_mc_opts {
     uint64_t n_samples;
     int32_t  device;          /* CUDA ordinal                                                       */
     int32_t  batch_slabs;     /* slabs (4096 samples each) per batch; 0 = default                   */
-    void*    stream;          /* cudaStream_t to order the run on; NULL = library-owned stream      */
+    void*    stream;          /* cudaStream_t to order the run on; NULL = library-owned stream (pass
+                                 cudaStreamLegacy / cudaStreamPerThread explicitly for the default streams) */
     int32_t  overlap;         /* 1 (default when 0 is passed via canopy_mc_opts_default): sampler of batch i+1 overlaps gates of batch i */
     int32_t  profile;         /* 1: time sampler / gate kernels separately with CUDA events (serialises the two) */
     int32_t  reserved[4];
