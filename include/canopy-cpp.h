@@ -1,0 +1,222 @@
+/*
+ * canopy-cpp.h -- C++ layer over the C ABI of canopy.h.
+ *
+ * Keeps the shape of the reference header (reference include/canopy-cpp.h:32-40: C++ only, <memory>, then
+ * "canopy.h"); everything below it is new, because the reference header declares nothing.
+ *
+ *   canopy::GraphBuilder   incremental construction with the reference's vocabulary: basic events, house
+ *                          events, gates with Formula(connective, args, min, max)
+ *                          (reference src/mef/openpsa/event/formula.h:72-80, event/event.h:143-157)
+ *   canopy::Plan           RAII owner of a lowered graph (canopy_plan)
+ *   canopy::McSettings     Monte Carlo subset of reference Settings (settings.h:118-187,324-327)
+ *   canopy::lower_model()  adapter from reference mef::openpsa::Model objects; only compiled when the caller
+ *                          defines CANOPY_WITH_MEF_OPENPSA and has the reference headers (+ Boost) on its include
+ *                          path -- neither exists in this repository's build environment.
+ */
+#pragma once
+
+#ifndef __cplusplus
+#error "This header is for C++ only"
+#endif
+
+#include <cstddef>
+#include <cstdint>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <unordered_map>
+#include <utility>
+#include <vector>
+
+#include "canopy.h"
+
+namespace canopy {
+
+/// Thrown by this layer; carries the canopy_status of the failed C call.
+/// Status -> reference exception (src/mef/openpsa/error.h): E_VALIDITY ValidityError, E_CYCLE CycleError,
+/// E_DOMAIN DomainError, E_INVALID LogicError, E_IO IOError.
+class Error : public std::runtime_error {
+  public:
+    Error(canopy_status s, const std::string& msg) : std::runtime_error(msg), status_(s) {}
+    canopy_status status() const noexcept { return status_; }
+
+  private:
+    canopy_status status_;
+};
+
+inline void check(canopy_status s) {
+    if (s != CANOPY_OK) throw Error(s, std::string(canopy_status_string(s)) + ": " + canopy_last_error());
+}
+
+/// Same numbering as mef::openpsa::Connective.
+enum Connective : std::uint8_t {
+    kAnd = CANOPY_AND, kOr = CANOPY_OR, kAtleast = CANOPY_ATLEAST, kXor = CANOPY_XOR, kNot = CANOPY_NOT,
+    kNand = CANOPY_NAND, kNor = CANOPY_NOR, kNull = CANOPY_NULL, kIff = CANOPY_IFF, kImply = CANOPY_IMPLY,
+    kCardinality = CANOPY_CARDINALITY
+};
+
+/// A formula argument: node handle + complement flag (reference Formula::Arg, formula.h:12-15).
+struct Arg {
+    std::uint32_t node;
+    bool complement = false;
+};
+
+class GraphBuilder {
+  public:
+    /// @returns handle of a new basic event with mean probability p (BasicEvent::p(), event.h:93-96).
+    std::uint32_t basic_event(double p) {
+        if (!gates_op_.empty()) throw Error(CANOPY_E_INVALID, "add all basic events before the first gate");
+        p_.push_back(p);
+        return static_cast<std::uint32_t>(p_.size() - 1);
+    }
+    /// Handles of the two Boolean constants (HouseEvent::kTrue / kFalse, event.h:37-38).
+    static constexpr std::uint32_t constant(bool state) { return state ? CANOPY_CONST_TRUE : CANOPY_CONST_FALSE; }
+    /// A house event is its state (event.h:51).
+    static constexpr std::uint32_t house_event(bool state) { return constant(state); }
+
+    /// @returns handle of a new gate with formula (connective, args, min_number, max_number).
+    std::uint32_t gate(Connective c, const std::vector<Arg>& args, int min_number = 0, int max_number = 0) {
+        gates_op_.push_back(c);
+        kmin_.push_back(static_cast<std::uint16_t>(min_number));
+        kmax_.push_back(static_cast<std::uint16_t>(max_number));
+        for (const Arg& a : args) child_.push_back(a.node | (a.complement ? CANOPY_CHILD_COMPLEMENT : 0u));
+        child_off_.push_back(child_.size());
+        return static_cast<std::uint32_t>(p_.size() + gates_op_.size() - 1);
+    }
+    void root(std::uint32_t node) { roots_.push_back(node); }
+
+    canopy_graph_desc desc() const {
+        canopy_graph_desc d{};
+        d.n_basic = static_cast<std::uint32_t>(p_.size());
+        d.n_gates = static_cast<std::uint32_t>(gates_op_.size());
+        d.n_roots = static_cast<std::uint32_t>(roots_.size());
+        d.n_edges = child_.size();
+        d.p = p_.data(); d.op = gates_op_.data(); d.kmin = kmin_.data(); d.kmax = kmax_.data();
+        d.child_off = child_off_.data(); d.child = child_.data(); d.roots = roots_.data();
+        return d;
+    }
+
+  private:
+    std::vector<double> p_;
+    std::vector<std::uint8_t> gates_op_;
+    std::vector<std::uint16_t> kmin_, kmax_;
+    std::vector<std::uint64_t> child_off_{0};
+    std::vector<std::uint32_t> child_, roots_;
+};
+
+/// Monte Carlo knobs of reference Settings, widened from int to 64 bit.
+struct McSettings {
+    std::uint64_t num_trials = 1000;  ///< settings.h:325
+    std::uint64_t seed = 0;           ///< settings.h:324
+    std::uint64_t sample_begin = 0;   ///< restart / shard by counter range
+    int batch_size = 0;               ///< slabs per batch (settings.h:326 counts trials); 0 = engine default
+    int device = 0;
+    bool tally_all_gates = false;
+    int threshold_bits = 32;
+};
+
+struct Result {
+    std::vector<std::uint64_t> tallies;
+    canopy_mc_report report{};
+    canopy_estimate estimate(std::size_t i, std::uint64_t n) const {
+        canopy_estimate e{};
+        check(canopy_estimate_from_tally(tallies.at(i), n, &e));
+        return e;
+    }
+};
+
+class Plan {
+  public:
+    Plan(const canopy_graph_desc& d, bool tally_all_gates = false, int threshold_bits = 32) {
+        canopy_plan_opts o{};
+        o.tally_all_gates = tally_all_gates;
+        o.threshold_bits = threshold_bits;
+        canopy_plan* p = nullptr;
+        check(canopy_plan_create(&d, &o, &p));
+        plan_.reset(p);
+        check(canopy_plan_info(p, &stats_));
+    }
+    const canopy_plan_stats& stats() const noexcept { return stats_; }
+    canopy_plan* get() const noexcept { return plan_.get(); }
+
+    Result run(const McSettings& s, void* stream = nullptr) const {
+        canopy_mc_opts o;
+        canopy_mc_opts_default(&o);
+        o.seed = s.seed; o.sample_begin = s.sample_begin; o.n_samples = s.num_trials;
+        o.device = s.device; o.batch_slabs = s.batch_size; o.stream = stream;
+        Result r;
+        r.tallies.resize(stats_.n_tallies);
+        check(canopy_mc_run(plan_.get(), &o, r.tallies.data(), &r.report));
+        return r;
+    }
+
+  private:
+    struct Deleter { void operator()(canopy_plan* p) const noexcept { canopy_plan_destroy(p); } };
+    std::unique_ptr<canopy_plan, Deleter> plan_;
+    canopy_plan_stats stats_{};
+};
+
+inline Result quantify(const canopy_graph_desc& d, const McSettings& s) {
+    return Plan(d, s.tally_all_gates, s.threshold_bits).run(s);
+}
+
+}  // namespace canopy
+
+#ifdef CANOPY_WITH_MEF_OPENPSA
+// Adapter from the reference object model. Needs the reference headers (and Boost) on the include path.
+#include <variant>
+
+#include "mef/openpsa/event/event.h"
+#include "mef/openpsa/event/formula.h"
+#include "mef/openpsa/event/gate.h"
+#include "mef/openpsa/fault_tree.h"
+#include "mef/openpsa/model.h"
+#include "mef/openpsa/settings.h"
+
+namespace canopy {
+
+/// Flattens Model -> FaultTree::top_events() -> Gate::formula().args() into a GraphBuilder.
+/// Follows BasicEvent::ccf_gate() when settings.ccf_analysis() (event.h:108-114, settings.h:298).
+/// Must run on the thread that owns the model: MEF objects are not thread-safe (model.h:74-76).
+inline GraphBuilder lower_model(const mef::openpsa::Model& model, const mef::openpsa::Settings& settings) {
+    using namespace mef::openpsa;
+    GraphBuilder b;
+    std::unordered_map<const BasicEvent*, std::uint32_t> ev;
+    for (const BasicEvent& e : model.basic_events()) ev.emplace(&e, b.basic_event(e.p()));
+    std::unordered_map<const Gate*, std::uint32_t> done;
+    struct Walk {
+        GraphBuilder& b; decltype(ev)& ev; decltype(done)& done; bool ccf;
+        std::uint32_t gate(const Gate& g) {
+            auto it = done.find(&g);
+            if (it != done.end()) return it->second;
+            const Formula& f = g.formula();
+            std::vector<Arg> args;
+            for (const Formula::Arg& a : f.args()) {
+                std::uint32_t node = std::visit([&](auto* e) -> std::uint32_t {
+                    using T = std::decay_t<decltype(*e)>;
+                    if constexpr (std::is_same_v<T, Gate>) return gate(*e);
+                    else if constexpr (std::is_same_v<T, BasicEvent>) return ccf && e->HasCcf() ? gate(e->ccf_gate()) : ev.at(e);
+                    else return GraphBuilder::house_event(e->state());
+                }, a.event);
+                args.push_back({node, a.complement});
+            }
+            std::uint32_t h = b.gate(static_cast<Connective>(f.connective()), args, f.min_number().value_or(0),
+                                     f.max_number().value_or(0));
+            done.emplace(&g, h);
+            return h;
+        }
+    } walk{b, ev, done, settings.ccf_analysis()};
+    for (const FaultTree& ft : model.fault_trees())
+        for (const Gate* top : ft.top_events()) b.root(walk.gate(*top));
+    return b;
+}
+
+inline McSettings mc_settings(const mef::openpsa::Settings& s) {
+    McSettings m;
+    m.num_trials = static_cast<std::uint64_t>(s.num_trials());
+    m.seed = static_cast<std::uint64_t>(s.seed());
+    return m;
+}
+
+}  // namespace canopy
+#endif  // CANOPY_WITH_MEF_OPENPSA
