@@ -25,7 +25,8 @@ class CanopyError(RuntimeError):
 
 
 class CPlanOpts(C.Structure):
-    _fields_ = [("tally_all_gates", C.c_int32), ("threshold_bits", C.c_int32), ("reserved", C.c_int32 * 6)]
+    _fields_ = [("tally_all_gates", C.c_int32), ("threshold_bits", C.c_int32), ("sampler", C.c_int32),
+                ("reserved", C.c_int32 * 5)]
 
 
 class CPlanStats(C.Structure):

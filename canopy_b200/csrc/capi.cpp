@@ -44,6 +44,7 @@ canopy_status canopy_plan_create(const canopy_graph_desc* desc, const canopy_pla
         canopy_plan_opts o{};
         if (opts) o = *opts;
         if (o.threshold_bits == 0) o.threshold_bits = 32;
+        if (o.sampler == CANOPY_SAMPLER_DEFAULT) o.sampler = CANOPY_SPEC_VERSION;
         auto* p = new canopy_plan();
         try {
             canopy::lower_graph(*desc, o, p->low);

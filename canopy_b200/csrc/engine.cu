@@ -88,6 +88,69 @@ sampler_kernel(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_orig,
 }
 
 // ================================================================================================
+// Sliced sampler (SPEC v2).  Same geometry as above -- one warp per (event, slab), lane r owns the 128
+// samples of group g = slab*32 + r -- but the comparison u < thr runs MSB-first on bit planes:
+//   head: 8 Philox calls ctr = (g, e, 0x100+k); word j of call k is bit (7-k) of the variates' top byte
+//         for samples 32j..32j+31 of the group.  Per plane and word: a lane still undecided (all higher
+//         bits equal to the threshold's) becomes "less" where thr has 1 and u has 0, "greater" where thr
+//         has 0 and u has 1.  The threshold is warp-uniform, so the per-plane branch is uniform.
+//   tail: a sample still undecided after 8 planes (probability 2^-8) takes its low 24 (56) bits from
+//         output word 0 (words 1:0) of the per-sample call ctr = (s, e, 0x200) (resp. 0x201).
+// 8 + ~2.4 Philox calls per 128 samples instead of 32 (64 for 64-bit thresholds).
+// ================================================================================================
+template <int BITS>
+__global__ void __launch_bounds__(256)
+sampler_sliced_kernel(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_orig,
+                      const uint32_t* __restrict__ thr32, const uint64_t* __restrict__ thr64,
+                      uint32_t n_ev, uint32_t n_nodes, uint64_t first_slab, PhiloxKeys K) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t ev = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (ev >= n_ev) return;
+    const uint32_t slab = blockIdx.y;
+    const uint32_t e = __ldg(ev_orig + ev);
+    const uint64_t g = (first_slab + slab) * (kSlabSamples / 128) + lane;  // 128-sample group of this lane
+    const uint32_t g_lo = (uint32_t)g, g_hi = (uint32_t)(g >> 32);
+    uint32_t head;                 // top 8 bits of the threshold, left-aligned in a 32-bit word
+    uint32_t tail32 = 0; uint64_t tail64 = 0;  // (thr mod 2^(BITS-8)) << 8: compared with the raw tail variate
+    if (BITS == 32) { const uint32_t t = __ldg(thr32 + ev); head = t; tail32 = t << 8; }
+    else { const uint64_t t = __ldg(thr64 + ev); head = (uint32_t)(t >> 32); tail64 = t << 8; }
+    uint32_t u0 = ~0u, u1 = ~0u, u2 = ~0u, u3 = ~0u;  // undecided lanes
+    uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0;          // decided "u < thr"
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const uint4 x = philox4x32_10(g_lo, g_hi, e, 0x100u + k, K);
+        if (head & (0x80000000u >> k)) {
+            r0 |= u0 & ~x.x; r1 |= u1 & ~x.y; r2 |= u2 & ~x.z; r3 |= u3 & ~x.w;
+            u0 &= x.x; u1 &= x.y; u2 &= x.z; u3 &= x.w;
+        } else {
+            u0 &= ~x.x; u1 &= ~x.y; u2 &= ~x.z; u3 &= ~x.w;
+        }
+    }
+    // tail: resolve the few undecided samples one by one (lanes diverge; ~2.4 trips per warp). Branch-free
+    // inside a trip: `shl.b32` clamps, so 1 << (sl - 32w) is the sample's bit in word w and 0 in the others.
+    const uint64_t s_base = g * 128u;
+#pragma unroll 1
+    while (u0 | u1 | u2 | u3) {
+        const uint32_t sl = u0 ? __ffs(u0) - 1u : u1 ? __ffs(u1) + 31u : u2 ? __ffs(u2) + 63u : __ffs(u3) + 95u;
+        const uint64_t sidx = s_base + sl;
+        uint32_t lt;  // all-ones when the tail variate is below the tail threshold
+        if (BITS == 32) {
+            const uint32_t v = philox4x32_10_x((uint32_t)sidx, (uint32_t)(sidx >> 32), e, 0x200u, K);
+            lt = v < tail32 ? ~0u : 0u;
+        } else {
+            const uint2 v = philox4x32_10_xy((uint32_t)sidx, (uint32_t)(sidx >> 32), e, 0x201u, K);
+            lt = (((uint64_t)v.y << 32) | v.x) < tail64 ? ~0u : 0u;
+        }
+        const uint32_t b0 = shl_clamp(1u, sl), b1 = shl_clamp(1u, sl - 32u), b2 = shl_clamp(1u, sl - 64u),
+                       b3 = shl_clamp(1u, sl - 96u);
+        u0 &= ~b0; u1 &= ~b1; u2 &= ~b2; u3 &= ~b3;
+        r0 |= b0 & lt; r1 |= b1 & lt; r2 |= b2 & lt; r3 |= b3 & lt;
+    }
+    uint4* row = vals + ((size_t)slab * n_nodes + ev) * kRowVec;
+    st_cg(row + lane, make_uint4(r0, r1, r2, r3));
+}
+
+// ================================================================================================
 // Gate kernel (slab walker).
 // ================================================================================================
 __device__ __forceinline__ uint4 and4(uint4 a, uint4 b) { return make_uint4(a.x & b.x, a.y & b.y, a.z & b.z, a.w & b.w); }
@@ -494,7 +557,11 @@ static void launch_sampler(const DeviceState* s, const Lowered& L, uint4* vals, 
     const dim3 grid((L.n_events() + 7) / 8, n_slabs), block(256);
 #define CANOPY_SAMPLER_ARGS vals, s->ev_orig, s->thr32, s->thr64, L.n_events(), L.n_nodes(), first_slab, K
     static const int pack = getenv("CANOPY_SAMPLER_PACK") ? atoi(getenv("CANOPY_SAMPLER_PACK")) : 1;  // tuning knob
-    if (L.opts.threshold_bits == 64) sampler_kernel<64, 0><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
+    if (L.opts.sampler == CANOPY_SAMPLER_SLICED) {
+        if (L.opts.threshold_bits == 64) sampler_sliced_kernel<64><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
+        else sampler_sliced_kernel<32><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
+    }
+    else if (L.opts.threshold_bits == 64) sampler_kernel<64, 0><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
     else if (pack == 0) sampler_kernel<32, 0><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
     else sampler_kernel<32, 1><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
 #undef CANOPY_SAMPLER_ARGS

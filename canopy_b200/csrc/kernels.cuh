@@ -45,6 +45,26 @@ __device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_
     return make_uint4(c0, c1, c2, c3);
 }
 
+// Output word 0 only / words 0 and 1 only (the tail variate of SPEC v2): the last round's M0 product is dead.
+__device__ __forceinline__ uint2 philox4x32_10_xy(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                                  const PhiloxKeys& K) {
+#pragma unroll
+    for (int r = 0; r < 9; ++r) philox_round(c0, c1, c2, c3, K.k0[r], K.k1[r]);
+    const uint64_t p1 = (uint64_t)kPhiloxM1 * c2;
+    return make_uint2((uint32_t)(p1 >> 32) ^ c1 ^ K.k0[9], (uint32_t)p1);
+}
+__device__ __forceinline__ uint32_t philox4x32_10_x(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                                    const PhiloxKeys& K) {
+    return philox4x32_10_xy(c0, c1, c2, c3, K).x;
+}
+
+// PTX shl.b32 clamps shift amounts above 31 (result 0); `<<` in C++ would be undefined there.
+__device__ __forceinline__ uint32_t shl_clamp(uint32_t v, uint32_t n) {
+    uint32_t r;
+    asm("shl.b32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(n));
+    return r;
+}
+
 __device__ __forceinline__ uint4 ld_cg(const uint4* p) { return __ldcg(p); }
 __device__ __forceinline__ void st_cg(uint4* p, uint4 v) { __stcg(p, v); }
 

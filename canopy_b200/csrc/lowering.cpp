@@ -149,6 +149,8 @@ std::vector<uint32_t> topo_order(const canopy_graph_desc& d) {
 void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lowered& L) {
     if (opts.threshold_bits != 32 && opts.threshold_bits != 64)
         fail(CANOPY_E_INVALID, "threshold_bits must be 32 or 64");
+    if (opts.sampler != CANOPY_SAMPLER_DIRECT && opts.sampler != CANOPY_SAMPLER_SLICED)
+        fail(CANOPY_E_INVALID, "sampler must be CANOPY_SAMPLER_DIRECT (1) or CANOPY_SAMPLER_SLICED (2)");
     validate(d);
     const uint32_t B = d.n_basic, G = d.n_gates;
     const bool tally_all = opts.tally_all_gates != 0;
@@ -355,7 +357,7 @@ void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lower
     s.n_gates_stored = n_stored; s.n_gates_tallied = n_tallied; s.n_layers = L.n_layers();
     s.max_fanin = max_fanin; s.mean_fanin = L.n_gates() ? (double)L.child.size() / L.n_gates() : 0.0;
     s.n_tallies = n_tallies; s.n_const_nodes = n_const; s.n_alias_nodes = n_alias;
-    s.spec_version = CANOPY_SPEC_VERSION;
+    s.spec_version = (uint32_t)opts.sampler;  // spec number == sampler id
 }
 
 void shard_range(uint64_t begin, uint64_t n, int rank, int world, uint64_t* ob, uint64_t* on) {

@@ -28,6 +28,7 @@ class Settings:
     sample_begin: int = 0       # first global sample index (restart / shard by counter range)
     tally_all_gates: bool = False
     threshold_bits: int = 32
+    sampler: int = 0            # sampling spec: 0 = library default (2, "sliced"), 1 = "direct", 2 = "sliced"
     overlap: bool = True
     profile: bool = False
 
@@ -40,6 +41,8 @@ class Settings:
             raise SettingsError("The batch size cannot be negative.")
         if self.threshold_bits not in (32, 64):
             raise SettingsError("threshold_bits must be 32 or 64")
+        if self.sampler not in (0, 1, 2):
+            raise SettingsError("sampler must be 0 (default), 1 (direct) or 2 (sliced)")
         return self
 
 
@@ -76,17 +79,18 @@ def _arr(ptr, n, dtype):
 class Plan:
     """Lowered DAG (host) + lazily created per-device state (owned by libcanopy)."""
 
-    def __init__(self, graph: Graph, tally_all_gates: bool = False, threshold_bits: int = 32):
+    def __init__(self, graph: Graph, tally_all_gates: bool = False, threshold_bits: int = 32, sampler: int = 0):
         self._h = C.c_void_p()
         self.graph = graph
         self.tally_all_gates = bool(tally_all_gates)
         self.threshold_bits = threshold_bits
         desc = graph.c_desc()
-        opts = _lib.CPlanOpts(tally_all_gates=int(tally_all_gates), threshold_bits=threshold_bits)
+        opts = _lib.CPlanOpts(tally_all_gates=int(tally_all_gates), threshold_bits=threshold_bits, sampler=int(sampler))
         _lib.check(_lib.lib().canopy_plan_create(C.byref(desc), C.byref(opts), C.byref(self._h)))
         st = _lib.CPlanStats()
         _lib.check(_lib.lib().canopy_plan_info(self._h, C.byref(st)))
         self.stats = {f: getattr(st, f) for f, _ in _lib.CPlanStats._fields_}
+        self.spec = int(st.spec_version)  # the sampling spec the oracle must be asked for
 
     def close(self):
         if getattr(self, "_h", None) and self._h.value:
@@ -175,7 +179,7 @@ class Plan:
 def quantify(graph: Graph, settings: Settings, device: int = 0):
     """One-call analysis: lower, run, estimate.  Returns dict(tallies, p, sigma, ci_lo, ci_hi, report, stats)."""
     settings.validate()
-    with Plan(graph, settings.tally_all_gates, settings.threshold_bits) as plan:
+    with Plan(graph, settings.tally_all_gates, settings.threshold_bits, settings.sampler) as plan:
         t, rep = plan.run(settings.num_trials, settings.seed, settings.sample_begin, device, settings.batch_size,
                           overlap=settings.overlap, profile=settings.profile)
         est = [estimate(int(x), settings.num_trials) for x in t]

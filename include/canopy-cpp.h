@@ -113,6 +113,7 @@ struct McSettings {
     int device = 0;
     bool tally_all_gates = false;
     int threshold_bits = 32;
+    int sampler = CANOPY_SAMPLER_DEFAULT;  ///< sampling spec (canopy.h CANOPY_SAMPLER_*)
 };
 
 struct Result {
@@ -127,10 +128,12 @@ struct Result {
 
 class Plan {
   public:
-    Plan(const canopy_graph_desc& d, bool tally_all_gates = false, int threshold_bits = 32) {
+    Plan(const canopy_graph_desc& d, bool tally_all_gates = false, int threshold_bits = 32,
+         int sampler = CANOPY_SAMPLER_DEFAULT) {
         canopy_plan_opts o{};
         o.tally_all_gates = tally_all_gates;
         o.threshold_bits = threshold_bits;
+        o.sampler = sampler;
         canopy_plan* p = nullptr;
         check(canopy_plan_create(&d, &o, &p));
         plan_.reset(p);
@@ -157,7 +160,7 @@ class Plan {
 };
 
 inline Result quantify(const canopy_graph_desc& d, const McSettings& s) {
-    return Plan(d, s.tally_all_gates, s.threshold_bits).run(s);
+    return Plan(d, s.tally_all_gates, s.threshold_bits, s.sampler).run(s);
 }
 
 }  // namespace canopy

@@ -45,9 +45,18 @@ extern "C" {
 
 #define CANOPY_VERSION_MAJOR 0
 #define CANOPY_VERSION_MINOR 1
-/* Version of the sampling specification (DESIGN.md "SPEC v1"). Tallies are a pure
- * function of (spec version, graph, seed, sample range); bump invalidates goldens. */
-#define CANOPY_SPEC_VERSION 1
+/* Version of the sampling specification. Tallies are a pure function of
+ * (spec version, graph, seed, sample range). Two specs are implemented and selected per plan
+ * (canopy_plan_opts.sampler); both draw Philox4x32-10 variates and compare them with the event threshold:
+ *   spec 1  "direct": one 32/64-bit variate per (event, sample), compared whole.
+ *   spec 2  "sliced": the same comparison evaluated MSB-first; the top 8 bits of the variates of 128
+ *           consecutive samples come from 8 bit-sliced Philox calls, the remaining 24/56 bits from a
+ *           per-sample call that only the ~2^-8 samples still undecided after 8 bits ever need.
+ * CANOPY_SPEC_VERSION is the default spec of this build. */
+#define CANOPY_SPEC_VERSION 2
+#define CANOPY_SAMPLER_DEFAULT 0   /* = the build default (spec 2) */
+#define CANOPY_SAMPLER_DIRECT  1   /* spec 1 */
+#define CANOPY_SAMPLER_SLICED  2   /* spec 2 */
 
 typedef enum canopy_status {
     CANOPY_OK = 0,
@@ -109,8 +118,9 @@ typedef struct canopy_graph_desc {
 
 typedef struct canopy_plan_opts {
     int32_t tally_all_gates;   /* 0: tallies = [n_roots]; 1: tallies = [n_roots] ++ [n_gates] (descriptor order) */
-    int32_t threshold_bits;    /* 32 (SPEC v1 default) or 64 (two variates per Philox call)                      */
-    int32_t reserved[6];
+    int32_t threshold_bits;    /* 32 (default) or 64: width of the variate / threshold comparison                */
+    int32_t sampler;           /* CANOPY_SAMPLER_*: which sampling spec the plan's tallies follow (0 = default)   */
+    int32_t reserved[5];
 } canopy_plan_opts;
 
 /* Lowering statistics, reported before and after dead-code elimination / folding. */
@@ -128,7 +138,7 @@ typedef struct canopy_plan_stats {
     uint32_t n_tallies;        /* length of the tallies output array                             */
     uint32_t n_const_nodes;    /* roots/gates folded to constants                                */
     uint32_t n_alias_nodes;    /* gates folded to (possibly complemented) aliases                */
-    uint32_t spec_version;
+    uint32_t spec_version;     /* the spec this plan samples with (1 direct, 2 sliced)           */
 } canopy_plan_stats;
 
 typedef struct canopy_plan canopy_plan; /* opaque; immutable lowered graph + lazily created per-device state */

@@ -6,7 +6,7 @@
  *   (a) the connective semantics of the Open-PSA MEF as constrained by the reference's own
  *       validation rules (reference src/mef/openpsa/event/event.cpp:140-204, event/event.h:143-157,
  *       event/formula.h:9-15), and
- *   (b) this repository's written sampling spec ("SPEC v1"),
+ *   (b) this repository's written sampling specs (spec 1 "direct", spec 2 "sliced"),
  * pinned only by the published Philox4x32-10 known-answer vectors (Random123 kat_vectors) and by
  * exact 2^B enumeration on small trees.
  *
@@ -73,25 +73,119 @@ double oracle_quantised_p(double p, int bits) {
     return bits == 32 ? (double)thr / 4294967296.0 : (double)thr / 18446744073709551616.0;
 }
 
-/* SPEC v1 "Counter mapping": one basic-event bit for (seed, original event index e, global sample s). */
-int oracle_sample_bit(uint64_t seed, uint32_t e, uint64_t s, int kind, uint64_t thr, int bits) {
+/* The variate u(e, s) of DESIGN.md section 1, straight from its definition, and the basic-event bit
+ * x = u < thr.  spec 1 "direct": one Philox call per 4 (2) samples, output word s&3 (pair s&1).
+ * spec 2 "sliced": top byte of u from 8 bit-sliced calls of the sample's 128-group, the low 24 (56) bits
+ * from the high bits of output word 0 (words 1:0) of a per-sample call. */
+int oracle_sample_bit(uint64_t seed, uint32_t e, uint64_t s, int kind, uint64_t thr, int bits, int spec) {
     if (kind == 0) return 0;
     if (kind == 1) return 1;
     uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
     uint32_t ctr[4], out[4];
+    if (spec == 1) {
+        if (bits == 32) {
+            uint64_t q = s >> 2;
+            ctr[0] = (uint32_t)q; ctr[1] = (uint32_t)(q >> 32); ctr[2] = e; ctr[3] = 0;
+            oracle_philox4x32_10(ctr, key, out);
+            return out[s & 3] < (uint32_t)thr;
+        } else {
+            uint64_t q = s >> 1;
+            ctr[0] = (uint32_t)q; ctr[1] = (uint32_t)(q >> 32); ctr[2] = e; ctr[3] = 1;
+            oracle_philox4x32_10(ctr, key, out);
+            unsigned j = (unsigned)(s & 1) * 2;
+            uint64_t u = ((uint64_t)out[j + 1] << 32) | out[j];
+            return u < thr;
+        }
+    }
+    /* spec 2 */
+    uint64_t g = s >> 7; unsigned j = (unsigned)(s >> 5) & 3, t = (unsigned)s & 31;
+    uint64_t head = 0;
+    for (unsigned k = 0; k < 8; ++k) {
+        ctr[0] = (uint32_t)g; ctr[1] = (uint32_t)(g >> 32); ctr[2] = e; ctr[3] = 0x100u + k;
+        oracle_philox4x32_10(ctr, key, out);
+        head = (head << 1) | ((out[j] >> t) & 1u);
+    }
+    ctr[0] = (uint32_t)s; ctr[1] = (uint32_t)(s >> 32); ctr[2] = e; ctr[3] = bits == 32 ? 0x200u : 0x201u;
+    oracle_philox4x32_10(ctr, key, out);
     if (bits == 32) {
-        uint64_t q = s >> 2;
-        ctr[0] = (uint32_t)q; ctr[1] = (uint32_t)(q >> 32); ctr[2] = e; ctr[3] = 0;
-        oracle_philox4x32_10(ctr, key, out);
-        return out[s & 3] < (uint32_t)thr;
+        uint32_t u = (uint32_t)(head << 24) | (out[0] >> 8);
+        return u < (uint32_t)thr;
     } else {
-        uint64_t q = s >> 1;
-        ctr[0] = (uint32_t)q; ctr[1] = (uint32_t)(q >> 32); ctr[2] = e; ctr[3] = 1;
-        oracle_philox4x32_10(ctr, key, out);
-        unsigned j = (unsigned)(s & 1) * 2;
-        uint64_t u = ((uint64_t)out[j + 1] << 32) | out[j];
+        uint64_t v = ((uint64_t)out[1] << 32) | out[0];
+        uint64_t u = (head << 56) | (v >> 8);
         return u < thr;
     }
+}
+
+static uint64_t packed_sample_word(uint64_t seed, uint32_t e, uint64_t w, int kind, uint64_t thr, int bits) {
+    if (kind == 0) return 0;
+    if (kind == 1) return ~0ull;
+    uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
+    uint32_t ctr[4], out[4];
+    uint64_t word = 0;
+    if (bits == 32) {
+        uint32_t t = (uint32_t)thr;
+        uint64_t q0 = w * 16;
+        for (unsigned c = 0; c < 16; ++c) {
+            uint64_t q = q0 + c;
+            ctr[0] = (uint32_t)q; ctr[1] = (uint32_t)(q >> 32); ctr[2] = e; ctr[3] = 0;
+            oracle_philox4x32_10(ctr, key, out);
+            uint64_t nib = (uint64_t)(out[0] < t) | ((uint64_t)(out[1] < t) << 1) | ((uint64_t)(out[2] < t) << 2) | ((uint64_t)(out[3] < t) << 3);
+            word |= nib << (4 * c);
+        }
+    } else {
+        uint64_t q0 = w * 32;
+        for (unsigned c = 0; c < 32; ++c) {
+            uint64_t q = q0 + c;
+            ctr[0] = (uint32_t)q; ctr[1] = (uint32_t)(q >> 32); ctr[2] = e; ctr[3] = 1;
+            oracle_philox4x32_10(ctr, key, out);
+            uint64_t u0 = ((uint64_t)out[1] << 32) | out[0], u1 = ((uint64_t)out[3] << 32) | out[2];
+            word |= ((uint64_t)(u0 < thr) | ((uint64_t)(u1 < thr) << 1)) << (2 * c);
+        }
+    }
+    return word;
+}
+
+/* spec 2: the four 32-sample result words of 128-sample group g, evaluated lazily (MSB-first on bit
+ * planes, tail call only for samples still undecided after the 8 head planes).  Must agree bit for bit
+ * with oracle_sample_bit(..., spec = 2), which builds every variate in full; tests/test_oracle.py checks it. */
+static void sliced_group_words(uint64_t seed, uint32_t e, uint64_t g, int kind, uint64_t thr, int bits, uint64_t out2[2]) {
+    if (kind == 0) { out2[0] = out2[1] = 0; return; }
+    if (kind == 1) { out2[0] = out2[1] = ~0ull; return; }
+    uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
+    uint32_t ctr[4], x[4];
+    uint32_t und[4] = {~0u, ~0u, ~0u, ~0u}, res[4] = {0, 0, 0, 0};
+    unsigned head = (unsigned)(thr >> (bits - 8)) & 0xFFu;
+    for (unsigned k = 0; k < 8; ++k) {
+        ctr[0] = (uint32_t)g; ctr[1] = (uint32_t)(g >> 32); ctr[2] = e; ctr[3] = 0x100u + k;
+        oracle_philox4x32_10(ctr, key, x);
+        int tb = (head >> (7 - k)) & 1;
+        for (int j = 0; j < 4; ++j) {
+            if (tb) { res[j] |= und[j] & ~x[j]; und[j] &= x[j]; }
+            else und[j] &= ~x[j];
+        }
+    }
+    for (unsigned j = 0; j < 4; ++j)
+        for (unsigned t = 0; t < 32; ++t) {
+            if (!((und[j] >> t) & 1u)) continue;
+            uint64_t sidx = g * 128 + j * 32 + t;
+            int lt;
+            ctr[0] = (uint32_t)sidx; ctr[1] = (uint32_t)(sidx >> 32); ctr[2] = e; ctr[3] = bits == 32 ? 0x200u : 0x201u;
+            oracle_philox4x32_10(ctr, key, x);
+            if (bits == 32) lt = (x[0] >> 8) < ((uint32_t)thr & 0xFFFFFFu);
+            else lt = ((((uint64_t)x[1] << 32) | x[0]) >> 8) < (thr & 0x00FFFFFFFFFFFFFFull);
+            if (lt) res[j] |= 1u << t;
+        }
+    out2[0] = ((uint64_t)res[1] << 32) | res[0];
+    out2[1] = ((uint64_t)res[3] << 32) | res[2];
+}
+
+/* Words 2g and 2g+1 (samples [128g, 128g+128)) of one basic event under either spec. */
+static void group_words(int spec, uint64_t seed, uint32_t e, uint64_t g, int kind, uint64_t thr, int bits, uint64_t out2[2]) {
+    if (spec == 1) {
+        out2[0] = packed_sample_word(seed, e, 2 * g, kind, thr, bits);
+        out2[1] = packed_sample_word(seed, e, 2 * g + 1, kind, thr, bits);
+    } else sliced_group_words(seed, e, g, kind, thr, bits, out2);
 }
 
 /* ------------------------------------------------------------------------------------------------
@@ -152,7 +246,8 @@ static size_t n_tallies_of(const canopy_graph_desc* d, int tally_all) {
  * Outputs: roots in descriptor order, then (tally_all) every gate in descriptor order.
  * ---------------------------------------------------------------------------------------------- */
 int oracle_mc_scalar(const canopy_graph_desc* d, uint64_t seed, uint64_t begin, uint64_t n,
-                     int tally_all, int bits, uint64_t* tallies) {
+                     int tally_all, int bits, int spec, uint64_t* tallies) {
+    if (spec != 1 && spec != 2) return -9;
     uint32_t B = d->n_basic, G = d->n_gates;
     uint32_t* order = (uint32_t*)malloc(sizeof(uint32_t) * (G ? G : 1));
     int rc = topo_order(d, order);
@@ -173,9 +268,18 @@ int oracle_mc_scalar(const canopy_graph_desc* d, uint64_t seed, uint64_t begin, 
     uint32_t maxf = 1;
     for (uint32_t g = 0; g < G; ++g) { uint64_t f = d->child_off[g + 1] - d->child_off[g]; if (f > maxf) maxf = (uint32_t)f; }
     unsigned char* x = (unsigned char*)malloc(maxf);
+    /* basic-event bits are produced 128 samples (one group) at a time; gates are still evaluated one
+     * sample at a time on plain bytes */
+    uint64_t* evw = (uint64_t*)malloc(sizeof(uint64_t) * 2 * (B ? B : 1));
+    uint64_t cur_g = ~0ull;
     for (uint64_t s = begin; s < begin + n; ++s) {
+        if ((s >> 7) != cur_g) {
+            cur_g = s >> 7;
+            for (uint32_t e = 0; e < B; ++e)
+                if (used[e]) group_words(spec, seed, e, cur_g, kind[e], thr[e], bits, evw + 2 * (size_t)e);
+        }
         for (uint32_t e = 0; e < B; ++e)
-            val[e] = used[e] ? (unsigned char)oracle_sample_bit(seed, e, s, kind[e], thr[e], bits) : 0;
+            val[e] = used[e] ? (unsigned char)((evw[2 * (size_t)e + ((s >> 6) & 1)] >> (s & 63)) & 1u) : 0;
         for (uint32_t i = 0; i < G; ++i) {
             uint32_t g = order[i];
             uint64_t o = d->child_off[g]; uint32_t f = (uint32_t)(d->child_off[g + 1] - o);
@@ -189,22 +293,41 @@ int oracle_mc_scalar(const canopy_graph_desc* d, uint64_t seed, uint64_t begin, 
         for (uint32_t r = 0; r < d->n_roots; ++r) tallies[r] += val[d->roots[r]];
         if (tally_all) for (uint32_t g = 0; g < G; ++g) tallies[d->n_roots + g] += val[B + g];
     }
+    free(evw);
     free(order); free(kind); free(thr); free(used); free(val); free(x);
     return 0;
 }
 
 /* Raw sampler words, same layout as canopy_mc_sample_words: words[i*n_words + w] for the events
  * listed in event_ids[0..n_events). */
-int oracle_sample_words(const canopy_graph_desc* d, uint64_t seed, int bits, const uint32_t* event_ids,
+int oracle_sample_words(const canopy_graph_desc* d, uint64_t seed, int bits, int spec, const uint32_t* event_ids,
                         uint32_t n_events, uint64_t first_word, uint64_t n_words, uint64_t* words) {
+    if (spec != 1 && spec != 2) return -9;
     for (uint32_t i = 0; i < n_events; ++i) {
         uint32_t e = event_ids[i]; uint64_t thr; int kind = oracle_threshold(d->p[e], bits, &thr);
         if (kind < 0) return -8;
         for (uint64_t w = 0; w < n_words; ++w) {
             uint64_t word = 0;
             for (unsigned b = 0; b < 64; ++b)
-                word |= (uint64_t)oracle_sample_bit(seed, e, (first_word + w) * 64 + b, kind, thr, bits) << b;
+                word |= (uint64_t)oracle_sample_bit(seed, e, (first_word + w) * 64 + b, kind, thr, bits, spec) << b;
             words[(uint64_t)i * n_words + w] = word;
+        }
+    }
+    return 0;
+}
+
+/* Same output as oracle_sample_words through the lazily evaluated group routine (fast). */
+int oracle_sample_words_fast(const canopy_graph_desc* d, uint64_t seed, int bits, int spec, const uint32_t* event_ids,
+                             uint32_t n_events, uint64_t first_word, uint64_t n_words, uint64_t* words) {
+    if (spec != 1 && spec != 2) return -9;
+    for (uint32_t i = 0; i < n_events; ++i) {
+        uint32_t e = event_ids[i]; uint64_t thr; int kind = oracle_threshold(d->p[e], bits, &thr);
+        if (kind < 0) return -8;
+        uint64_t pair[2], have = ~0ull;
+        for (uint64_t w = 0; w < n_words; ++w) {
+            uint64_t gw = first_word + w;
+            if ((gw >> 1) != have) { have = gw >> 1; group_words(spec, seed, e, have, kind, thr, bits, pair); }
+            words[(uint64_t)i * n_words + w] = pair[gw & 1];
         }
     }
     return 0;
@@ -261,40 +384,11 @@ typedef struct {
     const canopy_graph_desc* d;
     const uint32_t* order;
     const int* kind; const uint64_t* thr; const unsigned char* used;
-    uint64_t seed, begin, n; int tally_all, bits;
-    uint64_t first_word, n_words; /* global word range covering [begin, begin+n) */
+    uint64_t seed, begin, n; int tally_all, bits, spec;
+    uint64_t first_group, n_groups; /* global 128-sample group range covering [begin, begin+n) */
     int tid, nthreads;
     uint64_t* tallies; /* private */
 } packed_job;
-
-static uint64_t packed_sample_word(uint64_t seed, uint32_t e, uint64_t w, int kind, uint64_t thr, int bits) {
-    if (kind == 0) return 0;
-    if (kind == 1) return ~0ull;
-    uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
-    uint32_t ctr[4], out[4];
-    uint64_t word = 0;
-    if (bits == 32) {
-        uint32_t t = (uint32_t)thr;
-        uint64_t q0 = w * 16;
-        for (unsigned c = 0; c < 16; ++c) {
-            uint64_t q = q0 + c;
-            ctr[0] = (uint32_t)q; ctr[1] = (uint32_t)(q >> 32); ctr[2] = e; ctr[3] = 0;
-            oracle_philox4x32_10(ctr, key, out);
-            uint64_t nib = (uint64_t)(out[0] < t) | ((uint64_t)(out[1] < t) << 1) | ((uint64_t)(out[2] < t) << 2) | ((uint64_t)(out[3] < t) << 3);
-            word |= nib << (4 * c);
-        }
-    } else {
-        uint64_t q0 = w * 32;
-        for (unsigned c = 0; c < 32; ++c) {
-            uint64_t q = q0 + c;
-            ctr[0] = (uint32_t)q; ctr[1] = (uint32_t)(q >> 32); ctr[2] = e; ctr[3] = 1;
-            oracle_philox4x32_10(ctr, key, out);
-            uint64_t u0 = ((uint64_t)out[1] << 32) | out[0], u1 = ((uint64_t)out[3] << 32) | out[2];
-            word |= ((uint64_t)(u0 < thr) | ((uint64_t)(u1 < thr) << 1)) << (2 * c);
-        }
-    }
-    return word;
-}
 
 /* count-in-range on 64 lanes with a ripple bit-sliced counter */
 static uint64_t packed_count_range(const uint64_t* x, uint32_t n, unsigned lo, unsigned hi) {
@@ -313,56 +407,73 @@ static uint64_t packed_count_range(const uint64_t* x, uint32_t n, unsigned lo, u
     return ge_lo & le_hi;
 }
 
+static uint64_t word_mask(uint64_t w, uint64_t begin, uint64_t end) {
+    uint64_t s0 = w * 64, mask = ~0ull;
+    if (s0 + 64 <= begin || s0 >= end) return 0;
+    if (s0 < begin) mask &= ~0ull << (begin - s0);
+    if (s0 + 64 > end) mask &= (1ull << (end - s0)) - 1;
+    return mask;
+}
+
+/* Work unit = one 128-sample group (two 64-bit word columns) of the whole DAG. */
 static void* packed_worker(void* arg) {
     packed_job* J = (packed_job*)arg;
     const canopy_graph_desc* d = J->d;
     uint32_t B = d->n_basic, G = d->n_gates;
-    uint64_t* val = (uint64_t*)malloc(sizeof(uint64_t) * ((size_t)B + G + 1));
+    uint64_t* val = (uint64_t*)malloc(sizeof(uint64_t) * 2 * ((size_t)B + G + 1));
     uint32_t maxf = 1;
     for (uint32_t g = 0; g < G; ++g) { uint64_t f = d->child_off[g + 1] - d->child_off[g]; if (f > maxf) maxf = (uint32_t)f; }
     uint64_t* x = (uint64_t*)malloc(sizeof(uint64_t) * maxf);
     uint64_t end = J->begin + J->n;
-    for (uint64_t wi = J->tid; wi < J->n_words; wi += J->nthreads) {
-        uint64_t w = J->first_word + wi;
-        uint64_t s0 = w * 64, mask = ~0ull;
-        if (s0 < J->begin) mask &= ~0ull << (J->begin - s0);
-        if (s0 + 64 > end) mask &= (end - s0 >= 64) ? ~0ull : ((1ull << (end - s0)) - 1);
-        for (uint32_t e = 0; e < B; ++e) val[e] = J->used[e] ? packed_sample_word(J->seed, e, w, J->kind[e], J->thr[e], J->bits) : 0;
-        for (uint32_t i = 0; i < G; ++i) {
-            uint32_t g = J->order[i];
-            uint64_t o = d->child_off[g]; uint32_t f = (uint32_t)(d->child_off[g + 1] - o);
-            for (uint32_t j = 0; j < f; ++j) {
-                uint32_t c = d->child[o + j]; uint32_t id = c & CANOPY_CHILD_ID_MASK;
-                uint64_t v = id == CANOPY_CONST_TRUE ? ~0ull : id == CANOPY_CONST_FALSE ? 0 : val[id];
-                x[j] = (c & CANOPY_CHILD_COMPLEMENT) ? ~v : v;
-            }
-            uint64_t r = 0;
-            switch (d->op[g]) {
-                case CANOPY_AND:  r = ~0ull; for (uint32_t j = 0; j < f; ++j) r &= x[j]; break;
-                case CANOPY_NAND: r = ~0ull; for (uint32_t j = 0; j < f; ++j) r &= x[j]; r = ~r; break;
-                case CANOPY_OR:   r = 0; for (uint32_t j = 0; j < f; ++j) r |= x[j]; break;
-                case CANOPY_NOR:  r = 0; for (uint32_t j = 0; j < f; ++j) r |= x[j]; r = ~r; break;
-                case CANOPY_XOR:  r = x[0] ^ x[1]; break;
-                case CANOPY_IFF:  r = ~(x[0] ^ x[1]); break;
-                case CANOPY_IMPLY: r = ~x[0] | x[1]; break;
-                case CANOPY_NOT:  r = ~x[0]; break;
-                case CANOPY_NULL: r = x[0]; break;
-                case CANOPY_ATLEAST: r = packed_count_range(x, f, d->kmin[g], 0xFFFFu); break;
-                case CANOPY_CARDINALITY: r = packed_count_range(x, f, d->kmin[g], d->kmax[g]); break;
-                default: r = 0;
-            }
-            val[B + g] = r;
+    for (uint64_t gi = (uint64_t)J->tid; gi < J->n_groups; gi += (uint64_t)J->nthreads) {
+        uint64_t grp = J->first_group + gi;
+        uint64_t mask[2] = {word_mask(2 * grp, J->begin, end), word_mask(2 * grp + 1, J->begin, end)};
+        for (uint32_t e = 0; e < B; ++e) {
+            if (J->used[e]) group_words(J->spec, J->seed, e, grp, J->kind[e], J->thr[e], J->bits, val + 2 * (size_t)e);
+            else val[2 * (size_t)e] = val[2 * (size_t)e + 1] = 0;
         }
-        for (uint32_t r = 0; r < d->n_roots; ++r) J->tallies[r] += (uint64_t)__builtin_popcountll(val[d->roots[r]] & mask);
-        if (J->tally_all) for (uint32_t g = 0; g < G; ++g) J->tallies[d->n_roots + g] += (uint64_t)__builtin_popcountll(val[B + g] & mask);
+        for (int h = 0; h < 2; ++h) {
+            if (!mask[h]) continue;
+            for (uint32_t i = 0; i < G; ++i) {
+                uint32_t g = J->order[i];
+                uint64_t o = d->child_off[g]; uint32_t f = (uint32_t)(d->child_off[g + 1] - o);
+                for (uint32_t j = 0; j < f; ++j) {
+                    uint32_t c = d->child[o + j]; uint32_t id = c & CANOPY_CHILD_ID_MASK;
+                    uint64_t v = id == CANOPY_CONST_TRUE ? ~0ull : id == CANOPY_CONST_FALSE ? 0 : val[2 * (size_t)id + h];
+                    x[j] = (c & CANOPY_CHILD_COMPLEMENT) ? ~v : v;
+                }
+                uint64_t r = 0;
+                switch (d->op[g]) {
+                    case CANOPY_AND:  r = ~0ull; for (uint32_t j = 0; j < f; ++j) r &= x[j]; break;
+                    case CANOPY_NAND: r = ~0ull; for (uint32_t j = 0; j < f; ++j) r &= x[j]; r = ~r; break;
+                    case CANOPY_OR:   r = 0; for (uint32_t j = 0; j < f; ++j) r |= x[j]; break;
+                    case CANOPY_NOR:  r = 0; for (uint32_t j = 0; j < f; ++j) r |= x[j]; r = ~r; break;
+                    case CANOPY_XOR:  r = x[0] ^ x[1]; break;
+                    case CANOPY_IFF:  r = ~(x[0] ^ x[1]); break;
+                    case CANOPY_IMPLY: r = ~x[0] | x[1]; break;
+                    case CANOPY_NOT:  r = ~x[0]; break;
+                    case CANOPY_NULL: r = x[0]; break;
+                    case CANOPY_ATLEAST: r = packed_count_range(x, f, d->kmin[g], 0xFFFFu); break;
+                    case CANOPY_CARDINALITY: r = packed_count_range(x, f, d->kmin[g], d->kmax[g]); break;
+                    default: r = 0;
+                }
+                val[2 * ((size_t)B + g) + h] = r;
+            }
+            for (uint32_t r = 0; r < d->n_roots; ++r)
+                J->tallies[r] += (uint64_t)__builtin_popcountll(val[2 * (size_t)d->roots[r] + h] & mask[h]);
+            if (J->tally_all)
+                for (uint32_t g = 0; g < G; ++g)
+                    J->tallies[d->n_roots + g] += (uint64_t)__builtin_popcountll(val[2 * ((size_t)B + g) + h] & mask[h]);
+        }
     }
     free(val); free(x);
     return NULL;
 }
 
 int oracle_mc_packed(const canopy_graph_desc* d, uint64_t seed, uint64_t begin, uint64_t n,
-                     int tally_all, int bits, int nthreads, uint64_t* tallies) {
+                     int tally_all, int bits, int spec, int nthreads, uint64_t* tallies) {
     uint32_t B = d->n_basic, G = d->n_gates;
+    if (spec != 1 && spec != 2) return -9;
     if (nthreads < 1) nthreads = 1;
     uint32_t* order = (uint32_t*)malloc(sizeof(uint32_t) * (G ? G : 1));
     int rc = topo_order(d, order);
@@ -379,14 +490,14 @@ int oracle_mc_packed(const canopy_graph_desc* d, uint64_t seed, uint64_t begin, 
     size_t nt = n_tallies_of(d, tally_all);
     memset(tallies, 0, sizeof(uint64_t) * nt);
     if (n == 0) { free(order); free(kind); free(thr); free(used); return 0; }
-    uint64_t first_word = begin / 64, last_word = (begin + n - 1) / 64;
+    uint64_t first_group = begin / 128, last_group = (begin + n - 1) / 128;
     packed_job* jobs = (packed_job*)calloc((size_t)nthreads, sizeof(packed_job));
     pthread_t* th = (pthread_t*)malloc(sizeof(pthread_t) * (size_t)nthreads);
     for (int t = 0; t < nthreads; ++t) {
         packed_job* J = &jobs[t];
         J->d = d; J->order = order; J->kind = kind; J->thr = thr; J->used = used;
-        J->seed = seed; J->begin = begin; J->n = n; J->tally_all = tally_all; J->bits = bits;
-        J->first_word = first_word; J->n_words = last_word - first_word + 1;
+        J->seed = seed; J->begin = begin; J->n = n; J->tally_all = tally_all; J->bits = bits; J->spec = spec;
+        J->first_group = first_group; J->n_groups = last_group - first_group + 1;
         J->tid = t; J->nthreads = nthreads;
         J->tallies = (uint64_t*)calloc(nt ? nt : 1, sizeof(uint64_t));
         pthread_create(&th[t], NULL, packed_worker, J);

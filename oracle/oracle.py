@@ -33,15 +33,19 @@ def lib():
         L.oracle_threshold.argtypes = [C.c_double, C.c_int, u64p]
         L.oracle_quantised_p.argtypes = [C.c_double, C.c_int]
         L.oracle_quantised_p.restype = C.c_double
-        L.oracle_sample_bit.argtypes = [C.c_uint64, C.c_uint32, C.c_uint64, C.c_int, C.c_uint64, C.c_int]
-        L.oracle_mc_scalar.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int, C.c_int, u64p]
-        L.oracle_mc_packed.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, u64p]
+        L.oracle_sample_bit.argtypes = [C.c_uint64, C.c_uint32, C.c_uint64, C.c_int, C.c_uint64, C.c_int, C.c_int]
+        L.oracle_mc_scalar.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, u64p]
+        L.oracle_mc_packed.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int, u64p]
         L.oracle_exact.argtypes = [C.c_void_p, C.c_int, C.c_int, dblp]
-        L.oracle_sample_words.argtypes = [C.c_void_p, C.c_uint64, C.c_int, u32p, C.c_uint32, C.c_uint64, C.c_uint64, u64p]
+        for fn in (L.oracle_sample_words, L.oracle_sample_words_fast):
+            fn.argtypes = [C.c_void_p, C.c_uint64, C.c_int, C.c_int, u32p, C.c_uint32, C.c_uint64, C.c_uint64, u64p]
     return _LIB
 
 
-_RC = {-1: "bad node id", -3: "cycle", -4: "too many basic events for enumeration", -8: "probability out of domain"}
+_RC = {-1: "bad node id", -3: "cycle", -4: "too many basic events for enumeration", -8: "probability out of domain",
+       -9: "unknown sampling spec"}
+
+SPEC = 2  # default sampling spec of the build (include/canopy.h CANOPY_SPEC_VERSION); 1 = direct, 2 = sliced
 
 
 def _check(rc):
@@ -67,18 +71,25 @@ def quantised_p(p: float, bits: int = 32) -> float:
     return float(lib().oracle_quantised_p(p, bits))
 
 
-def mc_scalar(graph, seed: int, begin: int, n: int, tally_all: bool = False, bits: int = 32) -> np.ndarray:
+def sample_bit(seed: int, e: int, s: int, p: float, bits: int = 32, spec: int = SPEC) -> int:
+    """One basic-event bit straight from the written definition of the variate (slow; the pin for everything else)."""
+    kind, thr = threshold(p, bits)
+    return int(lib().oracle_sample_bit(seed, e, s, kind, thr, bits, spec))
+
+
+def mc_scalar(graph, seed: int, begin: int, n: int, tally_all: bool = False, bits: int = 32, spec: int = SPEC) -> np.ndarray:
     d = graph.c_desc()
     out = np.zeros(graph.n_tallies(tally_all), dtype=np.uint64)
-    _check(lib().oracle_mc_scalar(C.addressof(d), seed, begin, n, int(tally_all), bits,
+    _check(lib().oracle_mc_scalar(C.addressof(d), seed, begin, n, int(tally_all), bits, spec,
                                   out.ctypes.data_as(C.POINTER(C.c_uint64))))
     return out
 
 
-def mc_packed(graph, seed: int, begin: int, n: int, tally_all: bool = False, bits: int = 32, nthreads: int = 1) -> np.ndarray:
+def mc_packed(graph, seed: int, begin: int, n: int, tally_all: bool = False, bits: int = 32, nthreads: int = 1,
+              spec: int = SPEC) -> np.ndarray:
     d = graph.c_desc()
     out = np.zeros(graph.n_tallies(tally_all), dtype=np.uint64)
-    _check(lib().oracle_mc_packed(C.addressof(d), seed, begin, n, int(tally_all), bits, nthreads,
+    _check(lib().oracle_mc_packed(C.addressof(d), seed, begin, n, int(tally_all), bits, spec, nthreads,
                                   out.ctypes.data_as(C.POINTER(C.c_uint64))))
     return out
 
@@ -90,10 +101,14 @@ def exact(graph, tally_all: bool = False, bits: int = 32) -> np.ndarray:
     return out
 
 
-def sample_words(graph, seed: int, event_ids, first_word: int, n_words: int, bits: int = 32) -> np.ndarray:
+def sample_words(graph, seed: int, event_ids, first_word: int, n_words: int, bits: int = 32, spec: int = SPEC,
+                 fast: bool = False) -> np.ndarray:
+    """Packed basic-event words. fast=False builds every bit from the definition (oracle_sample_bit);
+    fast=True uses the lazily evaluated group routine that mc_scalar / mc_packed use."""
     d = graph.c_desc()
     ev = np.ascontiguousarray(event_ids, dtype=np.uint32)
     out = np.zeros((len(ev), n_words), dtype=np.uint64)
-    _check(lib().oracle_sample_words(C.addressof(d), seed, bits, ev.ctypes.data_as(C.POINTER(C.c_uint32)), len(ev),
+    fn = lib().oracle_sample_words_fast if fast else lib().oracle_sample_words
+    _check(fn(C.addressof(d), seed, bits, spec, ev.ctypes.data_as(C.POINTER(C.c_uint32)), len(ev),
                                      first_word, n_words, out.ctypes.data_as(C.POINTER(C.c_uint64))))
     return out

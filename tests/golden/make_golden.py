@@ -1,7 +1,7 @@
 """Regenerates tests/golden/*.json from the CPU oracle (oracle/canopy_oracle.c).
 
 The reference (openpra-org/canopy) has no implementation, tests or golden vectors for this path, so these
-fixtures pin the behaviour of SPEC v1 as restated by the oracle -- they are NOT outputs of the reference.
+fixtures pin the behaviour of the two sampling specs (1 "direct", 2 "sliced") as restated by the oracle -- they are NOT outputs of the reference.
 What IS external: the three Philox4x32-10 known-answer vectors (Random123 kat_vectors, also listed in
 SURVEY.md Appendix B), which are written here literally and checked against the oracle before anything
 else is generated.
@@ -35,12 +35,12 @@ def graph_dict(g):
                 child=[int(x) for x in g.child], roots=[int(x) for x in g.roots])
 
 
-def case(name, g, seed, begin, n, tally_all, bits=32, words_of=(0, 1, 2)):
+def case(name, g, seed, begin, n, tally_all, bits=32, words_of=(0, 1, 2), spec=2):
     ev = [e for e in words_of if e < g.n_basic]
-    return dict(name=name, graph=graph_dict(g), seed=seed, begin=begin, n=n, tally_all=tally_all, bits=bits,
-                tallies=[int(x) for x in O.mc_scalar(g, seed, begin, n, tally_all, bits)],
+    return dict(name=f"{name}_spec{spec}", graph=graph_dict(g), seed=seed, begin=begin, n=n, tally_all=tally_all, bits=bits,
+                spec=spec, tallies=[int(x) for x in O.mc_scalar(g, seed, begin, n, tally_all, bits, spec)],
                 word_events=ev, first_word=begin // 64,
-                words=[[int(w) for w in row] for row in O.sample_words(g, seed, ev, begin // 64, 2, bits)])
+                words=[[int(w) for w in row] for row in O.sample_words(g, seed, ev, begin // 64, 2, bits, spec)])
 
 
 def main():
@@ -50,16 +50,19 @@ def main():
         json.dump(dict(source="Random123 kat_vectors, philox4x32-10; also SURVEY.md Appendix B", vectors=PHILOX_KAT), f, indent=1)
     cases = []
     c1 = load_mef(os.path.join(ROOT, "examples", "c1_small_ft.xml"))
-    cases.append(case("c1_small_ft", c1, seed=0, begin=0, n=1 << 14, tally_all=True))
-    cases.append(case("c1_small_ft_offset_seed", c1, seed=(0xDEADBEEF << 32) | 0x1234, begin=(1 << 40) + 77, n=5000, tally_all=False))
-    for s in range(6):
-        cases.append(case(f"random_{s}", random_graph(1000 + s, n_basic=12, n_gates=30, n_roots=3), seed=s * 7919 + 1,
-                          begin=64 * s + s, n=4096 + 321 * s, tally_all=True))
-    cases.append(case("random_thr64", random_graph(2000, n_basic=10, n_gates=20), seed=5, begin=3, n=3000, tally_all=True, bits=64))
     tiny = synth.generate(n_basic=120, n_gates=60, n_layers=5, max_fanin=16, seed=0xC0FFEE)
-    cases.append(case("synth_tiny", tiny, seed=42, begin=4096 * 3 - 10, n=4096 + 20, tally_all=True))
+    for spec in (1, 2):
+        cases.append(case("c1_small_ft", c1, seed=0, begin=0, n=1 << 14, tally_all=True, spec=spec))
+        cases.append(case("c1_small_ft_offset_seed", c1, seed=(0xDEADBEEF << 32) | 0x1234, begin=(1 << 40) + 77, n=5000,
+                          tally_all=False, spec=spec))
+        for s in range(6 if spec == 2 else 3):
+            cases.append(case(f"random_{s}", random_graph(1000 + s, n_basic=12, n_gates=30, n_roots=3), seed=s * 7919 + 1,
+                              begin=64 * s + s, n=4096 + 321 * s, tally_all=True, spec=spec))
+        cases.append(case("random_thr64", random_graph(2000, n_basic=10, n_gates=20), seed=5, begin=3, n=3000, tally_all=True,
+                          bits=64, spec=spec))
+        cases.append(case("synth_tiny", tiny, seed=42, begin=4096 * 3 - 10, n=4096 + 20, tally_all=True, spec=spec))
     with open(os.path.join(HERE, "golden_tallies.json"), "w") as f:
-        json.dump(dict(spec_version=1, generator="tests/golden/make_golden.py (oracle_mc_scalar / oracle_sample_words)",
+        json.dump(dict(spec_versions=[1, 2], generator="tests/golden/make_golden.py (oracle_mc_scalar / oracle_sample_words)",
                        cases=cases), f)
     print(f"wrote {len(cases)} cases")
 

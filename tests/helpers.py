@@ -66,14 +66,14 @@ def random_graph(seed: int, n_basic: int = 12, n_gates: int = 20, max_fanin: int
     return G.from_lists(p, gates, roots)
 
 
-def eval_lowered(view: dict, graph: G.Graph, seed: int, begin: int, n: int, bits: int = 32) -> np.ndarray:
+def eval_lowered(view: dict, graph: G.Graph, seed: int, begin: int, n: int, bits: int = 32, spec: int = O.SPEC) -> np.ndarray:
     """Evaluate the lowered CSR arrays with numpy on 64-bit words; event words come from the oracle sampler."""
     first_word, last_word = begin // 64, (begin + n - 1) // 64
     nw = last_word - first_word + 1
     n_ev, n_g = view["n_events"], view["n_gates"]
     vals = np.zeros((n_ev + n_g, nw), dtype=np.uint64)
     if n_ev:
-        vals[:n_ev] = O.sample_words(graph, seed, view["event_orig"], first_word, nw, bits)
+        vals[:n_ev] = O.sample_words(graph, seed, view["event_orig"], first_word, nw, bits, spec, fast=True)
     mask = np.full(nw, ~np.uint64(0), dtype=np.uint64)
     s0 = first_word * 64
     if begin > s0:

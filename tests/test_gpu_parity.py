@@ -25,9 +25,16 @@ def test_golden_fixtures(case):
     g = case["graph"]
     graph = G.Graph(p=g["p"], op=g["op"], kmin=g["kmin"], kmax=g["kmax"], child_off=g["child_off"], child=g["child"],
                     roots=g["roots"])
-    with Plan(graph, case["tally_all"], case["bits"]) as plan:
+    with Plan(graph, case["tally_all"], case["bits"], sampler=case["spec"]) as plan:
+        assert plan.spec == case["spec"]
         got, _ = plan.run(case["n"], seed=case["seed"], sample_begin=case["begin"])
+        ev = [int(np.nonzero(plan.view()["event_orig"] == e)[0][0]) for e in case["word_events"]
+              if e in plan.view()["event_orig"]]
+        w0 = case["first_word"] // 64 * 64
+        words = plan.sample_words(case["seed"], w0, 128)[ev][:, case["first_word"] - w0: case["first_word"] - w0 + 2]
     assert np.array_equal(got, np.array(case["tallies"], dtype=np.uint64))
+    if len(ev) == len(case["word_events"]):
+        assert np.array_equal(words, np.array(case["words"], dtype=np.uint64).reshape(words.shape))
 
 
 def test_c1_mef_example_2pow20():
@@ -57,24 +64,42 @@ def test_c2_full_graph_short_run():
     assert np.array_equal(got, O.mc_packed(g, 5, 0, n, True, nthreads=CORES))
 
 
-def test_sampler_words_every_live_event():
+@pytest.mark.parametrize("spec", [1, 2])
+@pytest.mark.parametrize("bits", [32, 64])
+def test_sampler_words_every_live_event(spec, bits):
     g = synth.config_graph("c2", 0.05)
-    with Plan(g) as plan:
+    with Plan(g, threshold_bits=bits, sampler=spec) as plan:
         v = plan.view()
         got = plan.sample_words(seed=(1 << 63) + 12345, first_word=64 * 1000, n_words=64)
-    assert np.array_equal(got, O.sample_words(g, (1 << 63) + 12345, v["event_orig"], 64 * 1000, 64))
+    assert np.array_equal(got, O.sample_words(g, (1 << 63) + 12345, v["event_orig"], 64 * 1000, 64, bits, spec, fast=True))
+
+
+@pytest.mark.parametrize("bits", [32, 64])
+def test_sliced_sampler_threshold_bytes(bits):
+    """Spec 2 decisions for thresholds whose top byte is 0x00 / 0xFF / mixed and whose tail is zero, against the
+    oracle's full-variate definition (fast=False)."""
+    b = G.GraphBuilder()
+    ps = [1e-9, 3e-5, 2.0 ** -8, 2.0 ** -8 + 2.0 ** -30, 0.0039, 0.1, 0.5, 0.75, 1 - 2.0 ** -9, 0.999999, 2.0 ** -31]
+    b.root(b.gate(G.OR, [b.basic_event(p) for p in ps]))
+    g = b.build()
+    with Plan(g, threshold_bits=bits) as plan:
+        v = plan.view()
+        got = plan.sample_words(seed=77, first_word=64 * 3, n_words=128)
+    assert np.array_equal(got, O.sample_words(g, 77, v["event_orig"], 64 * 3, 128, bits, 2, fast=False))
 
 
 @pytest.mark.parametrize("seed", range(12))
 def test_random_graphs_all_connectives(seed):
     g = random_graph(100 + seed, n_basic=16, n_gates=48, max_fanin=9, n_roots=4)
-    with Plan(g, tally_all_gates=True) as plan:
+    spec = 1 if seed % 4 == 3 else 2
+    with Plan(g, tally_all_gates=True, sampler=spec) as plan:
         got, _ = plan.run(20_000, seed=seed, sample_begin=1000 * seed + 7)
-    assert np.array_equal(got, O.mc_scalar(g, seed, 1000 * seed + 7, 20_000, True))
+    assert np.array_equal(got, O.mc_scalar(g, seed, 1000 * seed + 7, 20_000, True, spec=spec))
 
 
+@pytest.mark.parametrize("spec", [1, 2])
 @pytest.mark.parametrize("bits", [32, 64])
-def test_rare_events_and_threshold_width(bits):
+def test_rare_events_and_threshold_width(bits, spec):
     """p down to 1e-9: 32-bit thresholds quantise to multiples of 2^-32, 64-bit ones resolve them."""
     b = G.GraphBuilder()
     e = [b.basic_event(p) for p in (1e-9, 3e-7, 1e-4, 0.02, 0.5, 2.0 ** -33)]
@@ -82,9 +107,9 @@ def test_rare_events_and_threshold_width(bits):
     b.root(b.gate(G.AND, [e[3], e[4]]))
     g = b.build()
     n = 1 << 17
-    with Plan(g, tally_all_gates=True, threshold_bits=bits) as plan:
+    with Plan(g, tally_all_gates=True, threshold_bits=bits, sampler=spec) as plan:
         got, _ = plan.run(n, seed=31337)
-    assert np.array_equal(got, O.mc_packed(g, 31337, 0, n, True, bits=bits, nthreads=CORES))
+    assert np.array_equal(got, O.mc_packed(g, 31337, 0, n, True, bits=bits, nthreads=CORES, spec=spec))
 
 
 @pytest.mark.parametrize("fanin,lo,hi", [(5, 2, 0), (40, 7, 0), (300, 30, 0), (300, 20, 40), (700, 95, 0), (700, 90, 100), (33, 0, 3)])

@@ -46,20 +46,59 @@ def test_threshold_quantisation():
 def test_golden_scalar_and_packed(case):
     g = graph_of(case)
     want = np.array(case["tallies"], dtype=np.uint64)
-    got = O.mc_scalar(g, case["seed"], case["begin"], case["n"], case["tally_all"], case["bits"])
+    spec = case["spec"]
+    got = O.mc_scalar(g, case["seed"], case["begin"], case["n"], case["tally_all"], case["bits"], spec)
     assert np.array_equal(got, want)
-    got_p = O.mc_packed(g, case["seed"], case["begin"], case["n"], case["tally_all"], case["bits"], nthreads=3)
+    got_p = O.mc_packed(g, case["seed"], case["begin"], case["n"], case["tally_all"], case["bits"], nthreads=3, spec=spec)
     assert np.array_equal(got_p, want)
-    words = O.sample_words(g, case["seed"], case["word_events"], case["first_word"], 2, case["bits"])
-    assert np.array_equal(words, np.array(case["words"], dtype=np.uint64).reshape(words.shape))
+    for fast in (False, True):
+        words = O.sample_words(g, case["seed"], case["word_events"], case["first_word"], 2, case["bits"], spec, fast)
+        assert np.array_equal(words, np.array(case["words"], dtype=np.uint64).reshape(words.shape))
 
 
+@pytest.mark.parametrize("spec", [1, 2])
+@pytest.mark.parametrize("bits", [32, 64])
+def test_lazy_group_sampler_equals_the_written_definition(spec, bits):
+    """mc_scalar / mc_packed take basic-event bits from the lazily evaluated 128-sample group routine; the
+    definition (oracle_sample_bit) builds each variate in full. Same words, including p whose top threshold
+    byte is 0x00 / 0xFF / mixed, and tails that are all-zero."""
+    b = G.GraphBuilder()
+    ps = [1e-9, 3e-5, 2.0 ** -8, 2.0 ** -8 + 2.0 ** -30, 0.0039, 0.1, 0.5, 0.75, 1 - 2.0 ** -9, 0.999999, 2.0 ** -31]
+    e = [b.basic_event(p) for p in ps]
+    b.root(b.gate(G.OR, e))
+    g = b.build()
+    for seed, first in ((0, 0), ((1 << 63) | 77, (1 << 40) + 6)):
+        slow = O.sample_words(g, seed, range(len(ps)), first, 8, bits, spec, fast=False)
+        fast = O.sample_words(g, seed, range(len(ps)), first, 8, bits, spec, fast=True)
+        assert np.array_equal(slow, fast)
+    # and the single-bit entry point agrees with the packed words
+    w = O.sample_words(g, 5, [5], 3, 1, bits, spec)[0, 0]
+    assert [O.sample_bit(5, 5, 3 * 64 + i, ps[5], bits, spec) for i in range(64)] == [(int(w) >> i) & 1 for i in range(64)]
+
+
+@pytest.mark.parametrize("spec", [1, 2])
+def test_sampled_frequency_matches_quantised_probability(spec):
+    """Per-event frequency over 2^20 samples within 4 sigma of thr/2^32, for thresholds whose top byte is zero,
+    mixed and all-ones (exercises head-only, head+tail and tail-dominated decisions of the sliced spec)."""
+    b = G.GraphBuilder()
+    ps = [1e-4, 2.0 ** -8 * 0.999, 0.0123, 0.3, 0.5, 0.9, 0.998]
+    e = [b.basic_event(p) for p in ps]
+    for x in e:
+        b.root(b.gate(G.NULL, [x]))
+    g = b.build()
+    n = 1 << 20
+    t = O.mc_packed(g, 99, 12345, n, nthreads=4, spec=spec).astype(np.float64)
+    q = np.array([O.quantised_p(p) for p in ps])
+    assert np.all(np.abs(t / n - q) <= 4.0 * np.sqrt(q * (1 - q) / n))
+
+
+@pytest.mark.parametrize("spec", [1, 2])
 @pytest.mark.parametrize("seed", range(5))
-def test_mc_within_3_sigma_of_exact_enumeration(seed):
+def test_mc_within_3_sigma_of_exact_enumeration(seed, spec):
     g = random_graph(seed + 50, n_basic=10, n_gates=16, n_roots=2, extreme_p=False)
     exact = O.exact(g, True)
     n = 1 << 16
-    t = O.mc_packed(g, seed, 0, n, True, nthreads=4).astype(np.float64)
+    t = O.mc_packed(g, seed, 0, n, True, nthreads=4, spec=spec).astype(np.float64)
     sigma = np.sqrt(np.maximum(exact * (1 - exact), 1e-12) / n)
     assert np.all(np.abs(t / n - exact) <= 4.0 * sigma + 1e-9)
 

@@ -10,15 +10,15 @@ for kind, name in enumerate(["lop3", "imad_wide", "philox_round_mix", "popc"]):
     out["peak_" + name] = ops
     print(f"{name}: {ops/1e12:.2f} T lane-instr/s ({ms:.3f} ms)", flush=True)
 
-for cfg, nsamp in (("c2", 1 << 24), ("c4", 1 << 22)):
+for cfg, nsamp, spec in (("c2", 1 << 24, 1), ("c2", 1 << 24, 2), ("c4", 1 << 22, 1), ("c4", 1 << 22, 2)):
     g = synth.config_graph(cfg)
-    plan = Plan(g)
+    plan = Plan(g, sampler=spec)
     st = plan.stats
     for prof, ov in ((True, False), (False, False), (False, True)):
         plan.run(nsamp // 4, seed=1, profile=prof, overlap=ov)
         t, rep = plan.run(nsamp, seed=1, profile=prof, overlap=ov)
         sps = nsamp / (rep.total_ms * 1e-3)
-        line = dict(cfg=cfg, profile=prof, overlap=ov, n=nsamp, total_ms=rep.total_ms, sampler_ms=rep.sampler_ms, gate_ms=rep.gate_ms,
+        line = dict(cfg=cfg, spec=spec, profile=prof, overlap=ov, n=nsamp, total_ms=rep.total_ms, sampler_ms=rep.sampler_ms, gate_ms=rep.gate_ms,
                     samples_per_s=sps, batches=rep.n_batches, batch_slabs=rep.batch_slabs, top=int(t[0]))
         if prof and rep.gate_ms > 0:
             bytes_per_sample = (st["n_edges_live"] + st["n_gates_stored"]) / 8
