@@ -10,7 +10,7 @@ import os
 from .graph import CGraphDesc
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcanopy.so")
+LIB_PATH = os.environ.get("CANOPY_LIB") or os.path.join(_HERE, "libcanopy.so")  # CANOPY_LIB: kernel-tuning builds only
 
 STATUS_NAMES = {0: "OK", 1: "E_INVALID", 2: "E_VALIDITY", 3: "E_CYCLE", 4: "E_UNSUPPORTED", 5: "E_CUDA",
                 6: "E_NCCL", 7: "E_OOM", 8: "E_DOMAIN", 9: "E_IO"}

@@ -313,15 +313,15 @@ gate_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const uint
         if (g < g_end) {
             rec = __ldg(grec + g);
             if (g + n_warps < g_end) rec1 = __ldg(grec + g + n_warps);
-            if (lane < rec.y) ids = __ldg(child + rec.x + lane);
+            if (lane < (rec.y & 0xFFFFu)) ids = __ldg(child + rec.x + lane);
         }
         for (; g < g_end; g += n_warps) {
             uint4 rec2 = make_uint4(0, 0, 0, 0);
             uint32_t ids1 = 0;
             if (g + 2 * n_warps < g_end) rec2 = __ldg(grec + g + 2 * n_warps);
-            if (g + n_warps < g_end && lane < rec1.y) ids1 = __ldg(child + rec1.x + lane);
+            if (g + n_warps < g_end && lane < (rec1.y & 0xFFFFu)) ids1 = __ldg(child + rec1.x + lane);
             const uint32_t* ch = child + rec.x;
-            const uint32_t n = rec.y, op = rec.z & 0xFFu, flags = rec.z >> 8;
+            const uint32_t n = rec.y & 0xFFFFu, op = rec.z & 0xFFu, flags = rec.z >> 8;
             uint4 r;
             if (op == kDevAnd) r = eval_simple<kDevAnd>(base, ch, n, lane, ids);
             else if (op == kDevOr) r = eval_simple<kDevOr>(base, ch, n, lane, ids);
@@ -351,6 +351,244 @@ gate_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const uint
             rec = rec1; rec1 = rec2; ids = ids1;
         }
         __syncthreads();  // rows written in this layer are read by later layers of the same CTA only
+    }
+}
+
+// ================================================================================================
+// Ring gate kernel (slab walker, TMA-bulk staging).
+//
+// Same decomposition as gate_kernel -- one CTA walks every layer of one slab, __syncthreads() between
+// layers -- but child rows are no longer loaded into registers.  Each warp owns a ring of kRingSlots
+// 512-byte row slots in shared memory and streams the child rows of its share of the layer through it with
+// `cp.async.bulk.shared::cluster.global` (SASS UBLKCP), one copy per row, each completing on the slot's
+// own mbarrier.  The lowering cuts every layer into kGateWarps contiguous runs of equal cost
+// (Lowered::split / split_child), so the rows a warp needs are simply child[c0..c1) in order, independent
+// of gate boundaries: the producer side is a linear stream, the consumer side walks the gates and pops rows.
+// A row is re-requested into a slot one pop after the slot was read, so kRingSlots-1 rows (7.5 KB per warp,
+// 180 KB per SM at 3 CTAs) are in flight without holding a single register.
+// Arguments of a gate come plain-first, complemented-last (GateRec::n_children >> 16 = #complemented), so
+// the consumer needs no per-row flag.  Count gates use uint4 bit planes straight from shared memory
+// (3/6/9 planes, one pass); fan-in >= kWideFanin count gates sit at the end of the layer and take the
+// multi-pass register path of gate_kernel.
+// ================================================================================================
+#ifndef CANOPY_RING_GROUPS
+#define CANOPY_RING_GROUPS 2
+#endif
+#ifndef CANOPY_GROUP_ROWS
+#define CANOPY_GROUP_ROWS 4
+#endif
+constexpr uint32_t kGroupRows = CANOPY_GROUP_ROWS;         // rows per mbarrier phase (power of two, <= 8)
+constexpr uint32_t kRingGroups = CANOPY_RING_GROUPS;      // groups per warp ring (power of two)
+constexpr uint32_t kRingSlots = kGroupRows * kRingGroups; // rows per warp ring
+constexpr uint32_t kRingSmemBytes = kGateWarps * kRingSlots * kRowBytes + kGateWarps * kRingGroups * 8;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+// Per-warp stream of child rows through the shared-memory ring.  Rows travel in groups of kGroupRows
+// consecutive rows of the run: one mbarrier phase (one expect_tx, one try_wait) per group, so the
+// ~90-cycle mbarrier round trip and the copy-issue sequence are paid once per 2 KB, not once per row.
+struct RowRing {
+    const uint4* base;          // this slab's rows
+    const uint32_t* ids;        // child + c0: the warp's run of child codes for this layer
+    uint32_t ring;              // shared address of slot 0 of this warp's ring
+    uint32_t bars;              // shared address of mbarrier 0 of this warp's ring
+    const uint4* ring_ptr;      // generic pointer to this lane's 16 bytes of slot 0
+    uint32_t total;             // rows in the run
+    uint32_t popped;            // rows consumed so far in the run
+    uint32_t grp0;              // groups consumed by this warp before this run (ring position / parity continuity)
+    uint32_t idreg, idnext;     // child codes of rows [32k, 32k+32) of the run (and of the next 32), one per lane
+    uint32_t lane;
+
+    __device__ __forceinline__ void issue_group(uint32_t k) {  // request rows [4k, 4k+4) of the run (ascending k)
+        const uint32_t i = k * kGroupRows;
+        if ((i & 31u) == 8u) idnext = (i + 24u + lane < total) ? __ldg(ids + i + 24u + lane) : 0u;  // codes of the next 32 rows
+        if ((i & 31u) == 0u && i) idreg = idnext;
+        const uint32_t cnt = min(kGroupRows, total - i);
+        uint32_t code[kGroupRows];
+#pragma unroll
+        for (uint32_t r = 0; r < kGroupRows; ++r) code[r] = __shfl_sync(0xFFFFFFFFu, idreg, (i + r) & 31u);
+        if (lane == 0) {
+            const uint32_t gi = (grp0 + k) & (kRingGroups - 1);
+            const uint32_t bar = bars + gi * 8u;
+            const uint32_t dst = ring + gi * (kGroupRows * kRowBytes);
+            mbar_expect_tx(bar, cnt * kRowBytes);
+#pragma unroll
+            for (uint32_t r = 0; r < kGroupRows; ++r)
+                if (r < cnt) bulk_g2s(dst + r * kRowBytes, base + (size_t)(code[r] & 0x7FFFFFFFu) * kRowVec, kRowBytes, bar);
+        }
+    }
+    __device__ __forceinline__ void begin(const uint4* base_, const uint32_t* ids_, uint32_t total_) {
+        base = base_; ids = ids_; total = total_; popped = 0;
+        idreg = lane < total ? __ldg(ids + lane) : 0u; idnext = 0u;
+        const uint32_t ng = min((total + kGroupRows - 1) / kGroupRows, kRingGroups);
+        for (uint32_t k = 0; k < ng; ++k) issue_group(k);
+    }
+    __device__ __forceinline__ uint4 pop() {
+        if ((popped & (kGroupRows - 1)) == 0u) {
+            const uint32_t k = popped / kGroupRows;
+            // the group read before this one is free now (its values have been consumed by the ALU): refill it
+            if (k && (k - 1 + kRingGroups) * kGroupRows < total) issue_group(k - 1 + kRingGroups);
+            const uint32_t g = grp0 + k;
+            mbar_wait(bars + (g & (kRingGroups - 1)) * 8u, (g / kRingGroups) & 1u);
+        }
+        const uint32_t slot = ((grp0 * kGroupRows) + popped) & (kRingSlots - 1);
+        ++popped;
+        return ring_ptr[slot * kRowVec];
+    }
+    __device__ __forceinline__ void end() { grp0 += (total + kGroupRows - 1) / kGroupRows; }
+};
+
+template <int OP>
+__device__ __forceinline__ uint4 ring_simple(RowRing& R, uint32_t n_plain, uint32_t n_comp) {
+    uint4 acc = splat4(OP == kDevAnd ? 0xFFFFFFFFu : 0u);
+    for (uint32_t j = 0; j < n_plain; ++j) {
+        const uint4 v = R.pop();
+        acc = OP == kDevAnd ? and4(acc, v) : OP == kDevOr ? or4(acc, v) : xor4(acc, v);
+    }
+    for (uint32_t j = 0; j < n_comp; ++j) {
+        const uint4 v = xors4(R.pop(), 0xFFFFFFFFu);
+        acc = OP == kDevAnd ? and4(acc, v) : OP == kDevOr ? or4(acc, v) : xor4(acc, v);
+    }
+    return acc;
+}
+
+template <int P>
+__device__ __forceinline__ uint4 ring_range(RowRing& R, uint32_t n_plain, uint32_t n_comp, uint32_t lo, uint32_t hi) {
+    uint4 pl[P];
+#pragma unroll
+    for (int p = 0; p < P; ++p) pl[p] = splat4(0u);
+    const uint32_t n = n_plain + n_comp;
+    for (uint32_t j = 0; j < n; ++j) {
+        uint4 carry = xors4(R.pop(), j < n_plain ? 0u : 0xFFFFFFFFu);
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            const uint4 t = and4(pl[p], carry);
+            pl[p] = xor4(pl[p], carry);
+            carry = t;
+        }
+    }
+    uint4 gt = splat4(0u), eq = splat4(0xFFFFFFFFu);
+#pragma unroll
+    for (int p = P - 1; p >= 0; --p) {
+        if ((lo >> p) & 1u) eq = and4(eq, pl[p]);
+        else { gt = or4(gt, and4(eq, pl[p])); eq = andn4(eq, pl[p]); }
+    }
+    uint4 res = or4(gt, eq);
+    if (hi < n) {
+        uint4 lt = splat4(0u); eq = splat4(0xFFFFFFFFu);
+#pragma unroll
+        for (int p = P - 1; p >= 0; --p) {
+            if ((hi >> p) & 1u) { lt = or4(lt, andn4(eq, pl[p])); eq = and4(eq, pl[p]); }
+            else eq = andn4(eq, pl[p]);
+        }
+        res = and4(res, or4(lt, eq));
+    }
+    return res;
+}
+
+#ifndef CANOPY_RING_MIN_BLOCKS
+#define CANOPY_RING_MIN_BLOCKS 4
+#endif
+__global__ void __launch_bounds__(kGateThreads, CANOPY_RING_MIN_BLOCKS)
+gate_ring_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const uint32_t* __restrict__ child,
+                 const uint32_t* __restrict__ layer_off, const uint32_t* __restrict__ wide_off,
+                 const uint32_t* __restrict__ split, const uint32_t* __restrict__ split_child,
+                 uint32_t n_layers, uint32_t n_nodes, uint32_t n_ev, unsigned long long* __restrict__ tallies,
+                 uint64_t first_slab, uint32_t n_slabs, uint64_t begin, uint64_t end) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kGateWarps * kRingSlots * kRowBytes);
+    if (threadIdx.x < kGateWarps * kRingGroups) mbar_init(smem_u32(bars + threadIdx.x), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    __syncthreads();
+    RowRing R;
+    R.lane = lane; R.grp0 = 0;
+    R.ring = smem_u32(smem + warp * kRingSlots * kRowBytes);
+    R.bars = smem_u32(bars + warp * kRingGroups);
+    R.ring_ptr = reinterpret_cast<const uint4*>(smem + warp * kRingSlots * kRowBytes) + lane;
+
+    for (uint32_t slab = blockIdx.x; slab < n_slabs; slab += gridDim.x) {
+        uint4* base = vals + (size_t)slab * n_nodes * kRowVec;
+        const uint64_t s0 = (first_slab + slab) * (uint64_t)kSlabSamples + lane * 128u;
+        const uint4 mask = make_uint4(valid_mask32(s0, begin, end), valid_mask32(s0 + 32, begin, end),
+                                      valid_mask32(s0 + 64, begin, end), valid_mask32(s0 + 96, begin, end));
+        for (uint32_t l = 0; l < n_layers; ++l) {
+            const uint32_t* sp = split + l * (kGateWarps + 1) + warp;
+            const uint32_t* sc = split_child + l * (kGateWarps + 1) + warp;
+            const uint32_t g0 = __ldg(sp), g1 = __ldg(sp + 1);
+            const uint32_t c0 = __ldg(sc), c1 = __ldg(sc + 1);
+            bool stored = false;
+            if (g0 < g1) {
+                uint4 rec = __ldg(grec + g0);
+                uint4 rec1 = g0 + 1 < g1 ? __ldg(grec + g0 + 1) : make_uint4(0, 0, 0, 0);
+                R.begin(base, child + c0, c1 - c0);
+                for (uint32_t g = g0; g < g1; ++g) {
+                    const uint4 rec2 = g + 2 < g1 ? __ldg(grec + g + 2) : make_uint4(0, 0, 0, 0);
+                    const uint32_t n = rec.y & 0xFFFFu, n_comp = rec.y >> 16, n_plain = n - n_comp;
+                    const uint32_t op = rec.z & 0xFFu, flags = rec.z >> 8;
+                    uint4 r;
+                    if (op == kDevAnd) r = ring_simple<kDevAnd>(R, n_plain, n_comp);
+                    else if (op == kDevOr) r = ring_simple<kDevOr>(R, n_plain, n_comp);
+                    else if (op == kDevXor) r = ring_simple<kDevXor>(R, n_plain, n_comp);
+                    else {
+                        const uint32_t lo = rec.w & 0xFFFFu, hi = rec.w >> 16;
+                        if (n < 8) r = ring_range<3>(R, n_plain, n_comp, lo, hi);
+                        else if (n < 64) r = ring_range<6>(R, n_plain, n_comp, lo, hi);
+                        else r = ring_range<9>(R, n_plain, n_comp, lo, hi);
+                    }
+                    if (flags & kFlagStore) { st_cg(base + (size_t)(n_ev + g) * kRowVec + lane, r); stored = true; }
+                    if (flags & kFlagTally) {
+                        uint32_t c = __popc(r.x & mask.x) + __popc(r.y & mask.y) + __popc(r.z & mask.z) + __popc(r.w & mask.w);
+                        c = __reduce_add_sync(0xFFFFFFFFu, c);
+                        if (lane == 0 && c) atomicAdd(tallies + g, (unsigned long long)c);
+                    }
+                    rec = rec1; rec1 = rec2;
+                }
+                R.end();
+            }
+            // wide count gates (fan-in >= kWideFanin): multi-pass register path, dealt round-robin
+            const uint32_t w_end = __ldg(layer_off + l + 1);
+            for (uint32_t g = __ldg(wide_off + l) + warp; g < w_end; g += kGateWarps) {
+                const uint4 rec = __ldg(grec + g);
+                const uint32_t n = rec.y & 0xFFFFu, flags = rec.z >> 8, lo = rec.w & 0xFFFFu, hi = rec.w >> 16;
+                const uint32_t* ch = child + rec.x;
+                const uint32_t ids = lane < n ? __ldg(ch + lane) : 0u;
+                uint4 r;
+                r.x = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 0, ids);
+                r.y = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 1, ids);
+                r.z = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 2, ids);
+                r.w = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 3, ids);
+                if (flags & kFlagStore) { st_cg(base + (size_t)(n_ev + g) * kRowVec + lane, r); stored = true; }
+                if (flags & kFlagTally) {
+                    uint32_t c = __popc(r.x & mask.x) + __popc(r.y & mask.y) + __popc(r.z & mask.z) + __popc(r.w & mask.w);
+                    c = __reduce_add_sync(0xFFFFFFFFu, c);
+                    if (lane == 0 && c) atomicAdd(tallies + g, (unsigned long long)c);
+                }
+            }
+            // rows stored through the generic proxy are read by later layers through the async proxy (bulk copies)
+            if (stored) fence_proxy_async();
+            __syncthreads();
+        }
     }
 }
 
@@ -451,6 +689,8 @@ struct DeviceState {
     int device = -1;
     int sm_count = 0;
     uint32_t *ev_orig = nullptr, *thr32 = nullptr, *child = nullptr, *layer_off = nullptr, *tally_gate = nullptr;
+    uint32_t *wide_off = nullptr, *split = nullptr, *split_child = nullptr;
+    int ring_ctas_per_sm = 0;   // occupancy of gate_ring_kernel on this device
     uint64_t* thr64 = nullptr;
     uint4* grec = nullptr;
     uint8_t* tally_kind = nullptr;
@@ -471,6 +711,7 @@ void destroy_device_state(DeviceState* s) {
     if (!s) return;
     cudaSetDevice(s->device);
     cudaFree(s->ev_orig); cudaFree(s->thr32); cudaFree(s->thr64); cudaFree(s->child); cudaFree(s->layer_off);
+    cudaFree(s->wide_off); cudaFree(s->split); cudaFree(s->split_child);
     cudaFree(s->tally_gate); cudaFree(s->grec); cudaFree(s->tally_kind); cudaFree(s->gate_tallies);
     cudaFree(s->out_tallies); cudaFreeHost(s->host_tallies); cudaFree(s->vals[0]); cudaFree(s->vals[1]);
     if (s->main) cudaStreamDestroy(s->main);
@@ -513,6 +754,12 @@ static DeviceState* get_state(canopy_plan* plan, int device) {
         s->child = upload(L.child, s->h2d_bytes);
         s->layer_off = upload(L.layer_off.empty() ? std::vector<uint32_t>{0} : L.layer_off, s->h2d_bytes);
         s->tally_gate = upload(L.tally_gate, s->h2d_bytes);
+        s->wide_off = upload(L.wide_off, s->h2d_bytes);
+        s->split = upload(L.split, s->h2d_bytes);
+        s->split_child = upload(L.split_child, s->h2d_bytes);
+        CUDA_CHECK(cudaFuncSetAttribute(gate_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmemBytes));
+        CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->ring_ctas_per_sm, gate_ring_kernel, kGateThreads, kRingSmemBytes));
+        if (s->ring_ctas_per_sm < 1) throw Error(CANOPY_E_CUDA, "gate_ring_kernel does not fit on an SM");
         s->tally_kind = upload(L.tally_kind, s->h2d_bytes);
         static_assert(sizeof(GateRec) == sizeof(uint4), "GateRec must be 16 bytes");
         s->grec = reinterpret_cast<uint4*>(upload(L.gate_rec, s->h2d_bytes));
@@ -571,8 +818,19 @@ static void launch_sampler(const DeviceState* s, const Lowered& L, uint4* vals, 
 static void launch_gates(const DeviceState* s, const Lowered& L, uint4* vals, uint64_t first_slab, uint32_t n_slabs,
                          uint64_t begin, uint64_t end, cudaStream_t st) {
     if (L.n_gates() == 0 || n_slabs == 0) return;
-    gate_kernel<<<n_slabs, kGateThreads, 0, st>>>(vals, s->grec, s->child, s->layer_off, L.n_layers(), L.n_nodes(),
-                                                  L.n_events(), s->gate_tallies, first_slab, begin, end);
+    static const bool direct = getenv("CANOPY_GATE_KERNEL") && !strcmp(getenv("CANOPY_GATE_KERNEL"), "direct");  // A/B knob
+    if (direct) {
+        gate_kernel<<<n_slabs, kGateThreads, 0, st>>>(vals, s->grec, s->child, s->layer_off, L.n_layers(), L.n_nodes(),
+                                                      L.n_events(), s->gate_tallies, first_slab, begin, end);
+    } else {
+        // persistent: one CTA per resident slot, each walks slabs blockIdx.x, +gridDim.x, ...
+        static const int cap = getenv("CANOPY_RING_CTAS") ? atoi(getenv("CANOPY_RING_CTAS")) : 0;  // tuning knob
+        const int per_sm = cap > 0 ? std::min(cap, s->ring_ctas_per_sm) : s->ring_ctas_per_sm;
+        const uint32_t grid = std::min<uint32_t>(n_slabs, (uint32_t)(s->sm_count * per_sm));
+        gate_ring_kernel<<<grid, kGateThreads, kRingSmemBytes, st>>>(
+            vals, s->grec, s->child, s->layer_off, s->wide_off, s->split, s->split_child, L.n_layers(), L.n_nodes(),
+            L.n_events(), s->gate_tallies, first_slab, n_slabs, begin, end);
+    }
     CUDA_CHECK(cudaGetLastError());
 }
 

@@ -313,9 +313,13 @@ void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lower
     const uint32_t n_ev = L.n_events();
     std::vector<uint32_t> live_ids;
     for (uint32_t m = 0; m < M; ++m) if (live[m]) live_ids.push_back(m);
+    // inside a layer: ring-path gates by descending fan-in, then the "wide" count gates (fan-in >= kWideFanin,
+    // evaluated in several register passes outside the shared-memory ring) at the end of the layer
+    auto is_wide = [&](uint32_t m) { return mg[m].op == kDevRange && mg[m].count >= kWideFanin; };
     std::stable_sort(live_ids.begin(), live_ids.end(), [&](uint32_t a, uint32_t b) {
         if (mg[a].level != mg[b].level) return mg[a].level < mg[b].level;
-        return mg[a].count > mg[b].count;  // big gates first inside a layer (longest-processing-time order)
+        if (is_wide(a) != is_wide(b)) return is_wide(b);
+        return mg[a].count > mg[b].count;
     });
     std::vector<uint32_t> gate_dev(M, ~0u);
     for (uint32_t i = 0; i < live_ids.size(); ++i) gate_dev[live_ids[i]] = i;
@@ -327,13 +331,21 @@ void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lower
         L.layer_off[m.level] = i + 1;  // running end of this level
         const uint8_t flags = (stored[live_ids[i]] ? kFlagStore : 0) | (tallied[live_ids[i]] ? kFlagTally : 0);
         n_stored += stored[live_ids[i]]; n_tallied += tallied[live_ids[i]];
-        GateRec rec{(uint32_t)L.child.size(), m.count, (uint32_t)m.op | ((uint32_t)flags << 8),
+        if (m.count > 0xFFFFu)
+            fail(CANOPY_E_UNSUPPORTED, "a gate with more than 65535 arguments after folding is not supported");
+        // every device op is symmetric in its inputs, so the arguments are emitted plain-first,
+        // complemented-last: the kernel then needs one count instead of one flag per row
+        uint32_t n_comp = 0;
+        for (uint32_t j = 0; j < m.count; ++j) n_comp += mchild[m.first + j].comp ? 1u : 0u;
+        GateRec rec{(uint32_t)L.child.size(), m.count | (n_comp << 16), (uint32_t)m.op | ((uint32_t)flags << 8),
                     (uint32_t)m.lo | ((uint32_t)m.hi << 16)};
-        for (uint32_t j = 0; j < m.count; ++j) {
-            const Ref& a = mchild[m.first + j];
-            const uint32_t node = a.kind == kEvent ? ev_dev[a.id] : n_ev + gate_dev[a.id];
-            L.child.push_back(node | (a.comp ? 0x80000000u : 0u));
-        }
+        for (int pass = 0; pass < 2; ++pass)
+            for (uint32_t j = 0; j < m.count; ++j) {
+                const Ref& a = mchild[m.first + j];
+                if ((a.comp != 0) != (pass == 1)) continue;
+                const uint32_t node = a.kind == kEvent ? ev_dev[a.id] : n_ev + gate_dev[a.id];
+                L.child.push_back(node | (a.comp ? 0x80000000u : 0u));
+            }
         L.gate_rec.push_back(rec);
         L.gate_child_off.push_back((uint32_t)L.child.size());
         L.gate_op.push_back(m.op); L.gate_flags.push_back(flags);
@@ -343,6 +355,31 @@ void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lower
     // layer_off[l] currently holds the end of level l (0 for empty slots); make it a proper prefix array
     for (uint32_t l = 1; l <= max_level; ++l) if (L.layer_off[l] < L.layer_off[l - 1]) L.layer_off[l] = L.layer_off[l - 1];
     // layer_off has max_level+1 entries: [0]=0 start of level 1, [l]=end of level l
+    // ---- per-layer work split for the gate kernel ------------------------------------------------------
+    // wide_off[l]: first wide gate of layer l.  split[l*(kGateWarps+1) + w]: the ring-path gates of layer l are
+    // cut into kGateWarps contiguous chunks of equal cost (rows read + rows written + a per-gate constant),
+    // so each warp of the slab's CTA streams one contiguous run of the child array.
+    {
+        const uint32_t nl = max_level;
+        L.wide_off.resize(nl); L.split.assign((size_t)nl * (kGateWarps + 1), 0);
+        L.split_child.assign((size_t)nl * (kGateWarps + 1), 0);
+        for (uint32_t l = 0; l < nl; ++l) {
+            const uint32_t a = L.layer_off[l], b = L.layer_off[l + 1];
+            uint32_t wv = b;
+            while (wv > a && L.gate_op[wv - 1] == kDevRange && (L.gate_rec[wv - 1].n_children & 0xFFFFu) >= kWideFanin) --wv;
+            L.wide_off[l] = wv;
+            std::vector<uint64_t> cost(wv - a + 1, 0);
+            for (uint32_t g = a; g < wv; ++g) cost[g - a + 1] = cost[g - a] + (L.gate_rec[g].n_children & 0xFFFFu) + 2;
+            uint32_t* sp = &L.split[(size_t)l * (kGateWarps + 1)];
+            for (uint32_t w = 0; w <= kGateWarps; ++w) {
+                const uint64_t target = cost[wv - a] * w / kGateWarps;
+                sp[w] = a + (uint32_t)(std::lower_bound(cost.begin(), cost.end(), target) - cost.begin());
+            }
+            sp[0] = a; sp[kGateWarps] = wv;
+            uint32_t* sc = &L.split_child[(size_t)l * (kGateWarps + 1)];
+            for (uint32_t w = 0; w <= kGateWarps; ++w) sc[w] = L.gate_child_off[sp[w]];
+        }
+    }
     // ---- tally mapping -------------------------------------------------------------------------------
     L.tally_kind.resize(n_tallies); L.tally_gate.assign(n_tallies, 0);
     for (uint32_t i = 0; i < n_tallies; ++i) {

@@ -33,9 +33,13 @@ constexpr uint32_t kSlabSamples = kSlabWords * 64;   // 4096
 constexpr uint32_t kRowBytes = kSlabWords * 8;       // 512
 constexpr uint32_t kRowVec = 32;                     // uint4 per row
 
+// Gate kernel geometry fixed at lowering time.
+constexpr uint32_t kGateWarps = 8;     // warps of the CTA that walks one slab; the per-layer split is cut for this
+constexpr uint32_t kWideFanin = 512;   // count gates with at least this fan-in take the multi-pass register path
+
 struct GateRec {           // 16 bytes, loaded as one uint4 by the gate kernel
     uint32_t child_off;    // into Lowered::child
-    uint32_t n_children;
+    uint32_t n_children;   // fan-in | (number of complemented arguments, which come last) << 16
     uint32_t op_flags;     // op | flags << 8
     uint32_t krange;       // lo | hi << 16   (kDevRange only)
 };
@@ -54,6 +58,9 @@ struct Lowered {
     std::vector<uint8_t> gate_op, gate_flags;
     std::vector<uint16_t> gate_kmin, gate_kmax;
     std::vector<uint32_t> layer_off;       // [n_layers+1]
+    std::vector<uint32_t> wide_off;        // [n_layers] first wide count gate of the layer (== layer end if none)
+    std::vector<uint32_t> split;           // [n_layers][kGateWarps+1] equal-cost chunks of the ring-path gates
+    std::vector<uint32_t> split_child;     // [n_layers][kGateWarps+1] offsets into child[] at the same cut points
     // output mapping: user-visible tallies -> device gate tallies
     std::vector<uint8_t> tally_kind;
     std::vector<uint32_t> tally_gate;
