@@ -404,22 +404,40 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
 
+__device__ __forceinline__ bool elect_one() {  // one lane of the (converged) warp, chosen by the hardware
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xFFFFFFFF;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+
 // Per-warp stream of child rows through the shared-memory ring.  Rows travel in groups of kGroupRows
 // consecutive rows of the run: one mbarrier phase (one expect_tx, one try_wait) per group, so the
 // ~90-cycle mbarrier round trip and the copy-issue sequence are paid once per 2 KB, not once per row.
+// Every member except `lane_off`/`idreg`/`idnext` is warp-uniform and derived from values the compiler can
+// prove uniform (kernel parameters, blockIdx, loop counters, shuffles from a uniform lane), so the copy
+// operands live in uniform registers and UBLKCP issues without a per-lane serialisation loop.
 struct RowRing {
     const uint4* base;          // this slab's rows
     const uint32_t* ids;        // child + c0: the warp's run of child codes for this layer
     uint32_t ring;              // shared address of slot 0 of this warp's ring
     uint32_t bars;              // shared address of mbarrier 0 of this warp's ring
-    const uint4* ring_ptr;      // generic pointer to this lane's 16 bytes of slot 0
-    uint32_t total;             // rows in the run
-    uint32_t popped;            // rows consumed so far in the run
-    uint32_t grp0;              // groups consumed by this warp before this run (ring position / parity continuity)
-    uint32_t idreg, idnext;     // child codes of rows [32k, 32k+32) of the run (and of the next 32), one per lane
+    uint32_t lane_off;          // lane * 16
     uint32_t lane;
+    uint32_t total;             // rows in the run
+    uint32_t n_groups;          // groups in the run
+    uint32_t k_cur;             // groups of the run handed to the consumer so far
+    uint32_t gi_next;           // ring group the next consumed group sits in
+    uint32_t phase;             // bit g = parity of the phase the consumer waits for next on ring group g
+    uint32_t cur;               // shared address of this lane's 16 bytes of the next row to read
+    uint32_t in_group;          // rows of the current group not read yet
+    uint32_t idreg, idnext;     // child codes of rows [32k, 32k+32) of the run (and of the next 32), one per lane
 
-    __device__ __forceinline__ void issue_group(uint32_t k) {  // request rows [4k, 4k+4) of the run (ascending k)
+    __device__ __forceinline__ void issue_group(uint32_t k, uint32_t gi) {  // request rows [4k, 4k+4) of the run into ring group gi
         const uint32_t i = k * kGroupRows;
         if ((i & 31u) == 8u) idnext = (i + 24u + lane < total) ? __ldg(ids + i + 24u + lane) : 0u;  // codes of the next 32 rows
         if ((i & 31u) == 0u && i) idreg = idnext;
@@ -427,8 +445,7 @@ struct RowRing {
         uint32_t code[kGroupRows];
 #pragma unroll
         for (uint32_t r = 0; r < kGroupRows; ++r) code[r] = __shfl_sync(0xFFFFFFFFu, idreg, (i + r) & 31u);
-        if (lane == 0) {
-            const uint32_t gi = (grp0 + k) & (kRingGroups - 1);
+        if (elect_one()) {
             const uint32_t bar = bars + gi * 8u;
             const uint32_t dst = ring + gi * (kGroupRows * kRowBytes);
             mbar_expect_tx(bar, cnt * kRowBytes);
@@ -438,24 +455,29 @@ struct RowRing {
         }
     }
     __device__ __forceinline__ void begin(const uint4* base_, const uint32_t* ids_, uint32_t total_) {
-        base = base_; ids = ids_; total = total_; popped = 0;
+        base = base_; ids = ids_; total = total_; k_cur = 0; in_group = 0;
+        n_groups = (total + kGroupRows - 1) / kGroupRows;
         idreg = lane < total ? __ldg(ids + lane) : 0u; idnext = 0u;
-        const uint32_t ng = min((total + kGroupRows - 1) / kGroupRows, kRingGroups);
-        for (uint32_t k = 0; k < ng; ++k) issue_group(k);
+        const uint32_t ng = min(n_groups, kRingGroups);
+        for (uint32_t k = 0; k < ng; ++k) issue_group(k, (gi_next + k) & (kRingGroups - 1));
+    }
+    __device__ __forceinline__ void advance() {  // current group exhausted: recycle it, wait for the next one
+        const uint32_t gi = gi_next;
+        gi_next = (gi_next + 1) & (kRingGroups - 1);
+        // the group read before this one is free now (its values have been consumed by the ALU): refill it
+        if (k_cur && k_cur - 1 + kRingGroups < n_groups) issue_group(k_cur - 1 + kRingGroups, (gi - 1) & (kRingGroups - 1));
+        mbar_wait(bars + gi * 8u, (phase >> gi) & 1u);
+        phase ^= 1u << gi;
+        cur = ring + gi * (kGroupRows * kRowBytes) + lane_off;
+        in_group = min(kGroupRows, total - k_cur * kGroupRows);
+        ++k_cur;
     }
     __device__ __forceinline__ uint4 pop() {
-        if ((popped & (kGroupRows - 1)) == 0u) {
-            const uint32_t k = popped / kGroupRows;
-            // the group read before this one is free now (its values have been consumed by the ALU): refill it
-            if (k && (k - 1 + kRingGroups) * kGroupRows < total) issue_group(k - 1 + kRingGroups);
-            const uint32_t g = grp0 + k;
-            mbar_wait(bars + (g & (kRingGroups - 1)) * 8u, (g / kRingGroups) & 1u);
-        }
-        const uint32_t slot = ((grp0 * kGroupRows) + popped) & (kRingSlots - 1);
-        ++popped;
-        return ring_ptr[slot * kRowVec];
+        if (in_group == 0) advance();
+        const uint4 v = lds128(cur);
+        cur += kRowBytes; --in_group;
+        return v;
     }
-    __device__ __forceinline__ void end() { grp0 += (total + kGroupRows - 1) / kGroupRows; }
 };
 
 template <int OP>
@@ -516,16 +538,16 @@ gate_ring_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const
                  uint32_t n_layers, uint32_t n_nodes, uint32_t n_ev, unsigned long long* __restrict__ tallies,
                  uint64_t first_slab, uint32_t n_slabs, uint64_t begin, uint64_t end) {
     extern __shared__ __align__(128) unsigned char smem[];
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = __shfl_sync(0xFFFFFFFFu, threadIdx.x >> 5, 0);  // broadcast: provably warp-uniform
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kGateWarps * kRingSlots * kRowBytes);
     if (threadIdx.x < kGateWarps * kRingGroups) mbar_init(smem_u32(bars + threadIdx.x), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
     RowRing R;
-    R.lane = lane; R.grp0 = 0;
-    R.ring = smem_u32(smem + warp * kRingSlots * kRowBytes);
-    R.bars = smem_u32(bars + warp * kRingGroups);
-    R.ring_ptr = reinterpret_cast<const uint4*>(smem + warp * kRingSlots * kRowBytes) + lane;
+    R.lane = lane; R.lane_off = lane * 16u; R.gi_next = 0; R.phase = 0;
+    R.ring = smem_u32(smem) + warp * (kRingSlots * kRowBytes);
+    R.bars = smem_u32(bars) + warp * (kRingGroups * 8u);
 
     for (uint32_t slab = blockIdx.x; slab < n_slabs; slab += gridDim.x) {
         uint4* base = vals + (size_t)slab * n_nodes * kRowVec;
@@ -564,7 +586,6 @@ gate_ring_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const
                     }
                     rec = rec1; rec1 = rec2;
                 }
-                R.end();
             }
             // wide count gates (fan-in >= kWideFanin): multi-pass register path, dealt round-robin
             const uint32_t w_end = __ldg(layer_off + l + 1);
