@@ -90,16 +90,24 @@ sampler_kernel(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_orig,
 // ================================================================================================
 // Sliced sampler (SPEC v2).  Same geometry as above -- one warp per (event, slab), lane r owns the 128
 // samples of group g = slab*32 + r -- but the comparison u < thr runs MSB-first on bit planes:
-//   head: 8 Philox calls ctr = (g, e, 0x100+k); word j of call k is bit (7-k) of the variates' top byte
-//         for samples 32j..32j+31 of the group.  Per plane and word: a lane still undecided (all higher
-//         bits equal to the threshold's) becomes "less" where thr has 1 and u has 0, "greater" where thr
-//         has 0 and u has 1.  The threshold is warp-uniform, so the per-plane branch is uniform.
-//   tail: a sample still undecided after 8 planes (probability 2^-8) takes its low 24 (56) bits from
-//         output word 0 (words 1:0) of the per-sample call ctr = (s, e, 0x200) (resp. 0x201).
-// 8 + ~2.4 Philox calls per 128 samples instead of 32 (64 for 64-bit thresholds).
+//   head: H = CANOPY_SLICED_HEAD_BITS Philox calls ctr = (g, e, 0x100+k); word j of call k is bit (H-1-k)
+//         of the variates' top H bits for samples 32j..32j+31 of the group.  Per plane and word: a lane
+//         still undecided (all higher bits equal to the threshold's) becomes "less" where thr has 1 and u
+//         has 0, "greater" where thr has 0 and u has 1.  The threshold is warp-uniform, so the per-plane
+//         branch is uniform.
+//   tail: the samples of the group still undecided after H planes (probability 2^-H each) take their low
+//         32-H (64-H) bits, in ascending sample order, from the output words of the group's tail calls
+//         ctr = (g, e, 0x200+n) (resp. 0x300+n): four (two) undecided samples per call, so one tail call
+//         per lane covers all but ~1e-4 of the groups and is issued without divergence.
+// H + 1 Philox calls per 128 samples instead of 32 (64 for 64-bit thresholds).
 // ================================================================================================
+constexpr int kHeadBits = CANOPY_SLICED_HEAD_BITS;
+
+#ifndef CANOPY_SLICED_MIN_BLOCKS
+#define CANOPY_SLICED_MIN_BLOCKS 6
+#endif
 template <int BITS>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, CANOPY_SLICED_MIN_BLOCKS)
 sampler_sliced_kernel(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_orig,
                       const uint32_t* __restrict__ thr32, const uint64_t* __restrict__ thr64,
                       uint32_t n_ev, uint32_t n_nodes, uint64_t first_slab, PhiloxKeys K) {
@@ -110,44 +118,48 @@ sampler_sliced_kernel(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_
     const uint32_t e = __ldg(ev_orig + ev);
     const uint64_t g = (first_slab + slab) * (kSlabSamples / 128) + lane;  // 128-sample group of this lane
     const uint32_t g_lo = (uint32_t)g, g_hi = (uint32_t)(g >> 32);
-    uint32_t head;                 // top 8 bits of the threshold, left-aligned in a 32-bit word
-    uint32_t tail32 = 0; uint64_t tail64 = 0;  // (thr mod 2^(BITS-8)) << 8: compared with the raw tail variate
-    if (BITS == 32) { const uint32_t t = __ldg(thr32 + ev); head = t; tail32 = t << 8; }
-    else { const uint64_t t = __ldg(thr64 + ev); head = (uint32_t)(t >> 32); tail64 = t << 8; }
-    uint32_t u0 = ~0u, u1 = ~0u, u2 = ~0u, u3 = ~0u;  // undecided lanes
-    uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0;          // decided "u < thr"
+    uint32_t head;                 // top H bits of the threshold, left-aligned in a 32-bit word
+    uint32_t tail32 = 0; uint64_t tail64 = 0;  // (thr mod 2^(BITS-H)) << H: compared with the raw tail variate
+    if (BITS == 32) { const uint32_t t = __ldg(thr32 + ev); head = t; tail32 = t << kHeadBits; }
+    else { const uint64_t t = __ldg(thr64 + ev); head = (uint32_t)(t >> 32); tail64 = t << kHeadBits; }
+    uint32_t u[4] = {~0u, ~0u, ~0u, ~0u};  // undecided lanes
+    uint32_t r[4] = {0, 0, 0, 0};          // decided "u < thr"
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
+    for (int k = 0; k < kHeadBits; ++k) {
         const uint4 x = philox4x32_10(g_lo, g_hi, e, 0x100u + k, K);
         if (head & (0x80000000u >> k)) {
-            r0 |= u0 & ~x.x; r1 |= u1 & ~x.y; r2 |= u2 & ~x.z; r3 |= u3 & ~x.w;
-            u0 &= x.x; u1 &= x.y; u2 &= x.z; u3 &= x.w;
+            r[0] |= u[0] & ~x.x; r[1] |= u[1] & ~x.y; r[2] |= u[2] & ~x.z; r[3] |= u[3] & ~x.w;
+            u[0] &= x.x; u[1] &= x.y; u[2] &= x.z; u[3] &= x.w;
         } else {
-            u0 &= ~x.x; u1 &= ~x.y; u2 &= ~x.z; u3 &= ~x.w;
+            u[0] &= ~x.x; u[1] &= ~x.y; u[2] &= ~x.z; u[3] &= ~x.w;
         }
     }
-    // tail: resolve the few undecided samples one by one (lanes diverge; ~2.4 trips per warp). Branch-free
-    // inside a trip: `shl.b32` clamps, so 1 << (sl - 32w) is the sample's bit in word w and 0 in the others.
-    const uint64_t s_base = g * 128u;
+    if (__any_sync(0xFFFFFFFFu, (u[0] | u[1] | u[2] | u[3]) != 0u)) {
+        uint4 t = philox4x32_10(g_lo, g_hi, e, BITS == 32 ? 0x200u : 0x300u, K);  // tail call 0, whole warp
+        uint32_t rank = 0;  // undecided samples of this lane's group resolved so far
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
 #pragma unroll 1
-    while (u0 | u1 | u2 | u3) {
-        const uint32_t sl = u0 ? __ffs(u0) - 1u : u1 ? __ffs(u1) + 31u : u2 ? __ffs(u2) + 63u : __ffs(u3) + 95u;
-        const uint64_t sidx = s_base + sl;
-        uint32_t lt;  // all-ones when the tail variate is below the tail threshold
-        if (BITS == 32) {
-            const uint32_t v = philox4x32_10_x((uint32_t)sidx, (uint32_t)(sidx >> 32), e, 0x200u, K);
-            lt = v < tail32 ? ~0u : 0u;
-        } else {
-            const uint2 v = philox4x32_10_xy((uint32_t)sidx, (uint32_t)(sidx >> 32), e, 0x201u, K);
-            lt = (((uint64_t)v.y << 32) | v.x) < tail64 ? ~0u : 0u;
+            while (u[w]) {
+                const uint32_t b = u[w] & (0u - u[w]);  // lowest undecided sample of word w
+                u[w] ^= b;
+                bool lt;
+                if (BITS == 32) {
+                    if ((rank & 3u) == 0u && rank) t = philox4x32_10(g_lo, g_hi, e, 0x200u + (rank >> 2), K);  // > 4 undecided: rare
+                    const uint32_t v = (rank & 2u) ? ((rank & 1u) ? t.w : t.z) : ((rank & 1u) ? t.y : t.x);
+                    lt = v < tail32;
+                } else {
+                    if ((rank & 1u) == 0u && rank) t = philox4x32_10(g_lo, g_hi, e, 0x300u + (rank >> 1), K);
+                    const uint64_t v = (rank & 1u) ? (((uint64_t)t.w << 32) | t.z) : (((uint64_t)t.y << 32) | t.x);
+                    lt = v < tail64;
+                }
+                if (lt) r[w] |= b;
+                ++rank;
+            }
         }
-        const uint32_t b0 = shl_clamp(1u, sl), b1 = shl_clamp(1u, sl - 32u), b2 = shl_clamp(1u, sl - 64u),
-                       b3 = shl_clamp(1u, sl - 96u);
-        u0 &= ~b0; u1 &= ~b1; u2 &= ~b2; u3 &= ~b3;
-        r0 |= b0 & lt; r1 |= b1 & lt; r2 |= b2 & lt; r3 |= b3 & lt;
     }
     uint4* row = vals + ((size_t)slab * n_nodes + ev) * kRowVec;
-    st_cg(row + lane, make_uint4(r0, r1, r2, r3));
+    st_cg(row + lane, make_uint4(r[0], r[1], r[2], r[3]));
 }
 
 // ================================================================================================

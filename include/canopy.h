@@ -49,11 +49,15 @@ extern "C" {
  * (spec version, graph, seed, sample range). Two specs are implemented and selected per plan
  * (canopy_plan_opts.sampler); both draw Philox4x32-10 variates and compare them with the event threshold:
  *   spec 1  "direct": one 32/64-bit variate per (event, sample), compared whole.
- *   spec 2  "sliced": the same comparison evaluated MSB-first; the top 8 bits of the variates of 128
- *           consecutive samples come from 8 bit-sliced Philox calls, the remaining 24/56 bits from a
- *           per-sample call that only the ~2^-8 samples still undecided after 8 bits ever need.
+ *   spec 2  "sliced": the same comparison evaluated MSB-first; the top CANOPY_SLICED_HEAD_BITS bits of
+ *           the variates of 128 consecutive samples come from that many bit-sliced Philox calls, the
+ *           remaining bits from tail calls that only the ~2^-H samples still undecided after the head
+ *           bits ever consume (4 undecided samples per call; 2 with 64-bit thresholds).
  * CANOPY_SPEC_VERSION is the default spec of this build. */
 #define CANOPY_SPEC_VERSION 2
+#ifndef CANOPY_SLICED_HEAD_BITS
+#define CANOPY_SLICED_HEAD_BITS 8   /* H of spec 2; part of the spec (changing it changes every tally) */
+#endif
 #define CANOPY_SAMPLER_DEFAULT 0   /* = the build default (spec 2) */
 #define CANOPY_SAMPLER_DIRECT  1   /* spec 1 */
 #define CANOPY_SAMPLER_SLICED  2   /* spec 2 */

@@ -75,8 +75,9 @@ double oracle_quantised_p(double p, int bits) {
 
 /* The variate u(e, s) of DESIGN.md section 1, straight from its definition, and the basic-event bit
  * x = u < thr.  spec 1 "direct": one Philox call per 4 (2) samples, output word s&3 (pair s&1).
- * spec 2 "sliced": top byte of u from 8 bit-sliced calls of the sample's 128-group, the low 24 (56) bits
- * from the high bits of output word 0 (words 1:0) of a per-sample call. */
+ * spec 2 "sliced": the top H = CANOPY_SLICED_HEAD_BITS bits of u from H bit-sliced calls of the sample's
+ * 128-group; a sample whose head bits equal the threshold's takes its low 32-H (64-H) bits from the tail
+ * calls of the group, which are shared out in order among the group's undecided samples. */
 int oracle_sample_bit(uint64_t seed, uint32_t e, uint64_t s, int kind, uint64_t thr, int bits, int spec) {
     if (kind == 0) return 0;
     if (kind == 1) return 1;
@@ -97,23 +98,34 @@ int oracle_sample_bit(uint64_t seed, uint32_t e, uint64_t s, int kind, uint64_t 
             return u < thr;
         }
     }
-    /* spec 2 */
-    uint64_t g = s >> 7; unsigned j = (unsigned)(s >> 5) & 3, t = (unsigned)s & 31;
-    uint64_t head = 0;
-    for (unsigned k = 0; k < 8; ++k) {
+    /* spec 2: head bits of all 128 samples of the group (the tail word of a sample depends on how many
+     * samples before it in the group are still undecided after the head planes) */
+    const unsigned H = CANOPY_SLICED_HEAD_BITS;
+    uint64_t g = s >> 7; unsigned pos = (unsigned)(s & 127);
+    uint32_t und[4] = {~0u, ~0u, ~0u, ~0u}, res[4] = {0, 0, 0, 0};
+    unsigned head_thr = (unsigned)(thr >> (bits - H));
+    for (unsigned k = 0; k < H; ++k) {
         ctr[0] = (uint32_t)g; ctr[1] = (uint32_t)(g >> 32); ctr[2] = e; ctr[3] = 0x100u + k;
         oracle_philox4x32_10(ctr, key, out);
-        head = (head << 1) | ((out[j] >> t) & 1u);
+        int tb = (head_thr >> (H - 1 - k)) & 1;
+        for (int j = 0; j < 4; ++j) {
+            if (tb) { res[j] |= und[j] & ~out[j]; und[j] &= out[j]; }
+            else und[j] &= ~out[j];
+        }
     }
-    ctr[0] = (uint32_t)s; ctr[1] = (uint32_t)(s >> 32); ctr[2] = e; ctr[3] = bits == 32 ? 0x200u : 0x201u;
-    oracle_philox4x32_10(ctr, key, out);
+    if (!((und[pos >> 5] >> (pos & 31)) & 1u)) return (res[pos >> 5] >> (pos & 31)) & 1u;
+    unsigned rank = 0;  /* undecided samples of the group before this one */
+    for (unsigned q = 0; q < pos; ++q) rank += (und[q >> 5] >> (q & 31)) & 1u;
     if (bits == 32) {
-        uint32_t u = (uint32_t)(head << 24) | (out[0] >> 8);
-        return u < (uint32_t)thr;
+        ctr[0] = (uint32_t)g; ctr[1] = (uint32_t)(g >> 32); ctr[2] = e; ctr[3] = 0x200u + (rank >> 2);
+        oracle_philox4x32_10(ctr, key, out);
+        return (out[rank & 3] >> H) < ((uint32_t)thr & (0xFFFFFFFFu >> H));
     } else {
-        uint64_t v = ((uint64_t)out[1] << 32) | out[0];
-        uint64_t u = (head << 56) | (v >> 8);
-        return u < thr;
+        ctr[0] = (uint32_t)g; ctr[1] = (uint32_t)(g >> 32); ctr[2] = e; ctr[3] = 0x300u + (rank >> 1);
+        oracle_philox4x32_10(ctr, key, out);
+        unsigned j = (rank & 1) * 2;
+        uint64_t v = ((uint64_t)out[j + 1] << 32) | out[j];
+        return (v >> H) < (thr & (~0ull >> H));
     }
 }
 
@@ -152,29 +164,37 @@ static uint64_t packed_sample_word(uint64_t seed, uint32_t e, uint64_t w, int ki
 static void sliced_group_words(uint64_t seed, uint32_t e, uint64_t g, int kind, uint64_t thr, int bits, uint64_t out2[2]) {
     if (kind == 0) { out2[0] = out2[1] = 0; return; }
     if (kind == 1) { out2[0] = out2[1] = ~0ull; return; }
+    const unsigned H = CANOPY_SLICED_HEAD_BITS;
     uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
     uint32_t ctr[4], x[4];
     uint32_t und[4] = {~0u, ~0u, ~0u, ~0u}, res[4] = {0, 0, 0, 0};
-    unsigned head = (unsigned)(thr >> (bits - 8)) & 0xFFu;
-    for (unsigned k = 0; k < 8; ++k) {
+    unsigned head = (unsigned)(thr >> (bits - H));
+    for (unsigned k = 0; k < H; ++k) {
         ctr[0] = (uint32_t)g; ctr[1] = (uint32_t)(g >> 32); ctr[2] = e; ctr[3] = 0x100u + k;
         oracle_philox4x32_10(ctr, key, x);
-        int tb = (head >> (7 - k)) & 1;
+        int tb = (head >> (H - 1 - k)) & 1;
         for (int j = 0; j < 4; ++j) {
             if (tb) { res[j] |= und[j] & ~x[j]; und[j] &= x[j]; }
             else und[j] &= ~x[j];
         }
     }
+    /* tail: the r-th undecided sample of the group (ascending sample index) takes output word r&3 of tail
+     * call r>>2 (32-bit thresholds), or words 2(r&1)+1 : 2(r&1) of tail call r>>1 (64-bit thresholds) */
+    unsigned rank = 0, have = ~0u;
     for (unsigned j = 0; j < 4; ++j)
         for (unsigned t = 0; t < 32; ++t) {
             if (!((und[j] >> t) & 1u)) continue;
-            uint64_t sidx = g * 128 + j * 32 + t;
+            unsigned call = bits == 32 ? rank >> 2 : rank >> 1;
+            if (call != have) {
+                ctr[0] = (uint32_t)g; ctr[1] = (uint32_t)(g >> 32); ctr[2] = e; ctr[3] = (bits == 32 ? 0x200u : 0x300u) + call;
+                oracle_philox4x32_10(ctr, key, x);
+                have = call;
+            }
             int lt;
-            ctr[0] = (uint32_t)sidx; ctr[1] = (uint32_t)(sidx >> 32); ctr[2] = e; ctr[3] = bits == 32 ? 0x200u : 0x201u;
-            oracle_philox4x32_10(ctr, key, x);
-            if (bits == 32) lt = (x[0] >> 8) < ((uint32_t)thr & 0xFFFFFFu);
-            else lt = ((((uint64_t)x[1] << 32) | x[0]) >> 8) < (thr & 0x00FFFFFFFFFFFFFFull);
+            if (bits == 32) lt = (x[rank & 3] >> H) < ((uint32_t)thr & (0xFFFFFFFFu >> H));
+            else { unsigned w = (rank & 1) * 2; lt = ((((uint64_t)x[w + 1] << 32) | x[w]) >> H) < (thr & (~0ull >> H)); }
             if (lt) res[j] |= 1u << t;
+            ++rank;
         }
     out2[0] = ((uint64_t)res[1] << 32) | res[0];
     out2[1] = ((uint64_t)res[3] << 32) | res[2];
