@@ -259,7 +259,10 @@ def main():
     line = None
     if rank == 0:
         imadw_peak, _ = microbench_int(1, local)  # IMAD.WIDE.U32 lane-instr/s: the pipe that binds Philox4x32 on sm_100
-        imadw_per_bit = 581.0 / 128.0            # SASS count of sampler_kernel<32,1>: 581 IMAD.WIDE.U32 per 128 samples
+        # IMAD.WIDE.U32 per Bernoulli bit, from the SASS (profiles/README.md): spec 1 (sampler_kernel<32,1>) issues 581 per
+        # 128 samples; spec 2 (sampler_sliced_kernel<32>) issues H=8 head calls + 1 warp-wide tail call x 20 = 180 per 128.
+        sliced = stats["spec_version"] == 2
+        imadw_per_bit = (180.0 if sliced else 581.0) / 128.0
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -271,11 +274,11 @@ def main():
                     "d2h_bytes_per_step": int(nt * 8), "steps": e2e_steps,
                     "what": "canopy_plan_create from host arrays + upload + run + allreduce + tallies to host, wall clock"},
             "gpu_launches": int(launches_per_step * args.steps),
-            "roofline": {"kernel": "gate_kernel", "bound": "hbm", "achieved": gate_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+            "roofline": {"kernel": "gate_ring_kernel", "bound": "hbm", "achieved": gate_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": gate_gbs / peaks["hbm_gbs"], "traffic": None, "peak_source": peaks_src,
                          "alg_bytes_per_sample": alg_bytes_per_sample, "avg_launch_ms": gate_launch_ms,
                          "share_of_step": prof.gate_ms / max(prof.total_ms, 1e-9), "timed": "profile pass, kernels serialised"},
-            "roofline_sampler": {"kernel": "sampler_kernel", "bound": "int (FMA-pipe IMAD.WIDE.U32 issue rate)",
+            "roofline_sampler": {"kernel": "sampler_sliced_kernel<32>" if sliced else "sampler_kernel<32,1>", "bound": "int (FMA-pipe IMAD.WIDE.U32 issue rate)",
                                  "achieved": sampler_rate * imadw_per_bit / 1e9, "peak": imadw_peak / 1e9, "unit": "G IMAD.WIDE lane-instr/s",
                                  "frac": sampler_rate * imadw_per_bit / imadw_peak,
                                  "bernoulli_bits_per_s": sampler_rate, "imad_wide_per_bit": imadw_per_bit,
