@@ -106,60 +106,91 @@ constexpr int kHeadBits = CANOPY_SLICED_HEAD_BITS;
 #ifndef CANOPY_SLICED_MIN_BLOCKS
 #define CANOPY_SLICED_MIN_BLOCKS 6
 #endif
+__device__ __forceinline__ uint32_t bcast0(uint32_t v) { return __shfl_sync(0xFFFFFFFFu, v, 0); }  // provably warp-uniform
+
+// Variate queue of the tail: the output words of one tail call, consumed in order (x, y, z, w).
+template <int BITS> struct TailQueue;
+template <> struct TailQueue<32> {
+    static constexpr uint32_t kPerCall = 4, kCtr = 0x200u;
+    uint32_t q0, q1, q2, q3;
+    __device__ __forceinline__ void fill(uint4 t) { q0 = t.x; q1 = t.y; q2 = t.z; q3 = t.w; }
+    __device__ __forceinline__ bool pop_lt(uint32_t tail32, uint64_t) { const bool lt = q0 < tail32; q0 = q1; q1 = q2; q2 = q3; return lt; }
+};
+template <> struct TailQueue<64> {
+    static constexpr uint32_t kPerCall = 2, kCtr = 0x300u;
+    uint64_t q0, q1;
+    __device__ __forceinline__ void fill(uint4 t) { q0 = ((uint64_t)t.y << 32) | t.x; q1 = ((uint64_t)t.w << 32) | t.z; }
+    __device__ __forceinline__ bool pop_lt(uint32_t, uint64_t tail64) { const bool lt = q0 < tail64; q0 = q1; return lt; }
+};
+
+#ifndef CANOPY_SLICED_SLABS_PER_WARP
+#define CANOPY_SLICED_SLABS_PER_WARP 8
+#endif
 template <int BITS>
 __global__ void __launch_bounds__(256, CANOPY_SLICED_MIN_BLOCKS)
 sampler_sliced_kernel(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_orig,
                       const uint32_t* __restrict__ thr32, const uint64_t* __restrict__ thr64,
-                      uint32_t n_ev, uint32_t n_nodes, uint64_t first_slab, PhiloxKeys K) {
+                      uint32_t n_ev, uint32_t n_nodes, uint64_t first_slab, uint32_t n_slabs, PhiloxKeys K) {
     const uint32_t lane = threadIdx.x & 31;
-    const uint32_t ev = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const uint32_t ev = blockIdx.x * (blockDim.x >> 5) + bcast0(threadIdx.x >> 5);
     if (ev >= n_ev) return;
-    const uint32_t slab = blockIdx.y;
-    const uint32_t e = __ldg(ev_orig + ev);
-    const uint64_t g = (first_slab + slab) * (kSlabSamples / 128) + lane;  // 128-sample group of this lane
-    const uint32_t g_lo = (uint32_t)g, g_hi = (uint32_t)(g >> 32);
+    // Everything that depends on the event only is loaded once per warp and broadcast, so the compiler keeps
+    // it in uniform registers and the per-plane branch on the threshold bit is a uniform branch.
+    const uint32_t e = bcast0(__ldg(ev_orig + ev));
     uint32_t head;                 // top H bits of the threshold, left-aligned in a 32-bit word
     uint32_t tail32 = 0; uint64_t tail64 = 0;  // (thr mod 2^(BITS-H)) << H: compared with the raw tail variate
-    if (BITS == 32) { const uint32_t t = __ldg(thr32 + ev); head = t; tail32 = t << kHeadBits; }
-    else { const uint64_t t = __ldg(thr64 + ev); head = (uint32_t)(t >> 32); tail64 = t << kHeadBits; }
-    uint32_t u[4] = {~0u, ~0u, ~0u, ~0u};  // undecided lanes
-    uint32_t r[4] = {0, 0, 0, 0};          // decided "u < thr"
-#pragma unroll
-    for (int k = 0; k < kHeadBits; ++k) {
-        const uint4 x = philox4x32_10(g_lo, g_hi, e, 0x100u + k, K);
-        if (head & (0x80000000u >> k)) {
-            r[0] |= u[0] & ~x.x; r[1] |= u[1] & ~x.y; r[2] |= u[2] & ~x.z; r[3] |= u[3] & ~x.w;
-            u[0] &= x.x; u[1] &= x.y; u[2] &= x.z; u[3] &= x.w;
-        } else {
-            u[0] &= ~x.x; u[1] &= ~x.y; u[2] &= ~x.z; u[3] &= ~x.w;
-        }
+    if (BITS == 32) { const uint32_t t = bcast0(__ldg(thr32 + ev)); head = t; tail32 = t << kHeadBits; }
+    else {
+        const uint64_t t = __ldg(thr64 + ev);
+        const uint32_t lo = bcast0((uint32_t)t), hi = bcast0((uint32_t)(t >> 32));
+        head = hi; tail64 = (((uint64_t)hi << 32) | lo) << kHeadBits;
     }
-    if (__any_sync(0xFFFFFFFFu, (u[0] | u[1] | u[2] | u[3]) != 0u)) {
-        uint4 t = philox4x32_10(g_lo, g_hi, e, BITS == 32 ? 0x200u : 0x300u, K);  // tail call 0, whole warp
-        uint32_t rank = 0;  // undecided samples of this lane's group resolved so far
+    const uint32_t trans = head ^ (head >> 1);  // bit k (MSB first) set iff threshold bits k and k-1 differ
+    uint4* row = vals + ((size_t)blockIdx.y * n_nodes + ev) * kRowVec + lane;
+    const size_t row_step = (size_t)gridDim.y * n_nodes * kRowVec;
+    for (uint32_t slab = blockIdx.y; slab < n_slabs; slab += gridDim.y, row += row_step) {
+        const uint64_t g = (first_slab + slab) * (kSlabSamples / 128) + lane;  // 128-sample group of this lane
+        const uint32_t g_lo = (uint32_t)g, g_hi = (uint32_t)(g >> 32);
+        // Branch-free head, two LOP3 per word and plane.  With m_k = all-ones iff bit k (MSB first) of the
+        // threshold is set:   u_{k+1} = u_k & ~(x_k ^ m_k)   (stay undecided where the variate bit equals the
+        // threshold bit), and a sample decided at plane k is "less" iff m_k.  The decided sets u_k ^ u_{k+1}
+        // are disjoint, so   r = XOR_k m_k & (u_k ^ u_{k+1}) = XOR_k (m_k ^ m_{k-1}) & u_k  ^  m_{H-1} & u_H
+        // (m_{-1} = 0): one LOP3 on (r, u_k, c_k) with the warp-uniform transition mask c_k.
+        uint32_t u[4] = {~0u, ~0u, ~0u, ~0u};  // undecided samples
+        uint32_t r[4] = {0, 0, 0, 0};          // decided "u < thr"
 #pragma unroll
-        for (int w = 0; w < 4; ++w) {
+        for (int k = 0; k < kHeadBits; ++k) {
+            const uint4 x = philox4x32_10(g_lo, g_hi, e, 0x100u + k, K);
+            const uint32_t m = (uint32_t)((int32_t)(head << k) >> 31);
+            const uint32_t c = (uint32_t)((int32_t)(trans << k) >> 31);
+            r[0] ^= c & u[0]; r[1] ^= c & u[1]; r[2] ^= c & u[2]; r[3] ^= c & u[3];
+            u[0] &= ~(x.x ^ m); u[1] &= ~(x.y ^ m); u[2] &= ~(x.z ^ m); u[3] &= ~(x.w ^ m);
+        }
+        {   // closing term m_{H-1} & u_H (r is then exactly the decided-less set, disjoint from u)
+            const uint32_t m = (uint32_t)((int32_t)(head << (kHeadBits - 1)) >> 31);
+            r[0] ^= m & u[0]; r[1] ^= m & u[1]; r[2] ^= m & u[2]; r[3] ^= m & u[3];
+        }
+        if (__any_sync(0xFFFFFFFFu, (u[0] | u[1] | u[2] | u[3]) != 0u)) {
+            TailQueue<BITS> Q;
+            Q.fill(philox4x32_10(g_lo, g_hi, e, TailQueue<BITS>::kCtr, K));  // tail call 0, whole warp
+            uint32_t left = TailQueue<BITS>::kPerCall, call = 0;
+#pragma unroll
+            for (int w = 0; w < 4; ++w) {
 #pragma unroll 1
-            while (u[w]) {
-                const uint32_t b = u[w] & (0u - u[w]);  // lowest undecided sample of word w
-                u[w] ^= b;
-                bool lt;
-                if (BITS == 32) {
-                    if ((rank & 3u) == 0u && rank) t = philox4x32_10(g_lo, g_hi, e, 0x200u + (rank >> 2), K);  // > 4 undecided: rare
-                    const uint32_t v = (rank & 2u) ? ((rank & 1u) ? t.w : t.z) : ((rank & 1u) ? t.y : t.x);
-                    lt = v < tail32;
-                } else {
-                    if ((rank & 1u) == 0u && rank) t = philox4x32_10(g_lo, g_hi, e, 0x300u + (rank >> 1), K);
-                    const uint64_t v = (rank & 1u) ? (((uint64_t)t.w << 32) | t.z) : (((uint64_t)t.y << 32) | t.x);
-                    lt = v < tail64;
+                while (u[w]) {
+                    const uint32_t b = u[w] & (0u - u[w]);  // lowest undecided sample of word w
+                    u[w] ^= b;
+                    if (left == 0) {  // more undecided samples than one call serves: rare (1.7e-4 per group)
+                        Q.fill(philox4x32_10(g_lo, g_hi, e, TailQueue<BITS>::kCtr + (++call), K));
+                        left = TailQueue<BITS>::kPerCall;
+                    }
+                    --left;
+                    if (Q.pop_lt(tail32, tail64)) r[w] |= b;
                 }
-                if (lt) r[w] |= b;
-                ++rank;
             }
         }
+        st_cg(row, make_uint4(r[0], r[1], r[2], r[3]));
     }
-    uint4* row = vals + ((size_t)slab * n_nodes + ev) * kRowVec;
-    st_cg(row + lane, make_uint4(r[0], r[1], r[2], r[3]));
 }
 
 // ================================================================================================
@@ -835,16 +866,20 @@ static void launch_sampler(const DeviceState* s, const Lowered& L, uint4* vals, 
                            const PhiloxKeys& K, cudaStream_t st) {
     if (L.n_events() == 0 || n_slabs == 0) return;
     const dim3 grid((L.n_events() + 7) / 8, n_slabs), block(256);
+    // sliced sampler: each warp loops over up to CANOPY_SLICED_SLABS_PER_WARP slabs of its event
+    const dim3 sgrid(grid.x, (n_slabs + CANOPY_SLICED_SLABS_PER_WARP - 1) / CANOPY_SLICED_SLABS_PER_WARP);
 #define CANOPY_SAMPLER_ARGS vals, s->ev_orig, s->thr32, s->thr64, L.n_events(), L.n_nodes(), first_slab, K
+#define CANOPY_SLICED_ARGS vals, s->ev_orig, s->thr32, s->thr64, L.n_events(), L.n_nodes(), first_slab, n_slabs, K
     static const int pack = getenv("CANOPY_SAMPLER_PACK") ? atoi(getenv("CANOPY_SAMPLER_PACK")) : 1;  // tuning knob
     if (L.opts.sampler == CANOPY_SAMPLER_SLICED) {
-        if (L.opts.threshold_bits == 64) sampler_sliced_kernel<64><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
-        else sampler_sliced_kernel<32><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
+        if (L.opts.threshold_bits == 64) sampler_sliced_kernel<64><<<sgrid, block, 0, st>>>(CANOPY_SLICED_ARGS);
+        else sampler_sliced_kernel<32><<<sgrid, block, 0, st>>>(CANOPY_SLICED_ARGS);
     }
     else if (L.opts.threshold_bits == 64) sampler_kernel<64, 0><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
     else if (pack == 0) sampler_kernel<32, 0><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
     else sampler_kernel<32, 1><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
 #undef CANOPY_SAMPLER_ARGS
+#undef CANOPY_SLICED_ARGS
     CUDA_CHECK(cudaGetLastError());
 }
 
