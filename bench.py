@@ -258,11 +258,16 @@ def main():
 
     line = None
     if rank == 0:
-        imadw_peak, _ = microbench_int(1, local)  # IMAD.WIDE.U32 lane-instr/s: the pipe that binds Philox4x32 on sm_100
-        # IMAD.WIDE.U32 per Bernoulli bit, from the SASS (profiles/README.md): spec 1 (sampler_kernel<32,1>) issues 581 per
-        # 128 samples; spec 2 (sampler_sliced_kernel<32>) issues H=8 head calls + 1 warp-wide tail call x 20 = 180 per 128.
+        # Integer roofline of the sampler.  Measured on sm_100 (canopy_microbench_int): LOP3, IMAD.WIDE.U32 and
+        # any mix of the two issue at ONE shared rate of 64 lanes/clk/SM, so the bound is the integer instruction count.
+        # Algorithmic integer ops per Bernoulli bit (spec 2, H=8): per 128-sample group 148.6 Philox multiplies (9 calls x 20,
+        # minus the round-1..3 products the calls of a group share) x (1 IMAD.WIDE + 1 LOP3) + 2 LOP3 per word and plane
+        # + 4 = 365.2 per 4096 lane-samples... i.e. per warp-row of 4096 samples: 365.2 warp-instr x 32 lanes / 4096 = 2.853.
+        # Executed (ncu source page, profiles/r01c_*): 466.4 integer warp-instr per row = 3.644 per bit.  Spec 1: 12.3 per bit.
+        int_peak, _ = microbench_int(0, local)
         sliced = stats["spec_version"] == 2
-        imadw_per_bit = (180.0 if sliced else 581.0) / 128.0
+        alg_ops_per_bit = 2.853 if sliced else 581.0 * 2 / 128.0
+        exec_ops_per_bit = 3.644 if sliced else 12.3
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -278,13 +283,16 @@ def main():
                          "frac": gate_gbs / peaks["hbm_gbs"], "traffic": None, "peak_source": peaks_src,
                          "alg_bytes_per_sample": alg_bytes_per_sample, "avg_launch_ms": gate_launch_ms,
                          "share_of_step": prof.gate_ms / max(prof.total_ms, 1e-9), "timed": "profile pass, kernels serialised"},
-            "roofline_sampler": {"kernel": "sampler_sliced_kernel<32>" if sliced else "sampler_kernel<32,1>", "bound": "int (FMA-pipe IMAD.WIDE.U32 issue rate)",
-                                 "achieved": sampler_rate * imadw_per_bit / 1e9, "peak": imadw_peak / 1e9, "unit": "G IMAD.WIDE lane-instr/s",
-                                 "frac": sampler_rate * imadw_per_bit / imadw_peak,
-                                 "bernoulli_bits_per_s": sampler_rate, "imad_wide_per_bit": imadw_per_bit,
+            "roofline_sampler": {"kernel": "sampler_sliced_kernel<32>" if sliced else "sampler_kernel<32,1>",
+                                 "bound": "int (LOP3 + IMAD.WIDE share one issue rate of 64 lanes/clk/SM)",
+                                 "achieved": sampler_rate * alg_ops_per_bit / 1e9, "peak": int_peak / 1e9, "unit": "G int lane-instr/s",
+                                 "frac": sampler_rate * alg_ops_per_bit / int_peak,
+                                 "executed_frac": sampler_rate * exec_ops_per_bit / int_peak,
+                                 "bernoulli_bits_per_s": sampler_rate, "alg_int_ops_per_bit": alg_ops_per_bit,
+                                 "executed_int_ops_per_bit": exec_ops_per_bit,
                                  "avg_launch_ms": prof.sampler_ms / max(1, prof.sampler_launches),
                                  "share_of_step": prof.sampler_ms / max(prof.total_ms, 1e-9),
-                                 "peak_source": "canopy_microbench_int(kind=1) measured in this run; SASS count in profiles/"},
+                                 "peak_source": "canopy_microbench_int(kind=0) measured in this run; instruction counts from the ncu source page in profiles/"},
             "top_event_tally_last_step": top_tally,
         }
     if world == 1 and rank == 0:

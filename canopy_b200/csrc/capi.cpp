@@ -142,7 +142,7 @@ canopy_status canopy_estimate_from_tally(uint64_t tally, uint64_t n_samples, can
 
 canopy_status canopy_microbench_int(int32_t device, int32_t kind, double* out_lane_ops_per_s, double* out_ms) {
     return guard([&] {
-        require(out_lane_ops_per_s && out_ms && kind >= 0 && kind <= 3, "canopy_microbench_int: bad argument");
+        require(out_lane_ops_per_s && out_ms && kind >= 0 && kind <= 4, "canopy_microbench_int: bad argument");
         canopy::microbench_int(device, kind, out_lane_ops_per_s, out_ms);
     });
 }

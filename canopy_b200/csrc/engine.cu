@@ -130,7 +130,17 @@ template <int BITS>
 __global__ void __launch_bounds__(256, CANOPY_SLICED_MIN_BLOCKS)
 sampler_sliced_kernel(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_orig,
                       const uint32_t* __restrict__ thr32, const uint64_t* __restrict__ thr64,
-                      uint32_t n_ev, uint32_t n_nodes, uint64_t first_slab, uint32_t n_slabs, PhiloxKeys K) {
+                      uint32_t n_ev, uint32_t n_nodes, uint64_t first_slab, uint32_t n_slabs, PhiloxKeys Kparam) {
+#ifdef CANOPY_KEYS_IN_REGS  // tuning knob: round keys in vector registers instead of uniform registers
+    PhiloxKeys K;
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+        asm volatile("mov.u32 %0, %1;" : "=r"(K.k0[i]) : "r"(Kparam.k0[i]));
+        asm volatile("mov.u32 %0, %1;" : "=r"(K.k1[i]) : "r"(Kparam.k1[i]));
+    }
+#else
+    const PhiloxKeys& K = Kparam;
+#endif
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t ev = blockIdx.x * (blockDim.x >> 5) + bcast0(threadIdx.x >> 5);
     if (ev >= n_ev) return;
@@ -699,6 +709,11 @@ __global__ void __launch_bounds__(256) intpeak_kernel(uint32_t* out, uint32_t it
                     a[i] = hi ^ lo;  // +1 LOP3 on the other pipe; counted as one IMAD.WIDE
                 } else if (KIND == 3) {
                     asm volatile("popc.b32 %0, %0;" : "+r"(a[i]));
+                } else if (KIND == 4) {  // 1 IMAD.WIDE.U32 : 2 LOP3 per chain step
+                    uint32_t lo, hi;
+                    asm volatile("{ .reg .u64 t; mul.wide.u32 t, %2, %3; mov.b64 {%0, %1}, t; }" : "=r"(lo), "=r"(hi) : "r"(a[i]), "r"(kPhiloxM0));
+                    asm volatile("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(lo) : "r"(lo), "r"(b), "r"(c + i));
+                    asm volatile("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(a[i]) : "r"(lo), "r"(hi), "r"(c));
                 }
             }
             if (KIND == 2) {  // two interleaved Philox rounds-chains: 4 x (2 IMAD.WIDE + 2 LOP3)
@@ -727,6 +742,7 @@ void microbench_int(int device, int kind, double* lane_ops_per_s, double* ms_out
             case 0: intpeak_kernel<0><<<blocks, threads>>>(d, iters, 12345u); break;
             case 1: intpeak_kernel<1><<<blocks, threads>>>(d, iters, 12345u); break;
             case 2: intpeak_kernel<2><<<blocks, threads>>>(d, iters, 12345u); break;
+            case 4: intpeak_kernel<4><<<blocks, threads>>>(d, iters, 12345u); break;
             default: intpeak_kernel<3><<<blocks, threads>>>(d, iters, 12345u); break;
         }
     };
@@ -740,7 +756,8 @@ void microbench_int(int device, int kind, double* lane_ops_per_s, double* ms_out
     float ms = 0; CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
     ms /= reps;
     // lane-instructions per launch: kinds 0,1,3: iters*4*8 ; kind 2: iters*4*4 rounds * 4 instr
-    const double per_thread = kind == 2 ? (double)iters * 4 * 4 * 4 : (double)iters * 4 * 8;
+    // kind 4 counts all three instructions of a step (1 IMAD.WIDE + 2 LOP3)
+    const double per_thread = kind == 2 ? (double)iters * 4 * 4 * 4 : kind == 4 ? (double)iters * 4 * 8 * 3 : (double)iters * 4 * 8;
     *lane_ops_per_s = per_thread * blocks * threads / (ms * 1e-3);
     *ms_out = ms;
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
@@ -822,6 +839,8 @@ static DeviceState* get_state(canopy_plan* plan, int device) {
         s->split = upload(L.split, s->h2d_bytes);
         s->split_child = upload(L.split_child, s->h2d_bytes);
         CUDA_CHECK(cudaFuncSetAttribute(gate_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmemBytes));
+        CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->ring_ctas_per_sm, gate_ring_kernel, kGateThreads, kRingSmemBytes));
         if (s->ring_ctas_per_sm < 1) throw Error(CANOPY_E_CUDA, "gate_ring_kernel does not fit on an SM");
         s->tally_kind = upload(L.tally_kind, s->h2d_bytes);
@@ -833,7 +852,12 @@ static DeviceState* get_state(canopy_plan* plan, int device) {
         CUDA_CHECK(cudaMallocHost(&s->host_tallies, nt * 8));
         CUDA_CHECK(cudaStreamCreateWithFlags(&s->main, cudaStreamNonBlocking));
         CUDA_CHECK(cudaStreamCreateWithFlags(&s->s_sample, cudaStreamNonBlocking));
-        CUDA_CHECK(cudaStreamCreateWithFlags(&s->s_gate, cudaStreamNonBlocking));
+        {   // the gate walk of batch b competes with the sampler of batch b+1 for SM slots: its (few, persistent)
+            // CTAs must win, so its stream gets the highest priority
+            int lo_prio = 0, hi_prio = 0;
+            CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio));
+            CUDA_CHECK(cudaStreamCreateWithPriority(&s->s_gate, cudaStreamNonBlocking, hi_prio));
+        }
         for (cudaEvent_t* e : {&s->ev_fork, &s->ev_join, &s->ev_sampled[0], &s->ev_sampled[1], &s->ev_consumed[0], &s->ev_consumed[1]})
             CUDA_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
         CUDA_CHECK(cudaEventCreate(&s->ev_t0)); CUDA_CHECK(cudaEventCreate(&s->ev_t1));
@@ -862,8 +886,14 @@ static PhiloxKeys make_keys(uint64_t seed) {
     return K;
 }
 
+// `shared_sm`: the launch runs beside the other kernel of the pipeline (sampler of batch b+1 beside the gate walk of
+// batch b).  Measured on B200 (gpurun_out/ovl1.txt): the two co-reside best with the sampler capped at 4 CTAs per SM
+// (by a dummy dynamic-shared-memory request) and 2 persistent gate CTAs per SM on the high-priority stream.
+constexpr int kSharedSamplerSmem = 47000;  // 4 x 47 KB + 2 x 33 KB (gate rings) fit the 228 KB of an SM
+constexpr int kSharedRingCtas = 2;
+
 static void launch_sampler(const DeviceState* s, const Lowered& L, uint4* vals, uint64_t first_slab, uint32_t n_slabs,
-                           const PhiloxKeys& K, cudaStream_t st) {
+                           const PhiloxKeys& K, cudaStream_t st, bool shared_sm = false) {
     if (L.n_events() == 0 || n_slabs == 0) return;
     const dim3 grid((L.n_events() + 7) / 8, n_slabs), block(256);
     // sliced sampler: each warp loops over up to CANOPY_SLICED_SLABS_PER_WARP slabs of its event
@@ -872,8 +902,11 @@ static void launch_sampler(const DeviceState* s, const Lowered& L, uint4* vals, 
 #define CANOPY_SLICED_ARGS vals, s->ev_orig, s->thr32, s->thr64, L.n_events(), L.n_nodes(), first_slab, n_slabs, K
     static const int pack = getenv("CANOPY_SAMPLER_PACK") ? atoi(getenv("CANOPY_SAMPLER_PACK")) : 1;  // tuning knob
     if (L.opts.sampler == CANOPY_SAMPLER_SLICED) {
-        if (L.opts.threshold_bits == 64) sampler_sliced_kernel<64><<<sgrid, block, 0, st>>>(CANOPY_SLICED_ARGS);
-        else sampler_sliced_kernel<32><<<sgrid, block, 0, st>>>(CANOPY_SLICED_ARGS);
+        // tuning knob: dynamic shared memory requested only to cap the sampler's CTAs per SM (room for gate CTAs)
+        static const int env_smem = getenv("CANOPY_SAMPLER_SMEM") ? atoi(getenv("CANOPY_SAMPLER_SMEM")) : -1;
+        const int cap_smem = !shared_sm ? 0 : env_smem >= 0 ? env_smem : kSharedSamplerSmem;
+        if (L.opts.threshold_bits == 64) sampler_sliced_kernel<64><<<sgrid, block, cap_smem, st>>>(CANOPY_SLICED_ARGS);
+        else sampler_sliced_kernel<32><<<sgrid, block, cap_smem, st>>>(CANOPY_SLICED_ARGS);
     }
     else if (L.opts.threshold_bits == 64) sampler_kernel<64, 0><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
     else if (pack == 0) sampler_kernel<32, 0><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
@@ -884,7 +917,7 @@ static void launch_sampler(const DeviceState* s, const Lowered& L, uint4* vals, 
 }
 
 static void launch_gates(const DeviceState* s, const Lowered& L, uint4* vals, uint64_t first_slab, uint32_t n_slabs,
-                         uint64_t begin, uint64_t end, cudaStream_t st) {
+                         uint64_t begin, uint64_t end, cudaStream_t st, bool shared_sm = false) {
     if (L.n_gates() == 0 || n_slabs == 0) return;
     static const bool direct = getenv("CANOPY_GATE_KERNEL") && !strcmp(getenv("CANOPY_GATE_KERNEL"), "direct");  // A/B knob
     if (direct) {
@@ -893,7 +926,8 @@ static void launch_gates(const DeviceState* s, const Lowered& L, uint4* vals, ui
     } else {
         // persistent: one CTA per resident slot, each walks slabs blockIdx.x, +gridDim.x, ...
         static const int cap = getenv("CANOPY_RING_CTAS") ? atoi(getenv("CANOPY_RING_CTAS")) : 0;  // tuning knob
-        const int per_sm = cap > 0 ? std::min(cap, s->ring_ctas_per_sm) : s->ring_ctas_per_sm;
+        const int want = cap > 0 ? cap : shared_sm ? kSharedRingCtas : s->ring_ctas_per_sm;
+        const int per_sm = std::min(want, s->ring_ctas_per_sm);
         const uint32_t grid = std::min<uint32_t>(n_slabs, (uint32_t)(s->sm_count * per_sm));
         gate_ring_kernel<<<grid, kGateThreads, kRingSmemBytes, st>>>(
             vals, s->grec, s->child, s->layer_off, s->wide_off, s->split, s->split_child, L.n_layers(), L.n_nodes(),
@@ -967,10 +1001,10 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
             const uint64_t fs = slab0 + b * batch;
             const uint32_t ns = (uint32_t)std::min<uint64_t>(batch, total_slabs - b * batch);
             if (b >= 2) CUDA_CHECK(cudaStreamWaitEvent(s->s_sample, s->ev_consumed[buf], 0));
-            launch_sampler(s, L, s->vals[buf], fs, ns, K, s->s_sample);
+            launch_sampler(s, L, s->vals[buf], fs, ns, K, s->s_sample, b > 0);               // batch 0 has the GPU to itself
             CUDA_CHECK(cudaEventRecord(s->ev_sampled[buf], s->s_sample));
             CUDA_CHECK(cudaStreamWaitEvent(s->s_gate, s->ev_sampled[buf], 0));
-            launch_gates(s, L, s->vals[buf], fs, ns, begin, end, s->s_gate);
+            launch_gates(s, L, s->vals[buf], fs, ns, begin, end, s->s_gate, b + 1 < n_batches);  // so has the last gate walk
             CUDA_CHECK(cudaEventRecord(s->ev_consumed[buf], s->s_gate));
             R.sampler_launches += L.n_events() ? 1 : 0; R.gate_launches += 1;
         }

@@ -237,7 +237,8 @@ typedef struct canopy_estimate { double p, sigma, ci_lo, ci_hi; } canopy_estimat
 CANOPY_API canopy_status canopy_estimate_from_tally(uint64_t tally, uint64_t n_samples, canopy_estimate* out);
 
 /* Integer-pipe microbenchmarks used for the sampler roofline (lane-instructions per second).
- * kind: 0 LOP3, 1 IMAD.WIDE.U32, 2 Philox4x32-10 rounds (2 IMAD.WIDE + 2 LOP3 per round), 3 POPC */
+ * kind: 0 LOP3, 1 IMAD.WIDE.U32 (+1 LOP3 each, counted once), 2 Philox4x32-10 rounds (2 IMAD.WIDE + 2 LOP3 per round),
+ *       3 POPC, 4 mix of 1 IMAD.WIDE.U32 : 2 LOP3 (all three counted) */
 CANOPY_API canopy_status canopy_microbench_int(int32_t device, int32_t kind, double* out_lane_ops_per_s,
                                                double* out_ms);
 
