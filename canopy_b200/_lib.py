@@ -62,6 +62,11 @@ class CMcReport(C.Structure):
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64)]
 
 
+class CMefOpts(C.Structure):
+    _fields_ = [("ccf_analysis", C.c_int32), ("reserved0", C.c_int32), ("mission_time", C.c_double),
+                ("reserved", C.c_int32 * 4)]
+
+
 class CEstimate(C.Structure):
     _fields_ = [("p", C.c_double), ("sigma", C.c_double), ("ci_lo", C.c_double), ("ci_hi", C.c_double)]
 
@@ -83,6 +88,10 @@ SYMBOLS = {
     "canopy_microbench_int": (C.c_int, [C.c_int32, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "canopy_model_load_mef": (C.c_int, [C.POINTER(C.c_char_p), C.c_int32, C.POINTER(C.c_void_p)]),
     "canopy_model_load_mef_string": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
+    "canopy_mef_opts_default": (None, [C.POINTER(CMefOpts)]),
+    "canopy_model_load_mef_ex": (C.c_int, [C.POINTER(C.c_char_p), C.c_int32, C.POINTER(CMefOpts), C.POINTER(C.c_void_p)]),
+    "canopy_model_load_mef_string_ex": (C.c_int, [C.c_char_p, C.POINTER(CMefOpts), C.POINTER(C.c_void_p)]),
+    "canopy_model_root_name": (C.c_char_p, [C.c_void_p, C.c_uint32]),
     "canopy_model_desc": (C.c_int, [C.c_void_p, C.POINTER(CGraphDesc)]),
     "canopy_model_basic_name": (C.c_char_p, [C.c_void_p, C.c_uint32]),
     "canopy_model_gate_name": (C.c_char_p, [C.c_void_p, C.c_uint32]),

@@ -206,17 +206,24 @@ def microbench_int(kind: int, device: int = 0):
     return ops.value, ms.value
 
 
-def load_mef(paths=None, text: str | None = None) -> Graph:
-    """Open-PSA MEF XML -> Graph via the C++ loader in libcanopy (canopy_model_load_mef*)."""
+def load_mef(paths=None, text: str | None = None, ccf_analysis: bool = False, mission_time: float | None = None) -> Graph:
+    """Open-PSA MEF XML -> Graph via the C++ loader in libcanopy (canopy_model_load_mef*_ex).
+    `ccf_analysis` / `mission_time` mirror reference Settings (settings.h:190-197,298-308).
+    Graph.meta["root_names"] names the outputs: fault-tree top events, then "<initiating event>.<sequence>"."""
     h = C.c_void_p()
     L = _lib.lib()
+    o = _lib.CMefOpts()
+    L.canopy_mef_opts_default(C.byref(o))
+    o.ccf_analysis = int(bool(ccf_analysis))
+    if mission_time is not None:
+        o.mission_time = float(mission_time)
     if text is not None:
-        _lib.check(L.canopy_model_load_mef_string(text.encode(), C.byref(h)))
+        _lib.check(L.canopy_model_load_mef_string_ex(text.encode(), C.byref(o), C.byref(h)))
     else:
         if isinstance(paths, (str, bytes)):
             paths = [paths]
         arr = (C.c_char_p * len(paths))(*[p.encode() if isinstance(p, str) else p for p in paths])
-        _lib.check(L.canopy_model_load_mef(arr, len(paths), C.byref(h)))
+        _lib.check(L.canopy_model_load_mef_ex(arr, len(paths), C.byref(o), C.byref(h)))
     try:
         d = CGraphDesc()
         _lib.check(L.canopy_model_desc(h, C.byref(d)))
@@ -228,6 +235,7 @@ def load_mef(paths=None, text: str | None = None) -> Graph:
                   roots=cp(d.roots, d.n_roots, np.uint32),
                   basic_names=[L.canopy_model_basic_name(h, i).decode() for i in range(d.n_basic)],
                   gate_names=[L.canopy_model_gate_name(h, i).decode() for i in range(d.n_gates)])
+        g.meta["root_names"] = [L.canopy_model_root_name(h, i).decode() for i in range(d.n_roots)]
         return g
     finally:
         L.canopy_model_destroy(h)

@@ -242,14 +242,29 @@ CANOPY_API canopy_status canopy_estimate_from_tally(uint64_t tally, uint64_t n_s
 CANOPY_API canopy_status canopy_microbench_int(int32_t device, int32_t kind, double* out_lane_ops_per_s,
                                                double* out_ms);
 
-/* Open-PSA MEF XML (fault-tree subset) -> flat graph. The returned model owns the arrays that
- * canopy_model_desc() points to. Stands in for reference Initializer (initializer.h:65-70). */
+/* Open-PSA MEF XML -> flat graph: fault trees, components, model-data, house events, parameters and
+ * expressions (mean value), CCF groups, event trees (one root per initiating event and sequence).
+ * The returned model owns the arrays that canopy_model_desc() points to; roots are the fault-tree top events
+ * (reference fault_tree.h:151-186) followed by the sequences. Stands in for reference Initializer
+ * (initializer.h:65-70); coverage is listed at the top of csrc/mef_model.cpp and in INTEGRATION.md. */
 typedef struct canopy_model canopy_model;
+typedef struct canopy_mef_opts {
+    int32_t ccf_analysis;   /* Settings::ccf_analysis (settings.h:298-308): replace CCF members by their proxy gates */
+    int32_t reserved0;
+    double  mission_time;   /* Settings::mission_time (settings.h:190-197,330), hours; default 8760          */
+    int32_t reserved[4];
+} canopy_mef_opts;
+CANOPY_API void          canopy_mef_opts_default(canopy_mef_opts* opts);
 CANOPY_API canopy_status canopy_model_load_mef(const char* const* xml_paths, int32_t n_paths, canopy_model** out);
 CANOPY_API canopy_status canopy_model_load_mef_string(const char* xml_text, canopy_model** out);
+CANOPY_API canopy_status canopy_model_load_mef_ex(const char* const* xml_paths, int32_t n_paths,
+                                                  const canopy_mef_opts* opts, canopy_model** out);
+CANOPY_API canopy_status canopy_model_load_mef_string_ex(const char* xml_text, const canopy_mef_opts* opts,
+                                                         canopy_model** out);
 CANOPY_API canopy_status canopy_model_desc(const canopy_model* model, canopy_graph_desc* out);
 CANOPY_API const char*   canopy_model_basic_name(const canopy_model* model, uint32_t i);
 CANOPY_API const char*   canopy_model_gate_name(const canopy_model* model, uint32_t i);
+CANOPY_API const char*   canopy_model_root_name(const canopy_model* model, uint32_t i);
 CANOPY_API void          canopy_model_destroy(canopy_model* model);
 
 CANOPY_API const char* canopy_last_error(void);   /* thread-local; valid until the next call on this thread */

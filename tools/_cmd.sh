@@ -1,10 +1,4 @@
-out=gpurun_out/ovl2.txt; : > $out
-python - >> $out 2>&1 <<'PY'
-import sys; sys.path.insert(0,'.')
-from canopy_b200.engine import microbench_int
-for k,n in enumerate(["lop3","imad_wide(+lop3)","philox_mix","popc","imadw:2lop3"]):
-    ops,ms=microbench_int(k); print(n, f"{ops/1e12:.2f} T lane-instr/s", f"{ms:.3f} ms")
-PY
-python tools/quick_overlap.py >> $out 2>&1
-timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -3 >> $out
-cat $out
+mkdir -p gpurun_out
+python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus 2 --steps 3 --warmup 3 > gpurun_out/r01c_bench_c2_n2.json 2> gpurun_out/r01c_bench_c2_n2.err; echo "n2 rc=$?"; tail -c 1500 gpurun_out/r01c_bench_c2_n2.json; tail -5 gpurun_out/r01c_bench_c2_n2.err
+python -m pytest tests -m gpu -q -k "run_multi" 2>&1 | tail -3
+python bench.py --workload c3 --steps 2 --warmup 3 --no-study > gpurun_out/r01c_bench_c3.json 2> gpurun_out/r01c_bench_c3.err; echo "c3 rc=$?"; tail -c 2500 gpurun_out/r01c_bench_c3.json
