@@ -62,6 +62,11 @@ class CMcReport(C.Structure):
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64)]
 
 
+class CCheckpoint(C.Structure):
+    _fields_ = [("magic", C.c_uint32), ("spec_version", C.c_uint32), ("threshold_bits", C.c_uint32), ("n_tallies", C.c_uint32),
+                ("plan_fingerprint", C.c_uint64), ("seed", C.c_uint64), ("sample_begin", C.c_uint64), ("next_sample", C.c_uint64)]
+
+
 class CMefOpts(C.Structure):
     _fields_ = [("ccf_analysis", C.c_int32), ("reserved0", C.c_int32), ("mission_time", C.c_double),
                 ("reserved", C.c_int32 * 4)]
@@ -82,6 +87,10 @@ SYMBOLS = {
     "canopy_mc_run": (C.c_int, [C.c_void_p, C.POINTER(CMcOpts), _u64p, C.POINTER(CMcReport)]),
     "canopy_mc_run_device": (C.c_int, [C.c_void_p, C.POINTER(CMcOpts), C.c_void_p, C.POINTER(CMcReport)]),
     "canopy_mc_run_multi": (C.c_int, [C.c_void_p, C.POINTER(CMcOpts), C.POINTER(C.c_int32), C.c_int32, _u64p, C.POINTER(CMcReport)]),
+    "canopy_plan_fingerprint": (C.c_int, [C.c_void_p, _u64p]),
+    "canopy_checkpoint_init": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(CCheckpoint)]),
+    "canopy_mc_run_resume": (C.c_int, [C.c_void_p, C.POINTER(CMcOpts), C.POINTER(CCheckpoint), _u64p, C.POINTER(CMcReport)]),
+    "canopy_plan_update_p": (C.c_int, [C.c_void_p, C.POINTER(C.c_double), C.c_uint32]),
     "canopy_mc_sample_words": (C.c_int, [C.c_void_p, C.POINTER(CMcOpts), C.c_uint64, C.c_uint64, _u64p]),
     "canopy_shard_range": (C.c_int, [C.c_uint64, C.c_uint64, C.c_int32, C.c_int32, _u64p, _u64p]),
     "canopy_estimate_from_tally": (C.c_int, [C.c_uint64, C.c_uint64, C.POINTER(CEstimate)]),

@@ -4,6 +4,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <vector>
 
 #include "plan.h"
 
@@ -109,6 +110,57 @@ canopy_status canopy_mc_run_multi(canopy_plan* plan, const canopy_mc_opts* opts,
         require(plan && opts && devices && n_devices > 0, "canopy_mc_run_multi: bad argument");
         require(tallies_host || plan->low.tally_kind.empty(), "canopy_mc_run_multi: tallies_host is null");
         canopy::mc_run_multi(plan, *opts, devices, n_devices, tallies_host, report);
+    });
+}
+
+canopy_status canopy_plan_fingerprint(const canopy_plan* plan, uint64_t* out) {
+    return guard([&] {
+        require(plan && out, "canopy_plan_fingerprint: null argument");
+        *out = canopy::fingerprint(plan->low);
+    });
+}
+
+canopy_status canopy_checkpoint_init(const canopy_plan* plan, uint64_t seed, uint64_t sample_begin, canopy_checkpoint* out) {
+    return guard([&] {
+        require(plan && out, "canopy_checkpoint_init: null argument");
+        std::memset(out, 0, sizeof *out);
+        out->magic = CANOPY_CHECKPOINT_MAGIC;
+        out->spec_version = plan->low.stats.spec_version;
+        out->threshold_bits = (uint32_t)plan->low.opts.threshold_bits;
+        out->n_tallies = (uint32_t)plan->low.tally_kind.size();
+        out->plan_fingerprint = canopy::fingerprint(plan->low);
+        out->seed = seed; out->sample_begin = sample_begin; out->next_sample = sample_begin;
+    });
+}
+
+canopy_status canopy_mc_run_resume(canopy_plan* plan, const canopy_mc_opts* opts, canopy_checkpoint* ck,
+                                   uint64_t* tallies_host_accum, canopy_mc_report* report) {
+    return guard([&] {
+        require(plan && opts && ck, "canopy_mc_run_resume: null argument");
+        require(tallies_host_accum || plan->low.tally_kind.empty(), "canopy_mc_run_resume: tallies_host_accum is null");
+        require(ck->magic == CANOPY_CHECKPOINT_MAGIC, "canopy_mc_run_resume: not a checkpoint record (bad magic)");
+        require(ck->spec_version == plan->low.stats.spec_version, "canopy_mc_run_resume: checkpoint was taken under another sampling spec");
+        require(ck->threshold_bits == (uint32_t)plan->low.opts.threshold_bits && ck->n_tallies == plan->low.tally_kind.size() &&
+                    ck->plan_fingerprint == canopy::fingerprint(plan->low),
+                "canopy_mc_run_resume: checkpoint belongs to another plan (graph, options or probabilities differ)");
+        require(ck->next_sample >= ck->sample_begin && ck->next_sample + opts->n_samples >= ck->next_sample,
+                "canopy_mc_run_resume: sample range overflows 64 bits");
+        canopy_mc_opts o = *opts;
+        o.seed = ck->seed; o.sample_begin = ck->next_sample;
+        std::vector<uint64_t> part(plan->low.tally_kind.size());
+        canopy_mc_report dummy;
+        canopy::mc_run(plan, o, part.data(), nullptr, report ? report : &dummy);
+        for (size_t i = 0; i < part.size(); ++i) tallies_host_accum[i] += part[i];
+        ck->next_sample += o.n_samples;
+    });
+}
+
+canopy_status canopy_plan_update_p(canopy_plan* plan, const double* p, uint32_t n_basic) {
+    return guard([&] {
+        require(plan && (p || n_basic == 0), "canopy_plan_update_p: null argument");
+        std::lock_guard<std::mutex> lock(plan->mu);
+        canopy::requantise(plan->low, p, n_basic);
+        canopy::refresh_thresholds(plan);
     });
 }
 

@@ -1061,4 +1061,16 @@ void mc_sample_words(canopy_plan* plan, const canopy_mc_opts& o, uint64_t first_
     CUDA_CHECK(e);
 }
 
+void refresh_thresholds(canopy_plan* plan) {
+    const Lowered& L = plan->low;
+    for (DeviceState* s : plan->dev) {
+        std::lock_guard<std::mutex> run_lock(s->run_mu);  // never under a run that is reading the old thresholds
+        CUDA_CHECK(cudaSetDevice(s->device));
+        if (!L.event_thr32.empty()) {
+            CUDA_CHECK(cudaMemcpy(s->thr32, L.event_thr32.data(), L.event_thr32.size() * 4, cudaMemcpyHostToDevice));
+            CUDA_CHECK(cudaMemcpy(s->thr64, L.event_thr64.data(), L.event_thr64.size() * 8, cudaMemcpyHostToDevice));
+        }
+    }
+}
+
 }  // namespace canopy

@@ -161,13 +161,15 @@ void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lower
     // ---- basic events: quantise (DESIGN.md SPEC v1 "Threshold quantisation") --------------------
     std::vector<Ref> ev_ref(B);
     std::vector<uint64_t> thr(B, 0);
+    L.event_class.assign(B, 0);
     for (uint32_t e = 0; e < B; ++e) {
         const double p = d.p[e];
         if (p <= 0.0) { ev_ref[e] = make_const(false); continue; }
-        if (p >= 1.0) { ev_ref[e] = make_const(true); continue; }
+        if (p >= 1.0) { ev_ref[e] = make_const(true); L.event_class[e] = 1; continue; }
         thr[e] = wide ? (uint64_t)(p * 18446744073709551616.0) : (uint64_t)(p * 4294967296.0);
         if (thr[e] == 0) { ev_ref[e] = make_const(false); continue; }  // u < 0 never holds
         ev_ref[e] = Ref{e, kEvent, 0};
+        L.event_class[e] = 2;
     }
 
     // ---- resolve gates in children-first order --------------------------------------------------
@@ -412,6 +414,52 @@ void shard_range(uint64_t begin, uint64_t n, int rank, int world, uint64_t* ob, 
     };
     const uint64_t b = cut(rank), e = cut(rank + 1);
     *ob = b; *on = e - b;
+}
+
+void requantise(Lowered& L, const double* p, uint32_t n_basic) {
+    if (n_basic != L.event_class.size()) throw Error(CANOPY_E_INVALID, "canopy_plan_update_p: n_basic does not match the plan");
+    const bool wide = L.opts.threshold_bits == 64;
+    std::vector<uint64_t> thr(n_basic, 0);
+    for (uint32_t e = 0; e < n_basic; ++e) {
+        const double x = p[e];
+        if (!(x >= 0.0 && x <= 1.0)) throw Error(CANOPY_E_DOMAIN, "probability of basic event " + std::to_string(e) + " is outside [0,1]");
+        uint8_t cls = 2;
+        if (x <= 0.0) cls = 0;
+        else if (x >= 1.0) cls = 1;
+        else {
+            thr[e] = wide ? (uint64_t)(x * 18446744073709551616.0) : (uint64_t)(x * 4294967296.0);
+            if (thr[e] == 0) cls = 0;
+        }
+        if (cls != L.event_class[e])
+            throw Error(CANOPY_E_INVALID, "canopy_plan_update_p: basic event " + std::to_string(e) +
+                                              " changes between constant and sampled; lower the graph again");
+    }
+    for (size_t i = 0; i < L.event_orig.size(); ++i) {
+        const uint64_t t = thr[L.event_orig[i]];
+        L.event_thr32[i] = wide ? (uint32_t)(t >> 32) : (uint32_t)t;
+        L.event_thr64[i] = wide ? t : (t << 32);
+    }
+}
+
+uint64_t fingerprint(const Lowered& L) {
+    uint64_t h = 0xcbf29ce484222325ull;
+    auto mix = [&](const void* data, size_t n) {
+        const unsigned char* b = static_cast<const unsigned char*>(data);
+        for (size_t i = 0; i < n; ++i) { h ^= b[i]; h *= 0x100000001b3ull; }
+        const uint64_t len = n;  // length-delimited so adjacent arrays cannot trade bytes
+        for (int i = 0; i < 8; ++i) { h ^= (len >> (8 * i)) & 0xFF; h *= 0x100000001b3ull; }
+    };
+    const int32_t o[3] = {L.opts.tally_all_gates, L.opts.threshold_bits, L.opts.sampler};
+    mix(o, sizeof o);
+    mix(L.event_orig.data(), L.event_orig.size() * 4);
+    mix(L.event_thr32.data(), L.event_thr32.size() * 4);
+    mix(L.event_thr64.data(), L.event_thr64.size() * 8);
+    mix(L.gate_rec.data(), L.gate_rec.size() * sizeof(GateRec));
+    mix(L.child.data(), L.child.size() * 4);
+    mix(L.layer_off.data(), L.layer_off.size() * 4);
+    mix(L.tally_kind.data(), L.tally_kind.size());
+    mix(L.tally_gate.data(), L.tally_gate.size() * 4);
+    return h;
 }
 
 }  // namespace canopy

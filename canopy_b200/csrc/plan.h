@@ -51,6 +51,7 @@ struct Lowered {
     std::vector<uint32_t> event_orig;
     std::vector<uint32_t> event_thr32;
     std::vector<uint64_t> event_thr64;
+    std::vector<uint8_t> event_class;      // [n_basic_in] how lowering classed each ORIGINAL event: 0 false, 1 true, 2 sampled/dead
     // live gates in layer order; device node id == n_events + position
     std::vector<GateRec> gate_rec;
     std::vector<uint32_t> gate_child_off;  // [n_gates+1] (same offsets as GateRec, kept for the view)
@@ -71,6 +72,10 @@ struct Lowered {
 };
 
 void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lowered& out);
+// Re-quantise the thresholds of the live events from new probabilities (canopy_plan_update_p); throws if the
+// constant folding of the existing lowering would no longer hold.
+void requantise(Lowered& L, const double* p, uint32_t n_basic);
+uint64_t fingerprint(const Lowered& L);
 
 struct DeviceState;  // engine.cu
 void destroy_device_state(DeviceState*);
@@ -92,5 +97,6 @@ void mc_sample_words(canopy_plan* plan, const canopy_mc_opts& o, uint64_t first_
 void mc_run_multi(canopy_plan* plan, const canopy_mc_opts& o, const int32_t* devices, int32_t n_devices,
                   uint64_t* tallies_host, canopy_mc_report* rep);
 void microbench_int(int device, int kind, double* lane_ops_per_s, double* ms);
+void refresh_thresholds(canopy_plan* plan);  // re-upload thr32/thr64 to every device the plan is resident on
 void shard_range(uint64_t begin, uint64_t n, int rank, int world, uint64_t* ob, uint64_t* on);
 }  // namespace canopy

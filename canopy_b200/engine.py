@@ -166,6 +166,18 @@ class Plan:
                                                   out.ctypes.data_as(C.POINTER(C.c_uint64)), C.byref(rep)))
         return out[: self.n_tallies], _report(rep)
 
+    def fingerprint(self) -> int:
+        """64-bit hash of the lowered graph, thresholds and options (canopy_plan_fingerprint)."""
+        out = C.c_uint64()
+        _lib.check(_lib.lib().canopy_plan_fingerprint(self._h, C.byref(out)))
+        return int(out.value)
+
+    def update_p(self, p) -> None:
+        """New basic-event probabilities for the same lowered graph (parameter-uncertainty outer loop,
+        SURVEY.md 8f-4): thresholds are re-quantised and re-uploaded; raises if the constant folding changes."""
+        p = np.ascontiguousarray(p, dtype=np.float64)
+        _lib.check(_lib.lib().canopy_plan_update_p(self._h, p.ctypes.data_as(C.POINTER(C.c_double)), p.shape[0]))
+
     def sample_words(self, seed: int, first_word: int, n_words: int, device: int = 0) -> np.ndarray:
         """Raw sampler output [n_events_live, n_words] (parity hook)."""
         o = self._opts(seed, 0, 0, device, 0, None, False, False)
@@ -174,6 +186,66 @@ class Plan:
         _lib.check(_lib.lib().canopy_mc_sample_words(self._h, C.byref(o), first_word, n_words,
                                                      out.ctypes.data_as(C.POINTER(C.c_uint64))))
         return out[:n_ev]
+
+
+class Session:
+    """A restartable run: state = (seed, next sample index, tallies).  `advance(n)` evaluates the
+    next n samples and accumulates; `save`/`load` round-trip the record through an .npz file.  Any chunking gives
+    the tallies of one run over the same range (tests/test_gpu_properties.py)."""
+
+    def __init__(self, plan: Plan, seed: int = 0, sample_begin: int = 0):
+        self.plan = plan
+        self.ck = _lib.CCheckpoint()
+        _lib.check(_lib.lib().canopy_checkpoint_init(plan._h, int(seed), int(sample_begin), C.byref(self.ck)))
+        self.tallies = np.zeros(max(plan.n_tallies, 1), dtype=np.uint64)
+
+    @property
+    def n_done(self) -> int:
+        return int(self.ck.next_sample - self.ck.sample_begin)
+
+    def advance(self, n_samples: int, device: int = 0, batch_slabs: int = 0, overlap: bool = True):
+        o = self.plan._opts(0, 0, n_samples, device, batch_slabs, None, overlap, False)
+        rep = _lib.CMcReport()
+        _lib.check(_lib.lib().canopy_mc_run_resume(self.plan._h, C.byref(o), C.byref(self.ck),
+                                                   self.tallies.ctypes.data_as(C.POINTER(C.c_uint64)), C.byref(rep)))
+        return _report(rep)
+
+    def estimates(self):
+        """[(p_hat, sigma, ci_lo, ci_hi)] per output over the samples done so far."""
+        return [estimate(int(t), self.n_done) for t in self.tallies[: self.plan.n_tallies]]
+
+    def save(self, path: str) -> None:
+        rec = np.array([getattr(self.ck, f) for f, _ in _lib.CCheckpoint._fields_], dtype=np.uint64)
+        np.savez(path, record=rec, tallies=self.tallies)
+
+    @classmethod
+    def load(cls, path: str, plan: Plan) -> "Session":
+        z = np.load(path)
+        s = cls.__new__(cls)
+        s.plan = plan
+        s.ck = _lib.CCheckpoint(*[int(x) for x in z["record"]])
+        s.tallies = np.ascontiguousarray(z["tallies"], dtype=np.uint64).copy()
+        if s.tallies.shape[0] != max(plan.n_tallies, 1):
+            raise _lib.CanopyError(_lib.E_INVALID, "checkpoint has another number of tallies than the plan")
+        return s
+
+
+def uncertainty(graph: Graph, settings: Settings, sample_p, n_outer: int, device: int = 0):
+    """Parameter-uncertainty outer loop (SURVEY.md 8f-4; reference Settings::uncertainty_analysis, settings.h:281-295):
+    for each epistemic trial k draw basic-event probabilities with `sample_p(k) -> float64[n_basic]`, re-quantise the
+    thresholds of ONE lowered plan (canopy_plan_update_p) and rerun the inner Monte Carlo on a disjoint counter
+    range.  Returns dict(p=[n_outer, n_tallies], mean, std, quantiles 5/50/95 per output)."""
+    settings.validate()
+    out = []
+    with Plan(graph, settings.tally_all_gates, settings.threshold_bits, settings.sampler) as plan:
+        for k in range(n_outer):
+            plan.update_p(sample_p(k))
+            t, _ = plan.run(settings.num_trials, settings.seed, settings.sample_begin + k * settings.num_trials, device,
+                            settings.batch_size, overlap=settings.overlap)
+            out.append(t.astype(np.float64) / settings.num_trials)
+    p = np.stack(out)
+    return dict(p=p, mean=p.mean(axis=0), std=p.std(axis=0, ddof=1) if n_outer > 1 else np.zeros(p.shape[1]),
+                q05=np.quantile(p, 0.05, axis=0), q50=np.quantile(p, 0.5, axis=0), q95=np.quantile(p, 0.95, axis=0))
 
 
 def quantify(graph: Graph, settings: Settings, device: int = 0):

@@ -153,10 +153,44 @@ class Plan {
         return r;
     }
 
+    /// New basic-event probabilities on the same lowered graph (uncertainty outer loop; canopy_plan_update_p).
+    void update_p(const std::vector<double>& p) { check(canopy_plan_update_p(plan_.get(), p.data(), (std::uint32_t)p.size())); }
+    std::uint64_t fingerprint() const {
+        std::uint64_t f = 0;
+        check(canopy_plan_fingerprint(plan_.get(), &f));
+        return f;
+    }
+
   private:
     struct Deleter { void operator()(canopy_plan* p) const noexcept { canopy_plan_destroy(p); } };
     std::unique_ptr<canopy_plan, Deleter> plan_;
     canopy_plan_stats stats_{};
+};
+
+/// Restartable run: (seed, next sample index, tallies) -- canopy_checkpoint + canopy_mc_run_resume.
+/// `record` and `tallies` are plain data and may be written to disk between calls.
+class Session {
+  public:
+    Session(const Plan& plan, std::uint64_t seed, std::uint64_t sample_begin = 0) : plan_(&plan), tallies(plan.stats().n_tallies, 0) {
+        check(canopy_checkpoint_init(plan.get(), seed, sample_begin, &record));
+    }
+    Session(const Plan& plan, const canopy_checkpoint& rec, std::vector<std::uint64_t> t) : plan_(&plan), record(rec), tallies(std::move(t)) {}
+    std::uint64_t done() const noexcept { return record.next_sample - record.sample_begin; }
+    canopy_mc_report advance(std::uint64_t n_samples, int device = 0) {
+        canopy_mc_opts o;
+        canopy_mc_opts_default(&o);
+        o.n_samples = n_samples; o.device = device;
+        canopy_mc_report rep{};
+        check(canopy_mc_run_resume(plan_->get(), &o, &record, tallies.data(), &rep));
+        return rep;
+    }
+
+  private:
+    const Plan* plan_;
+
+  public:
+    canopy_checkpoint record{};
+    std::vector<std::uint64_t> tallies;
 };
 
 inline Result quantify(const canopy_graph_desc& d, const McSettings& s) {

@@ -219,6 +219,36 @@ CANOPY_API canopy_status canopy_mc_run_multi(canopy_plan* plan, const canopy_mc_
                                              const int32_t* devices, int32_t n_devices,
                                              uint64_t* tallies_host, canopy_mc_report* report);
 
+/* Restart record (SURVEY.md 8f-3, 5 "checkpoint / resume"): with a counter-based generator the whole state of a
+ * run is (seed, next sample index, tallies).  The caller keeps `canopy_checkpoint` + the uint64 tally array (plain
+ * data, safe to write to disk); canopy_mc_run_resume() evaluates the NEXT opts->n_samples samples, adds their
+ * tallies into `tallies_host_accum` and advances the record.  opts->seed / opts->sample_begin are ignored (the
+ * record holds them).  Tallies accumulated in any chunking equal a single run over the same range. */
+#define CANOPY_CHECKPOINT_MAGIC 0x59504E43u  /* "CNPY" */
+typedef struct canopy_checkpoint {
+    uint32_t magic;
+    uint32_t spec_version;      /* sampling spec of the plan                                      */
+    uint32_t threshold_bits;
+    uint32_t n_tallies;
+    uint64_t plan_fingerprint;  /* canopy_plan_fingerprint() of the plan the tallies belong to    */
+    uint64_t seed;
+    uint64_t sample_begin;      /* tallies cover samples [sample_begin, next_sample)              */
+    uint64_t next_sample;
+} canopy_checkpoint;
+/* 64-bit FNV-1a over the lowered arrays, thresholds and plan options: equal for equal (graph, options). */
+CANOPY_API canopy_status canopy_plan_fingerprint(const canopy_plan* plan, uint64_t* out);
+CANOPY_API canopy_status canopy_checkpoint_init(const canopy_plan* plan, uint64_t seed, uint64_t sample_begin,
+                                                canopy_checkpoint* out);
+CANOPY_API canopy_status canopy_mc_run_resume(canopy_plan* plan, const canopy_mc_opts* opts, canopy_checkpoint* ck,
+                                              uint64_t* tallies_host_accum, canopy_mc_report* report);
+
+/* Parameter-uncertainty outer loop: replace the basic-event probabilities of an existing plan
+ * (same graph, same lowering) and re-quantise the thresholds; the next run uses them.  p[n_basic] in descriptor
+ * order.  The constant folding done at lowering must stay valid: an event that was folded to a constant
+ * (p <= 0, p >= 1, or a threshold of 0) must fold to the same constant, and a sampled event must stay sampled;
+ * otherwise CANOPY_E_INVALID (create a new plan).  Changes canopy_plan_fingerprint(). */
+CANOPY_API canopy_status canopy_plan_update_p(canopy_plan* plan, const double* p, uint32_t n_basic);
+
 /* Parity hook: run only the sampler kernel and return the packed words of the live basic events,
  * words_host[e * n_words + w], e in canopy_plan_view.event_orig order, w = global word index
  * first_word .. first_word+n_words-1 (sample s is bit s&63 of word s>>6). */

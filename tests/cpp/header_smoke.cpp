@@ -10,5 +10,9 @@ int main() {
     try { canopy::McSettings s; s.num_trials = 1000; plan.run(s); } catch (const canopy::Error& e) { std::printf("run: status %d (%s)\n", e.status(), e.what()); }
     try { canopy::GraphBuilder c; auto x = c.basic_event(0.5); c.root(c.gate(canopy::kAnd, {{x}})); canopy::Plan p(c.desc()); }
     catch (const canopy::Error& e) { std::printf("validity: status %d\n", e.status()); }
+    canopy::Session sess(plan, 7, 4096);
+    std::printf("session: fingerprint %d done=%llu tallies=%zu\n", sess.record.plan_fingerprint == plan.fingerprint(),
+                (unsigned long long)sess.done(), sess.tallies.size());
+    try { plan.update_p({0.1, 0.2, 1.0}); } catch (const canopy::Error& e) { std::printf("update_p: status %d\n", e.status()); }
     return 0;
 }

@@ -17,6 +17,8 @@ def test_cpp_header_smoke(tmp_path):
     out = subprocess.check_output([exe], text=True)
     assert "layers=1 gates=1 tallies=2" in out
     assert "validity: status 2" in out
+    assert "session: fingerprint 1 done=0 tallies=2" in out
+    assert "update_p: status 1" in out      # an event cannot turn constant without a new lowering
     if not torch.cuda.is_available():
         assert "run: status 5" in out and "no CPU fallback" in out
 

@@ -124,3 +124,38 @@ def test_bad_run_arguments():
             plan.run(1 << 20, sample_begin=(1 << 64) - 10)
         with pytest.raises(_lib.CanopyError):
             plan.sample_words(1, 3, 64)
+
+
+@pytest.mark.gpu
+def test_session_chunks_equal_one_run_and_resume_from_disk(tmp_path):
+    from canopy_b200.engine import Session
+    g = synth.generate(n_basic=400, n_gates=250, n_layers=7, max_fanin=9, seed=21)
+    with Plan(g, tally_all_gates=True) as plan:
+        whole, _ = plan.run(3 * 4096 + 1000, seed=5, sample_begin=100)
+        s = Session(plan, seed=5, sample_begin=100)
+        s.advance(777)
+        s.advance(4096)
+        f = str(tmp_path / "ck.npz")
+        s.save(f)
+        r = Session.load(f, plan)                      # "restart": a fresh record from disk
+        r.advance(3 * 4096 + 1000 - 777 - 4096)
+        assert r.n_done == 3 * 4096 + 1000 and np.array_equal(r.tallies[: plan.n_tallies], whole)
+        e = r.estimates()[0]
+        assert e[0] == int(whole[0]) / r.n_done and e[2] <= e[0] <= e[3]
+
+
+@pytest.mark.gpu
+def test_update_p_equals_a_fresh_plan_and_uncertainty_loop():
+    from canopy_b200.engine import Settings, uncertainty
+    g = synth.generate(n_basic=300, n_gates=200, n_layers=6, max_fanin=8, seed=22)
+    rng = np.random.default_rng(0)
+    with Plan(g, tally_all_gates=True) as plan:
+        plan.run(4096, seed=1)                          # make the plan resident before the update
+        for k in range(3):
+            p = np.clip(g.p * rng.lognormal(0.0, 0.5, g.n_basic), 1e-6, 0.9)
+            plan.update_p(p)
+            got, _ = plan.run(2 * 4096 + 99, seed=9, sample_begin=k * 10000)
+            g2 = G.Graph(p=p, op=g.op, kmin=g.kmin, kmax=g.kmax, child_off=g.child_off, child=g.child, roots=g.roots)
+            assert np.array_equal(got, O.mc_scalar(g2, 9, k * 10000, 2 * 4096 + 99, True, spec=plan.spec))
+    u = uncertainty(g, Settings(num_trials=8192, seed=3), lambda k: np.clip(g.p * (1 + 0.1 * k), 0, 0.9), n_outer=4)
+    assert u["p"].shape == (4, len(g.roots)) and np.all(np.diff(u["p"][:, 0]) >= -0.05) and u["q05"][0] <= u["q95"][0]
