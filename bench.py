@@ -81,8 +81,27 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def ncu_traffic(workload_name: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE gate_ring_kernel launch (592 slabs) from the committed
+    `ncu --set full` capture of this workload under profiles/, in bytes; None if there is no capture for it."""
+    import csv
+    path = os.path.join(ROOT, "profiles", f"r01b_ncu_full_gate_{workload_name}.csv")
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+    try:
+        tot = 0.0
+        for row in csv.reader(open(path)):
+            if len(row) == 3 and row[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                tot += float(row[2]) * scale[row[1]]
+        return tot or None
+    except Exception:
+        return None
+
+
 def workload(name: str):
     from canopy_b200 import synth
+    if name == "c1":  # the hand-authored MEF example (the reference ships none), through the library's MEF reader
+        from canopy_b200.engine import load_mef
+        return load_mef(os.path.join(ROOT, "examples", "c1_small_ft.xml")), 1 << 20
     g = synth.config_graph(name)
     return g, synth.CONFIGS[name]["n_samples"]
 
@@ -134,7 +153,7 @@ def run_reference(args):
 
 
 def config_block(name, g, stats, S, n_step=None):
-    return {"workload": f"{name}: synthetic fault tree B={g.n_basic} G={g.n_gates} (after DCE: B={stats['n_basic_live']} "
+    return {"workload": f"{name}: {'MEF example examples/c1_small_ft.xml' if name == 'c1' else 'synthetic fault tree'} B={g.n_basic} G={g.n_gates} (after DCE: B={stats['n_basic_live']} "
                         f"G={stats['n_gates_live']} E={stats['n_edges_live']} G'={stats['n_gates_stored']} layers={stats['n_layers']} "
                         f"max_fanin={stats['max_fanin']} mean_fanin={stats['mean_fanin']:.2f}), {S} samples/step/GPU"
                         + (f" (this arm: {n_step} samples/step)" if n_step else ""),
@@ -150,7 +169,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="canopy_b200")
-    ap.add_argument("--workload", default="c2", choices=["c2", "c3", "c4"])
+    ap.add_argument("--workload", default="c2", choices=["c1", "c2", "c3", "c4"])
     ap.add_argument("--no-study", action="store_true", help="skip the bounded c4 roofline study on rank 0")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
@@ -280,7 +299,9 @@ def main():
                     "what": "canopy_plan_create from host arrays + upload + run + allreduce + tallies to host, wall clock"},
             "gpu_launches": int(launches_per_step * args.steps),
             "roofline": {"kernel": "gate_ring_kernel", "bound": "hbm", "achieved": gate_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                         "frac": gate_gbs / peaks["hbm_gbs"], "traffic": None, "peak_source": peaks_src,
+                         "frac": gate_gbs / peaks["hbm_gbs"], "traffic": ncu_traffic(args.workload),
+                         "traffic_note": "DRAM read+write bytes of one full launch (592 slabs) from the committed ncu --set full capture in profiles/",
+                         "alg_bytes_per_full_launch": alg_bytes_per_sample * 592 * 4096, "peak_source": peaks_src,
                          "alg_bytes_per_sample": alg_bytes_per_sample, "avg_launch_ms": gate_launch_ms,
                          "share_of_step": prof.gate_ms / max(prof.total_ms, 1e-9), "timed": "profile pass, kernels serialised"},
             "roofline_sampler": {"kernel": "sampler_sliced_kernel<32>" if sliced else "sampler_kernel<32,1>",
