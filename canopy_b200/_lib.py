@@ -87,6 +87,7 @@ SYMBOLS = {
     "canopy_mc_run": (C.c_int, [C.c_void_p, C.POINTER(CMcOpts), _u64p, C.POINTER(CMcReport)]),
     "canopy_mc_run_device": (C.c_int, [C.c_void_p, C.POINTER(CMcOpts), C.c_void_p, C.POINTER(CMcReport)]),
     "canopy_mc_run_multi": (C.c_int, [C.c_void_p, C.POINTER(CMcOpts), C.POINTER(C.c_int32), C.c_int32, _u64p, C.POINTER(CMcReport)]),
+    "canopy_trim_device_cache": (C.c_int, [C.c_int32]),
     "canopy_plan_fingerprint": (C.c_int, [C.c_void_p, _u64p]),
     "canopy_checkpoint_init": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(CCheckpoint)]),
     "canopy_mc_run_resume": (C.c_int, [C.c_void_p, C.POINTER(CMcOpts), C.POINTER(CCheckpoint), _u64p, C.POINTER(CMcReport)]),

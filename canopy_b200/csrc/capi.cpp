@@ -113,6 +113,10 @@ canopy_status canopy_mc_run_multi(canopy_plan* plan, const canopy_mc_opts* opts,
     });
 }
 
+canopy_status canopy_trim_device_cache(int32_t device) {
+    return guard([&] { canopy::trim_device_cache(device); });
+}
+
 canopy_status canopy_plan_fingerprint(const canopy_plan* plan, uint64_t* out) {
     return guard([&] {
         require(plan && out, "canopy_plan_fingerprint: null argument");

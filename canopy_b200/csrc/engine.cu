@@ -777,8 +777,9 @@ struct DeviceState {
     uint8_t* tally_kind = nullptr;
     unsigned long long* gate_tallies = nullptr;
     unsigned long long* out_tallies = nullptr;   // used when the caller wants host output
-    unsigned long long* host_tallies = nullptr;  // pinned staging
+    void* arena = nullptr;                       // one allocation holding every plan array above
     uint4* vals[2] = {nullptr, nullptr};
+    size_t vals_bytes[2] = {0, 0};  // capacity of each value buffer
     size_t vals_slabs = 0;  // capacity of each buffer in slabs
     int n_bufs = 0;
     cudaStream_t main = nullptr, s_sample = nullptr, s_gate = nullptr;
@@ -788,13 +789,84 @@ struct DeviceState {
     std::mutex run_mu;  // one run at a time per device (the value buffers and streams are per-device scratch)
 };
 
+// ------------------------------------------------------------------------------------------------
+// Value-buffer pool.  A value buffer is GBs (c2: 4 GB, c4: 48 GB per buffer); cudaMalloc + cudaFree of that size
+// cost tens of milliseconds, which a one-shot quantification (plan -> run -> destroy) or an uncertainty loop that
+// lowers a new plan per trial would pay every time.  Buffers of destroyed plans are parked here, per device, and
+// handed to the next plan that fits; canopy_trim_device_cache() returns them to the driver.
+// ------------------------------------------------------------------------------------------------
+struct ValPool {
+    struct Entry { int device; void* ptr; size_t bytes; };
+    std::mutex mu;
+    std::vector<Entry> parked;
+    static constexpr size_t kMaxParkedPerDevice = 2;
+
+    void* acquire(int device, size_t bytes, size_t* got) {
+        {
+            std::lock_guard<std::mutex> lock(mu);
+            int best = -1;
+            for (size_t i = 0; i < parked.size(); ++i)
+                if (parked[i].device == device && parked[i].bytes >= bytes && (best < 0 || parked[i].bytes < parked[best].bytes)) best = (int)i;
+            if (best >= 0) {
+                Entry e = parked[best];
+                parked.erase(parked.begin() + best);
+                *got = e.bytes;
+                return e.ptr;
+            }
+        }
+        void* p = nullptr;
+        if (cudaMalloc(&p, bytes) != cudaSuccess) {
+            cudaGetLastError();
+            trim(device);  // parked buffers that were too small still hold memory: give it back and retry once
+            if (cudaMalloc(&p, bytes) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        }
+        *got = bytes;
+        return p;
+    }
+    void release(int device, void* ptr, size_t bytes) {
+        if (!ptr) return;
+        std::lock_guard<std::mutex> lock(mu);
+        parked.push_back({device, ptr, bytes});
+        size_t n = 0;
+        for (auto& e : parked) n += e.device == device;
+        while (n > kMaxParkedPerDevice) {  // evict the smallest buffer of this device
+            int worst = -1;
+            for (size_t i = 0; i < parked.size(); ++i)
+                if (parked[i].device == device && (worst < 0 || parked[i].bytes < parked[worst].bytes)) worst = (int)i;
+            cudaFree(parked[worst].ptr);
+            parked.erase(parked.begin() + worst);
+            --n;
+        }
+    }
+    size_t parked_bytes(int device) {
+        std::lock_guard<std::mutex> lock(mu);
+        size_t b = 0;
+        for (auto& e : parked) if (e.device == device) b += e.bytes;
+        return b;
+    }
+    void trim(int device) {  // device < 0: every device
+        std::lock_guard<std::mutex> lock(mu);
+        int cur = -1; cudaGetDevice(&cur);
+        for (size_t i = 0; i < parked.size();) {
+            if (device < 0 || parked[i].device == device) {
+                cudaSetDevice(parked[i].device);
+                cudaFree(parked[i].ptr);
+                parked.erase(parked.begin() + i);
+            } else ++i;
+        }
+        if (cur >= 0) cudaSetDevice(cur);
+    }
+};
+static ValPool g_val_pool;
+
+void trim_device_cache(int device) { g_val_pool.trim(device); }
+
 void destroy_device_state(DeviceState* s) {
     if (!s) return;
     cudaSetDevice(s->device);
-    cudaFree(s->ev_orig); cudaFree(s->thr32); cudaFree(s->thr64); cudaFree(s->child); cudaFree(s->layer_off);
-    cudaFree(s->wide_off); cudaFree(s->split); cudaFree(s->split_child);
-    cudaFree(s->tally_gate); cudaFree(s->grec); cudaFree(s->tally_kind); cudaFree(s->gate_tallies);
-    cudaFree(s->out_tallies); cudaFreeHost(s->host_tallies); cudaFree(s->vals[0]); cudaFree(s->vals[1]);
+    cudaDeviceSynchronize();  // nothing of this plan (on its own or on a caller's stream) may still run on a parked buffer
+    cudaFree(s->arena);
+    for (int b = 0; b < 2; ++b) g_val_pool.release(s->device, s->vals[b], s->vals_bytes[b]);
     if (s->main) cudaStreamDestroy(s->main);
     if (s->s_sample) cudaStreamDestroy(s->s_sample);
     if (s->s_gate) cudaStreamDestroy(s->s_gate);
@@ -804,15 +876,25 @@ void destroy_device_state(DeviceState* s) {
     delete s;
 }
 
-template <class T>
-static T* upload(const std::vector<T>& v, uint64_t& bytes) {
-    T* d = nullptr;
-    const size_t n = std::max<size_t>(v.size(), 1) * sizeof(T);
-    if (cudaMalloc(&d, n) != cudaSuccess) throw Error(CANOPY_E_OOM, "cudaMalloc failed for plan arrays");
-    if (!v.empty()) CUDA_CHECK(cudaMemcpy(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
-    bytes += v.size() * sizeof(T);
-    return d;
-}
+// Plan arrays go into ONE device allocation (256-byte aligned pieces): a dozen cudaMalloc calls cost more than the
+// upload itself for the graphs of this path (c2: 0.3 MB, c4: 3.4 MB).
+struct ArenaPlan {
+    struct Piece { void** dst; const void* src; size_t bytes, off; };
+    std::vector<Piece> pieces;
+    size_t total = 0;
+    template <class P, class T>
+    void add(P*& dst, const std::vector<T>& v, size_t min_elems = 1) {
+        const size_t bytes = std::max(v.size(), min_elems) * sizeof(T);
+        pieces.push_back({reinterpret_cast<void**>(&dst), v.empty() ? nullptr : v.data(), bytes, total});
+        pieces.back().bytes = v.size() * sizeof(T);  // bytes to copy; the reservation below may be larger
+        total += (bytes + 255) & ~size_t(255);
+    }
+    template <class P>
+    void reserve(P*& dst, size_t bytes) {
+        pieces.push_back({reinterpret_cast<void**>(&dst), nullptr, 0, total});
+        total += (std::max<size_t>(bytes, 8) + 255) & ~size_t(255);
+    }
+};
 
 static DeviceState* get_state(canopy_plan* plan, int device) {
     for (DeviceState* s : plan->dev) if (s->device == device) { CUDA_CHECK(cudaSetDevice(device)); return s; }
@@ -829,27 +911,25 @@ static DeviceState* get_state(canopy_plan* plan, int device) {
     DeviceState* s = new DeviceState();
     s->device = device; s->sm_count = prop.multiProcessorCount;
     try {
-        s->ev_orig = upload(L.event_orig, s->h2d_bytes);
-        s->thr32 = upload(L.event_thr32, s->h2d_bytes);
-        s->thr64 = upload(L.event_thr64, s->h2d_bytes);
-        s->child = upload(L.child, s->h2d_bytes);
-        s->layer_off = upload(L.layer_off.empty() ? std::vector<uint32_t>{0} : L.layer_off, s->h2d_bytes);
-        s->tally_gate = upload(L.tally_gate, s->h2d_bytes);
-        s->wide_off = upload(L.wide_off, s->h2d_bytes);
-        s->split = upload(L.split, s->h2d_bytes);
-        s->split_child = upload(L.split_child, s->h2d_bytes);
+        static_assert(sizeof(GateRec) == sizeof(uint4), "GateRec must be 16 bytes");
+        ArenaPlan A;
+        A.add(s->ev_orig, L.event_orig); A.add(s->thr32, L.event_thr32); A.add(s->thr64, L.event_thr64);
+        A.add(s->child, L.child); A.add(s->layer_off, L.layer_off); A.add(s->tally_gate, L.tally_gate);
+        A.add(s->wide_off, L.wide_off); A.add(s->split, L.split); A.add(s->split_child, L.split_child);
+        A.add(s->tally_kind, L.tally_kind); A.add(s->grec, L.gate_rec);
+        A.reserve(s->gate_tallies, std::max<size_t>(L.n_gates(), 1) * 8);
+        A.reserve(s->out_tallies, std::max<size_t>(L.tally_kind.size(), 1) * 8);
+        if (cudaMalloc(&s->arena, A.total) != cudaSuccess) { cudaGetLastError(); throw Error(CANOPY_E_OOM, "cudaMalloc failed for plan arrays"); }
+        for (auto& p : A.pieces) {
+            *p.dst = static_cast<char*>(s->arena) + p.off;
+            if (p.bytes) CUDA_CHECK(cudaMemcpy(*p.dst, p.src, p.bytes, cudaMemcpyHostToDevice));
+            s->h2d_bytes += p.bytes;
+        }
         CUDA_CHECK(cudaFuncSetAttribute(gate_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmemBytes));
         CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->ring_ctas_per_sm, gate_ring_kernel, kGateThreads, kRingSmemBytes));
         if (s->ring_ctas_per_sm < 1) throw Error(CANOPY_E_CUDA, "gate_ring_kernel does not fit on an SM");
-        s->tally_kind = upload(L.tally_kind, s->h2d_bytes);
-        static_assert(sizeof(GateRec) == sizeof(uint4), "GateRec must be 16 bytes");
-        s->grec = reinterpret_cast<uint4*>(upload(L.gate_rec, s->h2d_bytes));
-        const size_t ng = std::max<size_t>(L.n_gates(), 1), nt = std::max<size_t>(L.tally_kind.size(), 1);
-        CUDA_CHECK(cudaMalloc(&s->gate_tallies, ng * 8));
-        CUDA_CHECK(cudaMalloc(&s->out_tallies, nt * 8));
-        CUDA_CHECK(cudaMallocHost(&s->host_tallies, nt * 8));
         CUDA_CHECK(cudaStreamCreateWithFlags(&s->main, cudaStreamNonBlocking));
         CUDA_CHECK(cudaStreamCreateWithFlags(&s->s_sample, cudaStreamNonBlocking));
         {   // the gate walk of batch b competes with the sampler of batch b+1 for SM slots: its (few, persistent)
@@ -867,15 +947,17 @@ static DeviceState* get_state(canopy_plan* plan, int device) {
 }
 
 static void ensure_vals(DeviceState* s, const Lowered& L, size_t slabs, int n_bufs) {
-    if (s->vals_slabs >= slabs && s->n_bufs >= n_bufs) return;
-    for (int b = 0; b < 2; ++b) { cudaFree(s->vals[b]); s->vals[b] = nullptr; }
+    const size_t per_slab = (size_t)L.n_nodes() * kRowBytes;
+    const size_t bytes = std::max<size_t>(slabs * per_slab, 16);
+    bool ok = s->n_bufs >= n_bufs;
+    for (int b = 0; ok && b < n_bufs; ++b) ok = s->vals_bytes[b] >= bytes;
+    if (ok) { s->vals_slabs = std::max(s->vals_slabs, slabs); return; }
+    for (int b = 0; b < 2; ++b) { g_val_pool.release(s->device, s->vals[b], s->vals_bytes[b]); s->vals[b] = nullptr; s->vals_bytes[b] = 0; }
     s->vals_slabs = 0; s->n_bufs = 0;
-    const size_t bytes = slabs * (size_t)L.n_nodes() * kRowBytes;
-    for (int b = 0; b < n_bufs; ++b)
-        if (cudaMalloc(&s->vals[b], std::max<size_t>(bytes, 16)) != cudaSuccess) {
-            cudaGetLastError();
-            throw Error(CANOPY_E_OOM, "cudaMalloc failed for the value buffer (" + std::to_string(bytes >> 20) + " MiB)");
-        }
+    for (int b = 0; b < n_bufs; ++b) {
+        s->vals[b] = static_cast<uint4*>(g_val_pool.acquire(s->device, bytes, &s->vals_bytes[b]));
+        if (!s->vals[b]) throw Error(CANOPY_E_OOM, "cudaMalloc failed for the value buffer (" + std::to_string(bytes >> 20) + " MiB)");
+    }
     s->vals_slabs = slabs; s->n_bufs = n_bufs;
 }
 
@@ -940,7 +1022,7 @@ static uint32_t pick_batch_slabs(const DeviceState* s, const Lowered& L, const c
     uint64_t want = o.batch_slabs > 0 ? (uint64_t)o.batch_slabs : (uint64_t)s->sm_count * 4;
     size_t free_b = 0, total_b = 0;
     CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
-    free_b += s->vals_slabs * (size_t)L.n_nodes() * kRowBytes * s->n_bufs;  // what we would release on regrow
+    free_b += s->vals_bytes[0] + s->vals_bytes[1] + g_val_pool.parked_bytes(s->device);  // what a regrow can reuse or release
     const size_t per_slab = (size_t)L.n_nodes() * kRowBytes;
     const uint64_t fit = per_slab ? (uint64_t)((free_b / 2) / (per_slab * n_bufs)) : want;
     if (fit == 0) throw Error(CANOPY_E_OOM, "one slab of node rows does not fit in device memory");
@@ -1019,12 +1101,11 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
     }
     CUDA_CHECK(cudaEventRecord(s->ev_t1, user));
     if (tallies_host && n_tallies) {
-        CUDA_CHECK(cudaMemcpyAsync(s->host_tallies, d_out, (size_t)n_tallies * 8, cudaMemcpyDeviceToHost, user));
+        CUDA_CHECK(cudaMemcpyAsync(tallies_host, d_out, (size_t)n_tallies * 8, cudaMemcpyDeviceToHost, user));
         R.d2h_bytes = (uint64_t)n_tallies * 8;
     }
     if (tallies_host || rep || profile) {
         CUDA_CHECK(cudaStreamSynchronize(user));
-        if (tallies_host && n_tallies) std::memcpy(tallies_host, s->host_tallies, (size_t)n_tallies * 8);
         float ms = 0; CUDA_CHECK(cudaEventElapsedTime(&ms, s->ev_t0, s->ev_t1)); R.total_ms = ms;
         for (size_t i = 0; i + 3 <= pe.size(); i += 3) {
             float a = 0, b2 = 0;

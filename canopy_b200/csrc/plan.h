@@ -97,6 +97,7 @@ void mc_sample_words(canopy_plan* plan, const canopy_mc_opts& o, uint64_t first_
 void mc_run_multi(canopy_plan* plan, const canopy_mc_opts& o, const int32_t* devices, int32_t n_devices,
                   uint64_t* tallies_host, canopy_mc_report* rep);
 void microbench_int(int device, int kind, double* lane_ops_per_s, double* ms);
+void trim_device_cache(int device);           // free the value buffers parked by destroyed plans (-1: all devices)
 void refresh_thresholds(canopy_plan* plan);  // re-upload thr32/thr64 to every device the plan is resident on
 void shard_range(uint64_t begin, uint64_t n, int rank, int world, uint64_t* ob, uint64_t* on);
 }  // namespace canopy

@@ -272,6 +272,11 @@ def shard_range(sample_begin: int, n_samples: int, rank: int, world: int):
     return int(b.value), int(n.value)
 
 
+def trim_device_cache(device: int = -1) -> None:
+    """Return the value buffers parked by destroyed plans to the driver (canopy_trim_device_cache)."""
+    _lib.check(_lib.lib().canopy_trim_device_cache(device))
+
+
 def microbench_int(kind: int, device: int = 0):
     ops, ms = C.c_double(), C.c_double()
     _lib.check(_lib.lib().canopy_microbench_int(device, kind, C.byref(ops), C.byref(ms)))

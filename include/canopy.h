@@ -219,6 +219,11 @@ CANOPY_API canopy_status canopy_mc_run_multi(canopy_plan* plan, const canopy_mc_
                                              const int32_t* devices, int32_t n_devices,
                                              uint64_t* tallies_host, canopy_mc_report* report);
 
+/* Value buffers (GBs) of destroyed plans are parked per device and reused by the next plan, so that a one-shot
+ * quantification or a loop that lowers a new plan per trial does not pay cudaMalloc/cudaFree of that size each time
+ * (at most two buffers per device are kept).  This returns them to the driver; device < 0 = every device. */
+CANOPY_API canopy_status canopy_trim_device_cache(int32_t device);
+
 /* Restart record (SURVEY.md 8f-3, 5 "checkpoint / resume"): with a counter-based generator the whole state of a
  * run is (seed, next sample index, tallies).  The caller keeps `canopy_checkpoint` + the uint64 tally array (plain
  * data, safe to write to disk); canopy_mc_run_resume() evaluates the NEXT opts->n_samples samples, adds their

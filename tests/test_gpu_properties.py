@@ -159,3 +159,16 @@ def test_update_p_equals_a_fresh_plan_and_uncertainty_loop():
             assert np.array_equal(got, O.mc_scalar(g2, 9, k * 10000, 2 * 4096 + 99, True, spec=plan.spec))
     u = uncertainty(g, Settings(num_trials=8192, seed=3), lambda k: np.clip(g.p * (1 + 0.1 * k), 0, 0.9), n_outer=4)
     assert u["p"].shape == (4, len(g.roots)) and np.all(np.diff(u["p"][:, 0]) >= -0.05) and u["q05"][0] <= u["q95"][0]
+
+
+@pytest.mark.gpu
+def test_parked_value_buffers_are_reused_correctly():
+    """Buffers of destroyed plans are parked and handed to the next plan (dirty, other graph, other size)."""
+    from canopy_b200.engine import trim_device_cache
+    for seed, nb in ((31, 500), (32, 200), (33, 800), (34, 500)):
+        g = synth.generate(n_basic=nb, n_gates=nb // 2, n_layers=6, max_fanin=7, seed=seed)
+        with Plan(g, tally_all_gates=True) as plan:
+            got, _ = plan.run(5 * 4096 + 17, seed=seed, sample_begin=4096 * seed)
+        assert np.array_equal(got, O.mc_packed(g, seed, 4096 * seed, 5 * 4096 + 17, True, nthreads=CORES, spec=2))
+        if seed == 32:
+            trim_device_cache()

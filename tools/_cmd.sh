@@ -1,4 +1,2 @@
-for tool in memcheck racecheck synccheck initcheck; do
-  timeout 900 compute-sanitizer --tool $tool --error-exitcode 7 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/r01c_sanitizer_$tool.log 2>&1; echo "$tool rc=$?"
-  tail -4 gpurun_out/r01c_sanitizer_$tool.log
-done
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -5
+python tools/quick_e2e.py 2>&1 | tee gpurun_out/e2e2.txt
