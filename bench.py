@@ -171,6 +171,8 @@ def main():
     ap.add_argument("--impl", default="canopy_b200")
     ap.add_argument("--workload", default="c2", choices=["c1", "c2", "c3", "c4"])
     ap.add_argument("--no-study", action="store_true", help="skip the bounded c4 roofline study on rank 0")
+    ap.add_argument("--samples", type=int, default=0,
+                    help="samples per step per GPU instead of the workload's full count (side studies only; the line says so)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
     if args.impl == "reference":
@@ -193,6 +195,8 @@ def main():
     dev = torch.device("cuda", local)
 
     g, S = workload(args.workload)
+    if args.samples:
+        S = args.samples
     tally_all = args.workload == "c3"
     plan = Plan(g, tally_all)
     stats = plan.stats
@@ -323,6 +327,8 @@ def main():
         if not args.no_study and args.workload != "c4":
             line["roofline_study_c4"] = c4_study(local, stream, peaks)
     if rank == 0:
+        if args.samples:
+            line["config"]["reduced"] = f"--samples {args.samples}: side study, NOT the workload's full sample count"
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
