@@ -50,7 +50,7 @@ class ClockSampler:
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200"],
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._pump, daemon=True).start()
         except Exception:
@@ -85,7 +85,7 @@ def ncu_traffic(workload_name: str):
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE gate_ring_kernel launch (592 slabs) from the committed
     `ncu --set full` capture of this workload under profiles/, in bytes; None if there is no capture for it."""
     import csv
-    path = os.path.join(ROOT, "profiles", f"r01b_ncu_full_gate_{workload_name}.csv")
+    path = os.path.join(ROOT, "profiles", f"r01e_ncu_full_gate_{workload_name}.csv")
     scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
     try:
         tot = 0.0
@@ -304,8 +304,9 @@ def main():
             "gpu_launches": int(launches_per_step * args.steps),
             "roofline": {"kernel": "gate_ring_kernel", "bound": "hbm", "achieved": gate_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": gate_gbs / peaks["hbm_gbs"], "traffic": ncu_traffic(args.workload),
-                         "traffic_note": "DRAM read+write bytes of one full launch (592 slabs) from the committed ncu --set full capture in profiles/",
-                         "alg_bytes_per_full_launch": alg_bytes_per_sample * 592 * 4096, "peak_source": peaks_src,
+                         "traffic_note": "DRAM read+write bytes of one full launch (2.42 M samples per launch: 16384 per SM) from the committed ncu --set full capture in profiles/; "
+                                         "frac can read a little above 1: the peak is a 1:1 read:write copy, this kernel's traffic is 4:1 reads",
+                         "alg_bytes_per_full_launch": alg_bytes_per_sample * 592 * 4096, "nominal_hbm_gbs": 7700.0, "frac_of_nominal": gate_gbs / 7700.0, "peak_source": peaks_src,
                          "alg_bytes_per_sample": alg_bytes_per_sample, "avg_launch_ms": gate_launch_ms,
                          "share_of_step": prof.gate_ms / max(prof.total_ms, 1e-9), "timed": "profile pass, kernels serialised"},
             "roofline_sampler": {"kernel": "sampler_sliced_kernel<32>" if sliced else "sampler_kernel<32,1>",

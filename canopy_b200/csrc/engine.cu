@@ -40,9 +40,9 @@ sampler_kernel(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_orig,
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t ev = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (ev >= n_ev) return;
-    const uint32_t slab = blockIdx.y;
+    const uint32_t blk = blockIdx.y;  // 4096-sample block of the batch: block h of slab blk / kRowHalves
     const uint32_t e = __ldg(ev_orig + ev);
-    const uint64_t w0 = (first_slab + slab) * kSlabWords + 2 * lane;  // first global word of this lane
+    const uint64_t w0 = (first_slab * kRowHalves + blk) * 64u + 2 * lane;  // first global word of this lane
     uint32_t out[4];
     if (BITS == 32) {
         const uint32_t thr = __ldg(thr32 + ev);
@@ -83,7 +83,7 @@ sampler_kernel(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_orig,
             out[h] = bits;
         }
     }
-    uint4* row = vals + ((size_t)slab * n_nodes + ev) * kRowVec;
+    uint4* row = vals + ((size_t)(blk / kRowHalves) * n_nodes + ev) * kRowVec + (blk % kRowHalves) * 32u;
     st_cg(row + lane, make_uint4(out[0], out[1], out[2], out[3]));
 }
 
@@ -156,10 +156,11 @@ sampler_sliced_kernel(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_
         head = hi; tail64 = (((uint64_t)hi << 32) | lo) << kHeadBits;
     }
     const uint32_t trans = head ^ (head >> 1);  // bit k (MSB first) set iff threshold bits k and k-1 differ
-    uint4* row = vals + ((size_t)blockIdx.y * n_nodes + ev) * kRowVec + lane;
-    const size_t row_step = (size_t)gridDim.y * n_nodes * kRowVec;
-    for (uint32_t slab = blockIdx.y; slab < n_slabs; slab += gridDim.y, row += row_step) {
-        const uint64_t g = (first_slab + slab) * (kSlabSamples / 128) + lane;  // 128-sample group of this lane
+    // the warp walks 4096-sample blocks blockIdx.y, +gridDim.y, ... of the batch: block h of slab blk / kRowHalves
+    const uint32_t n_blk = n_slabs * kRowHalves;
+    for (uint32_t blk = blockIdx.y; blk < n_blk; blk += gridDim.y) {
+        uint4* row = vals + ((size_t)(blk / kRowHalves) * n_nodes + ev) * kRowVec + (blk % kRowHalves) * 32u + lane;
+        const uint64_t g = (first_slab * kRowHalves + blk) * 32u + lane;  // 128-sample group of this lane
         const uint32_t g_lo = (uint32_t)g, g_hi = (uint32_t)(g >> 32);
         // Branch-free head, two LOP3 per word and plane.  With m_k = all-ones iff bit k (MSB first) of the
         // threshold is set:   u_{k+1} = u_k & ~(x_k ^ m_k)   (stay undecided where the variate bit equals the
@@ -346,6 +347,7 @@ constexpr int kGateThreads = 256;
 #endif
 constexpr int kGateMinBlocks = CANOPY_GATE_MIN_BLOCKS;
 
+#if CANOPY_ROW_HALVES == 1  // first-generation register-load kernel, kept for A/B on 512-byte rows only
 __global__ void __launch_bounds__(kGateThreads, kGateMinBlocks)
 gate_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const uint32_t* __restrict__ child,
             const uint32_t* __restrict__ layer_off, uint32_t n_layers, uint32_t n_nodes, uint32_t n_ev,
@@ -406,6 +408,8 @@ gate_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const uint
         __syncthreads();  // rows written in this layer are read by later layers of the same CTA only
     }
 }
+
+#endif
 
 // ================================================================================================
 // Ring gate kernel (slab walker, TMA-bulk staging).
@@ -468,6 +472,39 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
     return v;
 }
 
+// One lane's share of a node row: kRowHalves x 16 bytes (block h of the row sits at h * 512 + lane * 16).
+struct Row { uint4 h[kRowHalves]; };
+#define CANOPY_ROW_OP(name, expr)                                           \
+    __device__ __forceinline__ Row name(Row a, Row b) {                     \
+        Row r;                                                              \
+        _Pragma("unroll") for (uint32_t i = 0; i < kRowHalves; ++i) r.h[i] = expr; \
+        return r;                                                           \
+    }
+CANOPY_ROW_OP(and4, and4(a.h[i], b.h[i]))
+CANOPY_ROW_OP(or4, or4(a.h[i], b.h[i]))
+CANOPY_ROW_OP(xor4, xor4(a.h[i], b.h[i]))
+CANOPY_ROW_OP(andn4, andn4(a.h[i], b.h[i]))
+#undef CANOPY_ROW_OP
+__device__ __forceinline__ Row xors4(Row a, uint32_t m) {
+    Row r;
+#pragma unroll
+    for (uint32_t i = 0; i < kRowHalves; ++i) r.h[i] = xors4(a.h[i], m);
+    return r;
+}
+template <> __device__ __forceinline__ Row splat<Row>(uint32_t v) {
+    Row r;
+#pragma unroll
+    for (uint32_t i = 0; i < kRowHalves; ++i) r.h[i] = splat4(v);
+    return r;
+}
+__device__ __forceinline__ uint32_t popc_masked(Row r, Row m) {
+    uint32_t c = 0;
+#pragma unroll
+    for (uint32_t i = 0; i < kRowHalves; ++i)
+        c += __popc(r.h[i].x & m.h[i].x) + __popc(r.h[i].y & m.h[i].y) + __popc(r.h[i].z & m.h[i].z) + __popc(r.h[i].w & m.h[i].w);
+    return c;
+}
+
 // Per-warp stream of child rows through the shared-memory ring.  Rows travel in groups of kGroupRows
 // consecutive rows of the run: one mbarrier phase (one expect_tx, one try_wait) per group, so the
 // ~90-cycle mbarrier round trip and the copy-issue sequence are paid once per 2 KB, not once per row.
@@ -489,6 +526,9 @@ struct RowRing {
     uint32_t cur;               // shared address of this lane's 16 bytes of the next row to read
     uint32_t in_group;          // rows of the current group not read yet
     uint32_t idreg, idnext;     // child codes of rows [32k, 32k+32) of the run (and of the next 32), one per lane
+#ifdef CANOPY_RING_DUMMY_U
+    uint32_t dummy, dummy_zero;
+#endif
 
     __device__ __forceinline__ void issue_group(uint32_t k, uint32_t gi) {  // request rows [4k, 4k+4) of the run into ring group gi
         const uint32_t i = k * kGroupRows;
@@ -519,58 +559,68 @@ struct RowRing {
         gi_next = (gi_next + 1) & (kRingGroups - 1);
         // the group read before this one is free now (its values have been consumed by the ALU): refill it
         if (k_cur && k_cur - 1 + kRingGroups < n_groups) issue_group(k_cur - 1 + kRingGroups, (gi - 1) & (kRingGroups - 1));
+#ifdef CANOPY_RING_DUMMY_U
+        mbar_wait(bars + gi * 8u + (dummy & dummy_zero), (phase >> gi) & 1u);
+#else
         mbar_wait(bars + gi * 8u, (phase >> gi) & 1u);
+#endif
         phase ^= 1u << gi;
         cur = ring + gi * (kGroupRows * kRowBytes) + lane_off;
         in_group = min(kGroupRows, total - k_cur * kGroupRows);
         ++k_cur;
     }
-    __device__ __forceinline__ uint4 pop() {
+    __device__ __forceinline__ Row pop() {
         if (in_group == 0) advance();
-        const uint4 v = lds128(cur);
+#ifdef CANOPY_RING_DUMMY_U  // experiment: extra uniform-datapath instructions per row (3 per unit), see DESIGN.md 6
+#pragma unroll
+        for (int q = 0; q < CANOPY_RING_DUMMY_U; ++q) dummy = (dummy + 0x9E3779B9u) ^ (dummy >> 7);
+#endif
+        Row v;
+#pragma unroll
+        for (uint32_t h = 0; h < kRowHalves; ++h) v.h[h] = lds128(cur + h * 512u);
         cur += kRowBytes; --in_group;
         return v;
     }
 };
 
 template <int OP>
-__device__ __forceinline__ uint4 ring_simple(RowRing& R, uint32_t n_plain, uint32_t n_comp) {
-    uint4 acc = splat4(OP == kDevAnd ? 0xFFFFFFFFu : 0u);
+__device__ __forceinline__ Row ring_simple(RowRing& R, uint32_t n_plain, uint32_t n_comp) {
+    Row acc = splat<Row>(OP == kDevAnd ? 0xFFFFFFFFu : 0u);
     for (uint32_t j = 0; j < n_plain; ++j) {
-        const uint4 v = R.pop();
+        const Row v = R.pop();
         acc = OP == kDevAnd ? and4(acc, v) : OP == kDevOr ? or4(acc, v) : xor4(acc, v);
     }
     for (uint32_t j = 0; j < n_comp; ++j) {
-        const uint4 v = xors4(R.pop(), 0xFFFFFFFFu);
+        const Row v = xors4(R.pop(), 0xFFFFFFFFu);
         acc = OP == kDevAnd ? and4(acc, v) : OP == kDevOr ? or4(acc, v) : xor4(acc, v);
     }
     return acc;
 }
 
 template <int P>
-__device__ __forceinline__ uint4 ring_range(RowRing& R, uint32_t n_plain, uint32_t n_comp, uint32_t lo, uint32_t hi) {
-    uint4 pl[P];
+__device__ __forceinline__ Row ring_range(RowRing& R, uint32_t n_plain, uint32_t n_comp, uint32_t lo, uint32_t hi) {
+    Row pl[P];
 #pragma unroll
-    for (int p = 0; p < P; ++p) pl[p] = splat4(0u);
+    for (int p = 0; p < P; ++p) pl[p] = splat<Row>(0u);
     const uint32_t n = n_plain + n_comp;
     for (uint32_t j = 0; j < n; ++j) {
-        uint4 carry = xors4(R.pop(), j < n_plain ? 0u : 0xFFFFFFFFu);
+        Row carry = xors4(R.pop(), j < n_plain ? 0u : 0xFFFFFFFFu);
 #pragma unroll
         for (int p = 0; p < P; ++p) {
-            const uint4 t = and4(pl[p], carry);
+            const Row t = and4(pl[p], carry);
             pl[p] = xor4(pl[p], carry);
             carry = t;
         }
     }
-    uint4 gt = splat4(0u), eq = splat4(0xFFFFFFFFu);
+    Row gt = splat<Row>(0u), eq = splat<Row>(0xFFFFFFFFu);
 #pragma unroll
     for (int p = P - 1; p >= 0; --p) {
         if ((lo >> p) & 1u) eq = and4(eq, pl[p]);
         else { gt = or4(gt, and4(eq, pl[p])); eq = andn4(eq, pl[p]); }
     }
-    uint4 res = or4(gt, eq);
+    Row res = or4(gt, eq);
     if (hi < n) {
-        uint4 lt = splat4(0u); eq = splat4(0xFFFFFFFFu);
+        Row lt = splat<Row>(0u); eq = splat<Row>(0xFFFFFFFFu);
 #pragma unroll
         for (int p = P - 1; p >= 0; --p) {
             if ((hi >> p) & 1u) { lt = or4(lt, andn4(eq, pl[p])); eq = and4(eq, pl[p]); }
@@ -582,7 +632,7 @@ __device__ __forceinline__ uint4 ring_range(RowRing& R, uint32_t n_plain, uint32
 }
 
 #ifndef CANOPY_RING_MIN_BLOCKS
-#define CANOPY_RING_MIN_BLOCKS 4
+#define CANOPY_RING_MIN_BLOCKS (4 / CANOPY_ROW_HALVES)  // same bytes of rows in flight per SM for either row size
 #endif
 __global__ void __launch_bounds__(kGateThreads, CANOPY_RING_MIN_BLOCKS)
 gate_ring_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const uint32_t* __restrict__ child,
@@ -599,14 +649,21 @@ gate_ring_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const
     __syncthreads();
     RowRing R;
     R.lane = lane; R.lane_off = lane * 16u; R.gi_next = 0; R.phase = 0;
+#ifdef CANOPY_RING_DUMMY_U
+    R.dummy = blockIdx.x; R.dummy_zero = (n_layers >> 30) << 3;  // zero at run time, unknown at compile time
+#endif
     R.ring = smem_u32(smem) + warp * (kRingSlots * kRowBytes);
     R.bars = smem_u32(bars) + warp * (kRingGroups * 8u);
 
     for (uint32_t slab = blockIdx.x; slab < n_slabs; slab += gridDim.x) {
         uint4* base = vals + (size_t)slab * n_nodes * kRowVec;
-        const uint64_t s0 = (first_slab + slab) * (uint64_t)kSlabSamples + lane * 128u;
-        const uint4 mask = make_uint4(valid_mask32(s0, begin, end), valid_mask32(s0 + 32, begin, end),
-                                      valid_mask32(s0 + 64, begin, end), valid_mask32(s0 + 96, begin, end));
+        Row mask;
+#pragma unroll
+        for (uint32_t h = 0; h < kRowHalves; ++h) {
+            const uint64_t s0 = (first_slab + slab) * (uint64_t)kSlabSamples + h * 4096u + lane * 128u;
+            mask.h[h] = make_uint4(valid_mask32(s0, begin, end), valid_mask32(s0 + 32, begin, end),
+                                   valid_mask32(s0 + 64, begin, end), valid_mask32(s0 + 96, begin, end));
+        }
         for (uint32_t l = 0; l < n_layers; ++l) {
             const uint32_t* sp = split + l * (kGateWarps + 1) + warp;
             const uint32_t* sc = split_child + l * (kGateWarps + 1) + warp;
@@ -621,7 +678,7 @@ gate_ring_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const
                     const uint4 rec2 = g + 2 < g1 ? __ldg(grec + g + 2) : make_uint4(0, 0, 0, 0);
                     const uint32_t n = rec.y & 0xFFFFu, n_comp = rec.y >> 16, n_plain = n - n_comp;
                     const uint32_t op = rec.z & 0xFFu, flags = rec.z >> 8;
-                    uint4 r;
+                    Row r;
                     if (op == kDevAnd) r = ring_simple<kDevAnd>(R, n_plain, n_comp);
                     else if (op == kDevOr) r = ring_simple<kDevOr>(R, n_plain, n_comp);
                     else if (op == kDevXor) r = ring_simple<kDevXor>(R, n_plain, n_comp);
@@ -631,10 +688,13 @@ gate_ring_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const
                         else if (n < 64) r = ring_range<6>(R, n_plain, n_comp, lo, hi);
                         else r = ring_range<9>(R, n_plain, n_comp, lo, hi);
                     }
-                    if (flags & kFlagStore) { st_cg(base + (size_t)(n_ev + g) * kRowVec + lane, r); stored = true; }
+                    if (flags & kFlagStore) {
+#pragma unroll
+                        for (uint32_t h = 0; h < kRowHalves; ++h) st_cg(base + (size_t)(n_ev + g) * kRowVec + h * 32u + lane, r.h[h]);
+                        stored = true;
+                    }
                     if (flags & kFlagTally) {
-                        uint32_t c = __popc(r.x & mask.x) + __popc(r.y & mask.y) + __popc(r.z & mask.z) + __popc(r.w & mask.w);
-                        c = __reduce_add_sync(0xFFFFFFFFu, c);
+                        const uint32_t c = __reduce_add_sync(0xFFFFFFFFu, popc_masked(r, mask));
                         if (lane == 0 && c) atomicAdd(tallies + g, (unsigned long long)c);
                     }
                     rec = rec1; rec1 = rec2;
@@ -647,15 +707,22 @@ gate_ring_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const
                 const uint32_t n = rec.y & 0xFFFFu, flags = rec.z >> 8, lo = rec.w & 0xFFFFu, hi = rec.w >> 16;
                 const uint32_t* ch = child + rec.x;
                 const uint32_t ids = lane < n ? __ldg(ch + lane) : 0u;
-                uint4 r;
-                r.x = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 0, ids);
-                r.y = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 1, ids);
-                r.z = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 2, ids);
-                r.w = eval_range<16, uint32_t>(base, ch, n, lo, hi, lane, 3, ids);
-                if (flags & kFlagStore) { st_cg(base + (size_t)(n_ev + g) * kRowVec + lane, r); stored = true; }
+                Row r;
+#pragma unroll
+                for (uint32_t h = 0; h < kRowHalves; ++h) {
+                    const uint4* bh = base + h * 32u;  // block h of every row
+                    r.h[h].x = eval_range<16, uint32_t>(bh, ch, n, lo, hi, lane, 0, ids);
+                    r.h[h].y = eval_range<16, uint32_t>(bh, ch, n, lo, hi, lane, 1, ids);
+                    r.h[h].z = eval_range<16, uint32_t>(bh, ch, n, lo, hi, lane, 2, ids);
+                    r.h[h].w = eval_range<16, uint32_t>(bh, ch, n, lo, hi, lane, 3, ids);
+                }
+                if (flags & kFlagStore) {
+#pragma unroll
+                    for (uint32_t h = 0; h < kRowHalves; ++h) st_cg(base + (size_t)(n_ev + g) * kRowVec + h * 32u + lane, r.h[h]);
+                    stored = true;
+                }
                 if (flags & kFlagTally) {
-                    uint32_t c = __popc(r.x & mask.x) + __popc(r.y & mask.y) + __popc(r.z & mask.z) + __popc(r.w & mask.w);
-                    c = __reduce_add_sync(0xFFFFFFFFu, c);
+                    const uint32_t c = __reduce_add_sync(0xFFFFFFFFu, popc_masked(r, mask));
                     if (lane == 0 && c) atomicAdd(tallies + g, (unsigned long long)c);
                 }
             }
@@ -679,12 +746,16 @@ __global__ void finalize_kernel(unsigned long long* __restrict__ out, const unsi
     out[i] = v;
 }
 
-// Repack rows of one batch into [event][word] order for the sampler parity hook.
-__global__ void gather_words_kernel(const uint4* __restrict__ vals, uint32_t n_ev, uint32_t n_nodes, uint32_t n_slabs,
-                                    unsigned long long* __restrict__ out /* [n_ev][n_slabs*64] */) {
-    const uint32_t ev = blockIdx.x, slab = blockIdx.y, t = threadIdx.x;  // 64 threads: one word each
+// Repack rows of one batch into [event][word] order for the sampler parity hook: out[ev][w] = word (word_off + w) of
+// the batch's row of event ev (a row holds kSlabWords consecutive words per slab).
+__global__ void gather_words_kernel(const uint4* __restrict__ vals, uint32_t n_ev, uint32_t n_nodes, uint64_t word_off,
+                                    uint64_t n_words, unsigned long long* __restrict__ out /* [n_ev][n_words] */) {
+    const uint32_t ev = blockIdx.x;
+    const uint64_t w = (uint64_t)blockIdx.y * blockDim.x + threadIdx.x;
+    if (w >= n_words) return;
+    const uint64_t gw = word_off + w, slab = gw / kSlabWords;
     const unsigned long long* row = (const unsigned long long*)(vals + ((size_t)slab * n_nodes + ev) * kRowVec);
-    out[((size_t)ev * n_slabs + slab) * kSlabWords + t] = row[t];
+    out[(size_t)ev * n_words + w] = row[gw % kSlabWords];
 }
 
 // ================================================================================================
@@ -696,11 +767,19 @@ __global__ void __launch_bounds__(256) intpeak_kernel(uint32_t* out, uint32_t it
 #pragma unroll
     for (int i = 0; i < 8; ++i) a[i] = seed * (threadIdx.x + 1) + i * 0x9E3779B9u + blockIdx.x;
     const uint32_t b = seed ^ 0x5bd1e995u, c = seed + 77u;
+    uint32_t u[8];  // kinds 5, 6: chains on warp-uniform values (block index and parameters only) -> uniform datapath
+#pragma unroll
+    for (int i = 0; i < 8; ++i) u[i] = seed * (blockIdx.x + 1) + i * 0x85EBCA6Bu;
     for (uint32_t it = 0; it < iters; ++it) {
 #pragma unroll
         for (int rep = 0; rep < 4; ++rep) {
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
+                if (KIND == 5 || KIND == 6) u[i] = (u[i] + b) ^ (c + i);  // UIADD3 + ULOP3
+                if (KIND == 6) {  // ... beside two vector LOP3
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(b), "r"(c + i));
+                    asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(c), "r"(b + i));
+                }
                 if (KIND == 0) {  // LOP3 with a loop-carried dependency per chain
                     asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(b), "r"(c + i));
                 } else if (KIND == 1) {  // IMAD.WIDE.U32: 32x32 -> 64, consume hi ^ lo through the next multiply
@@ -726,7 +805,7 @@ __global__ void __launch_bounds__(256) intpeak_kernel(uint32_t* out, uint32_t it
     }
     uint32_t x = 0;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) x ^= a[i];
+    for (int i = 0; i < 8; ++i) x ^= a[i] ^ u[i];
     if (x == 0x12345678u) out[blockIdx.x * blockDim.x + threadIdx.x] = x;  // keep the chains alive
 }
 
@@ -743,6 +822,8 @@ void microbench_int(int device, int kind, double* lane_ops_per_s, double* ms_out
             case 1: intpeak_kernel<1><<<blocks, threads>>>(d, iters, 12345u); break;
             case 2: intpeak_kernel<2><<<blocks, threads>>>(d, iters, 12345u); break;
             case 4: intpeak_kernel<4><<<blocks, threads>>>(d, iters, 12345u); break;
+            case 5: intpeak_kernel<5><<<blocks, threads>>>(d, iters, 12345u); break;
+            case 6: intpeak_kernel<6><<<blocks, threads>>>(d, iters, 12345u); break;
             default: intpeak_kernel<3><<<blocks, threads>>>(d, iters, 12345u); break;
         }
     };
@@ -757,7 +838,10 @@ void microbench_int(int device, int kind, double* lane_ops_per_s, double* ms_out
     ms /= reps;
     // lane-instructions per launch: kinds 0,1,3: iters*4*8 ; kind 2: iters*4*4 rounds * 4 instr
     // kind 4 counts all three instructions of a step (1 IMAD.WIDE + 2 LOP3)
-    const double per_thread = kind == 2 ? (double)iters * 4 * 4 * 4 : kind == 4 ? (double)iters * 4 * 8 * 3 : (double)iters * 4 * 8;
+    // kind 5: 2 uniform instructions per step; kind 6: 2 uniform + 2 vector per step (uniform ones counted per warp x 32,
+    // so that "lane-instr/s" / 32 is warp instructions per second for every kind)
+    const double per_thread = kind == 2 ? (double)iters * 4 * 4 * 4 : kind == 4 ? (double)iters * 4 * 8 * 3
+                            : kind == 5 ? (double)iters * 4 * 8 * 2 : kind == 6 ? (double)iters * 4 * 8 * 4 : (double)iters * 4 * 8;
     *lane_ops_per_s = per_thread * blocks * threads / (ms * 1e-3);
     *ms_out = ms;
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
@@ -969,17 +1053,19 @@ static PhiloxKeys make_keys(uint64_t seed) {
 }
 
 // `shared_sm`: the launch runs beside the other kernel of the pipeline (sampler of batch b+1 beside the gate walk of
-// batch b).  Measured on B200 (gpurun_out/ovl1.txt): the two co-reside best with the sampler capped at 4 CTAs per SM
-// (by a dummy dynamic-shared-memory request) and 2 persistent gate CTAs per SM on the high-priority stream.
-constexpr int kSharedSamplerSmem = 47000;  // 4 x 47 KB + 2 x 33 KB (gate rings) fit the 228 KB of an SM
-constexpr int kSharedRingCtas = 2;
+// batch b).  Measured on B200 (gpurun_out/rows_sweep.txt, ovl1.txt): the two co-reside best with the sampler capped at
+// 4 CTAs per SM (by a dummy dynamic-shared-memory request that leaves room for the gate rings) and 64 KB of gate rings
+// per SM (1 CTA with 1 KB rows, 2 CTAs with 512 B rows) on the high-priority stream.
+constexpr int kSharedSamplerSmem = kRowHalves == 2 ? 38000 : 47000;
+constexpr int kSharedRingCtas = 2 / kRowHalves;
 
 static void launch_sampler(const DeviceState* s, const Lowered& L, uint4* vals, uint64_t first_slab, uint32_t n_slabs,
                            const PhiloxKeys& K, cudaStream_t st, bool shared_sm = false) {
     if (L.n_events() == 0 || n_slabs == 0) return;
-    const dim3 grid((L.n_events() + 7) / 8, n_slabs), block(256);
-    // sliced sampler: each warp loops over up to CANOPY_SLICED_SLABS_PER_WARP slabs of its event
-    const dim3 sgrid(grid.x, (n_slabs + CANOPY_SLICED_SLABS_PER_WARP - 1) / CANOPY_SLICED_SLABS_PER_WARP);
+    const uint32_t n_blk = n_slabs * kRowHalves;  // 4096-sample blocks
+    const dim3 grid((L.n_events() + 7) / 8, n_blk), block(256);
+    // sliced sampler: each warp loops over up to CANOPY_SLICED_SLABS_PER_WARP blocks of its event
+    const dim3 sgrid(grid.x, (n_blk + CANOPY_SLICED_SLABS_PER_WARP - 1) / CANOPY_SLICED_SLABS_PER_WARP);
 #define CANOPY_SAMPLER_ARGS vals, s->ev_orig, s->thr32, s->thr64, L.n_events(), L.n_nodes(), first_slab, K
 #define CANOPY_SLICED_ARGS vals, s->ev_orig, s->thr32, s->thr64, L.n_events(), L.n_nodes(), first_slab, n_slabs, K
     static const int pack = getenv("CANOPY_SAMPLER_PACK") ? atoi(getenv("CANOPY_SAMPLER_PACK")) : 1;  // tuning knob
@@ -1001,11 +1087,14 @@ static void launch_sampler(const DeviceState* s, const Lowered& L, uint4* vals, 
 static void launch_gates(const DeviceState* s, const Lowered& L, uint4* vals, uint64_t first_slab, uint32_t n_slabs,
                          uint64_t begin, uint64_t end, cudaStream_t st, bool shared_sm = false) {
     if (L.n_gates() == 0 || n_slabs == 0) return;
+#if CANOPY_ROW_HALVES == 1
     static const bool direct = getenv("CANOPY_GATE_KERNEL") && !strcmp(getenv("CANOPY_GATE_KERNEL"), "direct");  // A/B knob
     if (direct) {
         gate_kernel<<<n_slabs, kGateThreads, 0, st>>>(vals, s->grec, s->child, s->layer_off, L.n_layers(), L.n_nodes(),
                                                       L.n_events(), s->gate_tallies, first_slab, begin, end);
-    } else {
+    } else
+#endif
+    {
         // persistent: one CTA per resident slot, each walks slabs blockIdx.x, +gridDim.x, ...
         static const int cap = getenv("CANOPY_RING_CTAS") ? atoi(getenv("CANOPY_RING_CTAS")) : 0;  // tuning knob
         const int want = cap > 0 ? cap : shared_sm ? kSharedRingCtas : s->ring_ctas_per_sm;
@@ -1019,7 +1108,7 @@ static void launch_gates(const DeviceState* s, const Lowered& L, uint4* vals, ui
 }
 
 static uint32_t pick_batch_slabs(const DeviceState* s, const Lowered& L, const canopy_mc_opts& o, uint64_t total_slabs, int n_bufs) {
-    uint64_t want = o.batch_slabs > 0 ? (uint64_t)o.batch_slabs : (uint64_t)s->sm_count * 4;
+    uint64_t want = o.batch_slabs > 0 ? (uint64_t)o.batch_slabs : (uint64_t)s->sm_count * (4 / kRowHalves);  // 16384 samples per SM
     size_t free_b = 0, total_b = 0;
     CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
     free_b += s->vals_bytes[0] + s->vals_bytes[1] + g_val_pool.parked_bytes(s->device);  // what a regrow can reuse or release
@@ -1027,9 +1116,27 @@ static uint32_t pick_batch_slabs(const DeviceState* s, const Lowered& L, const c
     const uint64_t fit = per_slab ? (uint64_t)((free_b / 2) / (per_slab * n_bufs)) : want;
     if (fit == 0) throw Error(CANOPY_E_OOM, "one slab of node rows does not fit in device memory");
     want = std::min(want, fit);
-    want = std::min<uint64_t>(want, 65535);
+    want = std::min<uint64_t>(want, 65535 / kRowHalves);  // gridDim.y of the direct sampler
     want = std::min(want, std::max<uint64_t>(total_slabs, 1));
     return (uint32_t)want;
+}
+
+// Slabs per batch.  Uniform batches of `batch` slabs, except that a pipelined run (sampler of batch b+1 beside the
+// gate walk of batch b) tapers both ends: nothing overlaps the first sampler launch and the last gate walk, so the
+// first and the last batch are a quarter of a full one (at least one slab per SM) and the slabs in between are
+// spread evenly.  Tallies do not depend on the schedule (tests: batching invariance).
+static std::vector<uint32_t> batch_schedule(uint64_t total_slabs, uint32_t batch, bool taper, uint32_t sm_count) {
+    std::vector<uint32_t> v;
+    const uint32_t edge = std::max<uint32_t>(std::min<uint32_t>(batch, sm_count), batch / 4);
+    if (!taper || total_slabs < 2ull * edge + batch) {
+        for (uint64_t done = 0; done < total_slabs; done += batch) v.push_back((uint32_t)std::min<uint64_t>(batch, total_slabs - done));
+        return v;
+    }
+    const uint64_t mid = total_slabs - 2ull * edge, n_mid = (mid + batch - 1) / batch;
+    v.push_back(edge);
+    for (uint64_t i = 0; i < n_mid; ++i) v.push_back((uint32_t)(mid / n_mid + (i < mid % n_mid ? 1 : 0)));
+    v.push_back(edge);
+    return v;
 }
 
 void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, uint64_t* tallies_dev, canopy_mc_report* rep) {
@@ -1048,10 +1155,13 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
     unsigned long long* d_out = tallies_dev ? (unsigned long long*)tallies_dev : s->out_tallies;
 
     uint32_t batch = 1; uint64_t n_batches = 0;
+    std::vector<uint32_t> sched;  // slabs per batch, in order
     if (total_slabs && L.n_gates()) {
         batch = pick_batch_slabs(s, L, o, total_slabs, overlap ? 2 : 1);
-        n_batches = (total_slabs + batch - 1) / batch;
-        if (n_batches < 2) overlap = false;
+        if ((total_slabs + batch - 1) / batch < 2) overlap = false;
+        static const bool no_taper = getenv("CANOPY_NO_TAPER") != nullptr;  // A/B knob
+        sched = batch_schedule(total_slabs, batch, overlap && o.batch_slabs <= 0 && !no_taper, (uint32_t)s->sm_count);
+        n_batches = sched.size();
         ensure_vals(s, L, batch, overlap ? 2 : 1);
     }
     const PhiloxKeys K = make_keys(o.seed);
@@ -1063,9 +1173,9 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
     R.other_launches += 1;
     std::vector<cudaEvent_t> pe;  // profile events: 4 per batch
     if (!overlap) {
-        for (uint64_t b = 0; b < n_batches; ++b) {
-            const uint64_t fs = slab0 + b * batch;
-            const uint32_t ns = (uint32_t)std::min<uint64_t>(batch, total_slabs - b * batch);
+        uint64_t fs = slab0;
+        for (uint64_t b = 0; b < n_batches; fs += sched[b], ++b) {
+            const uint32_t ns = sched[b];
             if (profile) { cudaEvent_t e[3]; for (auto& x : e) { CUDA_CHECK(cudaEventCreate(&x)); pe.push_back(x); } CUDA_CHECK(cudaEventRecord(e[0], user)); }
             launch_sampler(s, L, s->vals[0], fs, ns, K, user);
             if (profile) CUDA_CHECK(cudaEventRecord(pe[pe.size() - 2], user));
@@ -1078,10 +1188,10 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
         CUDA_CHECK(cudaEventRecord(s->ev_fork, user));
         CUDA_CHECK(cudaStreamWaitEvent(s->s_sample, s->ev_fork, 0));
         CUDA_CHECK(cudaStreamWaitEvent(s->s_gate, s->ev_fork, 0));
-        for (uint64_t b = 0; b < n_batches; ++b) {
+        uint64_t fs = slab0;
+        for (uint64_t b = 0; b < n_batches; fs += sched[b], ++b) {
             const int buf = (int)(b & 1);
-            const uint64_t fs = slab0 + b * batch;
-            const uint32_t ns = (uint32_t)std::min<uint64_t>(batch, total_slabs - b * batch);
+            const uint32_t ns = sched[b];
             if (b >= 2) CUDA_CHECK(cudaStreamWaitEvent(s->s_sample, s->ev_consumed[buf], 0));
             launch_sampler(s, L, s->vals[buf], fs, ns, K, s->s_sample, b > 0);               // batch 0 has the GPU to itself
             CUDA_CHECK(cudaEventRecord(s->ev_sampled[buf], s->s_sample));
@@ -1124,18 +1234,19 @@ void mc_sample_words(canopy_plan* plan, const canopy_mc_opts& o, uint64_t first_
     DeviceState* s = nullptr;
     { std::lock_guard<std::mutex> lock(plan->mu); s = get_state(plan, o.device); }
     std::lock_guard<std::mutex> run_lock(s->run_mu);
-    if (first_word % kSlabWords || n_words % kSlabWords || n_words == 0)
-        throw Error(CANOPY_E_INVALID, "first_word and n_words must be multiples of 64 (one slab)");
+    if (first_word % 64 || n_words % 64 || n_words == 0)
+        throw Error(CANOPY_E_INVALID, "first_word and n_words must be multiples of 64 (4096 samples)");
     if (L.n_events() == 0) return;
-    const uint64_t n_slabs = n_words / kSlabWords;
-    if (n_slabs > 65535) throw Error(CANOPY_E_INVALID, "too many words requested");
+    const uint64_t slab0 = first_word / kSlabWords, n_slabs = (first_word + n_words - 1) / kSlabWords - slab0 + 1;
+    if (n_slabs > 65535 / kRowHalves || n_words / 64 > 65535) throw Error(CANOPY_E_INVALID, "too many words requested");
     ensure_vals(s, L, n_slabs, 1);
     const PhiloxKeys K = make_keys(o.seed);
-    launch_sampler(s, L, s->vals[0], first_word / kSlabWords, (uint32_t)n_slabs, K, s->main);
+    launch_sampler(s, L, s->vals[0], slab0, (uint32_t)n_slabs, K, s->main);
     unsigned long long* d = nullptr;
     const size_t bytes = (size_t)L.n_events() * n_words * 8;
     if (cudaMalloc(&d, bytes) != cudaSuccess) throw Error(CANOPY_E_OOM, "cudaMalloc failed");
-    gather_words_kernel<<<dim3(L.n_events(), (uint32_t)n_slabs), kSlabWords, 0, s->main>>>(s->vals[0], L.n_events(), L.n_nodes(), (uint32_t)n_slabs, d);
+    gather_words_kernel<<<dim3(L.n_events(), (uint32_t)(n_words / 64)), 64, 0, s->main>>>(
+        s->vals[0], L.n_events(), L.n_nodes(), first_word - slab0 * kSlabWords, n_words, d);
     cudaError_t e = cudaMemcpyAsync(words_host, d, bytes, cudaMemcpyDeviceToHost, s->main);
     if (e == cudaSuccess) e = cudaStreamSynchronize(s->main);
     cudaFree(d);

@@ -401,15 +401,15 @@ void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lower
 
 void shard_range(uint64_t begin, uint64_t n, int rank, int world, uint64_t* ob, uint64_t* on) {
     if (world < 1 || rank < 0 || rank >= world) fail(CANOPY_E_INVALID, "bad rank/world");
-    // split on slab (4096-sample) boundaries of the GLOBAL sample index so every rank's interior
-    // slabs are whole; the first and last rank absorb the ragged ends.
+    // split on 4096-sample boundaries of the GLOBAL sample index (the kernels mask ragged slab ends, so any cut is
+    // exact; aligned cuts keep every rank's interior blocks whole); the first and last rank absorb the ragged ends.
     const uint64_t end = begin + n;
-    const uint64_t s0 = begin / kSlabSamples, s1 = (end + kSlabSamples - 1) / kSlabSamples;  // slab index range
+    const uint64_t s0 = begin / kShardAlign, s1 = (end + kShardAlign - 1) / kShardAlign;  // 4096-sample block index range
     const uint64_t slabs = s1 - s0;
     auto cut = [&](int r) -> uint64_t {
         if (r <= 0) return begin;
         if (r >= world) return end;
-        const uint64_t c = (s0 + (slabs * (uint64_t)r) / (uint64_t)world) * kSlabSamples;
+        const uint64_t c = (s0 + (slabs * (uint64_t)r) / (uint64_t)world) * kShardAlign;
         return std::min(std::max(c, begin), end);
     };
     const uint64_t b = cut(rank), e = cut(rank + 1);

@@ -25,13 +25,20 @@ enum DevOp : uint8_t { kDevAnd = 0, kDevOr = 1, kDevXor = 2, kDevRange = 3 };
 enum GateFlags : uint8_t { kFlagInvert = 1, kFlagStore = 2, kFlagTally = 4 };
 enum TallyKind : uint8_t { kTallyFalse = 0, kTallyTrue = 1, kTallyGate = 2, kTallyNotGate = 3 };
 
-// Geometry of the value buffer. A slab is a tile of 4096 consecutive samples: 64 words of 64 samples;
-// one node row inside a slab is 64 words = 512 bytes = 32 lanes x 16 bytes, so one warp moves one row
-// with one 128-bit access per lane.
-constexpr uint32_t kSlabWords = 64;
-constexpr uint32_t kSlabSamples = kSlabWords * 64;   // 4096
-constexpr uint32_t kRowBytes = kSlabWords * 8;       // 512
-constexpr uint32_t kRowVec = 32;                     // uint4 per row
+// Geometry of the value buffer. A slab is a tile of kSlabSamples consecutive samples; one node row inside a slab is
+// kRowHalves blocks of 512 bytes = 32 lanes x 16 bytes (4096 samples each), so one warp moves one block with one
+// 128-bit access per lane.  kRowHalves = 2 (8192-sample slabs, 1 KB rows) halves the per-row bookkeeping of the gate
+// walk per byte moved: one bulk copy, one ring pop and one trip through the gate loop per KB.
+#ifndef CANOPY_ROW_HALVES
+#define CANOPY_ROW_HALVES 2
+#endif
+constexpr uint32_t kRowHalves = CANOPY_ROW_HALVES;   // 1 or 2
+constexpr uint32_t kSlabWords = 64 * kRowHalves;
+constexpr uint32_t kSlabSamples = kSlabWords * 64;   // 4096 * kRowHalves
+constexpr uint32_t kRowBytes = kSlabWords * 8;       // 512 * kRowHalves
+constexpr uint32_t kRowVec = 32 * kRowHalves;        // uint4 per row
+constexpr uint32_t kShardAlign = 4096;               // canopy_shard_range cuts on multiples of this (API contract)
+static_assert(kRowHalves == 1 || kRowHalves == 2, "CANOPY_ROW_HALVES must be 1 or 2");
 
 // Gate kernel geometry fixed at lowering time.
 constexpr uint32_t kGateWarps = 8;     // warps of the CTA that walks one slab; the per-layer split is cut for this

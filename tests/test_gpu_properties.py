@@ -30,7 +30,7 @@ def test_c2_full_size_decomposition_and_batching_invariance(c2_plan):
     assert np.array_equal(whole, a + b)
     small_batches, rep2 = c2_plan.run(S, seed=9, batch_slabs=148, overlap=False)
     assert np.array_equal(whole, small_batches) and rep2.n_batches > rep.n_batches
-    assert rep.n_batches * rep.batch_slabs * 4096 >= S
+    assert rep.n_batches * rep.batch_slabs * rep.slab_samples >= S
     # statistical sanity of the top event against its own binomial error (no oracle at this size)
     top = int(whole[0]); p = top / S
     assert 0 < top < S and (p * (1 - p) / S) ** 0.5 < 1e-3
