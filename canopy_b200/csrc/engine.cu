@@ -922,6 +922,12 @@ struct ValPool {
             --n;
         }
     }
+    int count_at_least(int device, size_t bytes) {
+        std::lock_guard<std::mutex> lock(mu);
+        int n = 0;
+        for (auto& e : parked) n += e.device == device && e.bytes >= bytes;
+        return n;
+    }
     size_t parked_bytes(int device) {
         std::lock_guard<std::mutex> lock(mu);
         size_t b = 0;
@@ -980,20 +986,48 @@ struct ArenaPlan {
     }
 };
 
-static DeviceState* get_state(canopy_plan* plan, int device) {
-    for (DeviceState* s : plan->dev) if (s->device == device) { CUDA_CHECK(cudaSetDevice(device)); return s; }
+// What the engine needs to know about a device, queried once per process: cudaGetDeviceProperties costs milliseconds
+// per call, which a one-shot plan -> run -> destroy would pay every time.
+struct DeviceInfo { bool ready = false; int major = 0, minor = 0, sm_count = 0, ring_ctas_per_sm = 0, hi_prio = 0; };
+static std::mutex g_info_mu;
+static DeviceInfo g_info[64];
+
+static DeviceInfo device_info(int device) {
+    std::lock_guard<std::mutex> lock(g_info_mu);
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
         throw Error(CANOPY_E_CUDA, "no CUDA device available: libcanopy has no CPU fallback");
-    if (device < 0 || device >= count) throw Error(CANOPY_E_INVALID, "device ordinal out of range");
-    cudaDeviceProp prop; CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
-    if (prop.major != 10)
-        throw Error(CANOPY_E_CUDA, std::string("device '") + prop.name + "' is sm_" + std::to_string(prop.major) +
-                                       std::to_string(prop.minor) + "; libcanopy is built for sm_100a only");
+    if (device < 0 || device >= count || device >= 64) throw Error(CANOPY_E_INVALID, "device ordinal out of range");
+    DeviceInfo& I = g_info[device];
+    if (I.ready) return I;
+    CUDA_CHECK(cudaDeviceGetAttribute(&I.major, cudaDevAttrComputeCapabilityMajor, device));
+    CUDA_CHECK(cudaDeviceGetAttribute(&I.minor, cudaDevAttrComputeCapabilityMinor, device));
+    CUDA_CHECK(cudaDeviceGetAttribute(&I.sm_count, cudaDevAttrMultiProcessorCount, device));
+    if (I.major != 10) {
+        cudaDeviceProp prop; CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
+        throw Error(CANOPY_E_CUDA, std::string("device '") + prop.name + "' is sm_" + std::to_string(I.major) +
+                                       std::to_string(I.minor) + "; libcanopy is built for sm_100a only");
+    }
+    CUDA_CHECK(cudaSetDevice(device));
+    // function attributes are per device (context): set once
+    CUDA_CHECK(cudaFuncSetAttribute(gate_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmemBytes));
+    CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&I.ring_ctas_per_sm, gate_ring_kernel, kGateThreads, kRingSmemBytes));
+    if (I.ring_ctas_per_sm < 1) throw Error(CANOPY_E_CUDA, "gate_ring_kernel does not fit on an SM");
+    int lo_prio = 0;
+    CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&lo_prio, &I.hi_prio));
+    I.ready = true;
+    return I;
+}
+
+static DeviceState* get_state(canopy_plan* plan, int device) {
+    for (DeviceState* s : plan->dev) if (s->device == device) { CUDA_CHECK(cudaSetDevice(device)); return s; }
+    const DeviceInfo info = device_info(device);
     CUDA_CHECK(cudaSetDevice(device));
     const Lowered& L = plan->low;
     DeviceState* s = new DeviceState();
-    s->device = device; s->sm_count = prop.multiProcessorCount;
+    s->device = device; s->sm_count = info.sm_count; s->ring_ctas_per_sm = info.ring_ctas_per_sm;
     try {
         static_assert(sizeof(GateRec) == sizeof(uint4), "GateRec must be 16 bytes");
         ArenaPlan A;
@@ -1004,24 +1038,20 @@ static DeviceState* get_state(canopy_plan* plan, int device) {
         A.reserve(s->gate_tallies, std::max<size_t>(L.n_gates(), 1) * 8);
         A.reserve(s->out_tallies, std::max<size_t>(L.tally_kind.size(), 1) * 8);
         if (cudaMalloc(&s->arena, A.total) != cudaSuccess) { cudaGetLastError(); throw Error(CANOPY_E_OOM, "cudaMalloc failed for plan arrays"); }
-        for (auto& p : A.pieces) {
-            *p.dst = static_cast<char*>(s->arena) + p.off;
-            if (p.bytes) CUDA_CHECK(cudaMemcpy(*p.dst, p.src, p.bytes, cudaMemcpyHostToDevice));
-            s->h2d_bytes += p.bytes;
+        {   // one staged upload of all plan arrays instead of a dozen small synchronous copies
+            std::vector<char> stage(A.total);
+            for (auto& p : A.pieces) {
+                *p.dst = static_cast<char*>(s->arena) + p.off;
+                if (p.bytes) std::memcpy(stage.data() + p.off, p.src, p.bytes);
+                s->h2d_bytes += p.bytes;
+            }
+            CUDA_CHECK(cudaMemcpy(s->arena, stage.data(), A.total, cudaMemcpyHostToDevice));
         }
-        CUDA_CHECK(cudaFuncSetAttribute(gate_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmemBytes));
-        CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-        CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-        CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&s->ring_ctas_per_sm, gate_ring_kernel, kGateThreads, kRingSmemBytes));
-        if (s->ring_ctas_per_sm < 1) throw Error(CANOPY_E_CUDA, "gate_ring_kernel does not fit on an SM");
         CUDA_CHECK(cudaStreamCreateWithFlags(&s->main, cudaStreamNonBlocking));
         CUDA_CHECK(cudaStreamCreateWithFlags(&s->s_sample, cudaStreamNonBlocking));
-        {   // the gate walk of batch b competes with the sampler of batch b+1 for SM slots: its (few, persistent)
-            // CTAs must win, so its stream gets the highest priority
-            int lo_prio = 0, hi_prio = 0;
-            CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio));
-            CUDA_CHECK(cudaStreamCreateWithPriority(&s->s_gate, cudaStreamNonBlocking, hi_prio));
-        }
+        // the gate walk of batch b competes with the sampler of batch b+1 for SM slots: its (few, persistent)
+        // CTAs must win, so its stream gets the highest priority
+        CUDA_CHECK(cudaStreamCreateWithPriority(&s->s_gate, cudaStreamNonBlocking, info.hi_prio));
         for (cudaEvent_t* e : {&s->ev_fork, &s->ev_join, &s->ev_sampled[0], &s->ev_sampled[1], &s->ev_consumed[0], &s->ev_consumed[1]})
             CUDA_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
         CUDA_CHECK(cudaEventCreate(&s->ev_t0)); CUDA_CHECK(cudaEventCreate(&s->ev_t1));
@@ -1109,6 +1139,15 @@ static void launch_gates(const DeviceState* s, const Lowered& L, uint4* vals, ui
 
 static uint32_t pick_batch_slabs(const DeviceState* s, const Lowered& L, const canopy_mc_opts& o, uint64_t total_slabs, int n_bufs) {
     uint64_t want = o.batch_slabs > 0 ? (uint64_t)o.batch_slabs : (uint64_t)s->sm_count * (4 / kRowHalves);  // 16384 samples per SM
+    want = std::min<uint64_t>(want, 65535 / kRowHalves);  // gridDim.y of the direct sampler
+    want = std::min(want, std::max<uint64_t>(total_slabs, 1));
+    {   // buffers on hand (own or parked by an earlier plan) that already hold `want` slabs: no need to ask the driver
+        // how much memory is free (cudaMemGetInfo is slow)
+        const size_t need = (size_t)want * L.n_nodes() * kRowBytes;
+        int have = 0;
+        for (int b = 0; b < 2; ++b) have += s->vals_bytes[b] >= need;
+        if (have >= n_bufs || have + g_val_pool.count_at_least(s->device, need) >= n_bufs) return (uint32_t)want;
+    }
     size_t free_b = 0, total_b = 0;
     CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
     free_b += s->vals_bytes[0] + s->vals_bytes[1] + g_val_pool.parked_bytes(s->device);  // what a regrow can reuse or release
