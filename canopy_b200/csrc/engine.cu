@@ -641,6 +641,9 @@ gate_ring_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const
                  uint32_t n_layers, uint32_t n_nodes, uint32_t n_ev, unsigned long long* __restrict__ tallies,
                  uint64_t first_slab, uint32_t n_slabs, uint64_t begin, uint64_t end) {
     extern __shared__ __align__(128) unsigned char smem[];
+    // Pipelined run: the sampler of the next batch is launched as a programmatic dependent of this walk and needs
+    // nothing from it, so it may start as soon as every CTA of this (persistent, single-wave) grid is resident.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = __shfl_sync(0xFFFFFFFFu, threadIdx.x >> 5, 0);  // broadcast: provably warp-uniform
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kGateWarps * kRingSlots * kRowBytes);
@@ -1089,8 +1092,10 @@ static PhiloxKeys make_keys(uint64_t seed) {
 constexpr int kSharedSamplerSmem = kRowHalves == 2 ? 38000 : 47000;
 constexpr int kSharedRingCtas = 2 / kRowHalves;
 
+// `pdl`: launch as a programmatic dependent of the kernel before it in the stream (the gate walk of the previous
+// batch): the sampler starts once that walk's CTAs are resident instead of when the walk has finished.
 static void launch_sampler(const DeviceState* s, const Lowered& L, uint4* vals, uint64_t first_slab, uint32_t n_slabs,
-                           const PhiloxKeys& K, cudaStream_t st, bool shared_sm = false) {
+                           const PhiloxKeys& K, cudaStream_t st, bool shared_sm = false, bool pdl = false) {
     if (L.n_events() == 0 || n_slabs == 0) return;
     const uint32_t n_blk = n_slabs * kRowHalves;  // 4096-sample blocks
     const dim3 grid((L.n_events() + 7) / 8, n_blk), block(256);
@@ -1102,9 +1107,21 @@ static void launch_sampler(const DeviceState* s, const Lowered& L, uint4* vals, 
     if (L.opts.sampler == CANOPY_SAMPLER_SLICED) {
         // tuning knob: dynamic shared memory requested only to cap the sampler's CTAs per SM (room for gate CTAs)
         static const int env_smem = getenv("CANOPY_SAMPLER_SMEM") ? atoi(getenv("CANOPY_SAMPLER_SMEM")) : -1;
-        const int cap_smem = !shared_sm ? 0 : env_smem >= 0 ? env_smem : kSharedSamplerSmem;
-        if (L.opts.threshold_bits == 64) sampler_sliced_kernel<64><<<sgrid, block, cap_smem, st>>>(CANOPY_SLICED_ARGS);
-        else sampler_sliced_kernel<32><<<sgrid, block, cap_smem, st>>>(CANOPY_SLICED_ARGS);
+        // (a programmatic dependent starts after the walk's CTAs are resident: no room has to be kept for them)
+        const int cap_smem = !shared_sm ? 0 : env_smem >= 0 ? env_smem : pdl ? 0 : kSharedSamplerSmem;
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = sgrid; cfg.blockDim = block; cfg.dynamicSmemBytes = (size_t)cap_smem; cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
+        const uint32_t n_ev = L.n_events(), n_nodes = L.n_nodes();
+        if (L.opts.threshold_bits == 64)
+            CUDA_CHECK(cudaLaunchKernelEx(&cfg, sampler_sliced_kernel<64>, vals, (const uint32_t*)s->ev_orig, (const uint32_t*)s->thr32,
+                                          (const uint64_t*)s->thr64, n_ev, n_nodes, first_slab, n_slabs, K));
+        else
+            CUDA_CHECK(cudaLaunchKernelEx(&cfg, sampler_sliced_kernel<32>, vals, (const uint32_t*)s->ev_orig, (const uint32_t*)s->thr32,
+                                          (const uint64_t*)s->thr64, n_ev, n_nodes, first_slab, n_slabs, K));
     }
     else if (L.opts.threshold_bits == 64) sampler_kernel<64, 0><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
     else if (pack == 0) sampler_kernel<32, 0><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
@@ -1160,10 +1177,10 @@ static uint32_t pick_batch_slabs(const DeviceState* s, const Lowered& L, const c
     return (uint32_t)want;
 }
 
-// Slabs per batch.  Uniform batches of `batch` slabs, except that a pipelined run (sampler of batch b+1 beside the
-// gate walk of batch b) tapers both ends: nothing overlaps the first sampler launch and the last gate walk, so the
-// first and the last batch are a quarter of a full one (at least one slab per SM) and the slabs in between are
-// spread evenly.  Tallies do not depend on the schedule (tests: batching invariance).
+// Slabs per batch.  Uniform batches of `batch` slabs; with `taper` (experiment, CANOPY_TAPER=1) a pipelined run makes
+// its first and last batch a quarter of a full one, because nothing overlaps the first sampler launch and the last gate
+// walk.  Measured neutral (gpurun_out/pdl_taper_*.json): the pipelined step costs sampler + stolen issue slots, not
+// fill/drain.  Tallies do not depend on the schedule (tests: batching invariance).
 static std::vector<uint32_t> batch_schedule(uint64_t total_slabs, uint32_t batch, bool taper, uint32_t sm_count) {
     std::vector<uint32_t> v;
     const uint32_t edge = std::max<uint32_t>(std::min<uint32_t>(batch, sm_count), batch / 4);
@@ -1198,8 +1215,8 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
     if (total_slabs && L.n_gates()) {
         batch = pick_batch_slabs(s, L, o, total_slabs, overlap ? 2 : 1);
         if ((total_slabs + batch - 1) / batch < 2) overlap = false;
-        static const bool no_taper = getenv("CANOPY_NO_TAPER") != nullptr;  // A/B knob
-        sched = batch_schedule(total_slabs, batch, overlap && o.batch_slabs <= 0 && !no_taper, (uint32_t)s->sm_count);
+        static const bool taper = getenv("CANOPY_TAPER") != nullptr;  // A/B knob: measured neutral on B200, off by default
+        sched = batch_schedule(total_slabs, batch, overlap && o.batch_slabs <= 0 && taper, (uint32_t)s->sm_count);
         n_batches = sched.size();
         ensure_vals(s, L, batch, overlap ? 2 : 1);
     }
@@ -1223,7 +1240,24 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
             R.sampler_launches += L.n_events() ? 1 : 0; R.gate_launches += 1;
         }
     } else {
-        // sampler of batch b+1 (integer-pipe bound) runs beside the gate walk of batch b (HBM bound)
+        // sampler of batch b+1 (integer-issue bound) runs beside the gate walk of batch b (HBM bound)
+        static const bool use_streams = getenv("CANOPY_PIPELINE") && !strcmp(getenv("CANOPY_PIPELINE"), "streams");  // A/B knob
+        if (!use_streams) {
+            // One stream, programmatic dependent launch: S0, G0, S1*, G1, S2*, ...  (* = dependent of the walk before
+            // it).  G_b is an ordinary launch, so it starts when S_b and everything before it have finished; S_{b+1}
+            // starts as soon as the CTAs of G_b (one per SM, all resident at once on the idle GPU) have signalled, fills
+            // the rest of every SM and keeps it full when the walk ends.  The order in which the two kernels get their
+            // SM slots is fixed by construction; with two streams it depended on how the driver mapped the streams
+            // to hardware queues (40 % of fresh plans ran without any overlap, gpurun_out/var.txt).
+            // Hazards: S_{b+2} rewrites the buffer G_b read; it starts after G_{b+1} started, i.e. after G_b finished.
+            uint64_t fs = slab0;
+            for (uint64_t b = 0; b < n_batches; fs += sched[b], ++b) {
+                const int buf = (int)(b & 1);
+                launch_sampler(s, L, s->vals[buf], fs, sched[b], K, user, b > 0, b > 0);
+                launch_gates(s, L, s->vals[buf], fs, sched[b], begin, end, user, b + 1 < n_batches);
+                R.sampler_launches += L.n_events() ? 1 : 0; R.gate_launches += 1;
+            }
+        } else {
         CUDA_CHECK(cudaEventRecord(s->ev_fork, user));
         CUDA_CHECK(cudaStreamWaitEvent(s->s_sample, s->ev_fork, 0));
         CUDA_CHECK(cudaStreamWaitEvent(s->s_gate, s->ev_fork, 0));
@@ -1241,6 +1275,7 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
         }
         CUDA_CHECK(cudaEventRecord(s->ev_join, s->s_gate));
         CUDA_CHECK(cudaStreamWaitEvent(user, s->ev_join, 0));
+        }
     }
     if (n_tallies) {
         finalize_kernel<<<(n_tallies + 255) / 256, 256, 0, user>>>(d_out, s->gate_tallies, s->tally_kind, s->tally_gate,

@@ -1,7 +1,10 @@
 #!/bin/bash
-# scratch: co-residency sweep for 1 KB rows
-out=gpurun_out/rows_sweep.txt; : > $out
-for rc in 1 2; do for sm in 0 30000 38000 47000 60000; do
-  CANOPY_RING_CTAS=$rc CANOPY_SAMPLER_SMEM=$sm python tools/quick_overlap.py >> $out 2>&1
-done; done
-cat $out
+# scratch: taper A/B under the PDL pipeline
+out=gpurun_out; mkdir -p $out
+for i in 1 2; do
+CANOPY_NO_TAPER=1 timeout 300 python bench.py --steps 5 --warmup 3 --no-study > $out/pdl_taper_off_$i.json 2>&1
+timeout 300 python bench.py --steps 5 --warmup 3 --no-study > $out/pdl_taper_on_$i.json 2>&1
+done
+CANOPY_NO_TAPER=1 python tools/quick_var.py > $out/pdl_var_notaper.txt 2>&1
+for f in $out/pdl_taper_o*.json; do echo "== $f"; grep -o '"value": [0-9.e+]*, "unit": "samples/s", "n_gpus": [0-9]*' $f | head -2; grep -o '"e2e": {"value": [0-9.e+]*' $f; done
+cat $out/pdl_var_notaper.txt
