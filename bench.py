@@ -286,7 +286,7 @@ def main():
         # Algorithmic integer ops per Bernoulli bit (spec 2, H=8): per 128-sample group 148.6 Philox multiplies (9 calls x 20,
         # minus the round-1..3 products the calls of a group share) x (1 IMAD.WIDE + 1 LOP3) + 2 LOP3 per word and plane
         # + 4 = 365.2 per 4096 lane-samples... i.e. per warp-row of 4096 samples: 365.2 warp-instr x 32 lanes / 4096 = 2.853.
-        # Executed (ncu source page, profiles/r01c_*): 466.4 integer warp-instr per row = 3.644 per bit.  Spec 1: 12.3 per bit.
+        # Executed (ncu source page, profiles/r01d_ncu_source_sampler_c2_opcodes.csv): 466.4 integer warp-instr per row = 3.644 per bit.  Spec 1: 12.3 per bit.
         int_peak, _ = microbench_int(0, local)
         sliced = stats["spec_version"] == 2
         alg_ops_per_bit = 2.853 if sliced else 581.0 * 2 / 128.0

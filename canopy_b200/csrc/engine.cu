@@ -634,7 +634,11 @@ __device__ __forceinline__ Row ring_range(RowRing& R, uint32_t n_plain, uint32_t
 #ifndef CANOPY_RING_MIN_BLOCKS
 #define CANOPY_RING_MIN_BLOCKS (4 / CANOPY_ROW_HALVES)  // same bytes of rows in flight per SM for either row size
 #endif
+#ifdef CANOPY_RING_MAXREG  // tuning knob: cap registers so one more sampler CTA fits beside the walk
+__global__ void __maxnreg__(CANOPY_RING_MAXREG)
+#else
 __global__ void __launch_bounds__(kGateThreads, CANOPY_RING_MIN_BLOCKS)
+#endif
 gate_ring_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const uint32_t* __restrict__ child,
                  const uint32_t* __restrict__ layer_off, const uint32_t* __restrict__ wide_off,
                  const uint32_t* __restrict__ split, const uint32_t* __restrict__ split_child,
