@@ -49,26 +49,34 @@ class ClockSampler:
         self.lines = []
 
     def start(self):
+        """Start polling (before the warm-up, so nvidia-smi is up when the timed region begins)."""
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._pump, daemon=True).start()
         except Exception:
             self.proc = None
 
     def _pump(self):
         for ln in self.proc.stdout:
-            self.lines.append(ln.strip())
+            self.lines.append((time.time(), ln.strip()))
+
+    def mark_begin(self):
+        self.t0 = time.time()
 
     def stop(self):
+        """Samples that arrived between mark_begin() and now (the timed region)."""
+        t1 = time.time()
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.25)
+        time.sleep(0.1)
         self.proc.terminate()
         sm, smax, reasons = [], None, set()
-        for ln in self.lines:
+        for t, ln in self.lines:
+            if t < getattr(self, "t0", 0.0) or t > t1 + 0.06:
+                continue
             f = [x.strip() for x in ln.split(",")]
-            if len(f) < 9 or not f[0].isdigit() or int(f[0]) != self.index:
+            if len(f) < 9 or not f[0].isdigit():
                 continue
             try:
                 sm.append(float(f[1])); smax = float(f[2])
@@ -85,7 +93,7 @@ def ncu_traffic(workload_name: str):
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE gate_ring_kernel launch (592 slabs) from the committed
     `ncu --set full` capture of this workload under profiles/, in bytes; None if there is no capture for it."""
     import csv
-    path = os.path.join(ROOT, "profiles", f"r01f_ncu_full_gate_{workload_name}.csv")
+    path = os.path.join(ROOT, "profiles", f"r01g_ncu_full_gate_{workload_name}.csv")
     scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
     try:
         tot = 0.0
@@ -160,7 +168,7 @@ def config_block(name, g, stats, S, n_step=None):
             "samples_per_step_per_gpu": n_step or S, "B_live": stats["n_basic_live"], "G_live": stats["n_gates_live"],
             "E_live": stats["n_edges_live"], "G_stored": stats["n_gates_stored"], "layers": stats["n_layers"],
             "spec_version": stats["spec_version"], "threshold_bits": 32,
-            "l2": "no flush needed: each batch streams a value buffer of n_nodes*512 B*batch_slabs (GBs) >> 126 MB L2"}
+            "l2": "no flush needed: each batch streams a value buffer of n_nodes*1 KB*batch_slabs (GBs) >> 126 MB L2"}
 
 
 def main():
@@ -221,14 +229,15 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    clocks = ClockSampler(local); clocks.start()
     rep0 = step(0, want_report=True)
     for w in range(1, args.warmup):
         step(w)
     launches_per_step = rep0.launches + (1 if world > 1 else 0)
     barrier()
-    clocks = ClockSampler(local); clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    clocks.mark_begin()
     e0.record()
     for k in range(args.steps):
         step(args.warmup + k)
@@ -281,16 +290,17 @@ def main():
 
     line = None
     if rank == 0:
-        # Integer roofline of the sampler.  Measured on sm_100 (canopy_microbench_int, DESIGN.md 5.1): LOP3, IMAD.WIDE.U32 and
+        # Integer roofline of the sampler.  Measured on sm_100 (canopy_microbench_int, DESIGN.md 5.0): LOP3, IMAD.WIDE.U32 and
         # any mix of the two issue at ONE shared rate of 64 lanes/clk/SM, so the bound is the integer instruction count.
-        # Algorithmic integer ops per Bernoulli bit (spec 2, H=8): per 128-sample group 148.6 Philox multiplies (9 calls x 20,
-        # minus the round-1..3 products the calls of a group share) x (1 IMAD.WIDE + 1 LOP3) + 2 LOP3 per word and plane
-        # + 4 = 365.2 per 4096 lane-samples... i.e. per warp-row of 4096 samples: 365.2 warp-instr x 32 lanes / 4096 = 2.853.
-        # Executed (ncu source page, profiles/r01d_ncu_source_sampler_c2_opcodes.csv): 466.4 integer warp-instr per row = 3.644 per bit.  Spec 1: 12.3 per bit.
+        # Spec 2 with H = 7, per warp-row of 4096 samples (one 128-sample group per lane), from the ncu source page
+        # profiles/r01g_ncu_source_sampler_c2_opcodes.csv: 135.1 IMAD.WIDE executed (8 Philox calls x 20 minus the
+        # round-1..2 products the calls of a group share).  Algorithmic: each multiply pairs with one LOP3, + 2 LOP3 per
+        # word and plane (56) + 4 = 330.2 warp-instr x 32 lanes / 4096 = 2.580 per Bernoulli bit.  Executed integer-class
+        # (LOP3, IMAD*, ISETP, VIADD, SEL, SHF, ...): 453.5 per row = 3.543 per bit.  Spec 1: 12.3 per bit.
         int_peak, _ = microbench_int(0, local)
         sliced = stats["spec_version"] == 2
-        alg_ops_per_bit = 2.853 if sliced else 581.0 * 2 / 128.0
-        exec_ops_per_bit = 3.644 if sliced else 12.3
+        alg_ops_per_bit = 2.580 if sliced else 581.0 * 2 / 128.0
+        exec_ops_per_bit = 3.543 if sliced else 12.3
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

@@ -98,7 +98,7 @@ sampler_kernel(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_orig,
 //   tail: the samples of the group still undecided after H planes (probability 2^-H each) take their low
 //         32-H (64-H) bits, in ascending sample order, from the output words of the group's tail calls
 //         ctr = (g, e, 0x200+n) (resp. 0x300+n): four (two) undecided samples per call, so one tail call
-//         per lane covers all but ~1e-4 of the groups and is issued without divergence.
+//         per lane covers all but 3.5e-3 of the groups (H = 7) and is issued without divergence.
 // H + 1 Philox calls per 128 samples instead of 32 (64 for 64-bit thresholds).
 // ================================================================================================
 constexpr int kHeadBits = CANOPY_SLICED_HEAD_BITS;
@@ -191,7 +191,7 @@ sampler_sliced_kernel(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_
                 while (u[w]) {
                     const uint32_t b = u[w] & (0u - u[w]);  // lowest undecided sample of word w
                     u[w] ^= b;
-                    if (left == 0) {  // more undecided samples than one call serves: rare (1.7e-4 per group)
+                    if (left == 0) {  // more undecided samples than one call serves: rare (3.5e-3 per group)
                         Q.fill(philox4x32_10(g_lo, g_hi, e, TailQueue<BITS>::kCtr + (++call), K));
                         left = TailQueue<BITS>::kPerCall;
                     }

@@ -56,7 +56,7 @@ extern "C" {
  * CANOPY_SPEC_VERSION is the default spec of this build. */
 #define CANOPY_SPEC_VERSION 2
 #ifndef CANOPY_SLICED_HEAD_BITS
-#define CANOPY_SLICED_HEAD_BITS 8   /* H of spec 2; part of the spec (changing it changes every tally) */
+#define CANOPY_SLICED_HEAD_BITS 7   /* H of spec 2; part of the spec (changing it changes every tally) */
 #endif
 #define CANOPY_SAMPLER_DEFAULT 0   /* = the build default (spec 2) */
 #define CANOPY_SAMPLER_DIRECT  1   /* spec 1 */
@@ -182,16 +182,17 @@ typedef struct canopy_mc_opts {
     uint64_t sample_begin;
     uint64_t n_samples;
     int32_t  device;          /* CUDA ordinal                                                       */
-    int32_t  batch_slabs;     /* slabs (4096 samples each) per batch; 0 = default                   */
+    int32_t  batch_slabs;     /* slabs (canopy_mc_report.slab_samples samples each) per batch; 0 = default */
     void*    stream;          /* cudaStream_t to order the run on; NULL = library-owned stream (pass
                                  cudaStreamLegacy / cudaStreamPerThread explicitly for the default streams) */
-    int32_t  overlap;         /* 1 (default when 0 is passed via canopy_mc_opts_default): sampler of batch i+1 overlaps gates of batch i */
+    int32_t  overlap;         /* 1 (set by canopy_mc_opts_default): the sampler of batch i+1 runs beside the gate walk of
+                                 batch i (programmatic dependent launch on the run's stream) */
     int32_t  profile;         /* 1: time sampler / gate kernels separately with CUDA events (serialises the two) */
     int32_t  reserved[4];
 } canopy_mc_opts;
 CANOPY_API void canopy_mc_opts_default(canopy_mc_opts* opts);
 
-/* Per-run measurements taken with CUDA events on the run's streams. */
+/* Per-run measurements taken with CUDA events on the run's stream. */
 typedef struct canopy_mc_report {
     double   total_ms;          /* device time first launch -> last kernel done                     */
     double   sampler_ms;        /* sum over batches (profile=1 only, else 0)                        */
@@ -200,7 +201,7 @@ typedef struct canopy_mc_report {
     uint64_t gate_launches;
     uint64_t other_launches;    /* tally clear etc.                                                 */
     uint64_t n_batches;
-    uint64_t slab_samples;      /* samples per slab (4096)                                          */
+    uint64_t slab_samples;      /* samples per slab (8192: one 1-KB row per node)                   */
     uint64_t batch_slabs;
     uint64_t h2d_bytes, d2h_bytes;
 } canopy_mc_report;

@@ -159,7 +159,7 @@ static uint64_t packed_sample_word(uint64_t seed, uint32_t e, uint64_t w, int ki
 }
 
 /* spec 2: the four 32-sample result words of 128-sample group g, evaluated lazily (MSB-first on bit
- * planes, tail call only for samples still undecided after the 8 head planes).  Must agree bit for bit
+ * planes, tail call only for samples still undecided after the H head planes).  Must agree bit for bit
  * with oracle_sample_bit(..., spec = 2), which builds every variate in full; tests/test_oracle.py checks it. */
 static void sliced_group_words(uint64_t seed, uint32_t e, uint64_t g, int kind, uint64_t thr, int bits, uint64_t out2[2]) {
     if (kind == 0) { out2[0] = out2[1] = 0; return; }
