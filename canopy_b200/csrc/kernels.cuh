@@ -1,17 +1,17 @@
 // Device kernels of the Monte Carlo hot path, hand-written for sm_100a.
 //
-//   sampler_kernel      north-star subsystem 2 (ABSENT in the reference):
-//                       counter-based Philox4x32-10 variates, compare against the per-event threshold,
-//                       pack 64 samples per word, one 128-bit coalesced store per lane.
-//   gate_kernel         north-star subsystem 3 (ABSENT in the reference):
-//                       one CTA walks every layer of the DAG for one 4096-sample slab; one warp per gate,
-//                       one 128-bit load per lane per child row, bit-sliced adders for k-of-n, fused
+//   sampler_sliced_kernel / sampler_kernel   north-star subsystem 2 (ABSENT in the reference):
+//                       counter-based Philox4x32-10 variates, compared against the per-event threshold (MSB-first on
+//                       bit planes in spec 2, whole in spec 1), 64 samples per word, one 128-bit coalesced store per lane.
+//   gate_ring_kernel    north-star subsystem 3 (ABSENT in the reference):
+//                       one CTA walks every layer of the DAG for one slab; child rows stream through per-warp
+//                       shared-memory rings filled by TMA bulk copies, bit-sliced adders for k-of-n, fused
 //                       popcount tallies reduced with warp REDUX and one 64-bit RED per (gate, slab).
 //   finalize_kernel     maps device gate tallies to the caller-visible outputs (roots, per-gate) in place
 //                       in the buffer that the NCCL all-reduce consumes.
 //
-// Value buffer layout (HBM):  vals[slab][node][lane] as uint4 -- node row = 512 B = 64 words x 64 samples.
-// Sample s of the run lives in slab s/4096, word (s%4096)/64, bit s%64.
+// Value buffer layout (HBM):  vals[slab][node][half][lane] as uint4 -- node row = kRowBytes = 1 KB = 128 words x 64 samples
+// (plan.h).  Sample s of the run lives in slab s/8192, word (s%8192)/64, bit s%64.
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
