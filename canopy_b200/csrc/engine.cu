@@ -226,7 +226,7 @@ __device__ __forceinline__ uint4 load_child(const uint4* __restrict__ base, uint
 #ifndef CANOPY_SIMPLE_UNROLL
 #define CANOPY_SIMPLE_UNROLL 4
 #endif
-constexpr int kSimpleUnroll = CANOPY_SIMPLE_UNROLL;
+[[maybe_unused]] constexpr int kSimpleUnroll = CANOPY_SIMPLE_UNROLL;  // used by the 512-B-row A/B kernel only
 template <int OP>  // kDevAnd / kDevOr / kDevXor
 __device__ __forceinline__ uint4 eval_simple(const uint4* __restrict__ base, const uint32_t* __restrict__ child,
                                              uint32_t n, uint32_t lane, uint32_t first_ids) {
@@ -345,7 +345,7 @@ constexpr int kGateThreads = 256;
 #ifndef CANOPY_GATE_MIN_BLOCKS
 #define CANOPY_GATE_MIN_BLOCKS 4
 #endif
-constexpr int kGateMinBlocks = CANOPY_GATE_MIN_BLOCKS;
+[[maybe_unused]] constexpr int kGateMinBlocks = CANOPY_GATE_MIN_BLOCKS;
 
 #if CANOPY_ROW_HALVES == 1  // first-generation register-load kernel, kept for A/B on 512-byte rows only
 __global__ void __launch_bounds__(kGateThreads, kGateMinBlocks)
