@@ -172,3 +172,16 @@ def test_parked_value_buffers_are_reused_correctly():
         assert np.array_equal(got, O.mc_packed(g, seed, 4096 * seed, 5 * 4096 + 17, True, nthreads=CORES, spec=2))
         if seed == 32:
             trim_device_cache()
+
+
+def test_pipelined_run_is_the_same_on_every_kind_of_stream_and_pipeline():
+    """The pipelined run (sampler of batch b+1 launched as a programmatic dependent of gate walk b) on the library's
+    stream, on the legacy default stream (handle 1), on the per-thread default stream (handle 2), serialised, and the
+    oracle: identical tallies.  Many small batches so that every buffer is rewritten several times."""
+    g = random_graph(17, n_basic=300, n_gates=160)
+    n = 20 * 3 * 8192 + 123
+    want = O.mc_packed(g, 3, 77, n, True, nthreads=CORES)
+    with Plan(g, tally_all_gates=True) as plan:
+        for kw in (dict(), dict(stream=1), dict(stream=2), dict(overlap=False)):
+            got, rep = plan.run(n, seed=3, sample_begin=77, batch_slabs=3, **kw)
+            assert rep.n_batches >= 20 and np.array_equal(got, want), kw
