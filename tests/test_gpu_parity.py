@@ -56,6 +56,17 @@ def test_scaled_configs(name, scale, n):
     assert rep.gate_launches >= 1 and rep.sampler_launches >= 1
 
 
+@pytest.mark.parametrize("name,n", [("c3", 8192 * 2 + 4096 + 77), ("c4", 8192 + 1234)])
+def test_c3_c4_full_graphs_short_run_per_gate(name, n):
+    """BASELINE configs 3 and 4 at their FULL graph size (20.2k gates with 200 sequence roots; 100k events with fan-in up
+    to 245, 36 layers), every gate tallied, over a ragged sample range that straddles slabs: bit-exact against the oracle."""
+    g = synth.config_graph(name)
+    begin = (1 << 40) + 8192 * 5 + 4000
+    with Plan(g, tally_all_gates=True) as plan:
+        got, _ = plan.run(n, seed=0xC0DE, sample_begin=begin)
+    assert np.array_equal(got, O.mc_packed(g, 0xC0DE, begin, n, True, nthreads=CORES))
+
+
 def test_c2_full_graph_short_run():
     g = synth.config_graph("c2")
     n = 1 << 13
