@@ -20,7 +20,7 @@
 //     paths; along a path collect-formula instructions are conjoined, collect-expression instructions multiply
 //     into one extra basic event, set-house-event overrides apply to the formulas collected after them.
 // Not covered (CANOPY_E_UNSUPPORTED): nested formulas (the reference's Formula::Arg cannot hold them either,
-// formula.h:9-15), periodic-test, histogram, extern functions, alignments/substitutions, XInclude, private roles
+// formula.h:9-15), periodic-test, extern functions, alignments/substitutions, XInclude, private roles
 // (every name is looked up as written; a dotted reference falls back to its last segment).
 #include <algorithm>
 #include <cmath>
@@ -365,6 +365,25 @@ struct Builder {
         }
         if (t == "gamma-deviate") { const auto v = eval_args(e, cx, 2, 2); if (v[0] <= 0 || v[1] <= 0) bad(CANOPY_E_DOMAIN, e, "The k and theta parameters of Gamma distribution must be positive."); return v[0] * v[1]; }
         if (t == "beta-deviate") { const auto v = eval_args(e, cx, 2, 2); if (v[0] <= 0 || v[1] <= 0) bad(CANOPY_E_DOMAIN, e, "The alpha and beta parameters of Beta distribution must be positive."); return v[0] / (v[0] + v[1]); }
+        if (t == "histogram") {
+            // <histogram> lower-bound <bin> upper-bound weight </bin>... (initializer.cpp:1094-1112); validation as
+            // random_deviate.h:240-247: boundaries strictly increasing, weights not negative.  value() has no body in
+            // the reference; the mean of the piecewise-constant distribution whose bin i carries probability mass
+            // w_i / sum(w) (random_deviate.h:234-238 "weights of intervals") is sum_i w_i (b_{i-1} + b_i) / (2 sum w).
+            const auto kids = kids_of(e);
+            if (kids.size() < 2) bad(CANOPY_E_VALIDITY, e, "<histogram> needs a lower boundary and at least one <bin>");
+            double prev = eval(*kids[0], cx), sum_w = 0, sum_wm = 0;
+            for (size_t i = 1; i < kids.size(); ++i) {
+                const auto bin = kids_of(*kids[i]);
+                if (kids[i]->name != "bin" || bin.size() != 2) bad(CANOPY_E_VALIDITY, *kids[i], "<bin> takes an upper boundary and a weight");
+                const double b = eval(*bin[0], cx), w = eval(*bin[1], cx);
+                if (!(b > prev)) bad(CANOPY_E_VALIDITY, e, "Histogram upper boundaries are not strictly increasing.");
+                if (w < 0) bad(CANOPY_E_VALIDITY, e, "Histogram weights cannot be negative.");
+                sum_w += w; sum_wm += w * (prev + b); prev = b;
+            }
+            if (sum_w <= 0) bad(CANOPY_E_VALIDITY, e, "Histogram weights sum to zero.");
+            return sum_wm / (2 * sum_w);
+        }
         bad(CANOPY_E_UNSUPPORTED, e, "expression <" + t + "> is not supported by this loader");
     }
 

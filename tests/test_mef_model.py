@@ -34,7 +34,7 @@ def test_expression_means_and_parameters():
     lam, mu, gam, t = 1e-4, 2e-3, 0.05, 8760.0
     xml = model(
         "<define-fault-tree name='ft'><define-gate name='top'><or>"
-        + "".join(f"<basic-event name='e{i}'/>" for i in range(12)) + "</or></define-gate></define-fault-tree><model-data>"
+        + "".join(f"<basic-event name='e{i}'/>" for i in range(13)) + "</or></define-gate></define-fault-tree><model-data>"
         + "<define-parameter name='lambda'><float value='1e-4'/></define-parameter>"
         + "<define-parameter name='twice'><mul><parameter name='lambda'/><int value='2'/></mul></define-parameter>"
         + be("e0", "<exponential><parameter name='lambda'/><system-mission-time/></exponential>")
@@ -49,11 +49,14 @@ def test_expression_means_and_parameters():
         + be("e9", "<switch><case><bool value='false'/><float value='0.7'/></case><case><geq><pi/><int value='3'/></geq><float value='0.0625'/></case><float value='0.9'/></switch>")
         + be("e10", "<gamma-deviate><float value='2'/><float value='0.01'/></gamma-deviate>")
         + be("e11", "<mul><normal-deviate><float value='0.5'/><float value='0.1'/></normal-deviate><exp><neg><parameter name='twice'/></neg></exp></mul>")
+        + be("e12", "<histogram><float value='0'/><bin><float value='0.1'/><float value='3'/></bin>"
+                    "<bin><float value='0.5'/><float value='1'/></bin></histogram>")
         + "</model-data>")
     g = load_mef(text=xml)
     r = lam + mu
     want = [1 - math.exp(-lam * t), (lam - (lam - gam * r) * math.exp(-r * t)) / r, 1 - math.exp(-(((t - 100) / 5000) ** 1.5)),
-            0.75, 0.2, 0.02, 0.25, 0.125, 0.125, 0.0625, 0.02, 0.5 * math.exp(-2e-4)]
+            0.75, 0.2, 0.02, 0.25, 0.125, 0.125, 0.0625, 0.02, 0.5 * math.exp(-2e-4),
+            (3 * 0.05 + 1 * 0.3) / 4]  # histogram: bin masses 3/4 and 1/4 at midpoints 0.05 and 0.3
     assert g.p == pytest.approx(want, rel=1e-14, abs=0)
     # mission time is a loader option (Settings::mission_time)
     g2 = load_mef(text=xml, mission_time=100.0)
@@ -68,6 +71,8 @@ def test_expression_means_and_parameters():
     ("<exponential><float value='-1'/><float value='1'/></exponential>", _lib.E_DOMAIN, "rate of failure"),
     ("<exponential/>", _lib.E_VALIDITY, "takes 2"),
     ("<periodic-test/>", _lib.E_UNSUPPORTED, "not supported"),
+    ("<histogram><float value='0.2'/><bin><float value='0.1'/><float value='1'/></bin></histogram>", _lib.E_VALIDITY, "strictly increasing"),
+    ("<histogram><float value='0'/><bin><float value='0.1'/><float value='-1'/></bin></histogram>", _lib.E_VALIDITY, "negative"),
     ("<add><float value='0.8'/><float value='0.8'/></add>", _lib.E_DOMAIN, "probability"),
 ])
 def test_expression_errors(expr, status, msg):
