@@ -7,6 +7,8 @@
 #include <string>
 #include <vector>
 
+#include <cuda.h>  // CUtensorMap (types only; the encoder is fetched through cudaGetDriverEntryPoint)
+
 #include "kernels.cuh"
 
 namespace canopy {
@@ -511,8 +513,11 @@ __device__ __forceinline__ uint32_t popc_masked(Row r, Row m) {
 // Every member except `lane_off`/`idreg`/`idnext` is warp-uniform and derived from values the compiler can
 // prove uniform (kernel parameters, blockIdx, loop counters, shuffles from a uniform lane), so the copy
 // operands live in uniform registers and UBLKCP issues without a per-lane serialisation loop.
+template <bool G4>
 struct RowRing {
     const uint4* base;          // this slab's rows
+    const CUtensorMap* tmap;    // G4: tensor map of the value buffer, rows of kRowBytes
+    uint32_t row0;              // G4: tensor row of node 0 of this slab
     const uint32_t* ids;        // child + c0: the warp's run of child codes for this layer
     uint32_t ring;              // shared address of slot 0 of this warp's ring
     uint32_t bars;              // shared address of mbarrier 0 of this warp's ring
@@ -538,7 +543,21 @@ struct RowRing {
         uint32_t code[kGroupRows];
 #pragma unroll
         for (uint32_t r = 0; r < kGroupRows; ++r) code[r] = __shfl_sync(0xFFFFFFFFu, idreg, (i + r) & 31u);
-        if (elect_one()) {
+        if (G4) {
+            // one tensor copy gathers the four rows of the group (tile::gather4: a column offset and four row
+            // coordinates; rows land back to back).  A short last group repeats its first row: always 4 rows, 4 KB.
+            static_assert(!G4 || kGroupRows == 4, "tile::gather4 moves four rows");
+            uint32_t row[4];
+#pragma unroll
+            for (uint32_t r = 0; r < 4; ++r) row[r] = row0 + ((r < cnt ? code[r] : code[0]) & 0x7FFFFFFFu);
+            if (elect_one()) {
+                const uint32_t bar = bars + gi * 8u;
+                const uint32_t dst = ring + gi * (kGroupRows * kRowBytes);
+                mbar_expect_tx(bar, kGroupRows * kRowBytes);
+                asm volatile("cp.async.bulk.tensor.2d.shared::cta.global.tile::gather4.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5, %6}], [%7];"
+                             ::"r"(dst), "l"(tmap), "r"(0), "r"(row[0]), "r"(row[1]), "r"(row[2]), "r"(row[3]), "r"(bar) : "memory");
+            }
+        } else if (elect_one()) {
             const uint32_t bar = bars + gi * 8u;
             const uint32_t dst = ring + gi * (kGroupRows * kRowBytes);
             mbar_expect_tx(bar, cnt * kRowBytes);
@@ -583,8 +602,8 @@ struct RowRing {
     }
 };
 
-template <int OP>
-__device__ __forceinline__ Row ring_simple(RowRing& R, uint32_t n_plain, uint32_t n_comp) {
+template <int OP, class RR>
+__device__ __forceinline__ Row ring_simple(RR& R, uint32_t n_plain, uint32_t n_comp) {
     Row acc = splat<Row>(OP == kDevAnd ? 0xFFFFFFFFu : 0u);
     for (uint32_t j = 0; j < n_plain; ++j) {
         const Row v = R.pop();
@@ -597,8 +616,8 @@ __device__ __forceinline__ Row ring_simple(RowRing& R, uint32_t n_plain, uint32_
     return acc;
 }
 
-template <int P>
-__device__ __forceinline__ Row ring_range(RowRing& R, uint32_t n_plain, uint32_t n_comp, uint32_t lo, uint32_t hi) {
+template <int P, class RR>
+__device__ __forceinline__ Row ring_range(RR& R, uint32_t n_plain, uint32_t n_comp, uint32_t lo, uint32_t hi) {
     Row pl[P];
 #pragma unroll
     for (int p = 0; p < P; ++p) pl[p] = splat<Row>(0u);
@@ -634,16 +653,20 @@ __device__ __forceinline__ Row ring_range(RowRing& R, uint32_t n_plain, uint32_t
 #ifndef CANOPY_RING_MIN_BLOCKS
 #define CANOPY_RING_MIN_BLOCKS (4 / CANOPY_ROW_HALVES)  // same bytes of rows in flight per SM for either row size
 #endif
+// G4: child rows are fetched four at a time with tile::gather4 tensor copies through `vmap` (a 2-D view of the value
+// buffer, one tensor row per node row); otherwise one bulk copy per row (`vmap` unused).
+template <bool G4>
 #ifdef CANOPY_RING_MAXREG  // tuning knob: cap registers so one more sampler CTA fits beside the walk
 __global__ void __maxnreg__(CANOPY_RING_MAXREG)
 #else
 __global__ void __launch_bounds__(kGateThreads, CANOPY_RING_MIN_BLOCKS)
 #endif
-gate_ring_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const uint32_t* __restrict__ child,
-                 const uint32_t* __restrict__ layer_off, const uint32_t* __restrict__ wide_off,
-                 const uint32_t* __restrict__ split, const uint32_t* __restrict__ split_child,
-                 uint32_t n_layers, uint32_t n_nodes, uint32_t n_ev, unsigned long long* __restrict__ tallies,
-                 uint64_t first_slab, uint32_t n_slabs, uint64_t begin, uint64_t end) {
+gate_ring_kernel_t(const __grid_constant__ CUtensorMap vmap, uint4* __restrict__ vals, const uint4* __restrict__ grec,
+                   const uint32_t* __restrict__ child,
+                   const uint32_t* __restrict__ layer_off, const uint32_t* __restrict__ wide_off,
+                   const uint32_t* __restrict__ split, const uint32_t* __restrict__ split_child,
+                   uint32_t n_layers, uint32_t n_nodes, uint32_t n_ev, unsigned long long* __restrict__ tallies,
+                   uint64_t first_slab, uint32_t n_slabs, uint64_t begin, uint64_t end) {
     extern __shared__ __align__(128) unsigned char smem[];
     // Pipelined run: the sampler of the next batch is launched as a programmatic dependent of this walk and needs
     // nothing from it, so it may start as soon as every CTA of this (persistent, single-wave) grid is resident.
@@ -654,7 +677,8 @@ gate_ring_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const
     if (threadIdx.x < kGateWarps * kRingGroups) mbar_init(smem_u32(bars + threadIdx.x), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
-    RowRing R;
+    RowRing<G4> R;
+    R.tmap = &vmap; R.row0 = 0;
     R.lane = lane; R.lane_off = lane * 16u; R.gi_next = 0; R.phase = 0;
 #ifdef CANOPY_RING_DUMMY_U
     R.dummy = blockIdx.x; R.dummy_zero = (n_layers >> 30) << 3;  // zero at run time, unknown at compile time
@@ -664,6 +688,7 @@ gate_ring_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const
 
     for (uint32_t slab = blockIdx.x; slab < n_slabs; slab += gridDim.x) {
         uint4* base = vals + (size_t)slab * n_nodes * kRowVec;
+        R.row0 = slab * n_nodes;
         Row mask;
 #pragma unroll
         for (uint32_t h = 0; h < kRowHalves; ++h) {
@@ -739,6 +764,9 @@ gate_ring_kernel(uint4* __restrict__ vals, const uint4* __restrict__ grec, const
         }
     }
 }
+
+constexpr auto gate_ring_kernel = gate_ring_kernel_t<false>;     // bulk copy per row
+constexpr auto gate_ring_kernel_g4 = gate_ring_kernel_t<true>;  // tile::gather4, four rows per copy
 
 __global__ void finalize_kernel(unsigned long long* __restrict__ out, const unsigned long long* __restrict__ gate_tallies,
                                 const uint8_t* __restrict__ kind, const uint32_t* __restrict__ gate, uint32_t n,
@@ -863,6 +891,8 @@ struct DeviceState {
     uint32_t *ev_orig = nullptr, *thr32 = nullptr, *child = nullptr, *layer_off = nullptr, *tally_gate = nullptr;
     uint32_t *wide_off = nullptr, *split = nullptr, *split_child = nullptr;
     int ring_ctas_per_sm = 0;   // occupancy of gate_ring_kernel on this device
+    CUtensorMap vmap[2];        // tile::gather4 view of vals[b]: tensor row = node row of kRowBytes; valid iff vmap_ok[b]
+    bool vmap_ok[2] = {false, false};
     uint64_t* thr64 = nullptr;
     uint4* grec = nullptr;
     uint8_t* tally_kind = nullptr;
@@ -1018,6 +1048,7 @@ static DeviceInfo device_info(int device) {
     CUDA_CHECK(cudaSetDevice(device));
     // function attributes are per device (context): set once
     CUDA_CHECK(cudaFuncSetAttribute(gate_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmemBytes));
+    CUDA_CHECK(cudaFuncSetAttribute(gate_ring_kernel_g4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmemBytes));
     CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&I.ring_ctas_per_sm, gate_ring_kernel, kGateThreads, kRingSmemBytes));
@@ -1067,17 +1098,39 @@ static DeviceState* get_state(canopy_plan* plan, int device) {
     return s;
 }
 
+// 2-D tensor map over a value buffer for the gather4 copies of the gate walk: [rows][kRowBytes / 4] of uint32, box = one
+// row (tile::gather4 takes four row coordinates per copy).  Row coordinates are int32: larger buffers fall back to the
+// per-row bulk copies.
+static bool encode_vals_map(CUtensorMap* map, void* base, size_t bytes) {
+    static const auto encode = []() {
+        void* fn = nullptr; cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess) fn = nullptr;
+        return reinterpret_cast<CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                             const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                             CUtensorMapL2promotion, CUtensorMapFloatOOBfill)>(fn);
+    }();
+    static const bool off = getenv("CANOPY_RING_GATHER4") && !strcmp(getenv("CANOPY_RING_GATHER4"), "0");  // A/B knob
+    const size_t rows = bytes / kRowBytes;
+    if (off || !encode || rows == 0 || rows > 0x7FFFFFFFull) return false;
+    const cuuint64_t gdim[2] = {kRowBytes / 4, (cuuint64_t)rows};
+    const cuuint64_t gstr[1] = {kRowBytes};
+    const cuuint32_t box[2] = {kRowBytes / 4, 1}, estr[2] = {1, 1};
+    return encode(map, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, base, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 static void ensure_vals(DeviceState* s, const Lowered& L, size_t slabs, int n_bufs) {
     const size_t per_slab = (size_t)L.n_nodes() * kRowBytes;
     const size_t bytes = std::max<size_t>(slabs * per_slab, 16);
     bool ok = s->n_bufs >= n_bufs;
     for (int b = 0; ok && b < n_bufs; ++b) ok = s->vals_bytes[b] >= bytes;
     if (ok) { s->vals_slabs = std::max(s->vals_slabs, slabs); return; }
-    for (int b = 0; b < 2; ++b) { g_val_pool.release(s->device, s->vals[b], s->vals_bytes[b]); s->vals[b] = nullptr; s->vals_bytes[b] = 0; }
+    for (int b = 0; b < 2; ++b) { g_val_pool.release(s->device, s->vals[b], s->vals_bytes[b]); s->vals[b] = nullptr; s->vals_bytes[b] = 0; s->vmap_ok[b] = false; }
     s->vals_slabs = 0; s->n_bufs = 0;
     for (int b = 0; b < n_bufs; ++b) {
         s->vals[b] = static_cast<uint4*>(g_val_pool.acquire(s->device, bytes, &s->vals_bytes[b]));
         if (!s->vals[b]) throw Error(CANOPY_E_OOM, "cudaMalloc failed for the value buffer (" + std::to_string(bytes >> 20) + " MiB)");
+        s->vmap_ok[b] = encode_vals_map(&s->vmap[b], s->vals[b], s->vals_bytes[b]);
     }
     s->vals_slabs = slabs; s->n_bufs = n_bufs;
 }
@@ -1151,9 +1204,15 @@ static void launch_gates(const DeviceState* s, const Lowered& L, uint4* vals, ui
         const int want = cap > 0 ? cap : shared_sm ? kSharedRingCtas : s->ring_ctas_per_sm;
         const int per_sm = std::min(want, s->ring_ctas_per_sm);
         const uint32_t grid = std::min<uint32_t>(n_slabs, (uint32_t)(s->sm_count * per_sm));
-        gate_ring_kernel<<<grid, kGateThreads, kRingSmemBytes, st>>>(
-            vals, s->grec, s->child, s->layer_off, s->wide_off, s->split, s->split_child, L.n_layers(), L.n_nodes(),
-            L.n_events(), s->gate_tallies, first_slab, n_slabs, begin, end);
+        const int b = vals == s->vals[1] ? 1 : 0;
+        if (vals == s->vals[b] && s->vmap_ok[b] && kGroupRows == 4)
+            gate_ring_kernel_g4<<<grid, kGateThreads, kRingSmemBytes, st>>>(
+                s->vmap[b], vals, s->grec, s->child, s->layer_off, s->wide_off, s->split, s->split_child, L.n_layers(), L.n_nodes(),
+                L.n_events(), s->gate_tallies, first_slab, n_slabs, begin, end);
+        else
+            gate_ring_kernel<<<grid, kGateThreads, kRingSmemBytes, st>>>(
+                s->vmap[0], vals, s->grec, s->child, s->layer_off, s->wide_off, s->split, s->split_child, L.n_layers(), L.n_nodes(),
+                L.n_events(), s->gate_tallies, first_slab, n_slabs, begin, end);
     }
     CUDA_CHECK(cudaGetLastError());
 }
