@@ -93,7 +93,7 @@ def ncu_traffic(workload_name: str):
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE gate_ring_kernel launch (592 slabs) from the committed
     `ncu --set full` capture of this workload under profiles/, in bytes; None if there is no capture for it."""
     import csv
-    path = os.path.join(ROOT, "profiles", f"r01g_ncu_full_gate_{workload_name}.csv")
+    path = os.path.join(ROOT, "profiles", f"r01h_ncu_full_gate_{workload_name}.csv")
     scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
     try:
         tot = 0.0
