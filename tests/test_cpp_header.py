@@ -1,6 +1,7 @@
 """include/canopy-cpp.h compiles as plain C++17 against libcanopy.so and behaves: lowering works on a CPU box,
 running without a GPU fails loudly with CANOPY_E_CUDA (no CPU fallback), validity errors carry their status."""
 import os
+import re
 import subprocess
 
 import torch
@@ -31,3 +32,35 @@ def test_c_header_is_plain_c(tmp_path):
     subprocess.check_call(["gcc", "-std=c99", "-Wall", "-pedantic", "-I", os.path.join(ROOT, "include"), str(src), "-o", exe,
                            os.path.join(lib_dir, "libcanopy.so"), f"-Wl,-rpath,{lib_dir}"])
     assert subprocess.call([exe]) == 0
+
+
+def test_cmake_package_roundtrip(tmp_path):
+    """SURVEY.md 8b packaging: `cmake --install` gives lib `canopy` + exactly the two public headers + a relocatable
+    find_package(canopy) that sets CANOPY_INCLUDE_DIR / CANOPY_LIB_DIR / CANOPY_BIN_DIR (reference
+    cmake/canopy-config.cmake.in:8-10); a C++23 consumer links the imported target and runs."""
+    import shutil
+    import pytest
+    if not (shutil.which("cmake") and shutil.which("ninja") and shutil.which("nvcc")):
+        pytest.skip("cmake / ninja / nvcc not on PATH")
+    build, prefix, moved = tmp_path / "b", tmp_path / "prefix", tmp_path / "moved"
+    subprocess.check_call(["cmake", "-S", ROOT, "-B", str(build), "-G", "Ninja", f"-DCMAKE_INSTALL_PREFIX={prefix}",
+                           "-DBUILD_TESTS=OFF"], stdout=subprocess.DEVNULL)
+    subprocess.check_call(["cmake", "--build", str(build), "-j", "8"], stdout=subprocess.DEVNULL)
+    subprocess.check_call(["cmake", "--install", str(build)], stdout=subprocess.DEVNULL)
+    assert sorted(os.listdir(prefix / "include")) == ["canopy-cpp.h", "canopy.h"]
+    flags = (build / "build.ninja").read_text()
+    assert "arch=compute_100a,code=[sm_100a]" in flags and "-lineinfo" in flags
+    shutil.move(str(prefix), str(moved))     # relocatable: the package must not remember its install prefix
+    cbuild = tmp_path / "c"
+    cfg = subprocess.check_output(["cmake", "-S", os.path.join(ROOT, "tests", "cpp", "consumer"), "-B", str(cbuild), "-G", "Ninja",
+                                   f"-DCMAKE_PREFIX_PATH={moved}"], text=True)
+    assert f"CANOPY_INCLUDE_DIR={moved}/include" in cfg
+    lib_dir = re.search(r"CANOPY_LIB_DIR=(\S+)", cfg).group(1)      # lib or lib64 (GNUInstallDirs)
+    assert lib_dir.startswith(f"{moved}/lib")
+    assert f"CANOPY_BIN_DIR={moved}/bin" in cfg
+    subprocess.check_call(["cmake", "--build", str(cbuild)], stdout=subprocess.DEVNULL)
+    out = subprocess.check_output([str(cbuild / "consumer")], text=True)
+    assert "layers=1 gates=1 tallies=2" in out and "validity: status 2" in out
+    # the installed library exports the same C ABI as the Makefile build
+    nm = subprocess.check_output(["nm", "-D", "--defined-only", os.path.join(lib_dir, "libcanopy.so")], text=True)
+    assert " T canopy_plan_create" in nm and " T canopy_mc_run" in nm
