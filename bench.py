@@ -114,15 +114,15 @@ def workload(name: str):
     return g, synth.CONFIGS[name]["n_samples"]
 
 
-def cpu_arm(graph, n_samples_hint: int, tally_all: bool, seconds_target: float = 12.0):
+def cpu_arm(graph, n_samples_hint: int, tally_all: bool, seconds_target: float = 12.0, spec: int = 2):
     """Bit-packed multi-threaded CPU port (oracle/) on a bounded sample of the same workload."""
     from oracle import oracle as O
     cores = len(os.sched_getaffinity(0))
     probe = 1 << 12
-    t0 = time.perf_counter(); O.mc_packed(graph, 1, 0, probe, tally_all, nthreads=cores); dt = time.perf_counter() - t0
+    t0 = time.perf_counter(); O.mc_packed(graph, 1, 0, probe, tally_all, nthreads=cores, spec=spec); dt = time.perf_counter() - t0
     n = int(min(n_samples_hint, max(probe, probe * seconds_target / max(dt, 1e-6))))
     n = max(64, n // 64 * 64)
-    t0 = time.perf_counter(); t = O.mc_packed(graph, 1, 0, n, tally_all, nthreads=cores); dt = time.perf_counter() - t0
+    t0 = time.perf_counter(); t = O.mc_packed(graph, 1, 0, n, tally_all, nthreads=cores, spec=spec); dt = time.perf_counter() - t0
     return n / dt, cores, n, dt, t
 
 
@@ -133,19 +133,20 @@ def run_reference(args):
     g, S = workload(args.workload)
     tally_all = args.workload == "c3"
     from canopy_b200.engine import Plan
-    stats = Plan(g, tally_all).stats  # host lowering only: sizes for the config block
+    stats = Plan(g, tally_all, sampler=args.sampler).stats  # host lowering only: sizes for the config block
+    spec = stats["spec_version"]
     cores = len(os.sched_getaffinity(0))
     from oracle import oracle as O
     # bounded sample per step, sized from a probe so K+W steps end within a few minutes
     probe = 1 << 12
-    t0 = time.perf_counter(); O.mc_packed(g, 1, 0, probe, tally_all, nthreads=cores); dt = time.perf_counter() - t0
+    t0 = time.perf_counter(); O.mc_packed(g, 1, 0, probe, tally_all, nthreads=cores, spec=spec); dt = time.perf_counter() - t0
     budget = 120.0 / max(1, args.steps + args.warmup)
     n = int(max(probe, min(S, probe * budget / max(dt, 1e-6)))) // 64 * 64
     for w in range(args.warmup):
-        O.mc_packed(g, 1, 0, n, tally_all, nthreads=cores)
+        O.mc_packed(g, 1, 0, n, tally_all, nthreads=cores, spec=spec)
     t0 = time.perf_counter()
     for k in range(args.steps):
-        O.mc_packed(g, 1, (k + 1) * n, n, tally_all, nthreads=cores)
+        O.mc_packed(g, 1, (k + 1) * n, n, tally_all, nthreads=cores, spec=spec)
     dt = time.perf_counter() - t0
     v = n * args.steps / dt
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
@@ -178,6 +179,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="canopy_b200")
     ap.add_argument("--workload", default="c2", choices=["c1", "c2", "c3", "c4"])
+    ap.add_argument("--sampler", type=int, default=0, choices=[0, 1, 2, 3],
+                    help="sampling spec of the plan (0 = build default; include/canopy.h CANOPY_SAMPLER_*)")
     ap.add_argument("--no-study", action="store_true", help="skip the bounded c4 roofline study on rank 0")
     ap.add_argument("--samples", type=int, default=0,
                     help="samples per step per GPU instead of the workload's full count (side studies only; the line says so)")
@@ -206,7 +209,7 @@ def main():
     if args.samples:
         S = args.samples
     tally_all = args.workload == "c3"
-    plan = Plan(g, tally_all)
+    plan = Plan(g, tally_all, sampler=args.sampler)
     stats = plan.stats
     nt = plan.n_tallies
     tallies = torch.zeros(max(nt, 1), dtype=torch.int64, device=dev)
@@ -257,7 +260,7 @@ def main():
     host_out = torch.zeros(max(nt, 1), dtype=torch.int64).pin_memory()
 
     def e2e_step(k):
-        p2 = Plan(g, tally_all)                       # host lowering from HOST arrays
+        p2 = Plan(g, tally_all, sampler=args.sampler)  # host lowering from HOST arrays
         r = p2.run_device(tallies.data_ptr(), S, seed=0xB200, sample_begin=(k * world + rank) * S, device=local,
                           stream=stream, want_report=True)   # uploads the CSR arrays (h2d) and runs
         if world > 1:
@@ -332,11 +335,11 @@ def main():
             "top_event_tally_last_step": top_tally,
         }
     if world == 1 and rank == 0:
-        cpu_v, cores, n_cpu, dt_cpu, _ = cpu_arm(g, S, tally_all)
+        cpu_v, cores, n_cpu, dt_cpu, _ = cpu_arm(g, S, tally_all, spec=stats["spec_version"])
         line["cpu_baseline"] = {"value": cpu_v, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": f"{n_cpu} samples of {args.workload} in {dt_cpu:.1f} s (bit-packed pthreads port in oracle/)"}
         if not args.no_study and args.workload != "c4":
-            line["roofline_study_c4"] = c4_study(local, stream, peaks)
+            line["roofline_study_c4"] = c4_study(local, stream, peaks, sampler=args.sampler)
     if rank == 0:
         if args.samples:
             line["config"]["reduced"] = f"--samples {args.samples}: side study, NOT the workload's full sample count"
@@ -346,12 +349,12 @@ def main():
     return 0
 
 
-def c4_study(local, stream, peaks, n=1 << 24):
+def c4_study(local, stream, peaks, n=1 << 24, sampler=0):
     """Bounded pass over the 100k-event / 60k-gate DAG (BASELINE.json config 4): per-kernel numbers."""
     from canopy_b200 import synth
     from canopy_b200.engine import Plan
     g = synth.config_graph("c4")
-    with Plan(g) as plan:
+    with Plan(g, sampler=sampler) as plan:
         st = plan.stats
         plan.run(n // 4, seed=7, device=local)
         _, full = plan.run(n, seed=7, device=local)

@@ -110,6 +110,7 @@ SYMBOLS = {
     "canopy_status_string": (C.c_char_p, [C.c_int]),
     "canopy_version": (C.c_uint32, []),
     "canopy_spec_version": (C.c_uint32, []),
+    "canopy_sparse_cdf": (C.c_int, [C.c_uint32, C.POINTER(C.c_uint64)]),
 }
 
 _LIB = None

@@ -224,6 +224,14 @@ const char* canopy_status_string(canopy_status s) {
 uint32_t canopy_version(void) { return (CANOPY_VERSION_MAJOR << 16) | CANOPY_VERSION_MINOR; }
 uint32_t canopy_spec_version(void) { return CANOPY_SPEC_VERSION; }
 
+canopy_status canopy_sparse_cdf(uint32_t thr32, uint64_t* out_cdf) {
+    return guard([&] {
+        require(out_cdf != nullptr, "canopy_sparse_cdf: null output");
+        require(thr32 != 0 && (thr32 >> (32 - CANOPY_SPARSE_MIN_ZEROS)) == 0, "canopy_sparse_cdf: threshold is not in the sparse range");
+        canopy::sparse_cdf(thr32, out_cdf);
+    });
+}
+
 }  // extern "C"
 
 namespace canopy {

@@ -128,11 +128,66 @@ template <> struct TailQueue<64> {
 #ifndef CANOPY_SLICED_SLABS_PER_WARP
 #define CANOPY_SLICED_SLABS_PER_WARP 8
 #endif
-template <int BITS>
+// Spec 3, sparse events: per 128-sample group ONE Philox call, ctr = (g, e, 0x400).  Words 0-1
+// are a 64-bit variate U; the number of ones of the group is N = #{j : U >= cdf_j} (Binomial(128, p) by inversion);
+// 7-bit fields of words 2-3 (then of calls 0x401, 0x402, ...: 16 fields each) are the positions, a field naming a
+// position already taken is skipped.  One lane = one group, as in the plane path; the count loop is warp-uniform
+// (table entries are broadcast loads), the placement loop runs max-N-of-the-warp times.
+__device__ __forceinline__ void sparse_rows(uint4* __restrict__ vals, const uint64_t* __restrict__ tab, uint32_t ev, uint32_t e,
+                                            uint32_t n_nodes, uint64_t first_slab, uint32_t n_slabs, const PhiloxKeys& K) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t c0 = __ldg(tab), c1 = __ldg(tab + 1);
+    const uint32_t n_blk = n_slabs * kRowHalves;
+    for (uint32_t blk = blockIdx.y; blk < n_blk; blk += gridDim.y) {
+        uint4* row = vals + ((size_t)(blk / kRowHalves) * n_nodes + ev) * kRowVec + (blk % kRowHalves) * 32u + lane;
+        const uint64_t g = (first_slab * kRowHalves + blk) * 32u + lane;
+        const uint32_t g_lo = (uint32_t)g, g_hi = (uint32_t)(g >> 32);
+        const uint4 x = philox4x32_10(g_lo, g_hi, e, 0x400u, K);
+        const uint64_t U = ((uint64_t)x.y << 32) | x.x;
+        uint32_t n = (U >= c0 ? 1u : 0u) + (U >= c1 ? 1u : 0u);
+        if (__any_sync(0xFFFFFFFFu, U >= c1)) {
+#pragma unroll 1
+            for (uint32_t j = 2; j < CANOPY_SPARSE_CDF_LEN; ++j) {
+                const bool ge = U >= __ldg(tab + j);
+                if (!__any_sync(0xFFFFFFFFu, ge)) break;
+                n += ge ? 1u : 0u;
+            }
+        }
+        uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0;
+        uint32_t f = x.z, i = 0;   // f: the unread fields of the current word, next field in its low 7 bits
+        uint4 ext = x;
+#pragma unroll 1
+        while (n) {
+            if ((i & 3u) == 0u && i) {  // word exhausted: fields 4-7 are word 3 of call 0x400, field 8 + 16c + 4w + .. word w of call 0x401 + c
+                if (i == 4u) f = x.w;
+                else {
+                    const uint32_t i2 = i - 8u;
+                    if ((i2 & 15u) == 0u) ext = philox4x32_10(g_lo, g_hi, e, 0x401u + (i2 >> 4), K);
+                    const uint32_t w = (i2 >> 2) & 3u;
+                    f = w == 0 ? ext.x : w == 1 ? ext.y : w == 2 ? ext.z : ext.w;
+                }
+            }
+            const uint32_t pos = f & 127u;
+            f >>= 7; ++i;
+            const uint32_t b = 1u << (pos & 31u), w = pos >> 5;
+            const uint32_t cur = w == 0 ? r0 : w == 1 ? r1 : w == 2 ? r2 : r3;
+            if (!(cur & b)) {
+                --n;
+                r0 |= w == 0 ? b : 0u; r1 |= w == 1 ? b : 0u; r2 |= w == 2 ? b : 0u; r3 |= w == 3 ? b : 0u;
+            }
+        }
+        st_cg(row, make_uint4(r0, r1, r2, r3));
+    }
+}
+
+// SPARSE (spec 3): the warps take the events in the order ev_perm (sliced events first); an event with fewer than
+// one expected 1 per 128-sample group (thr < 2^(32 - CANOPY_SPARSE_MIN_ZEROS)) takes sparse_rows() instead of the planes.
+template <int BITS, bool SPARSE>
 __global__ void __launch_bounds__(256, CANOPY_SLICED_MIN_BLOCKS)
 sampler_sliced_kernel(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_orig,
                       const uint32_t* __restrict__ thr32, const uint64_t* __restrict__ thr64,
-                      uint32_t n_ev, uint32_t n_nodes, uint64_t first_slab, uint32_t n_slabs, PhiloxKeys Kparam) {
+                      uint32_t n_ev, uint32_t n_nodes, uint64_t first_slab, uint32_t n_slabs, PhiloxKeys Kparam,
+                      const uint32_t* __restrict__ ev_perm, const uint64_t* __restrict__ cdf) {
 #ifdef CANOPY_KEYS_IN_REGS  // tuning knob: round keys in vector registers instead of uniform registers
     PhiloxKeys K;
 #pragma unroll
@@ -144,11 +199,19 @@ sampler_sliced_kernel(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_
     const PhiloxKeys& K = Kparam;
 #endif
     const uint32_t lane = threadIdx.x & 31;
-    const uint32_t ev = blockIdx.x * (blockDim.x >> 5) + bcast0(threadIdx.x >> 5);
+    uint32_t ev = blockIdx.x * (blockDim.x >> 5) + bcast0(threadIdx.x >> 5);
     if (ev >= n_ev) return;
+    if (SPARSE) ev = bcast0(__ldg(ev_perm + ev));
     // Everything that depends on the event only is loaded once per warp and broadcast, so the compiler keeps
     // it in uniform registers and the per-plane branch on the threshold bit is a uniform branch.
     const uint32_t e = bcast0(__ldg(ev_orig + ev));
+    if (SPARSE && BITS == 32) {
+        const uint32_t t = bcast0(__ldg(thr32 + ev));
+        if ((t >> (32 - CANOPY_SPARSE_MIN_ZEROS)) == 0) {
+            sparse_rows(vals, cdf + (size_t)ev * CANOPY_SPARSE_CDF_LEN, ev, e, n_nodes, first_slab, n_slabs, K);
+            return;
+        }
+    }
     uint32_t head;                 // top H bits of the threshold, left-aligned in a 32-bit word
     uint32_t tail32 = 0; uint64_t tail64 = 0;  // (thr mod 2^(BITS-H)) << H: compared with the raw tail variate
     if (BITS == 32) { const uint32_t t = bcast0(__ldg(thr32 + ev)); head = t; tail32 = t << kHeadBits; }
@@ -894,6 +957,8 @@ struct DeviceState {
     CUtensorMap vmap[2];        // tile::gather4 view of vals[b]: tensor row = node row of kRowBytes; valid iff vmap_ok[b]
     bool vmap_ok[2] = {false, false};
     uint64_t* thr64 = nullptr;
+    uint32_t* ev_perm = nullptr;   // spec 3 only
+    uint64_t* ev_cdf = nullptr;    // spec 3 only
     uint4* grec = nullptr;
     uint8_t* tally_kind = nullptr;
     unsigned long long* gate_tallies = nullptr;
@@ -1049,8 +1114,9 @@ static DeviceInfo device_info(int device) {
     // function attributes are per device (context): set once
     CUDA_CHECK(cudaFuncSetAttribute(gate_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmemBytes));
     CUDA_CHECK(cudaFuncSetAttribute(gate_ring_kernel_g4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmemBytes));
-    CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&I.ring_ctas_per_sm, gate_ring_kernel, kGateThreads, kRingSmemBytes));
     if (I.ring_ctas_per_sm < 1) throw Error(CANOPY_E_CUDA, "gate_ring_kernel does not fit on an SM");
     int lo_prio = 0;
@@ -1073,6 +1139,7 @@ static DeviceState* get_state(canopy_plan* plan, int device) {
         A.add(s->child, L.child); A.add(s->layer_off, L.layer_off); A.add(s->tally_gate, L.tally_gate);
         A.add(s->wide_off, L.wide_off); A.add(s->split, L.split); A.add(s->split_child, L.split_child);
         A.add(s->tally_kind, L.tally_kind); A.add(s->grec, L.gate_rec);
+        A.add(s->ev_cdf, L.event_cdf); A.add(s->ev_perm, L.event_perm);
         A.reserve(s->gate_tallies, std::max<size_t>(L.n_gates(), 1) * 8);
         A.reserve(s->out_tallies, std::max<size_t>(L.tally_kind.size(), 1) * 8);
         if (cudaMalloc(&s->arena, A.total) != cudaSuccess) { cudaGetLastError(); throw Error(CANOPY_E_OOM, "cudaMalloc failed for plan arrays"); }
@@ -1161,7 +1228,7 @@ static void launch_sampler(const DeviceState* s, const Lowered& L, uint4* vals, 
 #define CANOPY_SAMPLER_ARGS vals, s->ev_orig, s->thr32, s->thr64, L.n_events(), L.n_nodes(), first_slab, K
 #define CANOPY_SLICED_ARGS vals, s->ev_orig, s->thr32, s->thr64, L.n_events(), L.n_nodes(), first_slab, n_slabs, K
     static const int pack = getenv("CANOPY_SAMPLER_PACK") ? atoi(getenv("CANOPY_SAMPLER_PACK")) : 1;  // tuning knob
-    if (L.opts.sampler == CANOPY_SAMPLER_SLICED) {
+    if (L.opts.sampler == CANOPY_SAMPLER_SLICED || L.opts.sampler == CANOPY_SAMPLER_SPARSE) {
         // tuning knob: dynamic shared memory requested only to cap the sampler's CTAs per SM (room for gate CTAs)
         static const int env_smem = getenv("CANOPY_SAMPLER_SMEM") ? atoi(getenv("CANOPY_SAMPLER_SMEM")) : -1;
         // (a programmatic dependent starts after the walk's CTAs are resident: no room has to be kept for them)
@@ -1173,12 +1240,14 @@ static void launch_sampler(const DeviceState* s, const Lowered& L, uint4* vals, 
         attr[0].val.programmaticStreamSerializationAllowed = 1;
         cfg.attrs = attr; cfg.numAttrs = pdl ? 1 : 0;
         const uint32_t n_ev = L.n_events(), n_nodes = L.n_nodes();
-        if (L.opts.threshold_bits == 64)
-            CUDA_CHECK(cudaLaunchKernelEx(&cfg, sampler_sliced_kernel<64>, vals, (const uint32_t*)s->ev_orig, (const uint32_t*)s->thr32,
-                                          (const uint64_t*)s->thr64, n_ev, n_nodes, first_slab, n_slabs, K));
-        else
-            CUDA_CHECK(cudaLaunchKernelEx(&cfg, sampler_sliced_kernel<32>, vals, (const uint32_t*)s->ev_orig, (const uint32_t*)s->thr32,
-                                          (const uint64_t*)s->thr64, n_ev, n_nodes, first_slab, n_slabs, K));
+        // spec 3 with 64-bit thresholds is spec 2 (no event takes the sparse path): the plain kernel serves it
+        const bool sparse = L.opts.sampler == CANOPY_SAMPLER_SPARSE && L.opts.threshold_bits == 32;
+        auto kern = L.opts.threshold_bits == 64 ? sampler_sliced_kernel<64, false>
+                    : sparse                    ? sampler_sliced_kernel<32, true>
+                                                : sampler_sliced_kernel<32, false>;
+        CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, vals, (const uint32_t*)s->ev_orig, (const uint32_t*)s->thr32,
+                                      (const uint64_t*)s->thr64, n_ev, n_nodes, first_slab, n_slabs, K,
+                                      (const uint32_t*)s->ev_perm, (const uint64_t*)s->ev_cdf));
     }
     else if (L.opts.threshold_bits == 64) sampler_kernel<64, 0><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
     else if (pack == 0) sampler_kernel<32, 0><<<grid, block, 0, st>>>(CANOPY_SAMPLER_ARGS);
@@ -1398,6 +1467,10 @@ void refresh_thresholds(canopy_plan* plan) {
         if (!L.event_thr32.empty()) {
             CUDA_CHECK(cudaMemcpy(s->thr32, L.event_thr32.data(), L.event_thr32.size() * 4, cudaMemcpyHostToDevice));
             CUDA_CHECK(cudaMemcpy(s->thr64, L.event_thr64.data(), L.event_thr64.size() * 8, cudaMemcpyHostToDevice));
+        }
+        if (!L.event_perm.empty()) {   // spec 3: tables and warp order follow the thresholds (sizes do not change)
+            CUDA_CHECK(cudaMemcpy(s->ev_cdf, L.event_cdf.data(), L.event_cdf.size() * 8, cudaMemcpyHostToDevice));
+            CUDA_CHECK(cudaMemcpy(s->ev_perm, L.event_perm.data(), L.event_perm.size() * 4, cudaMemcpyHostToDevice));
         }
     }
 }

@@ -149,8 +149,8 @@ std::vector<uint32_t> topo_order(const canopy_graph_desc& d) {
 void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lowered& L) {
     if (opts.threshold_bits != 32 && opts.threshold_bits != 64)
         fail(CANOPY_E_INVALID, "threshold_bits must be 32 or 64");
-    if (opts.sampler != CANOPY_SAMPLER_DIRECT && opts.sampler != CANOPY_SAMPLER_SLICED)
-        fail(CANOPY_E_INVALID, "sampler must be CANOPY_SAMPLER_DIRECT (1) or CANOPY_SAMPLER_SLICED (2)");
+    if (opts.sampler != CANOPY_SAMPLER_DIRECT && opts.sampler != CANOPY_SAMPLER_SLICED && opts.sampler != CANOPY_SAMPLER_SPARSE)
+        fail(CANOPY_E_INVALID, "sampler must be CANOPY_SAMPLER_DIRECT (1), CANOPY_SAMPLER_SLICED (2) or CANOPY_SAMPLER_SPARSE (3)");
     validate(d);
     const uint32_t B = d.n_basic, G = d.n_gates;
     const bool tally_all = opts.tally_all_gates != 0;
@@ -397,6 +397,43 @@ void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lower
     s.max_fanin = max_fanin; s.mean_fanin = L.n_gates() ? (double)L.child.size() / L.n_gates() : 0.0;
     s.n_tallies = n_tallies; s.n_const_nodes = n_const; s.n_alias_nodes = n_alias;
     s.spec_version = (uint32_t)opts.sampler;  // spec number == sampler id
+    build_sparse_tables(L);
+}
+
+// Spec 3: cumulative table of Binomial(128, t / 2^32) in 0.64 fixed point, exact integer
+// arithmetic so that every implementation of the spec gets the same 64-bit words.
+//   a_0 = (1 - p)^128 by seven truncating squarings of (2^32 - t) * 2^32
+//   a_{j+1} = floor(a_j * (128 - j) * t / ((j + 1) * (2^32 - t)))          (fits 128 bits for t < 2^25)
+//   cdf_j = a_0 + ... + a_j
+void sparse_cdf(uint32_t t, uint64_t* cdf) {
+    typedef unsigned __int128 u128;
+    const uint64_t q = 4294967296ull - t;
+    uint64_t x = q << 32;
+    for (int i = 0; i < 7; ++i) x = (uint64_t)(((u128)x * x) >> 64);
+    u128 sum = 0;
+    uint64_t a = x;
+    for (uint32_t j = 0; j < CANOPY_SPARSE_CDF_LEN; ++j) {
+        sum += a;
+        cdf[j] = sum > (u128)~0ull ? ~0ull : (uint64_t)sum;
+        a = (uint64_t)(((u128)a * (128u - j) * t) / ((u128)(j + 1) * q));
+    }
+}
+
+// Per-plan arrays of spec 3: which events take the sparse path (their tables), and the order in which the sampler's
+// warps take the events (sliced events first, so that the CTAs still running at the end of a launch are the cheap ones).
+void build_sparse_tables(Lowered& L) {
+    const uint32_t n = L.n_events();
+    L.event_cdf.clear(); L.event_perm.clear();
+    if (L.opts.sampler != CANOPY_SAMPLER_SPARSE) return;
+    L.event_cdf.assign((size_t)n * CANOPY_SPARSE_CDF_LEN, ~0ull);
+    L.event_perm.reserve(n);
+    const bool narrow = L.opts.threshold_bits == 32;
+    auto sparse = [&](uint32_t i) { return narrow && (L.event_thr32[i] >> (32 - CANOPY_SPARSE_MIN_ZEROS)) == 0; };
+    for (uint32_t i = 0; i < n; ++i) if (!sparse(i)) L.event_perm.push_back(i);
+    for (uint32_t i = 0; i < n; ++i) if (sparse(i)) {
+        L.event_perm.push_back(i);
+        sparse_cdf(L.event_thr32[i], &L.event_cdf[(size_t)i * CANOPY_SPARSE_CDF_LEN]);
+    }
 }
 
 void shard_range(uint64_t begin, uint64_t n, int rank, int world, uint64_t* ob, uint64_t* on) {
@@ -439,6 +476,7 @@ void requantise(Lowered& L, const double* p, uint32_t n_basic) {
         L.event_thr32[i] = wide ? (uint32_t)(t >> 32) : (uint32_t)t;
         L.event_thr64[i] = wide ? t : (t << 32);
     }
+    build_sparse_tables(L);
 }
 
 uint64_t fingerprint(const Lowered& L) {

@@ -58,6 +58,8 @@ struct Lowered {
     std::vector<uint32_t> event_orig;
     std::vector<uint32_t> event_thr32;
     std::vector<uint64_t> event_thr64;
+    std::vector<uint64_t> event_cdf;       // spec 3: [n_events][CANOPY_SPARSE_CDF_LEN] cumulative count tables (empty otherwise)
+    std::vector<uint32_t> event_perm;      // spec 3: order in which the sampler's warps take the live events (empty otherwise)
     std::vector<uint8_t> event_class;      // [n_basic_in] how lowering classed each ORIGINAL event: 0 false, 1 true, 2 sampled/dead
     // live gates in layer order; device node id == n_events + position
     std::vector<GateRec> gate_rec;
@@ -82,6 +84,8 @@ void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lower
 // Re-quantise the thresholds of the live events from new probabilities (canopy_plan_update_p); throws if the
 // constant folding of the existing lowering would no longer hold.
 void requantise(Lowered& L, const double* p, uint32_t n_basic);
+void sparse_cdf(uint32_t thr32, uint64_t* cdf);   // spec 3 count table of one event (CANOPY_SPARSE_CDF_LEN words)
+void build_sparse_tables(Lowered& L);
 uint64_t fingerprint(const Lowered& L);
 
 struct DeviceState;  // engine.cu

@@ -28,7 +28,7 @@ class Settings:
     sample_begin: int = 0       # first global sample index (restart / shard by counter range)
     tally_all_gates: bool = False
     threshold_bits: int = 32
-    sampler: int = 0            # sampling spec: 0 = library default (2, "sliced"), 1 = "direct", 2 = "sliced"
+    sampler: int = 0            # sampling spec: 0 = library default (2, "sliced"), 1 = "direct", 2 = "sliced", 3 = "sparse"
     overlap: bool = True
     profile: bool = False
 
@@ -41,8 +41,8 @@ class Settings:
             raise SettingsError("The batch size cannot be negative.")
         if self.threshold_bits not in (32, 64):
             raise SettingsError("threshold_bits must be 32 or 64")
-        if self.sampler not in (0, 1, 2):
-            raise SettingsError("sampler must be 0 (default), 1 (direct) or 2 (sliced)")
+        if self.sampler not in (0, 1, 2, 3):
+            raise SettingsError("sampler must be 0 (default), 1 (direct), 2 (sliced) or 3 (sparse)")
         return self
 
 

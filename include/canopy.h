@@ -46,21 +46,35 @@ extern "C" {
 #define CANOPY_VERSION_MAJOR 0
 #define CANOPY_VERSION_MINOR 1
 /* Version of the sampling specification. Tallies are a pure function of
- * (spec version, graph, seed, sample range). Two specs are implemented and selected per plan
- * (canopy_plan_opts.sampler); both draw Philox4x32-10 variates and compare them with the event threshold:
+ * (spec version, graph, seed, sample range). Three specs are implemented and selected per plan
+ * (canopy_plan_opts.sampler); all draw Philox4x32-10 variates and compare them with thresholds derived from
+ * the event probability:
  *   spec 1  "direct": one 32/64-bit variate per (event, sample), compared whole.
  *   spec 2  "sliced": the same comparison evaluated MSB-first; the top CANOPY_SLICED_HEAD_BITS bits of
  *           the variates of 128 consecutive samples come from that many bit-sliced Philox calls, the
  *           remaining bits from tail calls that only the ~2^-H samples still undecided after the head
  *           bits ever consume (4 undecided samples per call; 2 with 64-bit thresholds).
+ *   spec 3  "sparse": spec 2 for every event with p >= 2^-CANOPY_SPARSE_MIN_ZEROS (and for all events with 64-bit
+ *           thresholds).  A rarer event draws, per 128-sample group, ONE Philox call: a 64-bit variate compared with
+ *           the event's Binomial(128, thr/2^32) cumulative table (CANOPY_SPARSE_CDF_LEN entries, exact integer
+ *           arithmetic) gives the number of ones of the group, 7-bit fields of the same call place them (duplicates
+ *           skipped; further calls only if the fields run out).  Same i.i.d. Bernoulli(thr/2^32) law per sample up to
+ *           the table's rounding (below 2^-55) and the mass beyond CANOPY_SPARSE_CDF_LEN ones (below 1e-18).
  * CANOPY_SPEC_VERSION is the default spec of this build. */
-#define CANOPY_SPEC_VERSION 2
+#define CANOPY_SPEC_VERSION 3
 #ifndef CANOPY_SLICED_HEAD_BITS
 #define CANOPY_SLICED_HEAD_BITS 7   /* H of spec 2; part of the spec (changing it changes every tally) */
 #endif
-#define CANOPY_SAMPLER_DEFAULT 0   /* = the build default (spec 2) */
+#define CANOPY_SAMPLER_DEFAULT 0   /* = the build default (spec 3) */
 #define CANOPY_SAMPLER_DIRECT  1   /* spec 1 */
 #define CANOPY_SAMPLER_SLICED  2   /* spec 2 */
+#define CANOPY_SAMPLER_SPARSE  3   /* spec 3 */
+#ifndef CANOPY_SPARSE_MIN_ZEROS
+#define CANOPY_SPARSE_MIN_ZEROS 5  /* spec 3: events with thr32 < 2^(32-5), i.e. fewer than four expected ones per 128-sample group */
+#endif
+#ifndef CANOPY_SPARSE_CDF_LEN
+#define CANOPY_SPARSE_CDF_LEN  32  /* spec 3: entries of the cumulative count table = largest count a group can draw */
+#endif
 
 typedef enum canopy_status {
     CANOPY_OK = 0,
@@ -307,6 +321,9 @@ CANOPY_API const char* canopy_last_error(void);   /* thread-local; valid until t
 CANOPY_API const char* canopy_status_string(canopy_status s);
 CANOPY_API uint32_t    canopy_version(void);      /* major<<16 | minor */
 CANOPY_API uint32_t    canopy_spec_version(void);
+/* Spec 3: the cumulative count table (CANOPY_SPARSE_CDF_LEN words, 0.64 fixed point) a plan builds for a sparse event
+ * with 32-bit threshold thr32 (0 < thr32 < 2^(32 - CANOPY_SPARSE_MIN_ZEROS)).  Host only; a parity hook for the tests. */
+CANOPY_API canopy_status canopy_sparse_cdf(uint32_t thr32, uint64_t* out_cdf);
 
 #ifdef __cplusplus
 } /* extern "C" */

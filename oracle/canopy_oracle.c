@@ -73,6 +73,57 @@ double oracle_quantised_p(double p, int bits) {
     return bits == 32 ? (double)thr / 4294967296.0 : (double)thr / 18446744073709551616.0;
 }
 
+/* ------------------------------------------------------------------------------------------------
+ * spec 3 "sparse" (DESIGN.md section 1), events with thr < 2^(32 - CANOPY_SPARSE_MIN_ZEROS), 32-bit thresholds.
+ * Count table: cdf_j = a_0 + ... + a_j in 0.64 fixed point, a_0 = (1-p)^128 by seven truncating squarings,
+ * a_{j+1} = floor(a_j (128-j) t / ((j+1)(2^32 - t))).  All integer, so every implementation gets the same words.
+ * ---------------------------------------------------------------------------------------------- */
+void oracle_sparse_cdf(uint32_t t, uint64_t* cdf) {
+    unsigned __int128 acc = 0;
+    uint64_t one_minus_p = (uint64_t)(4294967296ull - t) << 32;
+    uint64_t a = one_minus_p;
+    for (int sq = 0; sq < 7; ++sq) a = (uint64_t)(((unsigned __int128)a * a) >> 64);
+    for (unsigned j = 0; j < CANOPY_SPARSE_CDF_LEN; ++j) {
+        acc += a;
+        cdf[j] = (acc >> 64) ? ~0ull : (uint64_t)acc;
+        unsigned __int128 num = (unsigned __int128)a * (128u - j) * t;
+        unsigned __int128 den = (unsigned __int128)(j + 1u) * (4294967296ull - t);
+        a = (uint64_t)(num / den);
+    }
+}
+
+static int is_sparse_event(int spec, uint64_t thr, int bits) {
+    return spec == 3 && bits == 32 && ((uint32_t)thr >> (32 - CANOPY_SPARSE_MIN_ZEROS)) == 0;
+}
+
+/* Field i of group g of event e, straight from the text: fields 0-7 are the 7-bit digits of words 2 and 3 of call
+ * 0x400, field 8 + 16c + 4w + d is digit d of word w of call 0x401 + c. */
+static unsigned sparse_field(const uint32_t key[2], uint32_t e, uint64_t g, unsigned i) {
+    uint32_t ctr[4] = {(uint32_t)g, (uint32_t)(g >> 32), e, 0x400u}, out[4];
+    unsigned word, digit = i & 3u;
+    if (i < 8) word = 2 + (i >> 2);
+    else { ctr[3] = 0x401u + ((i - 8) >> 4); word = ((i - 8) >> 2) & 3u; }
+    oracle_philox4x32_10(ctr, key, out);
+    return (out[word] >> (7 * digit)) & 127u;
+}
+
+/* Definition form: the 128 sample values of one group as one flag per sample. */
+static void sparse_group_flags(uint64_t seed, uint32_t e, uint64_t g, uint32_t t, unsigned char flag[128]) {
+    uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
+    uint32_t ctr[4] = {(uint32_t)g, (uint32_t)(g >> 32), e, 0x400u}, out[4];
+    uint64_t cdf[CANOPY_SPARSE_CDF_LEN];
+    oracle_sparse_cdf(t, cdf);
+    oracle_philox4x32_10(ctr, key, out);
+    uint64_t U = ((uint64_t)out[1] << 32) | out[0];
+    unsigned n = 0;
+    for (unsigned j = 0; j < CANOPY_SPARSE_CDF_LEN; ++j) n += U >= cdf[j];
+    memset(flag, 0, 128);
+    for (unsigned i = 0, placed = 0; placed < n; ++i) {
+        unsigned pos = sparse_field(key, e, g, i);
+        if (!flag[pos]) { flag[pos] = 1; ++placed; }
+    }
+}
+
 /* The variate u(e, s) of DESIGN.md section 1, straight from its definition, and the basic-event bit
  * x = u < thr.  spec 1 "direct": one Philox call per 4 (2) samples, output word s&3 (pair s&1).
  * spec 2 "sliced": the top H = CANOPY_SLICED_HEAD_BITS bits of u from H bit-sliced calls of the sample's
@@ -83,6 +134,12 @@ int oracle_sample_bit(uint64_t seed, uint32_t e, uint64_t s, int kind, uint64_t 
     if (kind == 1) return 1;
     uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
     uint32_t ctr[4], out[4];
+    if (is_sparse_event(spec, thr, bits)) {
+        unsigned char flag[128];
+        sparse_group_flags(seed, e, s >> 7, (uint32_t)thr, flag);
+        return flag[s & 127];
+    }
+    /* spec 3 is spec 2 for every other event */
     if (spec == 1) {
         if (bits == 32) {
             uint64_t q = s >> 2;
@@ -200,12 +257,54 @@ static void sliced_group_words(uint64_t seed, uint32_t e, uint64_t g, int kind, 
     out2[1] = ((uint64_t)res[3] << 32) | res[2];
 }
 
-/* Words 2g and 2g+1 (samples [128g, 128g+128)) of one basic event under either spec. */
-static void group_words(int spec, uint64_t seed, uint32_t e, uint64_t g, int kind, uint64_t thr, int bits, uint64_t out2[2]) {
+/* spec 3, sparse event: the group's words in streaming form (one call, fields consumed word by word, further calls
+ * only when the fields run out).  Must agree with sparse_group_flags; tests/test_oracle.py checks it. */
+static void sparse_group_words(uint64_t seed, uint32_t e, uint64_t g, uint32_t t, const uint64_t* cdf, uint64_t out2[2]) {
+    uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
+    uint32_t ctr[4] = {(uint32_t)g, (uint32_t)(g >> 32), e, 0x400u}, x[4];
+    (void)t;
+    oracle_philox4x32_10(ctr, key, x);
+    uint64_t U = ((uint64_t)x[1] << 32) | x[0];
+    unsigned n = 0;
+    while (n < CANOPY_SPARSE_CDF_LEN && U >= cdf[n]) ++n;   /* cdf is non-decreasing */
+    uint32_t res[4] = {0, 0, 0, 0};
+    unsigned word = 2, digit = 0;
+    while (n) {
+        if (digit == 4) {
+            digit = 0;
+            if (++word == 4) { word = 0; ++ctr[3]; oracle_philox4x32_10(ctr, key, x); }
+        }
+        unsigned pos = (x[word] >> (7 * digit)) & 127u;
+        ++digit;
+        uint32_t b = 1u << (pos & 31);
+        if (!(res[pos >> 5] & b)) { res[pos >> 5] |= b; --n; }
+    }
+    out2[0] = ((uint64_t)res[1] << 32) | res[0];
+    out2[1] = ((uint64_t)res[3] << 32) | res[2];
+}
+
+/* Words 2g and 2g+1 (samples [128g, 128g+128)) of one basic event under any spec. */
+static void group_words_tab(int spec, uint64_t seed, uint32_t e, uint64_t g, int kind, uint64_t thr, int bits, const uint64_t* tab, uint64_t out2[2]) {
     if (spec == 1) {
         out2[0] = packed_sample_word(seed, e, 2 * g, kind, thr, bits);
         out2[1] = packed_sample_word(seed, e, 2 * g + 1, kind, thr, bits);
+    } else if (kind == 2 && is_sparse_event(spec, thr, bits)) {
+        uint64_t cdf[CANOPY_SPARSE_CDF_LEN];
+        if (!tab) { oracle_sparse_cdf((uint32_t)thr, cdf); tab = cdf; }   /* callers that loop over groups pass the event's table */
+        sparse_group_words(seed, e, g, (uint32_t)thr, tab, out2);
     } else sliced_group_words(seed, e, g, kind, thr, bits, out2);
+}
+static void group_words(int spec, uint64_t seed, uint32_t e, uint64_t g, int kind, uint64_t thr, int bits, uint64_t out2[2]) {
+    group_words_tab(spec, seed, e, g, kind, thr, bits, NULL, out2);
+}
+
+/* Count tables of every sparse event of a descriptor (spec 3), [B][CANOPY_SPARSE_CDF_LEN]; NULL under the other specs. */
+static uint64_t* sparse_tables(int spec, int bits, uint32_t B, const int* kind, const uint64_t* thr) {
+    if (spec != 3 || bits != 32) return NULL;
+    uint64_t* tab = (uint64_t*)calloc((size_t)(B ? B : 1) * CANOPY_SPARSE_CDF_LEN, sizeof(uint64_t));
+    for (uint32_t e = 0; e < B; ++e)
+        if (kind[e] == 2 && is_sparse_event(spec, thr[e], bits)) oracle_sparse_cdf((uint32_t)thr[e], tab + (size_t)e * CANOPY_SPARSE_CDF_LEN);
+    return tab;
 }
 
 /* ------------------------------------------------------------------------------------------------
@@ -267,7 +366,7 @@ static size_t n_tallies_of(const canopy_graph_desc* d, int tally_all) {
  * ---------------------------------------------------------------------------------------------- */
 int oracle_mc_scalar(const canopy_graph_desc* d, uint64_t seed, uint64_t begin, uint64_t n,
                      int tally_all, int bits, int spec, uint64_t* tallies) {
-    if (spec != 1 && spec != 2) return -9;
+    if (spec < 1 || spec > 3) return -9;
     uint32_t B = d->n_basic, G = d->n_gates;
     uint32_t* order = (uint32_t*)malloc(sizeof(uint32_t) * (G ? G : 1));
     int rc = topo_order(d, order);
@@ -322,7 +421,7 @@ int oracle_mc_scalar(const canopy_graph_desc* d, uint64_t seed, uint64_t begin, 
  * listed in event_ids[0..n_events). */
 int oracle_sample_words(const canopy_graph_desc* d, uint64_t seed, int bits, int spec, const uint32_t* event_ids,
                         uint32_t n_events, uint64_t first_word, uint64_t n_words, uint64_t* words) {
-    if (spec != 1 && spec != 2) return -9;
+    if (spec < 1 || spec > 3) return -9;
     for (uint32_t i = 0; i < n_events; ++i) {
         uint32_t e = event_ids[i]; uint64_t thr; int kind = oracle_threshold(d->p[e], bits, &thr);
         if (kind < 0) return -8;
@@ -339,14 +438,16 @@ int oracle_sample_words(const canopy_graph_desc* d, uint64_t seed, int bits, int
 /* Same output as oracle_sample_words through the lazily evaluated group routine (fast). */
 int oracle_sample_words_fast(const canopy_graph_desc* d, uint64_t seed, int bits, int spec, const uint32_t* event_ids,
                              uint32_t n_events, uint64_t first_word, uint64_t n_words, uint64_t* words) {
-    if (spec != 1 && spec != 2) return -9;
+    if (spec < 1 || spec > 3) return -9;
     for (uint32_t i = 0; i < n_events; ++i) {
         uint32_t e = event_ids[i]; uint64_t thr; int kind = oracle_threshold(d->p[e], bits, &thr);
         if (kind < 0) return -8;
-        uint64_t pair[2], have = ~0ull;
+        uint64_t pair[2], have = ~0ull, tab[CANOPY_SPARSE_CDF_LEN];
+        int sparse = kind == 2 && is_sparse_event(spec, thr, bits);
+        if (sparse) oracle_sparse_cdf((uint32_t)thr, tab);
         for (uint64_t w = 0; w < n_words; ++w) {
             uint64_t gw = first_word + w;
-            if ((gw >> 1) != have) { have = gw >> 1; group_words(spec, seed, e, have, kind, thr, bits, pair); }
+            if ((gw >> 1) != have) { have = gw >> 1; group_words_tab(spec, seed, e, have, kind, thr, bits, sparse ? tab : NULL, pair); }
             words[(uint64_t)i * n_words + w] = pair[gw & 1];
         }
     }
@@ -404,6 +505,7 @@ typedef struct {
     const canopy_graph_desc* d;
     const uint32_t* order;
     const int* kind; const uint64_t* thr; const unsigned char* used;
+    const uint64_t* tab; /* spec 3 count tables, or NULL */
     uint64_t seed, begin, n; int tally_all, bits, spec;
     uint64_t first_group, n_groups; /* global 128-sample group range covering [begin, begin+n) */
     int tid, nthreads;
@@ -449,7 +551,8 @@ static void* packed_worker(void* arg) {
         uint64_t grp = J->first_group + gi;
         uint64_t mask[2] = {word_mask(2 * grp, J->begin, end), word_mask(2 * grp + 1, J->begin, end)};
         for (uint32_t e = 0; e < B; ++e) {
-            if (J->used[e]) group_words(J->spec, J->seed, e, grp, J->kind[e], J->thr[e], J->bits, val + 2 * (size_t)e);
+            if (J->used[e]) group_words_tab(J->spec, J->seed, e, grp, J->kind[e], J->thr[e], J->bits,
+                                            J->tab ? J->tab + (size_t)e * CANOPY_SPARSE_CDF_LEN : NULL, val + 2 * (size_t)e);
             else val[2 * (size_t)e] = val[2 * (size_t)e + 1] = 0;
         }
         for (int h = 0; h < 2; ++h) {
@@ -493,7 +596,7 @@ static void* packed_worker(void* arg) {
 int oracle_mc_packed(const canopy_graph_desc* d, uint64_t seed, uint64_t begin, uint64_t n,
                      int tally_all, int bits, int spec, int nthreads, uint64_t* tallies) {
     uint32_t B = d->n_basic, G = d->n_gates;
-    if (spec != 1 && spec != 2) return -9;
+    if (spec < 1 || spec > 3) return -9;
     if (nthreads < 1) nthreads = 1;
     uint32_t* order = (uint32_t*)malloc(sizeof(uint32_t) * (G ? G : 1));
     int rc = topo_order(d, order);
@@ -511,11 +614,12 @@ int oracle_mc_packed(const canopy_graph_desc* d, uint64_t seed, uint64_t begin, 
     memset(tallies, 0, sizeof(uint64_t) * nt);
     if (n == 0) { free(order); free(kind); free(thr); free(used); return 0; }
     uint64_t first_group = begin / 128, last_group = (begin + n - 1) / 128;
+    uint64_t* tab = sparse_tables(spec, bits, B, kind, thr);
     packed_job* jobs = (packed_job*)calloc((size_t)nthreads, sizeof(packed_job));
     pthread_t* th = (pthread_t*)malloc(sizeof(pthread_t) * (size_t)nthreads);
     for (int t = 0; t < nthreads; ++t) {
         packed_job* J = &jobs[t];
-        J->d = d; J->order = order; J->kind = kind; J->thr = thr; J->used = used;
+        J->d = d; J->order = order; J->kind = kind; J->thr = thr; J->used = used; J->tab = tab;
         J->seed = seed; J->begin = begin; J->n = n; J->tally_all = tally_all; J->bits = bits; J->spec = spec;
         J->first_group = first_group; J->n_groups = last_group - first_group + 1;
         J->tid = t; J->nthreads = nthreads;
@@ -527,8 +631,10 @@ int oracle_mc_packed(const canopy_graph_desc* d, uint64_t seed, uint64_t begin, 
         for (size_t i = 0; i < nt; ++i) tallies[i] += jobs[t].tallies[i];
         free(jobs[t].tallies);
     }
-    free(jobs); free(th); free(order); free(kind); free(thr); free(used);
+    free(jobs); free(th); free(order); free(kind); free(thr); free(used); free(tab);
     return 0;
 }
 
 int oracle_spec_version(void) { return CANOPY_SPEC_VERSION; }
+int oracle_sparse_cdf_len(void) { return CANOPY_SPARSE_CDF_LEN; }
+int oracle_sparse_min_zeros(void) { return CANOPY_SPARSE_MIN_ZEROS; }

@@ -45,7 +45,7 @@ def lib():
 _RC = {-1: "bad node id", -3: "cycle", -4: "too many basic events for enumeration", -8: "probability out of domain",
        -9: "unknown sampling spec"}
 
-SPEC = 2  # default sampling spec of the build (include/canopy.h CANOPY_SPEC_VERSION); 1 = direct, 2 = sliced
+SPEC = 3  # default sampling spec of the build (include/canopy.h CANOPY_SPEC_VERSION); 1 = direct, 2 = sliced, 3 = sparse
 
 
 def _check(rc):
@@ -69,6 +69,15 @@ def threshold(p: float, bits: int = 32):
 
 def quantised_p(p: float, bits: int = 32) -> float:
     return float(lib().oracle_quantised_p(p, bits))
+
+
+def sparse_cdf(thr32: int) -> list:
+    """Spec 3 count table of one sparse event (CANOPY_SPARSE_CDF_LEN words of 0.64 fixed point)."""
+    out = (C.c_uint64 * int(lib().oracle_sparse_cdf_len()))()
+    lib().oracle_sparse_cdf.argtypes = [C.c_uint32, C.POINTER(C.c_uint64)]
+    lib().oracle_sparse_cdf.restype = None
+    lib().oracle_sparse_cdf(thr32, out)
+    return [int(x) for x in out]
 
 
 def sample_bit(seed: int, e: int, s: int, p: float, bits: int = 32, spec: int = SPEC) -> int:

@@ -169,7 +169,7 @@ def test_parked_value_buffers_are_reused_correctly():
         g = synth.generate(n_basic=nb, n_gates=nb // 2, n_layers=6, max_fanin=7, seed=seed)
         with Plan(g, tally_all_gates=True) as plan:
             got, _ = plan.run(5 * 4096 + 17, seed=seed, sample_begin=4096 * seed)
-        assert np.array_equal(got, O.mc_packed(g, seed, 4096 * seed, 5 * 4096 + 17, True, nthreads=CORES, spec=2))
+        assert np.array_equal(got, O.mc_packed(g, seed, 4096 * seed, 5 * 4096 + 17, True, nthreads=CORES, spec=plan.spec))
         if seed == 32:
             trim_device_cache()
 

@@ -20,7 +20,7 @@ def test_library_exports_every_declared_symbol():
     L = C.CDLL(_lib.LIB_PATH)
     for name in declared:
         assert hasattr(L, name), name
-    assert _lib.lib().canopy_spec_version() == 2
+    assert _lib.lib().canopy_spec_version() == 3
     assert _lib.lib().canopy_status_string(3) == b"cycle error"
 
 
