@@ -154,27 +154,29 @@ __device__ __forceinline__ void sparse_rows(uint4* __restrict__ vals, const uint
             }
         }
         uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0;
-        uint32_t f = x.z, i = 0;   // f: the unread fields of the current word, next field in its low 7 bits
+        // f: the unread fields of the current field word (next field in its low 7 bits), avail of them left; field word fw
+        // is word 2 + fw of call 0x400 for fw < 2, else word (fw - 2) & 3 of call 0x401 + ((fw - 2) >> 2)
+        uint32_t f = x.z, avail = 4, fw = 0;
         uint4 ext = x;
 #pragma unroll 1
         while (n) {
-            if ((i & 3u) == 0u && i) {  // word exhausted: fields 4-7 are word 3 of call 0x400, field 8 + 16c + 4w + .. word w of call 0x401 + c
-                if (i == 4u) f = x.w;
+            if (avail == 0) {
+                avail = 4; ++fw;
+                if (fw == 1u) f = x.w;
                 else {
-                    const uint32_t i2 = i - 8u;
-                    if ((i2 & 15u) == 0u) ext = philox4x32_10(g_lo, g_hi, e, 0x401u + (i2 >> 4), K);
-                    const uint32_t w = (i2 >> 2) & 3u;
-                    f = w == 0 ? ext.x : w == 1 ? ext.y : w == 2 ? ext.z : ext.w;
+                    const uint32_t k = fw - 2u;
+                    if ((k & 3u) == 0u) ext = philox4x32_10(g_lo, g_hi, e, 0x401u + (k >> 2), K);
+                    f = (k & 3u) == 0u ? ext.x : (k & 3u) == 1u ? ext.y : (k & 3u) == 2u ? ext.z : ext.w;
                 }
             }
             const uint32_t pos = f & 127u;
-            f >>= 7; ++i;
-            const uint32_t b = 1u << (pos & 31u), w = pos >> 5;
-            const uint32_t cur = w == 0 ? r0 : w == 1 ? r1 : w == 2 ? r2 : r3;
-            if (!(cur & b)) {
-                --n;
-                r0 |= w == 0 ? b : 0u; r1 |= w == 1 ? b : 0u; r2 |= w == 2 ? b : 0u; r3 |= w == 3 ? b : 0u;
-            }
+            f >>= 7; --avail;
+            // branch-free test-and-set: shl clamps shift counts outside 0..31 to a zero result, so exactly one of the four
+            // masks is non-zero; OR-ing a bit that is already set changes nothing, so only the count depends on `hit`
+            const uint32_t b0 = shl_clamp(1u, pos), b1 = shl_clamp(1u, pos - 32u), b2 = shl_clamp(1u, pos - 64u), b3 = shl_clamp(1u, pos - 96u);
+            const uint32_t hit = (r0 & b0) | (r1 & b1) | (r2 & b2) | (r3 & b3);
+            r0 |= b0; r1 |= b1; r2 |= b2; r3 |= b3;
+            n -= hit == 0u ? 1u : 0u;
         }
         st_cg(row, make_uint4(r0, r1, r2, r3));
     }

@@ -19,6 +19,7 @@
 #include <cmath>
 #include <cstring>
 #include <numeric>
+#include <thread>
 
 #include "plan.h"
 
@@ -415,6 +416,10 @@ void sparse_cdf(uint32_t t, uint64_t* cdf) {
     for (uint32_t j = 0; j < CANOPY_SPARSE_CDF_LEN; ++j) {
         sum += a;
         cdf[j] = sum > (u128)~0ull ? ~0ull : (uint64_t)sum;
+        if (a == 0) {  // every later term is 0 as well: the table is flat from here on
+            for (uint32_t k = j + 1; k < CANOPY_SPARSE_CDF_LEN; ++k) cdf[k] = cdf[j];
+            break;
+        }
         a = (uint64_t)(((u128)a * (128u - j) * t) / ((u128)(j + 1) * q));
     }
 }
@@ -430,9 +435,23 @@ void build_sparse_tables(Lowered& L) {
     const bool narrow = L.opts.threshold_bits == 32;
     auto sparse = [&](uint32_t i) { return narrow && (L.event_thr32[i] >> (32 - CANOPY_SPARSE_MIN_ZEROS)) == 0; };
     for (uint32_t i = 0; i < n; ++i) if (!sparse(i)) L.event_perm.push_back(i);
-    for (uint32_t i = 0; i < n; ++i) if (sparse(i)) {
-        L.event_perm.push_back(i);
-        sparse_cdf(L.event_thr32[i], &L.event_cdf[(size_t)i * CANOPY_SPARSE_CDF_LEN]);
+    const uint32_t n_dense = (uint32_t)L.event_perm.size();
+    for (uint32_t i = 0; i < n; ++i) if (sparse(i)) L.event_perm.push_back(i);
+    // the tables cost one 128-bit division per entry: spread large plans over a few host threads (pure functions of thr)
+    const uint32_t n_sparse = n - n_dense;
+    const uint32_t n_thr = n_sparse < 2048 ? 1 : std::min<uint32_t>(8, std::max(1u, std::thread::hardware_concurrency()));
+    auto work = [&](uint32_t lo, uint32_t hi) {
+        for (uint32_t k = lo; k < hi; ++k) {
+            const uint32_t i = L.event_perm[n_dense + k];
+            sparse_cdf(L.event_thr32[i], &L.event_cdf[(size_t)i * CANOPY_SPARSE_CDF_LEN]);
+        }
+    };
+    if (n_thr == 1) work(0, n_sparse);
+    else {
+        std::vector<std::thread> pool;
+        for (uint32_t t = 0; t < n_thr; ++t)
+            pool.emplace_back(work, (uint32_t)((uint64_t)n_sparse * t / n_thr), (uint32_t)((uint64_t)n_sparse * (t + 1) / n_thr));
+        for (auto& th : pool) th.join();
     }
 }
 

@@ -93,7 +93,8 @@ void oracle_sparse_cdf(uint32_t t, uint64_t* cdf) {
 }
 
 static int is_sparse_event(int spec, uint64_t thr, int bits) {
-    return spec == 3 && bits == 32 && ((uint32_t)thr >> (32 - CANOPY_SPARSE_MIN_ZEROS)) == 0;
+    /* thr = 0 (p below 2^-32) never fires under any spec; it stays on the compare path, where u < 0 is never true */
+    return spec == 3 && bits == 32 && (uint32_t)thr != 0 && ((uint32_t)thr >> (32 - CANOPY_SPARSE_MIN_ZEROS)) == 0;
 }
 
 /* Field i of group g of event e, straight from the text: fields 0-7 are the 7-bit digits of words 2 and 3 of call
