@@ -93,16 +93,19 @@ def ncu_traffic(workload_name: str):
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE gate_ring_kernel launch (592 slabs) from the committed
     `ncu --set full` capture of this workload under profiles/, in bytes; None if there is no capture for it."""
     import csv
-    path = os.path.join(ROOT, "profiles", f"r01h_ncu_full_gate_{workload_name}.csv")
     scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
-    try:
-        tot = 0.0
-        for row in csv.reader(open(path)):
-            if len(row) == 3 and row[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
-                tot += float(row[2]) * scale[row[1]]
-        return tot or None
-    except Exception:
-        return None
+    for tag in ("r01j", "r01i", "r01h"):      # newest evidence set first
+        path = os.path.join(ROOT, "profiles", f"{tag}_ncu_full_gate_{workload_name}.csv")
+        try:
+            tot = 0.0
+            for row in csv.reader(open(path)):
+                if len(row) == 3 and row[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                    tot += float(row[2]) * scale[row[1]]
+            if tot:
+                return tot
+        except Exception:
+            continue
+    return None
 
 
 def workload(name: str):
@@ -140,7 +143,7 @@ def run_reference(args):
     # bounded sample per step, sized from a probe so K+W steps end within a few minutes
     probe = 1 << 12
     t0 = time.perf_counter(); O.mc_packed(g, 1, 0, probe, tally_all, nthreads=cores, spec=spec); dt = time.perf_counter() - t0
-    budget = 120.0 / max(1, args.steps + args.warmup)
+    budget = 60.0 / max(1, args.steps + args.warmup)
     n = int(max(probe, min(S, probe * budget / max(dt, 1e-6)))) // 64 * 64
     for w in range(args.warmup):
         O.mc_packed(g, 1, 0, n, tally_all, nthreads=cores, spec=spec)
@@ -301,9 +304,30 @@ def main():
         # word and plane (56) + 4 = 330.2 warp-instr x 32 lanes / 4096 = 2.580 per Bernoulli bit.  Executed integer-class
         # (LOP3, IMAD*, ISETP, VIADD, SEL, SHF, ...): 453.5 per row = 3.543 per bit.  Spec 1: 12.3 per bit.
         int_peak, _ = microbench_int(0, local)
-        sliced = stats["spec_version"] == 2
-        alg_ops_per_bit = 2.580 if sliced else 581.0 * 2 / 128.0
-        exec_ops_per_bit = 3.543 if sliced else 12.3
+        spec = stats["spec_version"]
+        kernel_name = {1: "sampler_kernel<32,1>", 2: "sampler_sliced_kernel<32,false>", 3: "sampler_sliced_kernel<32,true>"}[spec]
+        if spec == 3:
+            # Spec 3: events below 2^-5 take the sparse path.  Algorithmic integer work per 128-sample group (one lane): a
+            # plane event 330.2 as above; a sparse event one Philox call (19 IMAD.WIDE -- the round-1 product of the event id
+            # is warp-uniform -- + 20 LOP3) + a 64-bit compare (2) per table entry inspected (N + 1) + 4 per placed one
+            # (extract 2, shift, or): 41 + 6 * 128 p.  Executed counts come from the ncu source page of this workload
+            # (tools/sampler_opcounts.py -> profiles/sampler_opcounts.json), counted per warp instruction x 32 lanes.
+            view = plan.view()
+            thr = view["event_thr32"].astype(np.float64)
+            sparse = thr < 2.0 ** 27
+            per_group = np.where(sparse, 41.0 + 6.0 * 128.0 * thr / 2.0 ** 32, 330.2)
+            alg_ops_per_bit = float(per_group.mean() / 128.0) if len(thr) else 0.0
+            try:
+                with open(os.path.join(ROOT, "profiles", "sampler_opcounts.json")) as f:
+                    exec_ops_per_bit = float(json.load(f)["3"]["executed_int_ops_per_bit"]) if args.workload == "c2" else None
+            except Exception:
+                exec_ops_per_bit = None
+            sampler_mix = {"sparse_events": int(sparse.sum()), "plane_events": int((~sparse).sum()),
+                           "mean_ones_per_group_sparse": float((128.0 * thr[sparse] / 2.0 ** 32).mean()) if sparse.any() else 0.0}
+        else:
+            alg_ops_per_bit = 2.580 if spec == 2 else 581.0 * 2 / 128.0
+            exec_ops_per_bit = 3.543 if spec == 2 else 12.3
+            sampler_mix = None
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -322,11 +346,12 @@ def main():
                          "alg_bytes_per_full_launch": alg_bytes_per_sample * 592 * 4096, "nominal_hbm_gbs": 7700.0, "frac_of_nominal": gate_gbs / 7700.0, "peak_source": peaks_src,
                          "alg_bytes_per_sample": alg_bytes_per_sample, "avg_launch_ms": gate_launch_ms,
                          "share_of_step": prof.gate_ms / max(prof.total_ms, 1e-9), "timed": "profile pass, kernels serialised"},
-            "roofline_sampler": {"kernel": "sampler_sliced_kernel<32>" if sliced else "sampler_kernel<32,1>",
+            "roofline_sampler": {"kernel": kernel_name,
                                  "bound": "int (LOP3 + IMAD.WIDE share one issue rate of 64 lanes/clk/SM)",
                                  "achieved": sampler_rate * alg_ops_per_bit / 1e9, "peak": int_peak / 1e9, "unit": "G int lane-instr/s",
                                  "frac": sampler_rate * alg_ops_per_bit / int_peak,
-                                 "executed_frac": sampler_rate * exec_ops_per_bit / int_peak,
+                                 "executed_frac": sampler_rate * exec_ops_per_bit / int_peak if exec_ops_per_bit else None,
+                                 "event_mix": sampler_mix,
                                  "bernoulli_bits_per_s": sampler_rate, "alg_int_ops_per_bit": alg_ops_per_bit,
                                  "executed_int_ops_per_bit": exec_ops_per_bit,
                                  "avg_launch_ms": prof.sampler_ms / max(1, prof.sampler_launches),
