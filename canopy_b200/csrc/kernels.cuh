@@ -2,7 +2,8 @@
 //
 //   sampler_sliced_kernel / sampler_kernel   north-star subsystem 2 (ABSENT in the reference):
 //                       counter-based Philox4x32-10 variates, compared against the per-event threshold (MSB-first on
-//                       bit planes in spec 2, whole in spec 1), 64 samples per word, one 128-bit coalesced store per lane.
+//                       bit planes in spec 2, whole in spec 1; spec 3 draws the count and positions of the ones of a
+//                       128-sample group for rare events), 64 samples per word, one 128-bit coalesced store per lane.
 //   gate_ring_kernel    north-star subsystem 3 (ABSENT in the reference):
 //                       one CTA walks every layer of the DAG for one slab; child rows stream through per-warp
 //                       shared-memory rings filled by TMA bulk copies, bit-sliced adders for k-of-n, fused

@@ -156,7 +156,7 @@ typedef struct canopy_plan_stats {
     uint32_t n_tallies;        /* length of the tallies output array                             */
     uint32_t n_const_nodes;    /* roots/gates folded to constants                                */
     uint32_t n_alias_nodes;    /* gates folded to (possibly complemented) aliases                */
-    uint32_t spec_version;     /* the spec this plan samples with (1 direct, 2 sliced)           */
+    uint32_t spec_version;     /* the spec this plan samples with (1 direct, 2 sliced, 3 sparse) */
 } canopy_plan_stats;
 
 typedef struct canopy_plan canopy_plan; /* opaque; immutable lowered graph + lazily created per-device state */

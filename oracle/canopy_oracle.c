@@ -6,7 +6,7 @@
  *   (a) the connective semantics of the Open-PSA MEF as constrained by the reference's own
  *       validation rules (reference src/mef/openpsa/event/event.cpp:140-204, event/event.h:143-157,
  *       event/formula.h:9-15), and
- *   (b) this repository's written sampling specs (spec 1 "direct", spec 2 "sliced"),
+ *   (b) this repository's written sampling specs (spec 1 "direct", spec 2 "sliced", spec 3 "sparse"),
  * pinned only by the published Philox4x32-10 known-answer vectors (Random123 kat_vectors) and by
  * exact 2^B enumeration on small trees.
  *
