@@ -508,6 +508,10 @@ uint64_t fingerprint(const Lowered& L) {
     };
     const int32_t o[3] = {L.opts.tally_all_gates, L.opts.threshold_bits, L.opts.sampler};
     mix(o, sizeof o);
+    if (L.opts.sampler == CANOPY_SAMPLER_SPARSE) {  // the constants of spec 3 are part of what a restart record must match
+        const int32_t c[3] = {CANOPY_SLICED_HEAD_BITS, CANOPY_SPARSE_MIN_ZEROS, CANOPY_SPARSE_CDF_LEN};
+        mix(c, sizeof c);
+    }
     mix(L.event_orig.data(), L.event_orig.size() * 4);
     mix(L.event_thr32.data(), L.event_thr32.size() * 4);
     mix(L.event_thr64.data(), L.event_thr64.size() * 8);
