@@ -93,6 +93,25 @@ def test_groups_that_need_a_second_call(ev, grp, ones):
     assert np.array_equal(slow, fast) and _popcount(fast) == ones
 
 
+def test_streaming_form_equals_the_definition_on_random_inputs():
+    """Property test over random thresholds (log-uniform across the sparse range and just above it), seeds, events, groups."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=150, deadline=None, derandomize=True)
+    @given(st.floats(min_value=-31.9, max_value=-4.5), st.integers(0, 2 ** 64 - 1), st.integers(0, 2 ** 32 - 1),
+           st.integers(0, 2 ** 57 - 1))
+    def check(log2p, seed, e_pad, grp):
+        b = G.GraphBuilder()
+        ev = [b.basic_event(2.0 ** log2p) for _ in range(1 + e_pad % 5)]
+        b.root(b.gate(G.NULL, [ev[-1]]))
+        g = b.build()
+        slow = O.sample_words(g, seed, [len(ev) - 1], 2 * grp, 2, 32, 3, fast=False)
+        fast = O.sample_words(g, seed, [len(ev) - 1], 2 * grp, 2, 32, 3, fast=True)
+        assert np.array_equal(slow, fast)
+
+    check()
+
+
 def test_law_of_the_sparse_bits():
     """Frequencies within 4 sigma of thr/2^32; ones per group distributed as Binomial(128, p); positions uniform."""
     b = G.GraphBuilder()
