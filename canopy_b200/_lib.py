@@ -111,6 +111,7 @@ SYMBOLS = {
     "canopy_version": (C.c_uint32, []),
     "canopy_spec_version": (C.c_uint32, []),
     "canopy_sparse_cdf": (C.c_int, [C.c_uint32, C.POINTER(C.c_uint64)]),
+    "canopy_plan_debug_set_sparse_table": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint64)]),
 }
 
 _LIB = None

@@ -1,5 +1,6 @@
 // C ABI glue: exception -> status translation, thread-local error text, small host helpers.
 // Boundary declared in include/canopy.h; replaces the empty reference TU src/canopy.cpp.
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <new>
@@ -164,6 +165,20 @@ canopy_status canopy_plan_update_p(canopy_plan* plan, const double* p, uint32_t 
         require(plan && (p || n_basic == 0), "canopy_plan_update_p: null argument");
         std::lock_guard<std::mutex> lock(plan->mu);
         canopy::requantise(plan->low, p, n_basic);
+        canopy::refresh_thresholds(plan);
+    });
+}
+
+canopy_status canopy_plan_debug_set_sparse_table(canopy_plan* plan, uint32_t live_event, const uint64_t* cdf) {
+    return guard([&] {
+        require(plan && cdf, "canopy_plan_debug_set_sparse_table: null argument");
+        std::lock_guard<std::mutex> lock(plan->mu);
+        canopy::Lowered& L = plan->low;
+        require(L.opts.sampler == CANOPY_SAMPLER_SPARSE && L.opts.threshold_bits == 32 && live_event < L.n_events() &&
+                    (L.event_thr32[live_event] >> (32 - CANOPY_SPARSE_MIN_ZEROS)) == 0,
+                "canopy_plan_debug_set_sparse_table: not a sparse event of a spec 3 plan");
+        for (uint32_t j = 0; j + 1 < CANOPY_SPARSE_CDF_LEN; ++j) require(cdf[j] <= cdf[j + 1], "canopy_plan_debug_set_sparse_table: table must be non-decreasing");
+        std::copy(cdf, cdf + CANOPY_SPARSE_CDF_LEN, L.event_cdf.begin() + (size_t)live_event * CANOPY_SPARSE_CDF_LEN);
         canopy::refresh_thresholds(plan);
     });
 }

@@ -178,6 +178,11 @@ class Plan:
         p = np.ascontiguousarray(p, dtype=np.float64)
         _lib.check(_lib.lib().canopy_plan_update_p(self._h, p.ctypes.data_as(C.POINTER(C.c_double)), p.shape[0]))
 
+    def debug_set_sparse_table(self, live_event: int, cdf) -> None:
+        """Spec 3 test hook: replace the count table of one sparse event (canopy_plan_debug_set_sparse_table)."""
+        t = np.ascontiguousarray(cdf, dtype=np.uint64)
+        _lib.check(_lib.lib().canopy_plan_debug_set_sparse_table(self._h, live_event, t.ctypes.data_as(C.POINTER(C.c_uint64))))
+
     def sample_words(self, seed: int, first_word: int, n_words: int, device: int = 0) -> np.ndarray:
         """Raw sampler output [n_events_live, n_words] (parity hook)."""
         o = self._opts(seed, 0, 0, device, 0, None, False, False)

@@ -324,6 +324,12 @@ CANOPY_API uint32_t    canopy_spec_version(void);
 /* Spec 3: the cumulative count table (CANOPY_SPARSE_CDF_LEN words, 0.64 fixed point) a plan builds for a sparse event
  * with 32-bit threshold thr32 (0 < thr32 < 2^(32 - CANOPY_SPARSE_MIN_ZEROS)).  Host only; a parity hook for the tests. */
 CANOPY_API canopy_status canopy_sparse_cdf(uint32_t thr32, uint64_t* out_cdf);
+/* Spec 3 test hook: replace the count table of one sparse event of a plan (live_event = position in
+ * canopy_plan_view.event_orig) by cdf[CANOPY_SPARSE_CDF_LEN] (non-decreasing).  Lets the parity tests drive the count, and
+ * with it the number of position fields and Philox calls a group consumes, far beyond what a real probability reaches
+ * (an all-zero table gives 32 ones in every group).  The next canopy_plan_update_p restores the real table.
+ * CANOPY_E_INVALID unless the plan samples with spec 3 and the event takes the sparse path. */
+CANOPY_API canopy_status canopy_plan_debug_set_sparse_table(canopy_plan* plan, uint32_t live_event, const uint64_t* cdf);
 
 #ifdef __cplusplus
 } /* extern "C" */

@@ -455,6 +455,37 @@ int oracle_sample_words_fast(const canopy_graph_desc* d, uint64_t seed, int bits
     return 0;
 }
 
+/* Test hook (spec 3): the words of one sparse event under an explicit count table instead of the one its threshold
+ * gives; stream = 1 uses the streaming form, 0 the definition form (one flag per sample, one Philox call per field). */
+int oracle_sparse_words_with_table(uint64_t seed, uint32_t e, const uint64_t* tab, int stream, uint64_t first_word,
+                                   uint64_t n_words, uint64_t* words) {
+    uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
+    uint64_t pair[2] = {0, 0}, have = ~0ull;
+    for (uint64_t w = 0; w < n_words; ++w) {
+        uint64_t gw = first_word + w, g = gw >> 1;
+        if (g != have) {
+            have = g;
+            if (stream) sparse_group_words(seed, e, g, 0, tab, pair);
+            else {
+                uint32_t ctr[4] = {(uint32_t)g, (uint32_t)(g >> 32), e, 0x400u}, out[4];
+                oracle_philox4x32_10(ctr, key, out);
+                uint64_t U = ((uint64_t)out[1] << 32) | out[0];
+                unsigned n = 0; unsigned char flag[128];
+                for (unsigned j = 0; j < CANOPY_SPARSE_CDF_LEN; ++j) n += U >= tab[j];
+                memset(flag, 0, 128);
+                for (unsigned i = 0, placed = 0; placed < n; ++i) {
+                    unsigned pos = sparse_field(key, e, g, i);
+                    if (!flag[pos]) { flag[pos] = 1; ++placed; }
+                }
+                pair[0] = pair[1] = 0;
+                for (unsigned q = 0; q < 128; ++q) if (flag[q]) pair[q >> 6] |= 1ull << (q & 63);
+            }
+        }
+        words[w] = pair[gw & 1];
+    }
+    return 0;
+}
+
 /* ------------------------------------------------------------------------------------------------
  * Exact probabilities by enumeration of all 2^B states (B <= 24), with the quantised p.
  * probs[] has the same layout as tallies.

@@ -80,6 +80,17 @@ def sparse_cdf(thr32: int) -> list:
     return [int(x) for x in out]
 
 
+def sparse_words_with_table(seed: int, e: int, table, first_word: int, n_words: int, stream: bool = True) -> np.ndarray:
+    """Test hook (spec 3): packed words of sparse event `e` under an explicit count table."""
+    tab = np.ascontiguousarray(table, dtype=np.uint64)
+    out = np.zeros(n_words, dtype=np.uint64)
+    fn = lib().oracle_sparse_words_with_table
+    fn.argtypes = [C.c_uint64, C.c_uint32, C.POINTER(C.c_uint64), C.c_int, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]
+    _check(fn(seed, e, tab.ctypes.data_as(C.POINTER(C.c_uint64)), int(stream), first_word, n_words,
+              out.ctypes.data_as(C.POINTER(C.c_uint64))))
+    return out
+
+
 def sample_bit(seed: int, e: int, s: int, p: float, bits: int = 32, spec: int = SPEC) -> int:
     """One basic-event bit straight from the written definition of the variate (slow; the pin for everything else)."""
     kind, thr = threshold(p, bits)

@@ -112,6 +112,24 @@ def test_streaming_form_equals_the_definition_on_random_inputs():
     check()
 
 
+def _forced_tables():
+    full = np.zeros(K, dtype=np.uint64)                                     # every group draws 32 ones
+    stair = np.array([0] * 20 + [1 << 63] * 12, dtype=np.uint64)            # 20 or 32 ones per group
+    return {"all32": full, "20or32": stair}
+
+
+@pytest.mark.parametrize("name", ["all32", "20or32"])
+def test_forced_counts_reach_the_third_and_fourth_position_call(name):
+    """With the count table overridden (test hook) every group needs 20 to 40+ position fields, i.e. calls 0x401, 0x402 and
+    often 0x403: the two oracle forms agree there too."""
+    tab = _forced_tables()[name]
+    a = O.sparse_words_with_table(2024, 7, tab, 128 * 5, 512, stream=True)
+    b = O.sparse_words_with_table(2024, 7, tab, 128 * 5, 512, stream=False)
+    assert np.array_equal(a, b)
+    per_group = np.unpackbits(a.view(np.uint8)).reshape(-1, 128).sum(axis=1)
+    assert set(per_group.tolist()) <= ({32} if name == "all32" else {20, 32}) and per_group.max() == 32
+
+
 def test_law_of_the_sparse_bits():
     """Frequencies within 4 sigma of thr/2^32; ones per group distributed as Binomial(128, p); positions uniform."""
     b = G.GraphBuilder()
@@ -222,9 +240,35 @@ def test_gpu_long_sparse_stream_matches_oracle():
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("name", ["all32", "20or32"])
+def test_gpu_forced_counts_reach_the_third_and_fourth_position_call(name):
+    """Kernel against oracle where every group consumes 20 to 40+ position fields (count table overridden by the test hook)."""
+    tab = _forced_tables()[name]
+    b = G.GraphBuilder()
+    ev = [b.basic_event(p) for p in (0.5, 0.01, 0.0078, 0.2, 0.02)]
+    b.root(b.gate(G.OR, ev))
+    g = b.build()
+    n_words = 128 * 64
+    with Plan(g, sampler=3) as plan:
+        orig = [int(x) for x in plan.view()["event_orig"]]
+        before = plan.sample_words(seed=2024, first_word=128 * 5, n_words=n_words)
+        plan.debug_set_sparse_table(orig.index(2), tab)
+        got = plan.sample_words(seed=2024, first_word=128 * 5, n_words=n_words)
+        with pytest.raises(Exception):
+            plan.debug_set_sparse_table(orig.index(0), tab)          # p = 0.5 is not a sparse event
+        plan.update_p([0.5, 0.01, 0.0078, 0.2, 0.02])                # restores the real table
+        after = plan.sample_words(seed=2024, first_word=128 * 5, n_words=n_words)
+    want = O.sample_words(g, 2024, orig, 128 * 5, n_words, 32, 3, fast=True)
+    assert np.array_equal(before, want) and np.array_equal(after, want)
+    want[orig.index(2)] = O.sparse_words_with_table(2024, 2, tab, 128 * 5, n_words, stream=True)
+    assert np.array_equal(got, want)
+
+
+@pytest.mark.gpu
 def test_gpu_long_stream_near_four_ones_per_group():
     """p = 0.031 (3.97 expected ones per group): long count-table walks, the second position call (more than 8 fields) is
-    routine.  A third call needs more than 24 fields, about 1e-11 per group: not reachable by a test."""
+    routine.  A third call needs more than 24 fields, about 1e-11 per group at a real probability: the forced-count tests above
+    cover it."""
     b = G.GraphBuilder()
     b.root(b.gate(G.OR, [b.basic_event(p) for p in (0.031, 0.031, 0.025, 0.016)]))
     g = b.build()
