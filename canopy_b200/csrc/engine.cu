@@ -145,6 +145,16 @@ __device__ __forceinline__ void sparse_rows(uint4* __restrict__ vals, const uint
         const uint4 x = philox4x32_10(g_lo, g_hi, e, 0x400u, K);
         const uint64_t U = ((uint64_t)x.y << 32) | x.x;
         uint32_t n = (U >= c0 ? 1u : 0u) + (U >= c1 ? 1u : 0u);
+#ifdef CANOPY_SPARSE_BSEARCH  // tuning experiment, not measured yet: per-lane binary search over entries 1..31 for
+                              // events where a second one is common (cdf_1 < 3/4), instead of the warp-uniform linear walk
+        if (c1 < 0xC000000000000000ull) {
+            uint32_t m = 0;   // largest index in 1..31 with cdf[m] <= U (0: none) = number of such entries, the table being sorted
+#pragma unroll
+            for (uint32_t step = 16; step; step >>= 1)
+                if (U >= __ldg(tab + m + step)) m += step;
+            n = (U >= c0 ? 1u : 0u) + m;
+        } else
+#endif
         if (__any_sync(0xFFFFFFFFu, U >= c1)) {
 #pragma unroll 1
             for (uint32_t j = 2; j < CANOPY_SPARSE_CDF_LEN; ++j) {

@@ -5,7 +5,10 @@ from canopy_b200 import synth
 from canopy_b200.engine import Plan
 
 spec = int(sys.argv[1]) if len(sys.argv) > 1 else 3
+only = sys.argv[2] if len(sys.argv) > 2 else None
 for cfg, n in (("c2", 1 << 25), ("c4", 1 << 22)):
+    if only and cfg != only:
+        continue
     g = synth.config_graph(cfg)
     with Plan(g, sampler=spec) as plan:
         plan.run(n // 4, seed=1)
