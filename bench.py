@@ -143,7 +143,7 @@ def run_reference(args):
     # bounded sample per step, sized from a probe so K+W steps end within a few minutes
     probe = 1 << 12
     t0 = time.perf_counter(); O.mc_packed(g, 1, 0, probe, tally_all, nthreads=cores, spec=spec); dt = time.perf_counter() - t0
-    budget = 60.0 / max(1, args.steps + args.warmup)
+    budget = float(os.environ.get("CANOPY_BENCH_REF_BUDGET_S", "60")) / max(1, args.steps + args.warmup)  # seconds of CPU work per step
     n = int(max(probe, min(S, probe * budget / max(dt, 1e-6)))) // 64 * 64
     for w in range(args.warmup):
         O.mc_packed(g, 1, 0, n, tally_all, nthreads=cores, spec=spec)
