@@ -73,31 +73,31 @@ void validate(const canopy_graph_desc& d) {
         const uint64_t o = d.child_off[g], n = d.child_off[g + 1] - o;
         if (d.child_off[g + 1] > d.n_edges) fail(CANOPY_E_INVALID, "child_off beyond n_edges");
         const uint8_t op = d.op[g];
-        const std::string where = "gate " + std::to_string(g) + ": ";
-        if (op >= CANOPY_NUM_CONNECTIVES) fail(CANOPY_E_INVALID, where + "unknown connective");
+        auto where = [g] { return "gate " + std::to_string(g) + ": "; };   // built only when a rule fails
+        if (op >= CANOPY_NUM_CONNECTIVES) fail(CANOPY_E_INVALID, where() + "unknown connective");
         const unsigned lo = d.kmin ? d.kmin[g] : 0, hi = d.kmax ? d.kmax[g] : 0;
         switch (op) {  // reference event.cpp:140-191
             case CANOPY_AND: case CANOPY_OR: case CANOPY_NAND: case CANOPY_NOR:
-                if (n < 2) fail(CANOPY_E_VALIDITY, where + "The connective must have 2 or more arguments.");
+                if (n < 2) fail(CANOPY_E_VALIDITY, where() + "The connective must have 2 or more arguments.");
                 break;
             case CANOPY_NOT: case CANOPY_NULL:
-                if (n != 1) fail(CANOPY_E_VALIDITY, where + "The connective must have only one argument.");
+                if (n != 1) fail(CANOPY_E_VALIDITY, where() + "The connective must have only one argument.");
                 break;
             case CANOPY_XOR: case CANOPY_IFF: case CANOPY_IMPLY:
-                if (n != 2) fail(CANOPY_E_VALIDITY, where + "The connective must have exactly 2 arguments.");
+                if (n != 2) fail(CANOPY_E_VALIDITY, where() + "The connective must have exactly 2 arguments.");
                 break;
             case CANOPY_ATLEAST:
-                if (!d.kmin) fail(CANOPY_E_VALIDITY, where + "The connective requires min number for its args.");
-                if (lo < 2) fail(CANOPY_E_VALIDITY, where + "Min number cannot be less than 2: " + std::to_string(lo));
-                if (n <= lo) fail(CANOPY_E_VALIDITY, where + "The connective must have more arguments than its min number:" +
+                if (!d.kmin) fail(CANOPY_E_VALIDITY, where() + "The connective requires min number for its args.");
+                if (lo < 2) fail(CANOPY_E_VALIDITY, where() + "Min number cannot be less than 2: " + std::to_string(lo));
+                if (n <= lo) fail(CANOPY_E_VALIDITY, where() + "The connective must have more arguments than its min number:" +
                                                         std::to_string(n) + " <= " + std::to_string(lo));
                 break;
             case CANOPY_CARDINALITY:
-                if (!d.kmin || !d.kmax) fail(CANOPY_E_VALIDITY, where + "The connective requires min and max numbers for args.");
-                if (lo > hi) fail(CANOPY_E_VALIDITY, where + "The connective min number cannot be greater than max number:" +
+                if (!d.kmin || !d.kmax) fail(CANOPY_E_VALIDITY, where() + "The connective requires min and max numbers for args.");
+                if (lo > hi) fail(CANOPY_E_VALIDITY, where() + "The connective min number cannot be greater than max number:" +
                                                      std::to_string(lo) + " > " + std::to_string(hi));
-                if (n == 0) fail(CANOPY_E_VALIDITY, where + "The connective requires one or more arguments.");
-                if (n < hi) fail(CANOPY_E_VALIDITY, where + "The connective max number cannot be greater than the number of arguments: " +
+                if (n == 0) fail(CANOPY_E_VALIDITY, where() + "The connective requires one or more arguments.");
+                if (n < hi) fail(CANOPY_E_VALIDITY, where() + "The connective max number cannot be greater than the number of arguments: " +
                                                     std::to_string(hi) + " > " + std::to_string(n));
                 break;
         }
@@ -105,17 +105,17 @@ void validate(const canopy_graph_desc& d) {
         for (uint64_t j = 0; j < n; ++j) {
             const uint32_t c = d.child[o + j], id = c & CANOPY_CHILD_ID_MASK;
             const bool is_const = id == CANOPY_CONST_FALSE || id == CANOPY_CONST_TRUE;
-            if (!is_const && id >= B + G) fail(CANOPY_E_INVALID, where + "argument id out of range");
-            if (!is_const && id == B + g) fail(CANOPY_E_CYCLE, where + "gate is its own argument");
+            if (!is_const && id >= B + G) fail(CANOPY_E_INVALID, where() + "argument id out of range");
+            if (!is_const && id == B + g) fail(CANOPY_E_CYCLE, where() + "gate is its own argument");
             if ((c & CANOPY_CHILD_COMPLEMENT) && (op == CANOPY_NOT || op == CANOPY_NULL))
-                fail(CANOPY_E_INVALID, where + "Invalid nesting of a complement arg.");   // event.cpp:194-197
+                fail(CANOPY_E_INVALID, where() + "Invalid nesting of a complement arg.");   // event.cpp:194-197
             if (is_const && op == CANOPY_NOT)
-                fail(CANOPY_E_INVALID, where + "Invalid nesting of a constant arg.");     // event.cpp:198-203
+                fail(CANOPY_E_INVALID, where() + "Invalid nesting of a constant arg.");     // event.cpp:198-203
             ids.push_back(id);
         }
         std::sort(ids.begin(), ids.end());
         if (std::adjacent_find(ids.begin(), ids.end()) != ids.end())
-            fail(CANOPY_E_VALIDITY, where + "Duplicate Element Error: duplicate argument");  // event.cpp:35-45
+            fail(CANOPY_E_VALIDITY, where() + "Duplicate Element Error: duplicate argument");  // event.cpp:35-45
     }
     for (uint32_t r = 0; r < d.n_roots; ++r)
         if (d.roots[r] >= B + G) fail(CANOPY_E_INVALID, "root id out of range");
@@ -327,6 +327,11 @@ void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lower
     std::vector<uint32_t> gate_dev(M, ~0u);
     for (uint32_t i = 0; i < live_ids.size(); ++i) gate_dev[live_ids[i]] = i;
     L.layer_off.assign(max_level + 1, 0);
+    {
+        const size_t ng = live_ids.size();
+        L.child.reserve(mchild.size()); L.gate_rec.reserve(ng); L.gate_child_off.reserve(ng + 1);
+        L.gate_op.reserve(ng); L.gate_flags.reserve(ng); L.gate_kmin.reserve(ng); L.gate_kmax.reserve(ng);
+    }
     L.gate_child_off.push_back(0);
     uint32_t max_fanin = 0, n_stored = 0, n_tallied = 0;
     for (uint32_t i = 0; i < live_ids.size(); ++i) {
