@@ -1,12 +1,21 @@
 #!/usr/bin/env python
 """bench.py -- headline benchmark of the Monte Carlo hot path (driver contract in the task statement).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c3|c4] [--impl reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c4|c2|c3|c1] [--impl reference]
   torchrun --nproc-per-node N ... bench.py --gpus N ...       (one rank per GPU, NCCL)
 
-A "step" is one pass of the hot path over the whole workload on every rank: rank r evaluates the
-workload's S samples on the disjoint Philox counter range [r*S, (r+1)*S) (weak scaling), then ONE
-all-reduce of the int64 tallies over NCCL.  `value` = N*S*K / max-over-ranks device time.
+Default workload: BASELINE.json config 4 / 5, the 100k-event / 60k-gate deep DAG with fan-in up to 256 (the
+configuration north_star states its target on).  The config asks for 2^30 samples on one GPU (2^36 over eight): one
+step here is 2^27 samples per GPU, because the driver times 25 steps per arm, four GPU counts and the CPU arm in one
+lease and 2^30 per step would take minutes per step count; the graph, and therefore bytes and instructions per
+sample, are the full configuration's (a step is 55 full batches of the pipeline, fill and drain are below 2 %).
+tools/run_c5.py runs the 2^36-sample configuration in one go.
+
+A "step" is one pass of the hot path over the workload's S samples on every rank: rank r evaluates the disjoint
+Philox counter range [(k*N + r)*S, +S) (weak scaling), then ONE all-reduce of the int64 tallies over NCCL.
+`value` = N*S*K / max-over-ranks device time.  Before the timed region `tally_check` runs a FIXED range cut over the
+N ranks by canopy_shard_range with every gate tallied, all-reduces it, and compares it on rank 0 with the same range on
+one GPU and (a prefix) with the CPU oracle; a mismatch exits non-zero.
 `e2e` goes through the public host API every step: lower the graph from HOST arrays (canopy_plan_create),
 upload, run, all-reduce, and read the tallies back to the host.
 The CPU arm (`cpu_baseline`, `--impl reference`) is the in-repo bit-packed multi-threaded port in oracle/
@@ -89,37 +98,98 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def ncu_traffic(workload_name: str):
-    """dram__bytes_read.sum + dram__bytes_write.sum of ONE gate_ring_kernel launch (592 slabs) from the committed
-    `ncu --set full` capture of this workload under profiles/, in bytes; None if there is no capture for it."""
-    import csv
-    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
-    for tag in ("r01j", "r01i", "r01h"):      # newest evidence set first
-        path = os.path.join(ROOT, "profiles", f"{tag}_ncu_full_gate_{workload_name}.csv")
-        try:
-            tot = 0.0
-            for row in csv.reader(open(path)):
-                if len(row) == 3 and row[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
-                    tot += float(row[2]) * scale[row[1]]
-            if tot:
-                return tot
-        except Exception:
-            continue
-    return None
+def build_tag() -> str:
+    """Hash of the kernel sources: profiles/ captures carry the tag of the build they were taken from, and a number read
+    from a capture of ANOTHER build is reported as null instead of silently going stale."""
+    import hashlib
+    h = hashlib.sha1()
+    for f in ("engine.cu", "kernels.cuh", "plan.h", "lowering.cpp"):
+        with open(os.path.join(ROOT, "canopy_b200", "csrc", f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:12]
 
 
-def workload(name: str):
+def captured(workload_name: str):
+    """profiles/captures.json: per workload the DRAM bytes of one gate-walk launch (ncu --set full,
+    dram__bytes_read.sum + dram__bytes_write.sum) and the executed integer instructions per Bernoulli bit of the sampler
+    (ncu source page), each with the build tag it was measured on (tools/gpu_evidence.sh writes it)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "captures.json")) as f:
+            c = json.load(f).get(workload_name)
+    except Exception:
+        return None, None, "no capture in profiles/captures.json"
+    if not c:
+        return None, None, "no capture for this workload in profiles/captures.json"
+    if c.get("build_tag") != build_tag():
+        return None, None, f"capture is of build {c.get('build_tag')}, this build is {build_tag()}: not quoted"
+    return c.get("gate_dram_bytes_per_launch"), c.get("sampler_executed_int_ops_per_bit"), f"ncu capture of build {c['build_tag']}"
+
+
+# samples per step per GPU where the configuration's full count makes a step too long for 25 timed steps per arm
+STEP_SAMPLES = {"c4": 1 << 27}
+
+
+def _c1_graph_stdlib(path):
+    """The c1 example (AND/OR gates over basic events with float probabilities) read with xml.etree: the CPU arm must not
+    load libcanopy.so, not even for parsing.  Same node order as the library's reader (tests/test_bench_contract.py)."""
+    import xml.etree.ElementTree as ET
+    from canopy_b200.graph import AND, OR, GraphBuilder
+    root = ET.parse(path).getroot()
+    gates = [(d.get("name"), d[0]) for d in root.iter("define-gate")]
+    used = {a.get("name") for _, f in gates for a in f if a.tag == "gate"}
+    basics = [(d.get("name"), float(d.find("float").get("value"))) for d in root.iter("define-basic-event")]
+    b = GraphBuilder()
+    ev = {n: b.basic_event(p, n) for n, p in basics}
+    gh = {n: ("g", i) for i, (n, _) in enumerate(gates)}
+    for n, f in gates:
+        b.gate({"and": AND, "or": OR}[f.tag], [gh[a.get("name")] if a.tag == "gate" else ev[a.get("name")] for a in f], name=n)
+    for n, _ in gates:
+        if n not in used:
+            b.root(gh[n])
+    return b.build()
+
+
+def workload(name: str, native: bool = True):
+    """(graph, samples per step per GPU, samples of the full configuration)"""
     from canopy_b200 import synth
-    if name == "c1":  # the hand-authored MEF example (the reference ships none), through the library's MEF reader
-        from canopy_b200.engine import load_mef
-        return load_mef(os.path.join(ROOT, "examples", "c1_small_ft.xml")), 1 << 20
+    if name == "c1":  # the hand-authored MEF example (the reference ships none)
+        path = os.path.join(ROOT, "examples", "c1_small_ft.xml")
+        if native:   # through the library's MEF reader
+            from canopy_b200.engine import load_mef
+            return load_mef(path), 1 << 20, 1 << 20
+        return _c1_graph_stdlib(path), 1 << 20, 1 << 20
     g = synth.config_graph(name)
-    return g, synth.CONFIGS[name]["n_samples"]
+    full = synth.CONFIGS[name]["n_samples"]
+    return g, STEP_SAMPLES.get(name, full), full
 
 
-def cpu_arm(graph, n_samples_hint: int, tally_all: bool, seconds_target: float = 12.0, spec: int = 2):
+WHAT = {"c1": "MEF example examples/c1_small_ft.xml", "c2": "synthetic fault tree incl. ATLEAST and NOT",
+        "c3": "synthetic event tree, 200 sequences over one shared DAG, per-sequence and per-gate tallies",
+        "c4": "deep synthetic DAG, fan-in up to 256 (BASELINE configs 4 and 5)"}
+
+
+def config_block(name, g, S, S_full, stats=None, n_step=None):
+    """`workload` is built from the DESCRIPTOR only, so both arms print the same string; the GPU arm adds the sizes after
+    dead-code elimination from the plan."""
+    import numpy as np
+    fan = np.diff(g.child_off.astype(np.int64))
+    c = {"workload": f"{name}: {WHAT[name]}; B={g.n_basic} G={g.n_gates} E={g.n_edges} max_fanin={int(fan.max()) if len(fan) else 0}; "
+                     f"{S} samples/step/GPU" + (f" (the configuration's {S_full} samples = {S_full // S} such steps)" if S_full != S else ""),
+         "samples_per_step_per_gpu": n_step or S, "threshold_bits": 32,
+         "l2": "no flush needed: each batch streams a value buffer of n_nodes*1 KB*batch_slabs (GBs) >> 126 MB L2"}
+    if n_step and n_step != S:
+        c["this_arm"] = f"{n_step} samples/step (bounded CPU sample of the same workload)"
+    if stats:
+        c.update({"B_live": stats["n_basic_live"], "G_live": stats["n_gates_live"], "E_live": stats["n_edges_live"],
+                  "G_stored": stats["n_gates_stored"], "layers": stats["n_layers"], "max_fanin_live": stats["max_fanin"],
+                  "mean_fanin_live": stats["mean_fanin"], "spec_version": stats["spec_version"]})
+    return c
+
+
+def cpu_arm(graph, n_samples_hint: int, tally_all: bool, seconds_target: float = 12.0, spec: int = 0):
     """Bit-packed multi-threaded CPU port (oracle/) on a bounded sample of the same workload."""
     from oracle import oracle as O
+    spec = spec or O.SPEC
     cores = len(os.sched_getaffinity(0))
     probe = 1 << 12
     t0 = time.perf_counter(); O.mc_packed(graph, 1, 0, probe, tally_all, nthreads=cores, spec=spec); dt = time.perf_counter() - t0
@@ -130,16 +200,16 @@ def cpu_arm(graph, n_samples_hint: int, tally_all: bool, seconds_target: float =
 
 
 def run_reference(args):
+    """The CPU arm on the driver's clock.  Nothing of canopy_b200's native code is loaded here: the graph generator is
+    pure Python, the timed loop is oracle/ only (the reference has no implementation of this path to time)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    g, S = workload(args.workload)
+    g, S, S_full = workload(args.workload, native=False)
     tally_all = args.workload == "c3"
-    from canopy_b200.engine import Plan
-    stats = Plan(g, tally_all, sampler=args.sampler).stats  # host lowering only: sizes for the config block
-    spec = stats["spec_version"]
     cores = len(os.sched_getaffinity(0))
     from oracle import oracle as O
+    spec = args.sampler or O.SPEC
     # bounded sample per step, sized from a probe so K+W steps end within a few minutes
     probe = 1 << 12
     t0 = time.perf_counter(); O.mc_packed(g, 1, 0, probe, tally_all, nthreads=cores, spec=spec); dt = time.perf_counter() - t0
@@ -155,24 +225,100 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-            "config": config_block(args.workload, g, stats, S, n_step=n),
+            "config": config_block(args.workload, g, S, S_full, n_step=n),
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                             "sample": f"{n} samples/step of {args.workload} (bit-packed pthreads port in oracle/; the reference has no CPU path)"},
+                             "sample": f"{n} samples/step of {args.workload} (bit-packed pthreads port in oracle/, spec {spec}; the reference has no CPU path)"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gate_evals_per_sec": v * stats["n_gates_live"]}
+            "gate_evals_per_sec_descriptor_gates": v * g.n_gates}
     print(json.dumps(line), flush=True)
     return 0
 
 
-def config_block(name, g, stats, S, n_step=None):
-    return {"workload": f"{name}: {'MEF example examples/c1_small_ft.xml' if name == 'c1' else 'synthetic fault tree'} B={g.n_basic} G={g.n_gates} (after DCE: B={stats['n_basic_live']} "
-                        f"G={stats['n_gates_live']} E={stats['n_edges_live']} G'={stats['n_gates_stored']} layers={stats['n_layers']} "
-                        f"max_fanin={stats['max_fanin']} mean_fanin={stats['mean_fanin']:.2f}), {S} samples/step/GPU"
-                        + (f" (this arm: {n_step} samples/step)" if n_step else ""),
-            "samples_per_step_per_gpu": n_step or S, "B_live": stats["n_basic_live"], "G_live": stats["n_gates_live"],
-            "E_live": stats["n_edges_live"], "G_stored": stats["n_gates_stored"], "layers": stats["n_layers"],
-            "spec_version": stats["spec_version"], "threshold_bits": 32,
-            "l2": "no flush needed: each batch streams a value buffer of n_nodes*1 KB*batch_slabs (GBs) >> 126 MB L2"}
+CHECK_SEED = 0x7A11
+
+
+def tally_check(g, world, rank, local, dev, stream, sampler, n_fixed=1 << 24, n_prefix=1 << 14):
+    """In-run parity evidence on the driver's clock, every gate tallied:
+       (i)  the fixed range [0, n_fixed) cut over the N ranks by canopy_shard_range + ONE all-reduce == the same range on
+            one GPU (at N = 1: three ragged pieces summed == the whole);
+       (ii) its first n_prefix samples on the GPU == oracle.mc_packed on the host."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from canopy_b200.engine import Plan, shard_range
+    res = {"range": [0, n_fixed], "ranks": world, "prefix": n_prefix, "tallies": 0}
+    with Plan(g, tally_all_gates=True, sampler=sampler) as plan:
+        nt = plan.n_tallies
+        res["tallies"] = nt
+        buf = torch.zeros(max(nt, 1), dtype=torch.int64, device=dev)
+        b, n = shard_range(0, n_fixed, rank, world)
+        plan.run_device(buf.data_ptr(), n, seed=CHECK_SEED, sample_begin=b, device=local, stream=stream)
+        if world > 1:
+            dist.all_reduce(buf)      # the collective under test: nt int64 tallies (c4: 460 KB)
+        torch.cuda.synchronize()
+        flags = torch.ones(3, dtype=torch.int64, device=dev)
+        if rank == 0:
+            nway = buf.cpu().numpy().astype(np.uint64)[:nt]
+            one, _ = plan.run(n_fixed, seed=CHECK_SEED, sample_begin=0, device=local)
+            flags[0] = int(np.array_equal(one, nway))
+            cuts = [0, 4096 * 301 + 77, n_fixed // 2 + 12345, n_fixed]
+            pieces = sum(plan.run(cuts[i + 1] - cuts[i], seed=CHECK_SEED, sample_begin=cuts[i], device=local)[0] for i in range(3))
+            flags[1] = int(np.array_equal(one, pieces))
+            from oracle import oracle as O
+            pre, _ = plan.run(n_prefix, seed=CHECK_SEED, sample_begin=0, device=local)
+            want = O.mc_packed(g, CHECK_SEED, 0, n_prefix, True, nthreads=len(os.sched_getaffinity(0)), spec=plan.spec)
+            flags[2] = int(np.array_equal(pre, want))
+            res["top_event_tally"] = int(one[0]) if nt else 0
+            res["nonzero_tallies"] = int((one > 0).sum())
+        if world > 1:
+            dist.broadcast(flags, 0)
+        f = [bool(x) for x in flags.cpu().tolist()]
+    res.update({"n_way_equals_1_way": f[0], "pieces_equal_whole": f[1], "prefix_equals_oracle": f[2],
+                "allreduce_bytes": nt * 8 if world > 1 else 0})
+    return res
+
+
+def sampler_algorithmic_ops(plan, spec):
+    """Algorithmic integer lane-instructions per Bernoulli bit of the sampler for this plan's event mix."""
+    import numpy as np
+    if spec == 1:
+        return 581.0 * 2 / 128.0, None
+    if spec == 2:
+        return 2.580, None
+    view = plan.view()
+    thr = view["event_thr32"].astype(np.float64)
+    sparse = thr < 2.0 ** 27
+    # per 128-sample group (one lane): a plane event 330.2; a sparse event one Philox call (19 IMAD.WIDE + 20 LOP3) + a
+    # 64-bit compare (2) per table entry inspected (N + 1) + 4 per placed one: 41 + 6 * 128 p
+    per_group = np.where(sparse, 41.0 + 6.0 * 128.0 * thr / 2.0 ** 32, 330.2)
+    mix = {"sparse_events": int(sparse.sum()), "plane_events": int((~sparse).sum()),
+           "mean_ones_per_group_sparse": float((128.0 * thr[sparse] / 2.0 ** 32).mean()) if sparse.any() else 0.0}
+    return (float(per_group.mean() / 128.0) if len(thr) else 0.0), mix
+
+
+def side_line(name, local, stream, sampler, steps=2):
+    """A short device-timed line of another BASELINE config on rank 0 (extra key, not the headline)."""
+    import torch
+    from canopy_b200.engine import Plan
+    g, S, S_full = workload(name)
+    tally_all = name == "c3"
+    with Plan(g, tally_all, sampler=sampler) as plan:
+        nt = plan.n_tallies
+        out = torch.zeros(max(nt, 1), dtype=torch.int64, device=torch.device("cuda", local))
+        for w in range(2):
+            plan.run_device(out.data_ptr(), S, seed=0xB200, sample_begin=w * S, device=local, stream=stream)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for k in range(steps):
+            plan.run_device(out.data_ptr(), S, seed=0xB200, sample_begin=(2 + k) * S, device=local, stream=stream)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        st = plan.stats
+    return {"workload": config_block(name, g, S, S_full)["workload"], "samples_per_s": S / (ms * 1e-3), "ms_per_step": ms, "steps": steps,
+            "gate_evals_per_s": S / (ms * 1e-3) * st["n_gates_live"], "tallies": nt, "G_live": st["n_gates_live"],
+            "alg_bytes_per_sample": (st["n_edges_live"] + st["n_gates_stored"] + st["n_basic_live"]) / 8.0}
 
 
 def main():
@@ -181,12 +327,13 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="canopy_b200")
-    ap.add_argument("--workload", default="c2", choices=["c1", "c2", "c3", "c4"])
-    ap.add_argument("--sampler", type=int, default=0, choices=[0, 1, 2, 3],
+    ap.add_argument("--workload", default="c4", choices=["c1", "c2", "c3", "c4"])
+    ap.add_argument("--sampler", type=int, default=0,
                     help="sampling spec of the plan (0 = build default; include/canopy.h CANOPY_SAMPLER_*)")
-    ap.add_argument("--no-study", action="store_true", help="skip the bounded c4 roofline study on rank 0")
+    ap.add_argument("--no-study", action="store_true", help="skip the short c2 / c3 side lines on rank 0")
+    ap.add_argument("--no-check", action="store_true", help="skip tally_check (kernel-tuning runs only; the line says so)")
     ap.add_argument("--samples", type=int, default=0,
-                    help="samples per step per GPU instead of the workload's full count (side studies only; the line says so)")
+                    help="samples per step per GPU instead of the workload's count (side studies only; the line says so)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != "reference" else args.warmup
     if args.impl == "reference":
@@ -208,20 +355,33 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
 
-    g, S = workload(args.workload)
+    g, S, S_full = workload(args.workload)
     if args.samples:
         S = args.samples
     tally_all = args.workload == "c3"
-    plan = Plan(g, tally_all, sampler=args.sampler)
-    stats = plan.stats
-    nt = plan.n_tallies
-    tallies = torch.zeros(max(nt, 1), dtype=torch.int64, device=dev)
     # A dedicated (non-default) torch stream: the library orders the whole run on the stream handle it is given,
     # so torch.cuda.Event on this stream brackets exactly the kernels of the timed steps.
     tstream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(tstream)
     stream = tstream.cuda_stream
     assert stream != 0
+
+    # ---- parity evidence before anything is timed ------------------------------------------------------
+    check = None
+    if not args.no_check:
+        check = tally_check(g, world, rank, local, dev, stream, args.sampler)
+        if not (check["n_way_equals_1_way"] and check["pieces_equal_whole"] and check["prefix_equals_oracle"]):
+            if rank == 0:
+                print(json.dumps({"metric": METRIC, "error": "tally_check failed", "tally_check": check}), flush=True)
+            if world > 1:
+                dist.destroy_process_group()
+            return 3
+
+    plan = Plan(g, tally_all, sampler=args.sampler)
+    stats = plan.stats
+    spec = stats["spec_version"]
+    nt = plan.n_tallies
+    tallies = torch.zeros(max(nt, 1), dtype=torch.int64, device=dev)
 
     def step(k, want_report=False):
         rep = plan.run_device(tallies.data_ptr(), S, seed=0xB200, sample_begin=(k * world + rank) * S, device=local,
@@ -258,14 +418,20 @@ def main():
     value = world * S * args.steps / (ms * 1e-3)
     top_tally = int(tallies[0].item()) if nt else 0
 
+    # ---- per-kernel roofline pass (every rank, to keep them in step) --------------------------------------
+    prof = plan.run_device(tallies.data_ptr(), S, seed=0xB200, sample_begin=0, device=local, stream=stream,
+                           profile=True, want_report=True)
+    alg_ops_per_bit, sampler_mix = sampler_algorithmic_ops(plan, spec)
+    plan.close()   # its value buffers (c4: 2 x 48 GB) go to the library's pool: the e2e plans below reuse them
+
     # ---- e2e: public host API, host buffers, H2D + D2H inside the timed region ------------------------
     e2e_steps = max(1, min(args.steps, 5))
     host_out = torch.zeros(max(nt, 1), dtype=torch.int64).pin_memory()
 
     def e2e_step(k):
-        p2 = Plan(g, tally_all, sampler=args.sampler)  # host lowering from HOST arrays
+        p2 = Plan(g, tally_all, sampler=args.sampler)  # canopy_plan_create from HOST arrays
         r = p2.run_device(tallies.data_ptr(), S, seed=0xB200, sample_begin=(k * world + rank) * S, device=local,
-                          stream=stream, want_report=True)   # uploads the CSR arrays (h2d) and runs
+                          stream=stream, want_report=True)   # uploads the lowered arrays (h2d) and runs
         if world > 1:
             dist.all_reduce(tallies)
         host_out.copy_(tallies, non_blocking=False)   # d2h of the step's result
@@ -283,13 +449,11 @@ def main():
         dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
     e2e_value = world * S * e2e_steps / float(t_e.item())
 
-    # ---- per-kernel roofline pass (rank 0 work replicated on all ranks to keep them in step) -----------
-    prof = plan.run_device(tallies.data_ptr(), S, seed=0xB200, sample_begin=0, device=local, stream=stream,
-                           profile=True, want_report=True)
     peaks, peaks_src = load_peaks()
-    alg_bytes_per_sample = (stats["n_edges_live"] + stats["n_gates_stored"]) / 8.0
+    gate_bytes_per_sample = (stats["n_edges_live"] + stats["n_gates_stored"]) / 8.0
+    sampler_bytes_per_sample = stats["n_basic_live"] / 8.0
     gate_launch_ms = prof.gate_ms / max(1, prof.gate_launches)
-    gate_bytes_per_launch = alg_bytes_per_sample * S / max(1, prof.gate_launches)
+    gate_bytes_per_launch = gate_bytes_per_sample * S / max(1, prof.gate_launches)
     gate_gbs = gate_bytes_per_launch / (gate_launch_ms * 1e-3) / 1e9 if gate_launch_ms > 0 else 0.0
     sampler_bits = stats["n_basic_live"] * S
     sampler_rate = sampler_bits / (prof.sampler_ms * 1e-3) if prof.sampler_ms > 0 else 0.0
@@ -298,53 +462,28 @@ def main():
     if rank == 0:
         # Integer roofline of the sampler.  Measured on sm_100 (canopy_microbench_int): LOP3, IMAD.WIDE.U32 and
         # any mix of the two issue at ONE shared rate of 64 lanes/clk/SM, so the bound is the integer instruction count.
-        # Spec 2 with H = 7, per warp-row of 4096 samples (one 128-sample group per lane), from the ncu source page
-        # profiles/r01g_ncu_source_sampler_c2_opcodes.csv: 135.1 IMAD.WIDE executed (8 Philox calls x 20 minus the
-        # round-1..2 products the calls of a group share).  Algorithmic: each multiply pairs with one LOP3, + 2 LOP3 per
-        # word and plane (56) + 4 = 330.2 warp-instr x 32 lanes / 4096 = 2.580 per Bernoulli bit.  Executed integer-class
-        # (LOP3, IMAD*, ISETP, VIADD, SEL, SHF, ...): 453.5 per row = 3.543 per bit.  Spec 1: 12.3 per bit.
         int_peak, _ = microbench_int(0, local)
-        spec = stats["spec_version"]
-        kernel_name = {1: "sampler_kernel<32,1>", 2: "sampler_sliced_kernel<32,false>", 3: "sampler_sliced_kernel<32,true>"}[spec]
-        if spec == 3:
-            # Spec 3: events below 2^-5 take the sparse path.  Algorithmic integer work per 128-sample group (one lane): a
-            # plane event 330.2 as above; a sparse event one Philox call (19 IMAD.WIDE -- the round-1 product of the event id
-            # is warp-uniform -- + 20 LOP3) + a 64-bit compare (2) per table entry inspected (N + 1) + 4 per placed one
-            # (extract 2, shift, or): 41 + 6 * 128 p.  Executed counts come from the ncu source page of this workload
-            # (tools/sampler_opcounts.py -> profiles/sampler_opcounts.json), counted per warp instruction x 32 lanes.
-            view = plan.view()
-            thr = view["event_thr32"].astype(np.float64)
-            sparse = thr < 2.0 ** 27
-            per_group = np.where(sparse, 41.0 + 6.0 * 128.0 * thr / 2.0 ** 32, 330.2)
-            alg_ops_per_bit = float(per_group.mean() / 128.0) if len(thr) else 0.0
-            try:
-                with open(os.path.join(ROOT, "profiles", "sampler_opcounts.json")) as f:
-                    exec_ops_per_bit = float(json.load(f)["3"]["executed_int_ops_per_bit"]) if args.workload == "c2" else None
-            except Exception:
-                exec_ops_per_bit = None
-            sampler_mix = {"sparse_events": int(sparse.sum()), "plane_events": int((~sparse).sum()),
-                           "mean_ones_per_group_sparse": float((128.0 * thr[sparse] / 2.0 ** 32).mean()) if sparse.any() else 0.0}
-        else:
-            alg_ops_per_bit = 2.580 if spec == 2 else 581.0 * 2 / 128.0
-            exec_ops_per_bit = 3.543 if spec == 2 else 12.3
-            sampler_mix = None
+        kernel_name = {1: "sampler_kernel<32,1>", 2: "sampler_sliced_kernel<32,false>", 3: "sampler_sliced_kernel<32,true>"}.get(spec, "sampler")
+        traffic, exec_ops_per_bit, cap_note = captured(args.workload)
+        step_ms = ms / args.steps
+        step_bytes = (gate_bytes_per_sample + sampler_bytes_per_sample) * S
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u32", "data": "synthetic",
-            "config": config_block(args.workload, g, stats, S),
+            "config": config_block(args.workload, g, S, S_full, stats),
             "gate_evals_per_sec": value * stats["n_gates_live"],
             "clocks": clk,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(r_e2e.h2d_bytes + g.nbytes() * 0),
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(r_e2e.h2d_bytes),
                     "d2h_bytes_per_step": int(nt * 8), "steps": e2e_steps,
                     "what": "canopy_plan_create from host arrays + upload + run + allreduce + tallies to host, wall clock"},
             "gpu_launches": int(launches_per_step * args.steps),
             "roofline": {"kernel": "gate_ring_kernel", "bound": "hbm", "achieved": gate_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                         "frac": gate_gbs / peaks["hbm_gbs"], "traffic": ncu_traffic(args.workload),
-                         "traffic_note": "DRAM read+write bytes of one full launch (2.42 M samples per launch: 16384 per SM) from the committed ncu --set full capture in profiles/; "
-                                         "frac can read a little above 1: the peak is a 1:1 read:write copy, this kernel's traffic is 4:1 reads",
-                         "alg_bytes_per_full_launch": alg_bytes_per_sample * 592 * 4096, "nominal_hbm_gbs": 7700.0, "frac_of_nominal": gate_gbs / 7700.0, "peak_source": peaks_src,
-                         "alg_bytes_per_sample": alg_bytes_per_sample, "avg_launch_ms": gate_launch_ms,
+                         "frac": gate_gbs / peaks["hbm_gbs"], "traffic": traffic,
+                         "traffic_note": "DRAM read+write bytes of one full launch, " + cap_note + "; "
+                                         "frac can read a little above 1: the peak is a 1:1 read:write copy, this kernel's traffic is about 5:1 reads",
+                         "alg_bytes_per_launch": gate_bytes_per_launch, "nominal_hbm_gbs": 7700.0, "frac_of_nominal": gate_gbs / 7700.0,
+                         "peak_source": peaks_src, "alg_bytes_per_sample": gate_bytes_per_sample, "avg_launch_ms": gate_launch_ms,
                          "share_of_step": prof.gate_ms / max(prof.total_ms, 1e-9), "timed": "profile pass, kernels serialised"},
             "roofline_sampler": {"kernel": kernel_name,
                                  "bound": "int (LOP3 + IMAD.WIDE share one issue rate of 64 lanes/clk/SM)",
@@ -354,43 +493,34 @@ def main():
                                  "event_mix": sampler_mix,
                                  "bernoulli_bits_per_s": sampler_rate, "alg_int_ops_per_bit": alg_ops_per_bit,
                                  "executed_int_ops_per_bit": exec_ops_per_bit,
+                                 "hbm_write_GBs": sampler_bytes_per_sample * S / (prof.sampler_ms * 1e-3) / 1e9 if prof.sampler_ms > 0 else 0.0,
                                  "avg_launch_ms": prof.sampler_ms / max(1, prof.sampler_launches),
                                  "share_of_step": prof.sampler_ms / max(prof.total_ms, 1e-9),
-                                 "peak_source": "canopy_microbench_int(kind=0) measured in this run; instruction counts from the ncu source page in profiles/"},
+                                 "peak_source": "canopy_microbench_int(kind=0) measured in this run; executed counts: " + cap_note},
+            # the pipelined step against its two resources: what the step would take if the two kernels overlapped perfectly
+            # (max of the two, profile pass) and what the HBM alone allows (all bytes of the step at the measured copy peak)
+            "roofline_step": {"ms_per_step": step_ms, "sampler_ms_alone": prof.sampler_ms, "gate_ms_alone": prof.gate_ms,
+                              "frac_of_max_kernel": max(prof.sampler_ms, prof.gate_ms) / step_ms if step_ms > 0 else None,
+                              "alg_bytes_per_sample": gate_bytes_per_sample + sampler_bytes_per_sample,
+                              "achieved_GBs": step_bytes / (step_ms * 1e-3) / 1e9 if step_ms > 0 else None,
+                              "frac_hbm": step_bytes / (step_ms * 1e-3) / 1e9 / peaks["hbm_gbs"] if step_ms > 0 else None},
+            "tally_check": check if check is not None else "skipped (--no-check)",
             "top_event_tally_last_step": top_tally,
+            "build_tag": build_tag(),
         }
     if world == 1 and rank == 0:
-        cpu_v, cores, n_cpu, dt_cpu, _ = cpu_arm(g, S, tally_all, spec=stats["spec_version"])
+        cpu_v, cores, n_cpu, dt_cpu, _ = cpu_arm(g, S, tally_all, spec=spec)
         line["cpu_baseline"] = {"value": cpu_v, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": f"{n_cpu} samples of {args.workload} in {dt_cpu:.1f} s (bit-packed pthreads port in oracle/)"}
-        if not args.no_study and args.workload != "c4":
-            line["roofline_study_c4"] = c4_study(local, stream, peaks, sampler=args.sampler)
+        if not args.no_study:
+            line["other_configs"] = {n: side_line(n, local, stream, args.sampler) for n in ("c2", "c3") if n != args.workload}
     if rank == 0:
         if args.samples:
-            line["config"]["reduced"] = f"--samples {args.samples}: side study, NOT the workload's full sample count"
+            line["config"]["reduced"] = f"--samples {args.samples}: side study, NOT the workload's sample count"
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0
-
-
-def c4_study(local, stream, peaks, n=1 << 24, sampler=0):
-    """Bounded pass over the 100k-event / 60k-gate DAG (BASELINE.json config 4): per-kernel numbers."""
-    from canopy_b200 import synth
-    from canopy_b200.engine import Plan
-    g = synth.config_graph("c4")
-    with Plan(g, sampler=sampler) as plan:
-        st = plan.stats
-        plan.run(n // 4, seed=7, device=local)
-        _, full = plan.run(n, seed=7, device=local)
-        _, prof = plan.run(n, seed=7, device=local, profile=True)
-    b = (st["n_edges_live"] + st["n_gates_stored"]) / 8.0
-    gbs = b * n / (prof.gate_ms * 1e-3) / 1e9
-    return {"samples": n, "B_live": st["n_basic_live"], "G_live": st["n_gates_live"], "E_live": st["n_edges_live"],
-            "layers": st["n_layers"], "max_fanin": st["max_fanin"],
-            "samples_per_s_overlapped": n / (full.total_ms * 1e-3), "gate_evals_per_s": n / (full.total_ms * 1e-3) * st["n_gates_live"],
-            "gate_kernel_GBs": gbs, "gate_kernel_frac_hbm": gbs / peaks["hbm_gbs"], "gate_ms": prof.gate_ms,
-            "sampler_ms": prof.sampler_ms, "sampler_bits_per_s": st["n_basic_live"] * n / (prof.sampler_ms * 1e-3)}
 
 
 if __name__ == "__main__":

@@ -741,17 +741,29 @@ gate_ring_kernel_t(const __grid_constant__ CUtensorMap vmap, uint4* __restrict__
                    const uint32_t* __restrict__ layer_off, const uint32_t* __restrict__ wide_off,
                    const uint32_t* __restrict__ split, const uint32_t* __restrict__ split_child,
                    uint32_t n_layers, uint32_t n_nodes, uint32_t n_ev, unsigned long long* __restrict__ tallies,
-                   uint64_t first_slab, uint32_t n_slabs, uint64_t begin, uint64_t end) {
+                   uint64_t first_slab, uint32_t n_slabs, uint64_t begin, uint64_t end,
+                   uint32_t* __restrict__ walk_done, uint32_t parity, uint32_t wait_val) {
     extern __shared__ __align__(128) unsigned char smem[];
-    // Pipelined run: the sampler of the next batch is launched as a programmatic dependent of this walk and needs
-    // nothing from it, so it may start as soon as every CTA of this (persistent, single-wave) grid is resident.
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = __shfl_sync(0xFFFFFFFFu, threadIdx.x >> 5, 0);  // broadcast: provably warp-uniform
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kGateWarps * kRingSlots * kRowBytes);
     if (threadIdx.x < kGateWarps * kRingGroups) mbar_init(smem_u32(bars + threadIdx.x), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    // Buffer hazard of the pipelined run, closed explicitly: the sampler this walk releases below (S of batch b+1 ...
+    // of the NEXT walk: S(b+2)) rewrites the value buffer that the walk BEFORE this one, G(b-1) ... read.  Stream order
+    // already implies that walk is over (this launch is an ordinary one); CUDA does not document that for a chain of
+    // programmatic launches, so every walk CTA counts itself out in walk_done[parity] when it is done, and this walk
+    // only releases its dependents after the previous walk's count is complete.  All CTAs of the previous walk are
+    // resident or finished when this kernel starts, so the wait cannot deadlock; in practice it never spins.
+    if (threadIdx.x == 0 && wait_val) {
+        const volatile uint32_t* prev = walk_done + (parity ^ 1u);
+        while (*prev < wait_val) __nanosleep(64);
+        __threadfence();
+    }
     __syncthreads();
+    // Pipelined run: the sampler of the next batch is launched as a programmatic dependent of this walk and needs
+    // nothing from it, so it may start as soon as every CTA of this (persistent, single-wave) grid is resident.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     RowRing<G4> R;
     R.tmap = &vmap; R.row0 = 0;
     R.lane = lane; R.lane_off = lane * 16u; R.gi_next = 0; R.phase = 0;
@@ -838,6 +850,8 @@ gate_ring_kernel_t(const __grid_constant__ CUtensorMap vmap, uint4* __restrict__
             __syncthreads();
         }
     }
+    // every row this CTA had to read has been read (each layer ends in a CTA barrier after its last ring pop)
+    if (threadIdx.x == 0) { __threadfence(); atomicAdd(walk_done + parity, 1u); }
 }
 
 constexpr auto gate_ring_kernel = gate_ring_kernel_t<false>;     // bulk copy per row
@@ -985,7 +999,27 @@ struct DeviceState {
     cudaEvent_t ev_sampled[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
     uint64_t h2d_bytes = 0;
     std::mutex run_mu;  // one run at a time per device (the value buffers and streams are per-device scratch)
+    // Completion of the last run that used this state's scratch (value buffers, gate tallies, thresholds).  A run may
+    // return with its kernels still in flight (canopy_mc_run_device without a report): whatever touches the scratch
+    // next from ANOTHER stream, or from the host, waits on this event first.
+    cudaEvent_t ev_done = nullptr;
+    cudaStream_t last_stream = nullptr;
+    bool ran = false;
+    uint32_t* walk_done = nullptr;   // 2 counters: walk CTAs of even / odd batches that have finished (pipeline hazard guard)
 };
+
+// Order `st` after the last run on this state, if that run was on another stream.
+static void order_after_last_run(DeviceState* s, cudaStream_t st) {
+    if (s->ran && s->last_stream != st) CUDA_CHECK(cudaStreamWaitEvent(st, s->ev_done, 0));
+}
+static void mark_run(DeviceState* s, cudaStream_t st) {
+    CUDA_CHECK(cudaEventRecord(s->ev_done, st));
+    s->ran = true; s->last_stream = st;
+}
+// The host is about to touch (or give away) scratch that the last run may still be using.
+static void wait_last_run(DeviceState* s) {
+    if (s->ran) CUDA_CHECK(cudaEventSynchronize(s->ev_done));
+}
 
 // ------------------------------------------------------------------------------------------------
 // Value-buffer pool.  A value buffer is GBs (c2: 4 GB, c4: 48 GB per buffer); cudaMalloc + cudaFree of that size
@@ -1075,7 +1109,7 @@ void destroy_device_state(DeviceState* s) {
     if (s->s_sample) cudaStreamDestroy(s->s_sample);
     if (s->s_gate) cudaStreamDestroy(s->s_gate);
     for (cudaEvent_t e : {s->ev_fork, s->ev_join, s->ev_t0, s->ev_t1, s->ev_sampled[0], s->ev_sampled[1],
-                          s->ev_consumed[0], s->ev_consumed[1]})
+                          s->ev_consumed[0], s->ev_consumed[1], s->ev_done})
         if (e) cudaEventDestroy(e);
     delete s;
 }
@@ -1152,7 +1186,7 @@ static DeviceState* get_state(canopy_plan* plan, int device) {
         A.add(s->wide_off, L.wide_off); A.add(s->split, L.split); A.add(s->split_child, L.split_child);
         A.add(s->tally_kind, L.tally_kind); A.add(s->grec, L.gate_rec);
         A.add(s->ev_cdf, L.event_cdf); A.add(s->ev_perm, L.event_perm);
-        A.reserve(s->gate_tallies, std::max<size_t>(L.n_gates(), 1) * 8);
+        A.reserve(s->gate_tallies, (std::max<size_t>(L.n_gates(), 1) + 1) * 8);  // + the two walk_done counters
         A.reserve(s->out_tallies, std::max<size_t>(L.tally_kind.size(), 1) * 8);
         if (cudaMalloc(&s->arena, A.total) != cudaSuccess) { cudaGetLastError(); throw Error(CANOPY_E_OOM, "cudaMalloc failed for plan arrays"); }
         {   // one staged upload of all plan arrays instead of a dozen small synchronous copies
@@ -1169,9 +1203,10 @@ static DeviceState* get_state(canopy_plan* plan, int device) {
         // the gate walk of batch b competes with the sampler of batch b+1 for SM slots: its (few, persistent)
         // CTAs must win, so its stream gets the highest priority
         CUDA_CHECK(cudaStreamCreateWithPriority(&s->s_gate, cudaStreamNonBlocking, info.hi_prio));
-        for (cudaEvent_t* e : {&s->ev_fork, &s->ev_join, &s->ev_sampled[0], &s->ev_sampled[1], &s->ev_consumed[0], &s->ev_consumed[1]})
+        for (cudaEvent_t* e : {&s->ev_fork, &s->ev_join, &s->ev_sampled[0], &s->ev_sampled[1], &s->ev_consumed[0], &s->ev_consumed[1], &s->ev_done})
             CUDA_CHECK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
         CUDA_CHECK(cudaEventCreate(&s->ev_t0)); CUDA_CHECK(cudaEventCreate(&s->ev_t1));
+        s->walk_done = reinterpret_cast<uint32_t*>(s->gate_tallies + std::max<size_t>(L.n_gates(), 1));
     } catch (...) { destroy_device_state(s); throw; }
     plan->dev.push_back(s);
     return s;
@@ -1204,6 +1239,7 @@ static void ensure_vals(DeviceState* s, const Lowered& L, size_t slabs, int n_bu
     bool ok = s->n_bufs >= n_bufs;
     for (int b = 0; ok && b < n_bufs; ++b) ok = s->vals_bytes[b] >= bytes;
     if (ok) { s->vals_slabs = std::max(s->vals_slabs, slabs); return; }
+    wait_last_run(s);  // the buffers go back to the pool, where another plan may pick them up
     for (int b = 0; b < 2; ++b) { g_val_pool.release(s->device, s->vals[b], s->vals_bytes[b]); s->vals[b] = nullptr; s->vals_bytes[b] = 0; s->vmap_ok[b] = false; }
     s->vals_slabs = 0; s->n_bufs = 0;
     for (int b = 0; b < n_bufs; ++b) {
@@ -1269,9 +1305,11 @@ static void launch_sampler(const DeviceState* s, const Lowered& L, uint4* vals, 
     CUDA_CHECK(cudaGetLastError());
 }
 
-static void launch_gates(const DeviceState* s, const Lowered& L, uint4* vals, uint64_t first_slab, uint32_t n_slabs,
-                         uint64_t begin, uint64_t end, cudaStream_t st, bool shared_sm = false) {
-    if (L.n_gates() == 0 || n_slabs == 0) return;
+// Returns the number of CTAs launched (what the next walk waits for in walk_done[parity]).
+static uint32_t launch_gates(const DeviceState* s, const Lowered& L, uint4* vals, uint64_t first_slab, uint32_t n_slabs,
+                             uint64_t begin, uint64_t end, cudaStream_t st, bool shared_sm = false, uint32_t parity = 0,
+                             uint32_t wait_val = 0) {
+    if (L.n_gates() == 0 || n_slabs == 0) return 0;
 #if CANOPY_ROW_HALVES == 1
     static const bool direct = getenv("CANOPY_GATE_KERNEL") && !strcmp(getenv("CANOPY_GATE_KERNEL"), "direct");  // A/B knob
     if (direct) {
@@ -1289,13 +1327,16 @@ static void launch_gates(const DeviceState* s, const Lowered& L, uint4* vals, ui
         if (vals == s->vals[b] && s->vmap_ok[b] && kGroupRows == 4)
             gate_ring_kernel_g4<<<grid, kGateThreads, kRingSmemBytes, st>>>(
                 s->vmap[b], vals, s->grec, s->child, s->layer_off, s->wide_off, s->split, s->split_child, L.n_layers(), L.n_nodes(),
-                L.n_events(), s->gate_tallies, first_slab, n_slabs, begin, end);
+                L.n_events(), s->gate_tallies, first_slab, n_slabs, begin, end, s->walk_done, parity, wait_val);
         else
             gate_ring_kernel<<<grid, kGateThreads, kRingSmemBytes, st>>>(
                 s->vmap[0], vals, s->grec, s->child, s->layer_off, s->wide_off, s->split, s->split_child, L.n_layers(), L.n_nodes(),
-                L.n_events(), s->gate_tallies, first_slab, n_slabs, begin, end);
+                L.n_events(), s->gate_tallies, first_slab, n_slabs, begin, end, s->walk_done, parity, wait_val);
+        CUDA_CHECK(cudaGetLastError());
+        return grid;
     }
     CUDA_CHECK(cudaGetLastError());
+    return 0;
 }
 
 static uint32_t pick_batch_slabs(const DeviceState* s, const Lowered& L, const canopy_mc_opts& o, uint64_t total_slabs, int n_bufs) {
@@ -1368,10 +1409,17 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
     canopy_mc_report R{};
     R.slab_samples = kSlabSamples; R.batch_slabs = batch; R.n_batches = n_batches;
 
+    order_after_last_run(s, user);
     CUDA_CHECK(cudaEventRecord(s->ev_t0, user));
-    CUDA_CHECK(cudaMemsetAsync(s->gate_tallies, 0, std::max<size_t>(L.n_gates(), 1) * 8, user));
+    CUDA_CHECK(cudaMemsetAsync(s->gate_tallies, 0, (std::max<size_t>(L.n_gates(), 1) + 1) * 8, user));  // tallies + walk_done
     R.other_launches += 1;
-    std::vector<cudaEvent_t> pe;  // profile events: 4 per batch
+    struct EventList {  // profile events, 3 per batch; destroyed on every path out of this function
+        std::vector<cudaEvent_t> v;
+        ~EventList() { for (cudaEvent_t e : v) cudaEventDestroy(e); }
+        size_t size() const { return v.size(); }
+        cudaEvent_t operator[](size_t i) const { return v[i]; }
+        void push_back(cudaEvent_t e) { v.push_back(e); }
+    } pe;
     if (!overlap) {
         uint64_t fs = slab0;
         for (uint64_t b = 0; b < n_batches; fs += sched[b], ++b) {
@@ -1395,10 +1443,12 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
             // to hardware queues (40 % of fresh plans ran without any overlap, gpurun_out/var.txt).
             // Hazards: S_{b+2} rewrites the buffer G_b read; it starts after G_{b+1} started, i.e. after G_b finished.
             uint64_t fs = slab0;
+            uint32_t done[2] = {0, 0};  // walk CTAs launched so far on even / odd batches
             for (uint64_t b = 0; b < n_batches; fs += sched[b], ++b) {
                 const int buf = (int)(b & 1);
                 launch_sampler(s, L, s->vals[buf], fs, sched[b], K, user, b > 0, b > 0);
-                launch_gates(s, L, s->vals[buf], fs, sched[b], begin, end, user, b + 1 < n_batches);
+                done[buf] += launch_gates(s, L, s->vals[buf], fs, sched[b], begin, end, user, b + 1 < n_batches, (uint32_t)buf,
+                                          done[buf ^ 1]);
                 R.sampler_launches += L.n_events() ? 1 : 0; R.gate_launches += 1;
             }
         } else {
@@ -1442,7 +1492,7 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
             R.sampler_ms += a; R.gate_ms += b2;
         }
     }
-    for (cudaEvent_t e : pe) cudaEventDestroy(e);
+    mark_run(s, user);
     R.h2d_bytes = s->h2d_bytes;
     if (rep) *rep = R;
 }
@@ -1459,23 +1509,28 @@ void mc_sample_words(canopy_plan* plan, const canopy_mc_opts& o, uint64_t first_
     if (n_slabs > 65535 / kRowHalves || n_words / 64 > 65535) throw Error(CANOPY_E_INVALID, "too many words requested");
     ensure_vals(s, L, n_slabs, 1);
     const PhiloxKeys K = make_keys(o.seed);
+    order_after_last_run(s, s->main);
     launch_sampler(s, L, s->vals[0], slab0, (uint32_t)n_slabs, K, s->main);
-    unsigned long long* d = nullptr;
+    struct DevBuf {  // test hook only: a scratch buffer per call, freed on every path
+        unsigned long long* p = nullptr;
+        ~DevBuf() { if (p) cudaFree(p); }
+    } d;
     const size_t bytes = (size_t)L.n_events() * n_words * 8;
-    if (cudaMalloc(&d, bytes) != cudaSuccess) throw Error(CANOPY_E_OOM, "cudaMalloc failed");
+    if (cudaMalloc(&d.p, bytes) != cudaSuccess) { cudaGetLastError(); throw Error(CANOPY_E_OOM, "cudaMalloc failed"); }
     gather_words_kernel<<<dim3(L.n_events(), (uint32_t)(n_words / 64)), 64, 0, s->main>>>(
-        s->vals[0], L.n_events(), L.n_nodes(), first_word - slab0 * kSlabWords, n_words, d);
-    cudaError_t e = cudaMemcpyAsync(words_host, d, bytes, cudaMemcpyDeviceToHost, s->main);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(s->main);
-    cudaFree(d);
-    CUDA_CHECK(e);
+        s->vals[0], L.n_events(), L.n_nodes(), first_word - slab0 * kSlabWords, n_words, d.p);
+    CUDA_CHECK(cudaGetLastError());
+    CUDA_CHECK(cudaMemcpyAsync(words_host, d.p, bytes, cudaMemcpyDeviceToHost, s->main));
+    mark_run(s, s->main);
+    CUDA_CHECK(cudaStreamSynchronize(s->main));
 }
 
 void refresh_thresholds(canopy_plan* plan) {
     const Lowered& L = plan->low;
     for (DeviceState* s : plan->dev) {
-        std::lock_guard<std::mutex> run_lock(s->run_mu);  // never under a run that is reading the old thresholds
+        std::lock_guard<std::mutex> run_lock(s->run_mu);  // never while a run is being enqueued ...
         CUDA_CHECK(cudaSetDevice(s->device));
+        wait_last_run(s);  // ... nor under one still in flight on a user stream (blocking copies below do not order against it)
         if (!L.event_thr32.empty()) {
             CUDA_CHECK(cudaMemcpy(s->thr32, L.event_thr32.data(), L.event_thr32.size() * 4, cudaMemcpyHostToDevice));
             CUDA_CHECK(cudaMemcpy(s->thr64, L.event_thr64.data(), L.event_thr64.size() * 8, cudaMemcpyHostToDevice));

@@ -132,7 +132,9 @@ class Plan:
         _lib.lib().canopy_mc_opts_default(C.byref(o))
         o.seed, o.sample_begin, o.n_samples = int(seed), int(sample_begin), int(n_samples)
         o.device, o.batch_slabs = int(device), int(batch_slabs)
-        o.stream = stream
+        # None: the library's own stream.  A torch handle of 0 is the legacy default stream: the C ABI takes NULL as
+        # "library-owned", so the default streams are passed explicitly (cudaStreamLegacy = 1, include/canopy.h).
+        o.stream = None if stream is None else (1 if int(stream) == 0 else int(stream))
         o.overlap, o.profile = int(bool(overlap)), int(bool(profile))
         return o
 

@@ -194,7 +194,8 @@ def generate(n_basic: int, n_gates: int, n_layers: int, max_fanin: int, seed: in
     g = Graph(p=np.array(p), op=np.array(ops, dtype=np.uint8), kmin=np.array(kmins, dtype=np.uint16),
               kmax=np.zeros(len(ops), dtype=np.uint16), child_off=np.array(off, dtype=np.uint64),
               child=np.array(flat, dtype=np.uint32), roots=np.array(roots, dtype=np.uint32))
-    g.meta = dict(seed=seed, n_layers_requested=n_layers, max_fanin=max_fanin, est_p_top=q[n_basic + top])
+    g.meta = dict(seed=seed, n_layers_requested=n_layers, max_fanin=max_fanin, est_p_top=q[n_basic + top],
+                  est_q=np.array(q[n_basic:n_basic + n_gates]))
     return g
 
 
@@ -207,3 +208,62 @@ def config_graph(name: str, scale: float = 1.0) -> Graph:
     g = generate(nb, ng, nl, c["max_fanin"], 0xC0FFEE + c["cid"], int(c["n_seq"] * (scale if scale < 1 else 1)) if c["n_seq"] else 0)
     g.meta.update(config=name, scale=scale, n_samples=c["n_samples"])
     return g
+
+
+# ---- config 3 as BASELINE.json words it: an EVENT TREE whose sequences share one gate DAG, as Open-PSA MEF text ----------
+_MEF_CONNECTIVE = {AND: "and", OR: "or", ATLEAST: "atleast", XOR: "xor", NOT: "not", NAND: "nand", NOR: "nor"}
+
+
+def mef_xml(g: Graph, n_seq: int = 0, seed: int = 1, ft_name: str = "FT") -> str:
+    """Open-PSA MEF text of a generated DAG: one fault tree (gate i = "g<i>", basic event j = "e<j>", complemented
+    edges as <not>), and -- with n_seq > 0 -- an event tree "ET" with initiating event "IE": a binary tree of forks over
+    functional events F0, F1, ...; the path taken at depth d collects (state "fails") a mid-level gate of the DAG or
+    (state "works") its negation; each of the first n_seq leaves ends in its own sequence S<k>, the others in "REST".
+    A sequence formula is therefore the conjunction of 8 or so (possibly negated) gates of the one shared DAG, which the
+    library's event-tree walker (csrc/mef_model.cpp; reference data model event_tree.h:65-197, instruction.h:38-83)
+    has to derive.  Only the graph's own roots argument is ignored: the loader finds the top events itself."""
+    nb = g.n_basic
+    out = ["<?xml version='1.0'?>\n<opsa-mef>\n"]
+
+    def arg(code: int) -> str:
+        node = code & 0x7FFFFFFF
+        ref = f"<basic-event name='e{node}'/>" if node < nb else f"<gate name='g{node - nb}'/>"
+        return f"<not>{ref}</not>" if code & COMPLEMENT else ref
+
+    if n_seq:
+        rng = random.Random(seed)
+        depth = max(1, math.ceil(math.log2(n_seq)))
+        lo, hi = g.n_gates // 3, 2 * g.n_gates // 3
+        # one collected gate per functional event; gates whose independence estimate is moderate, so that both
+        # branches of every fork are taken and many sequences do occur
+        est = g.meta.get("est_q")
+        pool = [i for i in range(lo, hi) if est is None or 0.1 <= est[i] <= 0.9] or list(range(lo, hi))
+        fork_gate = rng.sample(pool, depth) if len(pool) >= depth else [pool[int(rng.random() * len(pool))] for _ in range(depth)]
+        out.append("<define-initiating-event name='IE' event-tree='ET'/>\n<define-event-tree name='ET'>\n")
+        out += [f"<define-functional-event name='F{d}'/>\n" for d in range(depth)]
+        out += [f"<define-sequence name='S{k}'/>\n" for k in range(n_seq)]
+        out.append("<define-sequence name='REST'/>\n<initial-state>\n")
+        leaf = [0]
+
+        def fork(d: int) -> str:
+            if d == depth:
+                k = leaf[0]; leaf[0] += 1
+                return f"<sequence name='{'S%d' % k if k < n_seq else 'REST'}'/>"
+            gate = f"<gate name='g{fork_gate[d]}'/>"
+            return (f"<fork functional-event='F{d}'>"
+                    f"<path state='fails'><collect-formula>{gate}</collect-formula>{fork(d + 1)}</path>"
+                    f"<path state='works'><collect-formula><not>{gate}</not></collect-formula>{fork(d + 1)}</path></fork>")
+        out.append(fork(0))
+        out.append("\n</initial-state>\n</define-event-tree>\n")
+    out.append(f"<define-fault-tree name='{ft_name}'>\n")
+    off = g.child_off
+    for i in range(g.n_gates):
+        op = int(g.op[i])
+        kids = "".join(arg(int(c)) for c in g.child[int(off[i]):int(off[i + 1])])
+        tag = _MEF_CONNECTIVE[op]
+        attr = f" min='{int(g.kmin[i])}'" if op == ATLEAST else ""
+        out.append(f"<define-gate name='g{i}'><{tag}{attr}>{kids}</{tag}></define-gate>\n")
+    out.append("</define-fault-tree>\n<model-data>\n")
+    out += [f"<define-basic-event name='e{j}'><float value='{float(g.p[j])!r}'/></define-basic-event>\n" for j in range(nb)]
+    out.append("</model-data>\n</opsa-mef>\n")
+    return "".join(out)

@@ -18,7 +18,7 @@ def test_reference_arm_json_line():
     assert d["impl"] == "reference" and d["metric"] == "mc_samples_per_sec" and d["unit"] == "samples/s"
     assert d["n_gpus"] == 1 and d["steps"] == 2 and d["warmup"] == 1 and d["higher_is_better"] is True
     assert d["value"] > 0 and d["ms_per_step"] > 0 and d["vs_baseline"] is None and d["data"] == "synthetic"
-    assert d["config"]["workload"].startswith("c1:") and d["config"]["spec_version"] == 3
+    assert d["config"]["workload"].startswith("c1:") and "B=50 G=16" in d["config"]["workload"]
     cb = d["cpu_baseline"]
     assert cb["kind"] == "port" and cb["cores"] == len(os.sched_getaffinity(0)) and cb["value"] == d["value"] and cb["sample"]
     assert d["e2e"] == {"value": d["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
@@ -29,3 +29,20 @@ def test_reference_arm_other_ranks_exit_quietly():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1",
                         "--warmup", "0"], env=env, text=True, capture_output=True, timeout=120)
     assert r.returncode == 0 and not [l for l in r.stdout.splitlines() if l.startswith("{")]
+
+
+def test_reference_arm_loads_no_native_code_of_the_product():
+    """The CPU arm must time oracle/ only: importing bench's reference path must not load libcanopy.so, and its stdlib
+    reader of the c1 example must produce the graph the library's reader produces."""
+    code = ("import sys, bench; sys.argv=['bench.py','--impl','reference','--workload','c1','--steps','1','--warmup','0'];"
+            "import os; os.environ['CANOPY_BENCH_REF_BUDGET_S']='0.5'; bench.main();"
+            "maps=open('/proc/self/maps').read(); assert 'libcanopy' not in maps, 'libcanopy.so loaded in the reference arm'; "
+            "assert 'liboracle' in maps")
+    subprocess.check_call([sys.executable, "-c", code], cwd=ROOT, timeout=120)
+    import numpy as np
+    import bench
+    from canopy_b200.engine import load_mef
+    a = bench._c1_graph_stdlib(os.path.join(ROOT, "examples", "c1_small_ft.xml"))
+    b = load_mef(os.path.join(ROOT, "examples", "c1_small_ft.xml"))
+    for f in ("p", "op", "child_off", "child", "roots"):
+        assert np.array_equal(getattr(a, f), getattr(b, f)), f

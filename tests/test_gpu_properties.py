@@ -95,6 +95,11 @@ def test_device_output_on_torch_stream_matches_host_output():
 
 
 def test_run_multi_equals_single_device():
+    """canopy_mc_run_multi (ncclCommInitAll + ncclAllReduce over every visible device) == one device.  Needs two
+    devices: on a 1-GPU lease this test is SKIPPED, not passed -- mc_run_multi's n_devices == 1 branch never touches NCCL."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("NEEDS >= 2 GPUS: canopy_mc_run_multi's NCCL all-reduce is not exercised on a single-device lease "
+                    "(bench.py's tally_check covers the N-way == 1-way sum on the driver's multi-GPU runs)")
     g = synth.config_graph("c2", 0.1)
     n = 4096 * 37 + 5
     devs = list(range(torch.cuda.device_count()))
@@ -185,3 +190,61 @@ def test_pipelined_run_is_the_same_on_every_kind_of_stream_and_pipeline():
         for kw in (dict(), dict(stream=1), dict(stream=2), dict(overlap=False)):
             got, rep = plan.run(n, seed=3, sample_begin=77, batch_slabs=3, **kw)
             assert rep.n_batches >= 20 and np.array_equal(got, want), kw
+
+
+def test_run_sharded_and_run_device_on_torchs_default_stream():
+    """canopy_b200.dist.run_sharded passes torch's CURRENT stream; on the default stream that handle is 0, which the C ABI
+    would read as "use the library's own stream" and leave the run unordered with the torch ops around it.  The Python
+    layer maps 0 to cudaStreamLegacy: fills before and reads after the run, on the default stream, must see the tallies."""
+    from canopy_b200.dist import run_sharded
+    g = synth.config_graph("c2", 0.1)
+    n = 1 << 20
+    with Plan(g, tally_all_gates=True) as plan:
+        want, _ = plan.run(n, seed=3, sample_begin=5)
+        assert torch.cuda.current_stream().cuda_stream == 0
+        for _ in range(5):
+            got = run_sharded(plan, n, seed=3, sample_begin=5)
+            doubled = got * 2                                    # default stream, right behind the run
+            assert np.array_equal(got.cpu().numpy().astype(np.uint64), want)
+            assert np.array_equal(doubled.cpu().numpy().astype(np.uint64), want * 2)
+        out = torch.full((plan.n_tallies,), -1, dtype=torch.int64, device="cuda")   # fill on the default stream ...
+        plan.run_device(out.data_ptr(), n, seed=3, sample_begin=5, stream=torch.cuda.current_stream().cuda_stream)
+        assert np.array_equal((out + 0).cpu().numpy().astype(np.uint64), want)     # ... and read right behind it
+
+
+def test_two_runs_of_one_plan_on_different_streams_do_not_overlap():
+    """Per-plan scratch (value buffers, gate tallies) is reused by every run: a second run on ANOTHER stream must wait for
+    the first (the library records a completion event per device state and makes the next run's stream wait on it)."""
+    g = synth.config_graph("c2", 0.2)
+    n = 1 << 22
+    with Plan(g, tally_all_gates=True) as plan:
+        want_a, _ = plan.run(n, seed=1)
+        want_b, _ = plan.run(n, seed=2)
+        sa, sb = torch.cuda.Stream(), torch.cuda.Stream()
+        a = torch.zeros(plan.n_tallies, dtype=torch.int64, device="cuda")
+        b = torch.zeros(plan.n_tallies, dtype=torch.int64, device="cuda")
+        torch.cuda.synchronize()
+        for _ in range(3):
+            plan.run_device(a.data_ptr(), n, seed=1, stream=sa.cuda_stream)    # asynchronous: returns with kernels in flight
+            plan.run_device(b.data_ptr(), n, seed=2, stream=sb.cuda_stream)
+            torch.cuda.synchronize()
+            assert np.array_equal(a.cpu().numpy().astype(np.uint64), want_a)
+            assert np.array_equal(b.cpu().numpy().astype(np.uint64), want_b)
+        # canopy_plan_update_p while a run is in flight on a user stream must not change that run's thresholds
+        plan.run_device(a.data_ptr(), n, seed=1, stream=sa.cuda_stream)
+        plan.update_p(np.clip(g.p * 1.5, 0, 0.9))
+        torch.cuda.synchronize()
+        assert np.array_equal(a.cpu().numpy().astype(np.uint64), want_a)
+
+
+def test_pipeline_hazard_on_a_gate_bound_graph():
+    """on a graph whose gate walk outlasts the sampler (c4-like: deep, high fan-in) the pipelined run with many
+    small batches must equal the serialised run, repeatedly (S(b+2) must not overwrite the buffer G(b) still reads)."""
+    g = synth.config_graph("c4", 0.05)
+    n = 24 * 4 * 8192 + 99
+    with Plan(g, tally_all_gates=True) as plan:
+        want, _ = plan.run(n, seed=7, batch_slabs=4, overlap=False)
+        assert np.array_equal(want, O.mc_packed(g, 7, 0, n, True, nthreads=CORES, spec=plan.spec))
+        for rep in range(12):
+            got, r = plan.run(n, seed=7, batch_slabs=4, overlap=True)
+            assert r.n_batches >= 24 and np.array_equal(got, want), rep
