@@ -46,7 +46,8 @@ class CPlanView(C.Structure):
                 ("gate_op", C.POINTER(C.c_uint8)), ("gate_flags", C.POINTER(C.c_uint8)),
                 ("gate_kmin", C.POINTER(C.c_uint16)), ("gate_kmax", C.POINTER(C.c_uint16)),
                 ("layer_off", C.POINTER(C.c_uint32)),
-                ("tally_kind", C.POINTER(C.c_uint8)), ("tally_gate", C.POINTER(C.c_uint32))]
+                ("tally_kind", C.POINTER(C.c_uint8)), ("tally_gate", C.POINTER(C.c_uint32)),
+                ("event_k", C.POINTER(C.c_uint8))]
 
 
 class CMcOpts(C.Structure):
@@ -110,7 +111,8 @@ SYMBOLS = {
     "canopy_status_string": (C.c_char_p, [C.c_int]),
     "canopy_version": (C.c_uint32, []),
     "canopy_spec_version": (C.c_uint32, []),
-    "canopy_sparse_cdf": (C.c_int, [C.c_uint32, C.POINTER(C.c_uint64)]),
+    "canopy_sparse_class": (C.c_int, [C.c_uint64, C.POINTER(C.c_uint32)]),
+    "canopy_sparse_cdf": (C.c_int, [C.c_uint64, C.c_uint32, C.POINTER(C.c_uint64)]),
     "canopy_plan_debug_set_sparse_table": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint64)]),
 }
 

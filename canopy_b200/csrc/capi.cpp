@@ -8,6 +8,8 @@
 #include <vector>
 
 #include "plan.h"
+#include "sparse_table.h"
+#include "canopy-testing.h"
 
 namespace {
 thread_local std::string g_last_error;
@@ -79,6 +81,7 @@ canopy_status canopy_plan_view_get(const canopy_plan* plan, canopy_plan_view* v)
         v->gate_op = L.gate_op.data(); v->gate_flags = L.gate_flags.data();
         v->gate_kmin = L.gate_kmin.data(); v->gate_kmax = L.gate_kmax.data();
         v->layer_off = L.layer_off.data(); v->tally_kind = L.tally_kind.data(); v->tally_gate = L.tally_gate.data();
+        v->event_k = L.event_k.empty() ? nullptr : L.event_k.data();
     });
 }
 
@@ -174,12 +177,10 @@ canopy_status canopy_plan_debug_set_sparse_table(canopy_plan* plan, uint32_t liv
         require(plan && cdf, "canopy_plan_debug_set_sparse_table: null argument");
         std::lock_guard<std::mutex> lock(plan->mu);
         canopy::Lowered& L = plan->low;
-        require(L.opts.sampler == CANOPY_SAMPLER_SPARSE && L.opts.threshold_bits == 32 && live_event < L.n_events() &&
-                    (L.event_thr32[live_event] >> (32 - CANOPY_SPARSE_MIN_ZEROS)) == 0,
-                "canopy_plan_debug_set_sparse_table: not a sparse event of a spec 3 plan");
+        require(L.opts.sampler == CANOPY_SAMPLER_SPARSE && live_event < L.n_events() && L.event_k[live_event] != 0,
+                "canopy_plan_debug_set_sparse_table: not a sparse event of a spec 4 plan");
         for (uint32_t j = 0; j + 1 < CANOPY_SPARSE_CDF_LEN; ++j) require(cdf[j] <= cdf[j + 1], "canopy_plan_debug_set_sparse_table: table must be non-decreasing");
-        std::copy(cdf, cdf + CANOPY_SPARSE_CDF_LEN, L.event_cdf.begin() + (size_t)live_event * CANOPY_SPARSE_CDF_LEN);
-        canopy::refresh_thresholds(plan);
+        canopy::debug_set_sparse_table(plan, live_event, cdf);
     });
 }
 
@@ -213,7 +214,7 @@ canopy_status canopy_estimate_from_tally(uint64_t tally, uint64_t n_samples, can
 
 canopy_status canopy_microbench_int(int32_t device, int32_t kind, double* out_lane_ops_per_s, double* out_ms) {
     return guard([&] {
-        require(out_lane_ops_per_s && out_ms && kind >= 0 && kind <= 4, "canopy_microbench_int: bad argument");
+        require(out_lane_ops_per_s && out_ms && kind >= 0 && kind <= 6, "canopy_microbench_int: bad argument");
         canopy::microbench_int(device, kind, out_lane_ops_per_s, out_ms);
     });
 }
@@ -239,11 +240,19 @@ const char* canopy_status_string(canopy_status s) {
 uint32_t canopy_version(void) { return (CANOPY_VERSION_MAJOR << 16) | CANOPY_VERSION_MINOR; }
 uint32_t canopy_spec_version(void) { return CANOPY_SPEC_VERSION; }
 
-canopy_status canopy_sparse_cdf(uint32_t thr32, uint64_t* out_cdf) {
+canopy_status canopy_sparse_class(uint64_t thr64, uint32_t* out_k) {
+    return guard([&] {
+        require(out_k != nullptr, "canopy_sparse_class: null output");
+        *out_k = canopy::sparse_class_k(thr64);
+    });
+}
+
+canopy_status canopy_sparse_cdf(uint64_t thr64, uint32_t k, uint64_t* out_cdf) {
     return guard([&] {
         require(out_cdf != nullptr, "canopy_sparse_cdf: null output");
-        require(thr32 != 0 && (thr32 >> (32 - CANOPY_SPARSE_MIN_ZEROS)) == 0, "canopy_sparse_cdf: threshold is not in the sparse range");
-        canopy::sparse_cdf(thr32, out_cdf);
+        require(thr64 != 0 && k >= 7 && k <= CANOPY_SPARSE_MAX_LOG2 && canopy::clz64(thr64) >= CANOPY_SPARSE_MIN_ZEROS,
+                "canopy_sparse_cdf: threshold is not in the sparse range, or k is not in 7..CANOPY_SPARSE_MAX_LOG2");
+        canopy::sparse_cdf(thr64, k, out_cdf);
     });
 }
 

@@ -22,6 +22,7 @@
 #include <thread>
 
 #include "plan.h"
+#include "sparse_table.h"
 
 namespace canopy {
 namespace {
@@ -150,8 +151,10 @@ std::vector<uint32_t> topo_order(const canopy_graph_desc& d) {
 void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lowered& L) {
     if (opts.threshold_bits != 32 && opts.threshold_bits != 64)
         fail(CANOPY_E_INVALID, "threshold_bits must be 32 or 64");
+    if (opts.sampler == 3)
+        fail(CANOPY_E_UNSUPPORTED, "sampling spec 3 was retired in favour of spec 4 (CANOPY_SAMPLER_SPARSE): tallies taken under it cannot be continued");
     if (opts.sampler != CANOPY_SAMPLER_DIRECT && opts.sampler != CANOPY_SAMPLER_SLICED && opts.sampler != CANOPY_SAMPLER_SPARSE)
-        fail(CANOPY_E_INVALID, "sampler must be CANOPY_SAMPLER_DIRECT (1), CANOPY_SAMPLER_SLICED (2) or CANOPY_SAMPLER_SPARSE (3)");
+        fail(CANOPY_E_INVALID, "sampler must be CANOPY_SAMPLER_DIRECT (1), CANOPY_SAMPLER_SLICED (2) or CANOPY_SAMPLER_SPARSE (4)");
     validate(d);
     const uint32_t B = d.n_basic, G = d.n_gates;
     const bool tally_all = opts.tally_all_gates != 0;
@@ -403,61 +406,29 @@ void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lower
     s.max_fanin = max_fanin; s.mean_fanin = L.n_gates() ? (double)L.child.size() / L.n_gates() : 0.0;
     s.n_tallies = n_tallies; s.n_const_nodes = n_const; s.n_alias_nodes = n_alias;
     s.spec_version = (uint32_t)opts.sampler;  // spec number == sampler id
-    build_sparse_tables(L);
+    build_sparse_classes(L);
 }
 
-// Spec 3: cumulative table of Binomial(128, t / 2^32) in 0.64 fixed point, exact integer
-// arithmetic so that every implementation of the spec gets the same 64-bit words.
-//   a_0 = (1 - p)^128 by seven truncating squarings of (2^32 - t) * 2^32
-//   a_{j+1} = floor(a_j * (128 - j) * t / ((j + 1) * (2^32 - t)))          (fits 128 bits for t < 2^25)
-//   cdf_j = a_0 + ... + a_j
-void sparse_cdf(uint32_t t, uint64_t* cdf) {
-    typedef unsigned __int128 u128;
-    const uint64_t q = 4294967296ull - t;
-    uint64_t x = q << 32;
-    for (int i = 0; i < 7; ++i) x = (uint64_t)(((u128)x * x) >> 64);
-    u128 sum = 0;
-    uint64_t a = x;
-    for (uint32_t j = 0; j < CANOPY_SPARSE_CDF_LEN; ++j) {
-        sum += a;
-        cdf[j] = sum > (u128)~0ull ? ~0ull : (uint64_t)sum;
-        if (a == 0) {  // every later term is 0 as well: the table is flat from here on
-            for (uint32_t k = j + 1; k < CANOPY_SPARSE_CDF_LEN; ++k) cdf[k] = cdf[j];
-            break;
-        }
-        a = (uint64_t)(((u128)a * (128u - j) * t) / ((u128)(j + 1) * q));
-    }
-}
-
-// Per-plan arrays of spec 3: which events take the sparse path (their tables), and the order in which the sampler's
-// warps take the events (sliced events first, so that the CTAs still running at the end of a launch are the cheap ones).
-void build_sparse_tables(Lowered& L) {
+// Spec 4: class of every live event and the sampler's order.  Pure functions of thr64.
+void build_sparse_classes(Lowered& L) {
     const uint32_t n = L.n_events();
-    L.event_cdf.clear(); L.event_perm.clear();
+    L.event_k.clear(); L.event_perm.clear(); L.n_dense = 0;
+    for (uint32_t& c : L.class_off) c = 0;
     if (L.opts.sampler != CANOPY_SAMPLER_SPARSE) return;
-    L.event_cdf.assign((size_t)n * CANOPY_SPARSE_CDF_LEN, ~0ull);
-    L.event_perm.reserve(n);
-    const bool narrow = L.opts.threshold_bits == 32;
-    auto sparse = [&](uint32_t i) { return narrow && (L.event_thr32[i] >> (32 - CANOPY_SPARSE_MIN_ZEROS)) == 0; };
-    for (uint32_t i = 0; i < n; ++i) if (!sparse(i)) L.event_perm.push_back(i);
-    const uint32_t n_dense = (uint32_t)L.event_perm.size();
-    for (uint32_t i = 0; i < n; ++i) if (sparse(i)) L.event_perm.push_back(i);
-    // the tables cost one 128-bit division per entry: spread large plans over a few host threads (pure functions of thr)
-    const uint32_t n_sparse = n - n_dense;
-    const uint32_t n_thr = n_sparse < 2048 ? 1 : std::min<uint32_t>(8, std::max(1u, std::thread::hardware_concurrency()));
-    auto work = [&](uint32_t lo, uint32_t hi) {
-        for (uint32_t k = lo; k < hi; ++k) {
-            const uint32_t i = L.event_perm[n_dense + k];
-            sparse_cdf(L.event_thr32[i], &L.event_cdf[(size_t)i * CANOPY_SPARSE_CDF_LEN]);
-        }
-    };
-    if (n_thr == 1) work(0, n_sparse);
-    else {
-        std::vector<std::thread> pool;
-        for (uint32_t t = 0; t < n_thr; ++t)
-            pool.emplace_back(work, (uint32_t)((uint64_t)n_sparse * t / n_thr), (uint32_t)((uint64_t)n_sparse * (t + 1) / n_thr));
-        for (auto& th : pool) th.join();
+    L.event_k.resize(n);
+    uint32_t count[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // [0] dense, [1 + c] class k = 7 + c
+    for (uint32_t i = 0; i < n; ++i) {
+        const uint32_t k = sparse_class_k(L.event_thr64[i]);
+        L.event_k[i] = (uint8_t)k;
+        ++count[k ? k - 6 : 0];
     }
+    uint32_t start[8], acc = 0;
+    for (int c = 0; c < 8; ++c) { start[c] = acc; acc += count[c]; }
+    L.n_dense = count[0];
+    for (int c = 0; c < 7; ++c) L.class_off[c] = start[c + 1];
+    L.class_off[7] = n;
+    L.event_perm.resize(n);
+    for (uint32_t i = 0; i < n; ++i) { const uint32_t k = L.event_k[i]; L.event_perm[start[k ? k - 6 : 0]++] = i; }
 }
 
 void shard_range(uint64_t begin, uint64_t n, int rank, int world, uint64_t* ob, uint64_t* on) {
@@ -500,7 +471,7 @@ void requantise(Lowered& L, const double* p, uint32_t n_basic) {
         L.event_thr32[i] = wide ? (uint32_t)(t >> 32) : (uint32_t)t;
         L.event_thr64[i] = wide ? t : (t << 32);
     }
-    build_sparse_tables(L);
+    build_sparse_classes(L);
 }
 
 uint64_t fingerprint(const Lowered& L) {
@@ -513,8 +484,8 @@ uint64_t fingerprint(const Lowered& L) {
     };
     const int32_t o[3] = {L.opts.tally_all_gates, L.opts.threshold_bits, L.opts.sampler};
     mix(o, sizeof o);
-    if (L.opts.sampler == CANOPY_SAMPLER_SPARSE) {  // the constants of spec 3 are part of what a restart record must match
-        const int32_t c[3] = {CANOPY_SLICED_HEAD_BITS, CANOPY_SPARSE_MIN_ZEROS, CANOPY_SPARSE_CDF_LEN};
+    if (L.opts.sampler == CANOPY_SAMPLER_SPARSE) {  // the constants of spec 4 are part of what a restart record must match
+        const int32_t c[4] = {CANOPY_SLICED_HEAD_BITS, CANOPY_SPARSE_MIN_ZEROS, CANOPY_SPARSE_CDF_LEN, CANOPY_SPARSE_MAX_LOG2};
         mix(c, sizeof c);
     }
     mix(L.event_orig.data(), L.event_orig.size() * 4);

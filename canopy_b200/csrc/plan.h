@@ -58,8 +58,14 @@ struct Lowered {
     std::vector<uint32_t> event_orig;
     std::vector<uint32_t> event_thr32;
     std::vector<uint64_t> event_thr64;
-    std::vector<uint64_t> event_cdf;       // spec 3: [n_events][CANOPY_SPARSE_CDF_LEN] cumulative count tables (empty otherwise)
-    std::vector<uint32_t> event_perm;      // spec 3: order in which the sampler's warps take the live events (empty otherwise)
+    // spec 4: group exponent k of each live event (0 = dense, spec 2 planes; 7..13 = sparse with 2^k-sample groups), the
+    // order in which the sampler takes the events (dense first, then k = 7, 8, ... 13: the expensive work is issued first
+    // and the events of one unit share a class), and the class boundaries inside that order.  The count tables are
+    // built on the device from thr64 (sparse_table.h).  All empty / zero under specs 1 and 2.
+    std::vector<uint8_t> event_k;
+    std::vector<uint32_t> event_perm;
+    uint32_t n_dense = 0;                  // event_perm[0, n_dense) are the dense events
+    uint32_t class_off[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // class c (k = 7 + c) is event_perm[class_off[c], class_off[c+1])
     std::vector<uint8_t> event_class;      // [n_basic_in] how lowering classed each ORIGINAL event: 0 false, 1 true, 2 sampled/dead
     // live gates in layer order; device node id == n_events + position
     std::vector<GateRec> gate_rec;
@@ -84,8 +90,7 @@ void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lower
 // Re-quantise the thresholds of the live events from new probabilities (canopy_plan_update_p); throws if the
 // constant folding of the existing lowering would no longer hold.
 void requantise(Lowered& L, const double* p, uint32_t n_basic);
-void sparse_cdf(uint32_t thr32, uint64_t* cdf);   // spec 3 count table of one event (CANOPY_SPARSE_CDF_LEN words)
-void build_sparse_tables(Lowered& L);
+void build_sparse_classes(Lowered& L);   // spec 4: event_k, event_perm, n_dense, class_off from event_thr64
 uint64_t fingerprint(const Lowered& L);
 
 struct DeviceState;  // engine.cu
@@ -109,6 +114,7 @@ void mc_run_multi(canopy_plan* plan, const canopy_mc_opts& o, const int32_t* dev
                   uint64_t* tallies_host, canopy_mc_report* rep);
 void microbench_int(int device, int kind, double* lane_ops_per_s, double* ms);
 void trim_device_cache(int device);           // free the value buffers parked by destroyed plans (-1: all devices)
-void refresh_thresholds(canopy_plan* plan);  // re-upload thr32/thr64 to every device the plan is resident on
+void refresh_thresholds(canopy_plan* plan);  // re-upload thresholds and sampler order to every device the plan is resident on; rebuild the tables
+void debug_set_sparse_table(canopy_plan* plan, uint32_t live_event, const uint64_t* cdf);  // canopy-testing.h hook
 void shard_range(uint64_t begin, uint64_t n, int rank, int world, uint64_t* ob, uint64_t* on);
 }  // namespace canopy

@@ -28,7 +28,7 @@ class Settings:
     sample_begin: int = 0       # first global sample index (restart / shard by counter range)
     tally_all_gates: bool = False
     threshold_bits: int = 32
-    sampler: int = 0            # sampling spec: 0 = library default (2, "sliced"), 1 = "direct", 2 = "sliced", 3 = "sparse"
+    sampler: int = 0            # sampling spec: 0 = library default (4), 1 = "direct", 2 = "sliced", 4 = "classed sparse"
     overlap: bool = True
     profile: bool = False
 
@@ -41,8 +41,8 @@ class Settings:
             raise SettingsError("The batch size cannot be negative.")
         if self.threshold_bits not in (32, 64):
             raise SettingsError("threshold_bits must be 32 or 64")
-        if self.sampler not in (0, 1, 2, 3):
-            raise SettingsError("sampler must be 0 (default), 1 (direct), 2 (sliced) or 3 (sparse)")
+        if self.sampler not in (0, 1, 2, 4):
+            raise SettingsError("sampler must be 0 (default), 1 (direct), 2 (sliced) or 4 (classed sparse)")
         return self
 
 
@@ -125,7 +125,8 @@ class Plan:
             gate_op=_arr(v.gate_op, v.n_gates, np.uint8), gate_flags=_arr(v.gate_flags, v.n_gates, np.uint8),
             gate_kmin=_arr(v.gate_kmin, v.n_gates, np.uint16), gate_kmax=_arr(v.gate_kmax, v.n_gates, np.uint16),
             layer_off=_arr(v.layer_off, v.n_layers + 1, np.uint32),
-            tally_kind=_arr(v.tally_kind, v.n_tallies, np.uint8), tally_gate=_arr(v.tally_gate, v.n_tallies, np.uint32))
+            tally_kind=_arr(v.tally_kind, v.n_tallies, np.uint8), tally_gate=_arr(v.tally_gate, v.n_tallies, np.uint32),
+            event_k=_arr(v.event_k, v.n_events, np.uint8) if v.event_k else np.zeros(v.n_events, dtype=np.uint8))
 
     def _opts(self, seed, sample_begin, n_samples, device, batch_slabs, stream, overlap, profile) -> _lib.CMcOpts:
         o = _lib.CMcOpts()
@@ -181,7 +182,7 @@ class Plan:
         _lib.check(_lib.lib().canopy_plan_update_p(self._h, p.ctypes.data_as(C.POINTER(C.c_double)), p.shape[0]))
 
     def debug_set_sparse_table(self, live_event: int, cdf) -> None:
-        """Spec 3 test hook: replace the count table of one sparse event (canopy_plan_debug_set_sparse_table)."""
+        """Spec 4 test hook (include/canopy-testing.h): replace the count table of one sparse event."""
         t = np.ascontiguousarray(cdf, dtype=np.uint64)
         _lib.check(_lib.lib().canopy_plan_debug_set_sparse_table(self._h, live_event, t.ctypes.data_as(C.POINTER(C.c_uint64))))
 

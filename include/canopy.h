@@ -54,26 +54,32 @@ extern "C" {
  *           the variates of 128 consecutive samples come from that many bit-sliced Philox calls, the
  *           remaining bits from tail calls that only the ~2^-H samples still undecided after the head
  *           bits ever consume (4 undecided samples per call; 2 with 64-bit thresholds).
- *   spec 3  "sparse": spec 2 for every event with p >= 2^-CANOPY_SPARSE_MIN_ZEROS (and for all events with 64-bit
- *           thresholds).  A rarer event draws, per 128-sample group, ONE Philox call: a 64-bit variate compared with
- *           the event's Binomial(128, thr/2^32) cumulative table (CANOPY_SPARSE_CDF_LEN entries, exact integer
- *           arithmetic) gives the number of ones of the group, 7-bit fields of the same call place them (duplicates
- *           skipped; further calls only if the fields run out).  Same i.i.d. Bernoulli(thr/2^32) law per sample up to
- *           the table's rounding (below 2^-55) and the mass beyond CANOPY_SPARSE_CDF_LEN ones (below 1e-18).
+ *   spec 4  "classed sparse": spec 2 for every event with p >= 2^-CANOPY_SPARSE_MIN_ZEROS.  A rarer event works on groups
+ *           of 2^k samples, k = min(CANOPY_SPARSE_MAX_LOG2, z + 2) with z the leading zero bits of its 64-bit threshold
+ *           (fewer than four expected ones per group): ONE Philox call per group; a 64-bit variate compared with the
+ *           event's Binomial(2^k, thr/2^64) cumulative table (CANOPY_SPARSE_CDF_LEN entries, exact integer arithmetic)
+ *           gives the number of ones of the group, k-bit fields of the same call place them (duplicates skipped;
+ *           further calls only if the fields run out).  Same i.i.d. Bernoulli(thr/2^bits) law per sample up to the
+ *           table's rounding (below 2^-50) and the mass beyond CANOPY_SPARSE_CDF_LEN ones (below 1e-17).  Serves 32- and
+ *           64-bit thresholds alike (a 32-bit threshold is widened to thr32 << 32).
+ *   (spec 3, this spec with 128-sample groups only, was retired in its favour: CANOPY_E_UNSUPPORTED.)
  * CANOPY_SPEC_VERSION is the default spec of this build. */
-#define CANOPY_SPEC_VERSION 3
+#define CANOPY_SPEC_VERSION 4
 #ifndef CANOPY_SLICED_HEAD_BITS
 #define CANOPY_SLICED_HEAD_BITS 7   /* H of spec 2; part of the spec (changing it changes every tally) */
 #endif
-#define CANOPY_SAMPLER_DEFAULT 0   /* = the build default (spec 3) */
+#define CANOPY_SAMPLER_DEFAULT 0   /* = the build default (spec 4) */
 #define CANOPY_SAMPLER_DIRECT  1   /* spec 1 */
 #define CANOPY_SAMPLER_SLICED  2   /* spec 2 */
-#define CANOPY_SAMPLER_SPARSE  3   /* spec 3 */
+#define CANOPY_SAMPLER_SPARSE  4   /* spec 4 */
 #ifndef CANOPY_SPARSE_MIN_ZEROS
-#define CANOPY_SPARSE_MIN_ZEROS 5  /* spec 3: events with thr32 < 2^(32-5), i.e. fewer than four expected ones per 128-sample group */
+#define CANOPY_SPARSE_MIN_ZEROS 5  /* spec 4: events with p < 2^-5 take the sparse path */
+#endif
+#ifndef CANOPY_SPARSE_MAX_LOG2
+#define CANOPY_SPARSE_MAX_LOG2 13  /* spec 4: largest group is 2^13 = 8192 samples (one slab row) */
 #endif
 #ifndef CANOPY_SPARSE_CDF_LEN
-#define CANOPY_SPARSE_CDF_LEN  32  /* spec 3: entries of the cumulative count table = largest count a group can draw */
+#define CANOPY_SPARSE_CDF_LEN  32  /* spec 4: entries of the cumulative count table = largest count a group can draw */
 #endif
 
 typedef enum canopy_status {
@@ -156,7 +162,7 @@ typedef struct canopy_plan_stats {
     uint32_t n_tallies;        /* length of the tallies output array                             */
     uint32_t n_const_nodes;    /* roots/gates folded to constants                                */
     uint32_t n_alias_nodes;    /* gates folded to (possibly complemented) aliases                */
-    uint32_t spec_version;     /* the spec this plan samples with (1 direct, 2 sliced, 3 sparse) */
+    uint32_t spec_version;     /* the spec this plan samples with (1 direct, 2 sliced, 4 classed sparse) */
 } canopy_plan_stats;
 
 typedef struct canopy_plan canopy_plan; /* opaque; immutable lowered graph + lazily created per-device state */
@@ -185,6 +191,7 @@ typedef struct canopy_plan_view {
     const uint32_t* layer_off;    /* [n_layers+1] gate index ranges                                         */
     const uint8_t*  tally_kind;   /* [n_tallies] 0 const-false, 1 const-true, 2 device gate, 3 complement of device gate */
     const uint32_t* tally_gate;   /* [n_tallies] device gate index for kinds 2/3                            */
+    const uint8_t*  event_k;      /* [n_events] spec 4: 0 dense (planes), else log2 of the event's group size; NULL under specs 1, 2 */
 } canopy_plan_view;
 CANOPY_API canopy_status canopy_plan_view_get(const canopy_plan* plan, canopy_plan_view* out);
 
@@ -288,7 +295,7 @@ CANOPY_API canopy_status canopy_estimate_from_tally(uint64_t tally, uint64_t n_s
 
 /* Integer-pipe microbenchmarks used for the sampler roofline (lane-instructions per second).
  * kind: 0 LOP3, 1 IMAD.WIDE.U32 (+1 LOP3 each, counted once), 2 Philox4x32-10 rounds (2 IMAD.WIDE + 2 LOP3 per round),
- *       3 POPC, 4 mix of 1 IMAD.WIDE.U32 : 2 LOP3 (all three counted) */
+ *       3 POPC, 4 mix of 1 IMAD.WIDE.U32 : 2 LOP3 (all three counted), 5 uniform-datapath pairs, 6 kind 5 beside 2 LOP3 */
 CANOPY_API canopy_status canopy_microbench_int(int32_t device, int32_t kind, double* out_lane_ops_per_s,
                                                double* out_ms);
 
@@ -321,15 +328,11 @@ CANOPY_API const char* canopy_last_error(void);   /* thread-local; valid until t
 CANOPY_API const char* canopy_status_string(canopy_status s);
 CANOPY_API uint32_t    canopy_version(void);      /* major<<16 | minor */
 CANOPY_API uint32_t    canopy_spec_version(void);
-/* Spec 3: the cumulative count table (CANOPY_SPARSE_CDF_LEN words, 0.64 fixed point) a plan builds for a sparse event
- * with 32-bit threshold thr32 (0 < thr32 < 2^(32 - CANOPY_SPARSE_MIN_ZEROS)).  Host only; a parity hook for the tests. */
-CANOPY_API canopy_status canopy_sparse_cdf(uint32_t thr32, uint64_t* out_cdf);
-/* Spec 3 test hook: replace the count table of one sparse event of a plan (live_event = position in
- * canopy_plan_view.event_orig) by cdf[CANOPY_SPARSE_CDF_LEN] (non-decreasing).  Lets the parity tests drive the count, and
- * with it the number of position fields and Philox calls a group consumes, far beyond what a real probability reaches
- * (an all-zero table gives 32 ones in every group).  The next canopy_plan_update_p restores the real table.
- * CANOPY_E_INVALID unless the plan samples with spec 3 and the event takes the sparse path. */
-CANOPY_API canopy_status canopy_plan_debug_set_sparse_table(canopy_plan* plan, uint32_t live_event, const uint64_t* cdf);
+/* Spec 4, host only, parity hooks for the tests: the group exponent k of an event with 64-bit threshold thr64 (0 = dense
+ * event; a 32-bit threshold is thr32 << 32), and the cumulative count table (CANOPY_SPARSE_CDF_LEN words, 0.64 fixed point)
+ * the engine builds for a sparse event (k = 7 .. CANOPY_SPARSE_MAX_LOG2, thr64 < 2^(64 - CANOPY_SPARSE_MIN_ZEROS)). */
+CANOPY_API canopy_status canopy_sparse_class(uint64_t thr64, uint32_t* out_k);
+CANOPY_API canopy_status canopy_sparse_cdf(uint64_t thr64, uint32_t k, uint64_t* out_cdf);
 
 #ifdef __cplusplus
 } /* extern "C" */

@@ -6,7 +6,7 @@
  *   (a) the connective semantics of the Open-PSA MEF as constrained by the reference's own
  *       validation rules (reference src/mef/openpsa/event/event.cpp:140-204, event/event.h:143-157,
  *       event/formula.h:9-15), and
- *   (b) this repository's written sampling specs (spec 1 "direct", spec 2 "sliced", spec 3 "sparse"),
+ *   (b) this repository's written sampling specs (spec 1 "direct", spec 2 "sliced", spec 4 "classed sparse"),
  * pinned only by the published Philox4x32-10 known-answer vectors (Random123 kat_vectors) and by
  * exact 2^B enumeration on small trees.
  *
@@ -74,53 +74,70 @@ double oracle_quantised_p(double p, int bits) {
 }
 
 /* ------------------------------------------------------------------------------------------------
- * spec 3 "sparse" (DESIGN.md section 1), events with thr < 2^(32 - CANOPY_SPARSE_MIN_ZEROS), 32-bit thresholds.
- * Count table: cdf_j = a_0 + ... + a_j in 0.64 fixed point, a_0 = (1-p)^128 by seven truncating squarings,
- * a_{j+1} = floor(a_j (128-j) t / ((j+1)(2^32 - t))).  All integer, so every implementation gets the same words.
+ * spec 4 "classed sparse" (DESIGN.md section 1).  Everything is a function of the 64-bit threshold t (32-bit
+ * thresholds are widened: t = thr32 << 32).  z = leading zero bits of t.  An event with z < Z (= CANOPY_SPARSE_MIN_ZEROS)
+ * samples as spec 2.  A rarer event works on groups of 2^k samples, k = min(KMAX, z + 2): ONE Philox call per group,
+ * ctr = (g_lo, g_hi, e, 0x400) with g = s >> k, gives a 64-bit variate U (words 1:0) and position fields (words 2, 3);
+ * N = #{j : U >= cdf_j} ones are placed at the first N distinct k-bit fields.
+ * Count table, 0.64 fixed point, all integer:  q = 2^64 - t;  r = floor(t 2^64 / q);  a_0 = q^(2^k) by k truncating
+ * squarings;  a_{j+1} = floor(floor(a_j r / 2^51) (2^k - j) / (j + 1)) >> 13;  cdf_j = min(2^64 - 1, a_0 + ... + a_j).
  * ---------------------------------------------------------------------------------------------- */
-void oracle_sparse_cdf(uint32_t t, uint64_t* cdf) {
+unsigned oracle_sparse_class_k(uint64_t t) {
+    if (t == 0) return 0;
+    unsigned z = 0;
+    while (!((t << z) >> 63)) ++z;
+    if (z < CANOPY_SPARSE_MIN_ZEROS) return 0;
+    return z + 2 < CANOPY_SPARSE_MAX_LOG2 ? z + 2 : CANOPY_SPARSE_MAX_LOG2;
+}
+
+void oracle_sparse_cdf(uint64_t t, unsigned k, uint64_t* cdf) {
+    const uint64_t q = (uint64_t)0 - t;
+    const uint64_t r = (uint64_t)(((unsigned __int128)t << 64) / q);
+    uint64_t a = q;
+    for (unsigned sq = 0; sq < k; ++sq) a = (uint64_t)(((unsigned __int128)a * a) >> 64);
     unsigned __int128 acc = 0;
-    uint64_t one_minus_p = (uint64_t)(4294967296ull - t) << 32;
-    uint64_t a = one_minus_p;
-    for (int sq = 0; sq < 7; ++sq) a = (uint64_t)(((unsigned __int128)a * a) >> 64);
     for (unsigned j = 0; j < CANOPY_SPARSE_CDF_LEN; ++j) {
         acc += a;
         cdf[j] = (acc >> 64) ? ~0ull : (uint64_t)acc;
-        unsigned __int128 num = (unsigned __int128)a * (128u - j) * t;
-        unsigned __int128 den = (unsigned __int128)(j + 1u) * (4294967296ull - t);
-        a = (uint64_t)(num / den);
+        unsigned __int128 y = ((unsigned __int128)a * r) >> 51;
+        y = y * ((1u << k) - j);
+        y = y / (j + 1u);
+        a = (uint64_t)(y >> 13);
     }
 }
 
-static int is_sparse_event(int spec, uint64_t thr, int bits) {
-    /* thr = 0 (p below 2^-32) never fires under any spec; it stays on the compare path, where u < 0 is never true */
-    return spec == 3 && bits == 32 && (uint32_t)thr != 0 && ((uint32_t)thr >> (32 - CANOPY_SPARSE_MIN_ZEROS)) == 0;
+static uint64_t thr64_of(uint64_t thr, int bits) { return bits == 32 ? thr << 32 : thr; }
+
+/* group exponent k of a sampled event under `spec`, 0 when the event takes the compare (plane) path */
+static unsigned sparse_k(int spec, uint64_t thr, int bits) {
+    /* thr = 0 (p below 2^-bits) never fires under any spec; it stays on the compare path, where u < 0 is never true */
+    if (spec != 4 || thr == 0) return 0;
+    return oracle_sparse_class_k(thr64_of(thr, bits));
 }
 
-/* Field i of group g of event e, straight from the text: fields 0-7 are the 7-bit digits of words 2 and 3 of call
- * 0x400, field 8 + 16c + 4w + d is digit d of word w of call 0x401 + c. */
-static unsigned sparse_field(const uint32_t key[2], uint32_t e, uint64_t g, unsigned i) {
+/* Field i of group g of event e, straight from the text: fpw = floor(32 / k) fields per word; fields 0 .. 2 fpw - 1 are
+ * the digits of words 2 and 3 of call 0x400; field 2 fpw + (4 c + w) fpw + d is digit d of word w of call 0x401 + c. */
+static unsigned sparse_field(const uint32_t key[2], uint32_t e, uint64_t g, unsigned k, unsigned i) {
     uint32_t ctr[4] = {(uint32_t)g, (uint32_t)(g >> 32), e, 0x400u}, out[4];
-    unsigned word, digit = i & 3u;
-    if (i < 8) word = 2 + (i >> 2);
-    else { ctr[3] = 0x401u + ((i - 8) >> 4); word = ((i - 8) >> 2) & 3u; }
+    const unsigned fpw = 32u / k;
+    unsigned word, digit = i % fpw;
+    if (i < 2 * fpw) word = 2 + i / fpw;
+    else { unsigned i2 = i - 2 * fpw; ctr[3] = 0x401u + i2 / (4 * fpw); word = (i2 / fpw) & 3u; }
     oracle_philox4x32_10(ctr, key, out);
-    return (out[word] >> (7 * digit)) & 127u;
+    return (out[word] >> (k * digit)) & ((1u << k) - 1u);
 }
 
-/* Definition form: the 128 sample values of one group as one flag per sample. */
-static void sparse_group_flags(uint64_t seed, uint32_t e, uint64_t g, uint32_t t, unsigned char flag[128]) {
+/* Definition form: the 2^k sample values of one group as one flag per sample (flag has room for 2^KMAX). */
+static void sparse_group_flags_tab(uint64_t seed, uint32_t e, uint64_t g, unsigned k, const uint64_t* cdf, unsigned char* flag) {
     uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
     uint32_t ctr[4] = {(uint32_t)g, (uint32_t)(g >> 32), e, 0x400u}, out[4];
-    uint64_t cdf[CANOPY_SPARSE_CDF_LEN];
-    oracle_sparse_cdf(t, cdf);
     oracle_philox4x32_10(ctr, key, out);
     uint64_t U = ((uint64_t)out[1] << 32) | out[0];
     unsigned n = 0;
     for (unsigned j = 0; j < CANOPY_SPARSE_CDF_LEN; ++j) n += U >= cdf[j];
-    memset(flag, 0, 128);
+    memset(flag, 0, (size_t)1 << k);
     for (unsigned i = 0, placed = 0; placed < n; ++i) {
-        unsigned pos = sparse_field(key, e, g, i);
+        unsigned pos = sparse_field(key, e, g, k, i);
         if (!flag[pos]) { flag[pos] = 1; ++placed; }
     }
 }
@@ -135,12 +152,15 @@ int oracle_sample_bit(uint64_t seed, uint32_t e, uint64_t s, int kind, uint64_t 
     if (kind == 1) return 1;
     uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
     uint32_t ctr[4], out[4];
-    if (is_sparse_event(spec, thr, bits)) {
-        unsigned char flag[128];
-        sparse_group_flags(seed, e, s >> 7, (uint32_t)thr, flag);
-        return flag[s & 127];
+    const unsigned k = sparse_k(spec, thr, bits);
+    if (k) {
+        unsigned char flag[1u << CANOPY_SPARSE_MAX_LOG2];
+        uint64_t cdf[CANOPY_SPARSE_CDF_LEN];
+        oracle_sparse_cdf(thr64_of(thr, bits), k, cdf);
+        sparse_group_flags_tab(seed, e, s >> k, k, cdf, flag);
+        return flag[s & ((1u << k) - 1u)];
     }
-    /* spec 3 is spec 2 for every other event */
+    /* spec 4 is spec 2 for every other event */
     if (spec == 1) {
         if (bits == 32) {
             uint64_t q = s >> 2;
@@ -258,53 +278,66 @@ static void sliced_group_words(uint64_t seed, uint32_t e, uint64_t g, int kind, 
     out2[1] = ((uint64_t)res[3] << 32) | res[2];
 }
 
-/* spec 3, sparse event: the group's words in streaming form (one call, fields consumed word by word, further calls
- * only when the fields run out).  Must agree with sparse_group_flags; tests/test_oracle.py checks it. */
-static void sparse_group_words(uint64_t seed, uint32_t e, uint64_t g, uint32_t t, const uint64_t* cdf, uint64_t out2[2]) {
+/* spec 4, sparse event: the ones of group g (2^k samples) in streaming form -- one call, fields consumed word by word,
+ * further calls only when the fields run out.  Writes the N distinct positions to pos[] (order of appearance) and returns
+ * N.  Must agree with sparse_group_flags_tab; tests/test_oracle.py checks it. */
+static unsigned sparse_group_positions(uint64_t seed, uint32_t e, uint64_t g, unsigned k, const uint64_t* cdf, uint16_t* pos) {
     uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
     uint32_t ctr[4] = {(uint32_t)g, (uint32_t)(g >> 32), e, 0x400u}, x[4];
-    (void)t;
     oracle_philox4x32_10(ctr, key, x);
     uint64_t U = ((uint64_t)x[1] << 32) | x[0];
     unsigned n = 0;
     while (n < CANOPY_SPARSE_CDF_LEN && U >= cdf[n]) ++n;   /* cdf is non-decreasing */
-    uint32_t res[4] = {0, 0, 0, 0};
-    unsigned word = 2, digit = 0;
-    while (n) {
-        if (digit == 4) {
+    const unsigned fpw = 32u / k, mask = (1u << k) - 1u;
+    unsigned word = 2, digit = 0, placed = 0;
+    while (placed < n) {
+        if (digit == fpw) {
             digit = 0;
             if (++word == 4) { word = 0; ++ctr[3]; oracle_philox4x32_10(ctr, key, x); }
         }
-        unsigned pos = (x[word] >> (7 * digit)) & 127u;
+        unsigned p = (x[word] >> (k * digit)) & mask;
         ++digit;
-        uint32_t b = 1u << (pos & 31);
-        if (!(res[pos >> 5] & b)) { res[pos >> 5] |= b; --n; }
+        unsigned dup = 0;
+        for (unsigned i = 0; i < placed; ++i) dup |= pos[i] == p;
+        if (!dup) pos[placed++] = (uint16_t)p;
     }
-    out2[0] = ((uint64_t)res[1] << 32) | res[0];
-    out2[1] = ((uint64_t)res[3] << 32) | res[2];
+    return n;
+}
+
+/* The 128-sample window `g128` of a sparse event: bits of the enclosing 2^k-group that fall into it. */
+static void sparse_window_words(uint64_t seed, uint32_t e, uint64_t g128, unsigned k, const uint64_t* cdf, uint64_t out2[2]) {
+    uint16_t pos[CANOPY_SPARSE_CDF_LEN];
+    const unsigned n = sparse_group_positions(seed, e, g128 >> (k - 7), k, cdf, pos);
+    const unsigned lo = (unsigned)(g128 & ((1u << (k - 7)) - 1u)) * 128u;   /* first position of the window inside the group */
+    out2[0] = out2[1] = 0;
+    for (unsigned i = 0; i < n; ++i)
+        if (pos[i] >= lo && pos[i] < lo + 128u) out2[(pos[i] - lo) >> 6] |= 1ull << ((pos[i] - lo) & 63u);
 }
 
 /* Words 2g and 2g+1 (samples [128g, 128g+128)) of one basic event under any spec. */
 static void group_words_tab(int spec, uint64_t seed, uint32_t e, uint64_t g, int kind, uint64_t thr, int bits, const uint64_t* tab, uint64_t out2[2]) {
+    unsigned k;
     if (spec == 1) {
         out2[0] = packed_sample_word(seed, e, 2 * g, kind, thr, bits);
         out2[1] = packed_sample_word(seed, e, 2 * g + 1, kind, thr, bits);
-    } else if (kind == 2 && is_sparse_event(spec, thr, bits)) {
+    } else if (kind == 2 && (k = sparse_k(spec, thr, bits)) != 0) {
         uint64_t cdf[CANOPY_SPARSE_CDF_LEN];
-        if (!tab) { oracle_sparse_cdf((uint32_t)thr, cdf); tab = cdf; }   /* callers that loop over groups pass the event's table */
-        sparse_group_words(seed, e, g, (uint32_t)thr, tab, out2);
+        if (!tab) { oracle_sparse_cdf(thr64_of(thr, bits), k, cdf); tab = cdf; }   /* callers that loop over groups pass the event's table */
+        sparse_window_words(seed, e, g, k, tab, out2);
     } else sliced_group_words(seed, e, g, kind, thr, bits, out2);
 }
 static void group_words(int spec, uint64_t seed, uint32_t e, uint64_t g, int kind, uint64_t thr, int bits, uint64_t out2[2]) {
     group_words_tab(spec, seed, e, g, kind, thr, bits, NULL, out2);
 }
 
-/* Count tables of every sparse event of a descriptor (spec 3), [B][CANOPY_SPARSE_CDF_LEN]; NULL under the other specs. */
+/* Count tables of every sparse event of a descriptor (spec 4), [B][CANOPY_SPARSE_CDF_LEN]; NULL under the other specs. */
 static uint64_t* sparse_tables(int spec, int bits, uint32_t B, const int* kind, const uint64_t* thr) {
-    if (spec != 3 || bits != 32) return NULL;
+    if (spec != 4) return NULL;
     uint64_t* tab = (uint64_t*)calloc((size_t)(B ? B : 1) * CANOPY_SPARSE_CDF_LEN, sizeof(uint64_t));
-    for (uint32_t e = 0; e < B; ++e)
-        if (kind[e] == 2 && is_sparse_event(spec, thr[e], bits)) oracle_sparse_cdf((uint32_t)thr[e], tab + (size_t)e * CANOPY_SPARSE_CDF_LEN);
+    for (uint32_t e = 0; e < B; ++e) {
+        unsigned k = kind[e] == 2 ? sparse_k(spec, thr[e], bits) : 0;
+        if (k) oracle_sparse_cdf(thr64_of(thr[e], bits), k, tab + (size_t)e * CANOPY_SPARSE_CDF_LEN);
+    }
     return tab;
 }
 
@@ -367,7 +400,7 @@ static size_t n_tallies_of(const canopy_graph_desc* d, int tally_all) {
  * ---------------------------------------------------------------------------------------------- */
 int oracle_mc_scalar(const canopy_graph_desc* d, uint64_t seed, uint64_t begin, uint64_t n,
                      int tally_all, int bits, int spec, uint64_t* tallies) {
-    if (spec < 1 || spec > 3) return -9;
+    if (spec != 1 && spec != 2 && spec != 4) return -9;
     uint32_t B = d->n_basic, G = d->n_gates;
     uint32_t* order = (uint32_t*)malloc(sizeof(uint32_t) * (G ? G : 1));
     int rc = topo_order(d, order);
@@ -422,7 +455,7 @@ int oracle_mc_scalar(const canopy_graph_desc* d, uint64_t seed, uint64_t begin, 
  * listed in event_ids[0..n_events). */
 int oracle_sample_words(const canopy_graph_desc* d, uint64_t seed, int bits, int spec, const uint32_t* event_ids,
                         uint32_t n_events, uint64_t first_word, uint64_t n_words, uint64_t* words) {
-    if (spec < 1 || spec > 3) return -9;
+    if (spec != 1 && spec != 2 && spec != 4) return -9;
     for (uint32_t i = 0; i < n_events; ++i) {
         uint32_t e = event_ids[i]; uint64_t thr; int kind = oracle_threshold(d->p[e], bits, &thr);
         if (kind < 0) return -8;
@@ -439,13 +472,14 @@ int oracle_sample_words(const canopy_graph_desc* d, uint64_t seed, int bits, int
 /* Same output as oracle_sample_words through the lazily evaluated group routine (fast). */
 int oracle_sample_words_fast(const canopy_graph_desc* d, uint64_t seed, int bits, int spec, const uint32_t* event_ids,
                              uint32_t n_events, uint64_t first_word, uint64_t n_words, uint64_t* words) {
-    if (spec < 1 || spec > 3) return -9;
+    if (spec != 1 && spec != 2 && spec != 4) return -9;
     for (uint32_t i = 0; i < n_events; ++i) {
         uint32_t e = event_ids[i]; uint64_t thr; int kind = oracle_threshold(d->p[e], bits, &thr);
         if (kind < 0) return -8;
         uint64_t pair[2], have = ~0ull, tab[CANOPY_SPARSE_CDF_LEN];
-        int sparse = kind == 2 && is_sparse_event(spec, thr, bits);
-        if (sparse) oracle_sparse_cdf((uint32_t)thr, tab);
+        unsigned k = kind == 2 ? sparse_k(spec, thr, bits) : 0;
+        int sparse = k != 0;
+        if (sparse) oracle_sparse_cdf(thr64_of(thr, bits), k, tab);
         for (uint64_t w = 0; w < n_words; ++w) {
             uint64_t gw = first_word + w;
             if ((gw >> 1) != have) { have = gw >> 1; group_words_tab(spec, seed, e, have, kind, thr, bits, sparse ? tab : NULL, pair); }
@@ -455,34 +489,29 @@ int oracle_sample_words_fast(const canopy_graph_desc* d, uint64_t seed, int bits
     return 0;
 }
 
-/* Test hook (spec 3): the words of one sparse event under an explicit count table instead of the one its threshold
- * gives; stream = 1 uses the streaming form, 0 the definition form (one flag per sample, one Philox call per field). */
-int oracle_sparse_words_with_table(uint64_t seed, uint32_t e, const uint64_t* tab, int stream, uint64_t first_word,
+/* Test hook (spec 4): the words of one sparse event of group exponent k under an explicit count table instead of the one
+ * its threshold gives; stream = 1 uses the streaming form, 0 the definition form (one flag per sample, one Philox call per
+ * field). */
+int oracle_sparse_words_with_table(uint64_t seed, uint32_t e, unsigned k, const uint64_t* tab, int stream, uint64_t first_word,
                                    uint64_t n_words, uint64_t* words) {
-    uint32_t key[2] = {(uint32_t)seed, (uint32_t)(seed >> 32)};
+    if (k < 7 || k > CANOPY_SPARSE_MAX_LOG2) return -9;
     uint64_t pair[2] = {0, 0}, have = ~0ull;
+    unsigned char* flag = (unsigned char*)malloc((size_t)1 << CANOPY_SPARSE_MAX_LOG2);
     for (uint64_t w = 0; w < n_words; ++w) {
-        uint64_t gw = first_word + w, g = gw >> 1;
+        uint64_t gw = first_word + w, g = gw >> 1;   /* 128-sample window */
         if (g != have) {
             have = g;
-            if (stream) sparse_group_words(seed, e, g, 0, tab, pair);
+            if (stream) sparse_window_words(seed, e, g, k, tab, pair);
             else {
-                uint32_t ctr[4] = {(uint32_t)g, (uint32_t)(g >> 32), e, 0x400u}, out[4];
-                oracle_philox4x32_10(ctr, key, out);
-                uint64_t U = ((uint64_t)out[1] << 32) | out[0];
-                unsigned n = 0; unsigned char flag[128];
-                for (unsigned j = 0; j < CANOPY_SPARSE_CDF_LEN; ++j) n += U >= tab[j];
-                memset(flag, 0, 128);
-                for (unsigned i = 0, placed = 0; placed < n; ++i) {
-                    unsigned pos = sparse_field(key, e, g, i);
-                    if (!flag[pos]) { flag[pos] = 1; ++placed; }
-                }
+                sparse_group_flags_tab(seed, e, g >> (k - 7), k, tab, flag);
+                const unsigned lo = (unsigned)(g & ((1u << (k - 7)) - 1u)) * 128u;
                 pair[0] = pair[1] = 0;
-                for (unsigned q = 0; q < 128; ++q) if (flag[q]) pair[q >> 6] |= 1ull << (q & 63);
+                for (unsigned q = 0; q < 128; ++q) if (flag[lo + q]) pair[q >> 6] |= 1ull << (q & 63);
             }
         }
         words[w] = pair[gw & 1];
     }
+    free(flag);
     return 0;
 }
 
@@ -537,7 +566,7 @@ typedef struct {
     const canopy_graph_desc* d;
     const uint32_t* order;
     const int* kind; const uint64_t* thr; const unsigned char* used;
-    const uint64_t* tab; /* spec 3 count tables, or NULL */
+    const uint64_t* tab; /* spec 4 count tables, or NULL */
     uint64_t seed, begin, n; int tally_all, bits, spec;
     uint64_t first_group, n_groups; /* global 128-sample group range covering [begin, begin+n) */
     int tid, nthreads;
@@ -569,7 +598,9 @@ static uint64_t word_mask(uint64_t w, uint64_t begin, uint64_t end) {
     return mask;
 }
 
-/* Work unit = one 128-sample group (two 64-bit word columns) of the whole DAG. */
+/* Work unit = one 128-sample window (two 64-bit word columns) of the whole DAG; a thread takes whole blocks of 64
+ * consecutive windows (8192 samples, the largest sparse group), so that the ones of a sparse event's 2^k-sample group are
+ * drawn once (one Philox call) and then dealt out to the 2^(k-7) windows of the group as they come by. */
 static void* packed_worker(void* arg) {
     packed_job* J = (packed_job*)arg;
     const canopy_graph_desc* d = J->d;
@@ -578,14 +609,38 @@ static void* packed_worker(void* arg) {
     uint32_t maxf = 1;
     for (uint32_t g = 0; g < G; ++g) { uint64_t f = d->child_off[g + 1] - d->child_off[g]; if (f > maxf) maxf = (uint32_t)f; }
     uint64_t* x = (uint64_t*)malloc(sizeof(uint64_t) * maxf);
+    /* per sparse event: the positions of the 2^k-group the thread is currently inside */
+    unsigned char* ev_k = (unsigned char*)calloc(B ? B : 1, 1);
+    unsigned char* cache_n = (unsigned char*)calloc(B ? B : 1, 1);
+    uint64_t* cache_g = (uint64_t*)malloc(sizeof(uint64_t) * (B ? B : 1));
+    uint16_t* cache_pos = (uint16_t*)malloc(sizeof(uint16_t) * CANOPY_SPARSE_CDF_LEN * (size_t)(B ? B : 1));
+    for (uint32_t e = 0; e < B; ++e) {
+        cache_g[e] = ~0ull;
+        if (J->used[e] && J->kind[e] == 2) ev_k[e] = (unsigned char)sparse_k(J->spec, J->thr[e], J->bits);
+    }
     uint64_t end = J->begin + J->n;
-    for (uint64_t gi = (uint64_t)J->tid; gi < J->n_groups; gi += (uint64_t)J->nthreads) {
-        uint64_t grp = J->first_group + gi;
+    const uint64_t first_block = J->first_group >> 6, last_block = (J->first_group + J->n_groups - 1) >> 6;
+    for (uint64_t blk = first_block + (uint64_t)J->tid; blk <= last_block; blk += (uint64_t)J->nthreads)
+    for (uint64_t grp = blk << 6; grp < (blk + 1) << 6; ++grp) {
+        if (grp < J->first_group || grp >= J->first_group + J->n_groups) continue;
         uint64_t mask[2] = {word_mask(2 * grp, J->begin, end), word_mask(2 * grp + 1, J->begin, end)};
         for (uint32_t e = 0; e < B; ++e) {
-            if (J->used[e]) group_words_tab(J->spec, J->seed, e, grp, J->kind[e], J->thr[e], J->bits,
-                                            J->tab ? J->tab + (size_t)e * CANOPY_SPARSE_CDF_LEN : NULL, val + 2 * (size_t)e);
-            else val[2 * (size_t)e] = val[2 * (size_t)e + 1] = 0;
+            uint64_t* v = val + 2 * (size_t)e;
+            if (!J->used[e]) { v[0] = v[1] = 0; continue; }
+            const unsigned k = ev_k[e];
+            if (!k) { group_words_tab(J->spec, J->seed, e, grp, J->kind[e], J->thr[e], J->bits, NULL, v); continue; }
+            const uint64_t big = grp >> (k - 7);
+            uint16_t* pos = cache_pos + (size_t)e * CANOPY_SPARSE_CDF_LEN;
+            if (cache_g[e] != big) {
+                cache_g[e] = big;
+                cache_n[e] = (unsigned char)sparse_group_positions(J->seed, e, big, k, J->tab + (size_t)e * CANOPY_SPARSE_CDF_LEN, pos);
+            }
+            const unsigned lo = (unsigned)(grp & ((1u << (k - 7)) - 1u)) * 128u;
+            v[0] = v[1] = 0;
+            for (unsigned i = 0; i < cache_n[e]; ++i) {
+                const unsigned q = (unsigned)pos[i] - lo;      /* wraps for positions below the window */
+                if (q < 128u) v[q >> 6] |= 1ull << (q & 63u);
+            }
         }
         for (int h = 0; h < 2; ++h) {
             if (!mask[h]) continue;
@@ -621,14 +676,14 @@ static void* packed_worker(void* arg) {
                     J->tallies[d->n_roots + g] += (uint64_t)__builtin_popcountll(val[2 * ((size_t)B + g) + h] & mask[h]);
         }
     }
-    free(val); free(x);
+    free(val); free(x); free(ev_k); free(cache_n); free(cache_g); free(cache_pos);
     return NULL;
 }
 
 int oracle_mc_packed(const canopy_graph_desc* d, uint64_t seed, uint64_t begin, uint64_t n,
                      int tally_all, int bits, int spec, int nthreads, uint64_t* tallies) {
     uint32_t B = d->n_basic, G = d->n_gates;
-    if (spec < 1 || spec > 3) return -9;
+    if (spec != 1 && spec != 2 && spec != 4) return -9;
     if (nthreads < 1) nthreads = 1;
     uint32_t* order = (uint32_t*)malloc(sizeof(uint32_t) * (G ? G : 1));
     int rc = topo_order(d, order);
@@ -670,3 +725,4 @@ int oracle_mc_packed(const canopy_graph_desc* d, uint64_t seed, uint64_t begin, 
 int oracle_spec_version(void) { return CANOPY_SPEC_VERSION; }
 int oracle_sparse_cdf_len(void) { return CANOPY_SPARSE_CDF_LEN; }
 int oracle_sparse_min_zeros(void) { return CANOPY_SPARSE_MIN_ZEROS; }
+int oracle_sparse_max_log2(void) { return CANOPY_SPARSE_MAX_LOG2; }

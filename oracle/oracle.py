@@ -45,7 +45,7 @@ def lib():
 _RC = {-1: "bad node id", -3: "cycle", -4: "too many basic events for enumeration", -8: "probability out of domain",
        -9: "unknown sampling spec"}
 
-SPEC = 3  # default sampling spec of the build (include/canopy.h CANOPY_SPEC_VERSION); 1 = direct, 2 = sliced, 3 = sparse
+SPEC = 4  # default sampling spec of the build (include/canopy.h CANOPY_SPEC_VERSION); 1 = direct, 2 = sliced, 4 = classed sparse
 
 
 def _check(rc):
@@ -71,22 +71,29 @@ def quantised_p(p: float, bits: int = 32) -> float:
     return float(lib().oracle_quantised_p(p, bits))
 
 
-def sparse_cdf(thr32: int) -> list:
-    """Spec 3 count table of one sparse event (CANOPY_SPARSE_CDF_LEN words of 0.64 fixed point)."""
+def sparse_class_k(thr64: int) -> int:
+    """Spec 4: group exponent k of an event with 64-bit threshold thr64 (0 = dense event, spec 2 planes)."""
+    lib().oracle_sparse_class_k.argtypes = [C.c_uint64]
+    lib().oracle_sparse_class_k.restype = C.c_uint
+    return int(lib().oracle_sparse_class_k(thr64))
+
+
+def sparse_cdf(thr64: int, k: int) -> list:
+    """Spec 4 count table of one sparse event (CANOPY_SPARSE_CDF_LEN words of 0.64 fixed point)."""
     out = (C.c_uint64 * int(lib().oracle_sparse_cdf_len()))()
-    lib().oracle_sparse_cdf.argtypes = [C.c_uint32, C.POINTER(C.c_uint64)]
+    lib().oracle_sparse_cdf.argtypes = [C.c_uint64, C.c_uint, C.POINTER(C.c_uint64)]
     lib().oracle_sparse_cdf.restype = None
-    lib().oracle_sparse_cdf(thr32, out)
+    lib().oracle_sparse_cdf(thr64, k, out)
     return [int(x) for x in out]
 
 
-def sparse_words_with_table(seed: int, e: int, table, first_word: int, n_words: int, stream: bool = True) -> np.ndarray:
-    """Test hook (spec 3): packed words of sparse event `e` under an explicit count table."""
+def sparse_words_with_table(seed: int, e: int, k: int, table, first_word: int, n_words: int, stream: bool = True) -> np.ndarray:
+    """Test hook (spec 4): packed words of sparse event `e` with group exponent k under an explicit count table."""
     tab = np.ascontiguousarray(table, dtype=np.uint64)
     out = np.zeros(n_words, dtype=np.uint64)
     fn = lib().oracle_sparse_words_with_table
-    fn.argtypes = [C.c_uint64, C.c_uint32, C.POINTER(C.c_uint64), C.c_int, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]
-    _check(fn(seed, e, tab.ctypes.data_as(C.POINTER(C.c_uint64)), int(stream), first_word, n_words,
+    fn.argtypes = [C.c_uint64, C.c_uint32, C.c_uint, C.POINTER(C.c_uint64), C.c_int, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]
+    _check(fn(seed, e, k, tab.ctypes.data_as(C.POINTER(C.c_uint64)), int(stream), first_word, n_words,
               out.ctypes.data_as(C.POINTER(C.c_uint64))))
     return out
 

@@ -1,7 +1,7 @@
 """Regenerates tests/golden/*.json from the CPU oracle (oracle/canopy_oracle.c).
 
 The reference (openpra-org/canopy) has no implementation, tests or golden vectors for this path, so these
-fixtures pin the behaviour of the three sampling specs (1 "direct", 2 "sliced", 3 "sparse") as restated by the oracle -- they are NOT outputs of the reference.
+fixtures pin the behaviour of the three sampling specs (1 "direct", 2 "sliced", 4 "classed sparse") as restated by the oracle -- they are NOT outputs of the reference.
 What IS external: the three Philox4x32-10 known-answer vectors (Random123 kat_vectors, also listed in
 SURVEY.md Appendix B), which are written here literally and checked against the oracle before anything
 else is generated.
@@ -51,14 +51,20 @@ def main():
     cases = []
     c1 = load_mef(os.path.join(ROOT, "examples", "c1_small_ft.xml"))
     tiny = synth.generate(n_basic=120, n_gates=60, n_layers=5, max_fanin=16, seed=0xC0FFEE)
-    for spec in (1, 2, 3):
+    for spec in (1, 2, 4):
         cases.append(case("c1_small_ft", c1, seed=0, begin=0, n=1 << 14, tally_all=True, spec=spec))
         cases.append(case("c1_small_ft_offset_seed", c1, seed=(0xDEADBEEF << 32) | 0x1234, begin=(1 << 40) + 77, n=5000,
                           tally_all=False, spec=spec))
-        if spec == 3:   # graphs whose events straddle the sparse boundary p = 2^-5 (the random graphs below are all dense)
+        if spec == 4:   # graphs whose events cover the sparse classes k = 7 .. 13 and the dense boundary p = 2^-5 (the random
+                        # graphs below are all dense); ranges straddle 8192-sample group boundaries; 32- and 64-bit thresholds
             for s in range(4):
                 cases.append(case(f"random_rare_{s}", random_graph(3000 + s, n_basic=14, n_gates=30, n_roots=3, p_lo=1e-3, p_hi=0.06),
                                   seed=s * 104729 + 3, begin=128 * s + 5 * s, n=8192 + 123 * s, tally_all=True, spec=spec))
+            for s in range(4):
+                cases.append(case(f"random_classes_{s}", random_graph(4000 + s, n_basic=16, n_gates=30, n_roots=3, p_lo=5e-5, p_hi=0.02,
+                                                                     extreme_p=s % 2 == 0),
+                                  seed=s * 15485863 + 11, begin=8192 * (3 + s) - 700 * (s + 1), n=2 * 8192 + 77 * s, tally_all=True,
+                                  bits=64 if s >= 2 else 32, spec=spec, words_of=(0, 1, 2, 3, 4, 5)))
         for s in range(6 if spec == 2 else 3):
             cases.append(case(f"random_{s}", random_graph(1000 + s, n_basic=12, n_gates=30, n_roots=3), seed=s * 7919 + 1,
                               begin=64 * s + s, n=4096 + 321 * s, tally_all=True, spec=spec))
@@ -66,7 +72,7 @@ def main():
                           bits=64, spec=spec))
         cases.append(case("synth_tiny", tiny, seed=42, begin=4096 * 3 - 10, n=4096 + 20, tally_all=True, spec=spec))
     with open(os.path.join(HERE, "golden_tallies.json"), "w") as f:
-        json.dump(dict(spec_versions=[1, 2, 3], generator="tests/golden/make_golden.py (oracle_mc_scalar / oracle_sample_words)",
+        json.dump(dict(spec_versions=[1, 2, 4], generator="tests/golden/make_golden.py (oracle_mc_scalar / oracle_sample_words)",
                        cases=cases), f)
     print(f"wrote {len(cases)} cases")
 

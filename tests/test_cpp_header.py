@@ -26,7 +26,7 @@ def test_cpp_header_smoke(tmp_path):
 
 def test_c_header_is_plain_c(tmp_path):
     src = tmp_path / "t.c"
-    src.write_text('#include "canopy.h"\nint main(void){ canopy_mc_opts o; canopy_mc_opts_default(&o); return (int)canopy_spec_version() - 3; }\n')
+    src.write_text('#include "canopy.h"\nint main(void){ canopy_mc_opts o; canopy_mc_opts_default(&o); return (int)canopy_spec_version() - CANOPY_SPEC_VERSION; }\n')
     exe = str(tmp_path / "t")
     lib_dir = os.path.join(ROOT, "canopy_b200")
     subprocess.check_call(["gcc", "-std=c99", "-Wall", "-pedantic", "-I", os.path.join(ROOT, "include"), str(src), "-o", exe,

@@ -27,7 +27,7 @@ CCF_CASES = [
 
 @pytest.mark.parametrize("ccf_analysis", [False, True], ids=["ccf_off", "ccf_on"])
 @pytest.mark.parametrize("model_name,n,q,factors", CCF_CASES, ids=[c[0] for c in CCF_CASES])
-@pytest.mark.parametrize("spec", [2, 3])
+@pytest.mark.parametrize("spec", [2, 4])
 def test_ccf_models_on_gpu(model_name, n, q, factors, ccf_analysis, spec):
     g = load_mef(text=ccf_xml(model_name, n, q, factors), ccf_analysis=ccf_analysis)
     assert g.n_basic == (n if not ccf_analysis else g.n_basic) and (ccf_analysis or g.n_gates == 1)
@@ -64,7 +64,7 @@ def test_ccf_members_replaced_by_proxy_gates_on_gpu():
         assert abs(ph - want) < 5 * (want / S) ** 0.5
 
 
-@pytest.mark.parametrize("spec", [2, 3])
+@pytest.mark.parametrize("spec", [2, 4])
 def test_event_tree_model_on_gpu(spec):
     """The hand-written event tree of tests/test_mef_model.py (forks, a named branch, a rule with
     test-functional-event, set-house-event clones, a link into a second tree): every sequence and every gate."""

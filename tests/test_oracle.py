@@ -56,7 +56,7 @@ def test_golden_scalar_and_packed(case):
         assert np.array_equal(words, np.array(case["words"], dtype=np.uint64).reshape(words.shape))
 
 
-@pytest.mark.parametrize("spec", [1, 2])
+@pytest.mark.parametrize("spec", [1, 2, 4])
 @pytest.mark.parametrize("bits", [32, 64])
 def test_lazy_group_sampler_equals_the_written_definition(spec, bits):
     """mc_scalar / mc_packed take basic-event bits from the lazily evaluated 128-sample group routine; the
@@ -76,7 +76,7 @@ def test_lazy_group_sampler_equals_the_written_definition(spec, bits):
     assert [O.sample_bit(5, 5, 3 * 64 + i, ps[5], bits, spec) for i in range(64)] == [(int(w) >> i) & 1 for i in range(64)]
 
 
-@pytest.mark.parametrize("spec", [1, 2])
+@pytest.mark.parametrize("spec", [1, 2, 4])
 def test_sampled_frequency_matches_quantised_probability(spec):
     """Per-event frequency over 2^20 samples within 4 sigma of thr/2^32, for thresholds whose top byte is zero,
     mixed and all-ones (exercises head-only, head+tail and tail-dominated decisions of the sliced spec)."""
@@ -92,7 +92,7 @@ def test_sampled_frequency_matches_quantised_probability(spec):
     assert np.all(np.abs(t / n - q) <= 4.0 * np.sqrt(q * (1 - q) / n))
 
 
-@pytest.mark.parametrize("spec", [1, 2])
+@pytest.mark.parametrize("spec", [1, 2, 4])
 @pytest.mark.parametrize("seed", range(5))
 def test_mc_within_3_sigma_of_exact_enumeration(seed, spec):
     g = random_graph(seed + 50, n_basic=10, n_gates=16, n_roots=2, extreme_p=False)
