@@ -26,7 +26,7 @@ class CanopyError(RuntimeError):
 
 class CPlanOpts(C.Structure):
     _fields_ = [("tally_all_gates", C.c_int32), ("threshold_bits", C.c_int32), ("sampler", C.c_int32),
-                ("reserved", C.c_int32 * 5)]
+                ("no_plan_cache", C.c_int32), ("reserved", C.c_int32 * 4)]
 
 
 class CPlanStats(C.Structure):
@@ -34,7 +34,8 @@ class CPlanStats(C.Structure):
                 ("n_basic_live", C.c_uint32), ("n_gates_live", C.c_uint32), ("n_edges_live", C.c_uint64),
                 ("n_gates_stored", C.c_uint32), ("n_gates_tallied", C.c_uint32), ("n_layers", C.c_uint32),
                 ("max_fanin", C.c_uint32), ("mean_fanin", C.c_double), ("n_tallies", C.c_uint32),
-                ("n_const_nodes", C.c_uint32), ("n_alias_nodes", C.c_uint32), ("spec_version", C.c_uint32)]
+                ("n_const_nodes", C.c_uint32), ("n_alias_nodes", C.c_uint32), ("spec_version", C.c_uint32),
+                ("plan_cache_hit", C.c_uint32)]
 
 
 class CPlanView(C.Structure):
@@ -89,6 +90,7 @@ SYMBOLS = {
     "canopy_mc_run_device": (C.c_int, [C.c_void_p, C.POINTER(CMcOpts), C.c_void_p, C.POINTER(CMcReport)]),
     "canopy_mc_run_multi": (C.c_int, [C.c_void_p, C.POINTER(CMcOpts), C.POINTER(C.c_int32), C.c_int32, _u64p, C.POINTER(CMcReport)]),
     "canopy_trim_device_cache": (C.c_int, [C.c_int32]),
+    "canopy_plan_cache_clear": (C.c_int, []),
     "canopy_plan_fingerprint": (C.c_int, [C.c_void_p, _u64p]),
     "canopy_checkpoint_init": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(CCheckpoint)]),
     "canopy_mc_run_resume": (C.c_int, [C.c_void_p, C.POINTER(CMcOpts), C.POINTER(CCheckpoint), _u64p, C.POINTER(CMcReport)]),

@@ -51,7 +51,7 @@ canopy_status canopy_plan_create(const canopy_graph_desc* desc, const canopy_pla
         if (o.sampler == CANOPY_SAMPLER_DEFAULT) o.sampler = CANOPY_SPEC_VERSION;
         auto* p = new canopy_plan();
         try {
-            canopy::lower_graph(*desc, o, p->low);
+            canopy::lower_graph_cached(*desc, o, p->low);
         } catch (...) { delete p; throw; }
         *out_plan = p;
     });
@@ -119,6 +119,10 @@ canopy_status canopy_mc_run_multi(canopy_plan* plan, const canopy_mc_opts* opts,
 
 canopy_status canopy_trim_device_cache(int32_t device) {
     return guard([&] { canopy::trim_device_cache(device); });
+}
+
+canopy_status canopy_plan_cache_clear(void) {
+    return guard([&] { canopy::plan_cache_clear(); });
 }
 
 canopy_status canopy_plan_fingerprint(const canopy_plan* plan, uint64_t* out) {

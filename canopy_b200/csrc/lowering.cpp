@@ -18,6 +18,8 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <deque>
+#include <memory>
 #include <numeric>
 #include <thread>
 
@@ -472,6 +474,101 @@ void requantise(Lowered& L, const double* p, uint32_t n_basic) {
         L.event_thr64[i] = wide ? t : (t << 32);
     }
     build_sparse_classes(L);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Plan cache.  Lowering a large graph costs tens of milliseconds of host time (c4: 42 ms), which a caller who
+// quantifies the same model again and again (one plan per request, per uncertainty trial, per rank of a job) would pay
+// every time.  canopy_plan_create keeps the last few lowered forms keyed by a 64-bit hash of the DESCRIPTOR (arrays
+// and options, hashed before any lowering work) and verifies a hit by comparing the arrays themselves, so a collision
+// can never hand out the wrong plan.  A hit costs one pass over the descriptor and one copy of the lowered arrays.
+// ------------------------------------------------------------------------------------------------
+namespace {
+struct DescCopy {
+    uint32_t n_basic = 0, n_gates = 0, n_roots = 0;
+    uint64_t n_edges = 0;
+    std::vector<double> p;
+    std::vector<uint8_t> op;
+    std::vector<uint16_t> kmin, kmax;
+    std::vector<uint64_t> child_off;
+    std::vector<uint32_t> child, roots;
+    explicit DescCopy(const canopy_graph_desc& d)
+        : n_basic(d.n_basic), n_gates(d.n_gates), n_roots(d.n_roots), n_edges(d.n_edges), p(d.p, d.p + d.n_basic),
+          op(d.op, d.op + d.n_gates), kmin(d.n_gates, 0), kmax(d.n_gates, 0), child_off(d.child_off, d.child_off + d.n_gates + 1),
+          child(d.child, d.child + d.n_edges), roots(d.roots, d.roots + d.n_roots) {
+        if (d.kmin) kmin.assign(d.kmin, d.kmin + d.n_gates);
+        if (d.kmax) kmax.assign(d.kmax, d.kmax + d.n_gates);
+    }
+    template <class T> static bool same(const std::vector<T>& v, const T* q) { return v.empty() || std::memcmp(v.data(), q, v.size() * sizeof(T)) == 0; }
+    bool equals(const canopy_graph_desc& d) const {
+        if (n_basic != d.n_basic || n_gates != d.n_gates || n_roots != d.n_roots || n_edges != d.n_edges) return false;
+        if (!same(p, d.p) || !same(op, d.op) || !same(child_off, d.child_off) || !same(child, d.child) || !same(roots, d.roots)) return false;
+        if (d.kmin ? !same(kmin, d.kmin) : std::any_of(kmin.begin(), kmin.end(), [](uint16_t v) { return v != 0; })) return false;
+        if (d.kmax ? !same(kmax, d.kmax) : std::any_of(kmax.begin(), kmax.end(), [](uint16_t v) { return v != 0; })) return false;
+        return true;
+    }
+};
+struct CacheEntry { uint64_t hash; canopy_plan_opts opts; DescCopy desc; std::shared_ptr<const Lowered> low; };
+std::mutex g_cache_mu;
+std::deque<CacheEntry> g_cache;
+constexpr size_t kCacheEntries = 4;
+
+uint64_t mix64(uint64_t h, uint64_t v) {
+    h ^= v; h *= 0x9E3779B97F4A7C15ull; h ^= h >> 29;
+    return h;
+}
+uint64_t hash_bytes(uint64_t h, const void* data, size_t n) {
+    const unsigned char* b = static_cast<const unsigned char*>(data);
+    size_t i = 0;
+    for (; i + 8 <= n; i += 8) { uint64_t v; std::memcpy(&v, b + i, 8); h = mix64(h, v); }
+    uint64_t tail = 0;
+    if (i < n) std::memcpy(&tail, b + i, n - i);
+    return mix64(mix64(h, tail), n);
+}
+uint64_t hash_desc(const canopy_graph_desc& d, const canopy_plan_opts& o) {
+    uint64_t h = 0x243F6A8885A308D3ull;
+    const uint64_t head[7] = {d.n_basic, d.n_gates, d.n_roots, d.n_edges, (uint64_t)o.tally_all_gates, (uint64_t)o.threshold_bits, (uint64_t)o.sampler};
+    h = hash_bytes(h, head, sizeof head);
+    h = hash_bytes(h, d.p, (size_t)d.n_basic * 8);
+    h = hash_bytes(h, d.op, d.n_gates);
+    if (d.kmin) h = hash_bytes(h, d.kmin, (size_t)d.n_gates * 2);
+    if (d.kmax) h = hash_bytes(h, d.kmax, (size_t)d.n_gates * 2);
+    h = hash_bytes(h, d.child_off, ((size_t)d.n_gates + 1) * 8);
+    h = hash_bytes(h, d.child, (size_t)d.n_edges * 4);
+    h = hash_bytes(h, d.roots, (size_t)d.n_roots * 4);
+    return h;
+}
+}  // namespace
+
+void lower_graph_cached(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lowered& out) {
+    if (opts.no_plan_cache) { lower_graph(d, opts, out); return; }
+    if (!d.p && d.n_basic) fail(CANOPY_E_INVALID, "descriptor array p is null");
+    if ((!d.op || !d.child_off) && d.n_gates) fail(CANOPY_E_INVALID, "descriptor arrays op / child_off are null");
+    if (!d.child_off || (!d.child && d.n_edges) || (!d.roots && d.n_roots)) { lower_graph(d, opts, out); return; }  // let validate() report it
+    if (d.child_off[d.n_gates] != d.n_edges) { lower_graph(d, opts, out); return; }
+    const uint64_t h = hash_desc(d, opts);
+    std::shared_ptr<const Lowered> hit;
+    {
+        std::lock_guard<std::mutex> lock(g_cache_mu);
+        for (auto it = g_cache.begin(); it != g_cache.end(); ++it)
+            if (it->hash == h && it->opts.tally_all_gates == opts.tally_all_gates && it->opts.threshold_bits == opts.threshold_bits &&
+                it->opts.sampler == opts.sampler && it->desc.equals(d)) {
+                hit = it->low;
+                if (it != g_cache.begin()) { CacheEntry e = std::move(*it); g_cache.erase(it); g_cache.push_front(std::move(e)); }
+                break;
+            }
+    }
+    if (hit) { out = *hit; out.opts = opts; out.stats.plan_cache_hit = 1; return; }
+    lower_graph(d, opts, out);
+    auto keep = std::make_shared<Lowered>(out);
+    std::lock_guard<std::mutex> lock(g_cache_mu);
+    g_cache.push_front(CacheEntry{h, opts, DescCopy(d), std::move(keep)});
+    while (g_cache.size() > kCacheEntries) g_cache.pop_back();
+}
+
+void plan_cache_clear() {
+    std::lock_guard<std::mutex> lock(g_cache_mu);
+    g_cache.clear();
 }
 
 uint64_t fingerprint(const Lowered& L) {

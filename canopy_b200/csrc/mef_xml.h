@@ -74,14 +74,31 @@ class XmlParser {
             std::string ent = v.substr(k + 1, e - k - 1);
             if (ent == "lt") o += '<'; else if (ent == "gt") o += '>'; else if (ent == "amp") o += '&';
             else if (ent == "quot") o += '"'; else if (ent == "apos") o += '\'';
-            else if (!ent.empty() && ent[0] == '#') o += (char)std::strtol(ent.c_str() + (ent[1] == 'x' ? 2 : 1), nullptr, ent[1] == 'x' ? 16 : 10);
+            else if (ent.size() > 1 && ent[0] == '#') {   // numeric character reference -> UTF-8
+                char* endp = nullptr;
+                const bool hex = ent[1] == 'x' || ent[1] == 'X';
+                const long cp = std::strtol(ent.c_str() + (hex ? 2 : 1), &endp, hex ? 16 : 10);
+                if (endp == ent.c_str() + (hex ? 2 : 1) || *endp || cp <= 0 || cp > 0x10FFFF || (cp >= 0xD800 && cp <= 0xDFFF))
+                    err("bad character reference &" + ent + ";");
+                if (cp < 0x80) o += (char)cp;
+                else if (cp < 0x800) { o += (char)(0xC0 | (cp >> 6)); o += (char)(0x80 | (cp & 0x3F)); }
+                else if (cp < 0x10000) { o += (char)(0xE0 | (cp >> 12)); o += (char)(0x80 | ((cp >> 6) & 0x3F)); o += (char)(0x80 | (cp & 0x3F)); }
+                else { o += (char)(0xF0 | (cp >> 18)); o += (char)(0x80 | ((cp >> 12) & 0x3F)); o += (char)(0x80 | ((cp >> 6) & 0x3F)); o += (char)(0x80 | (cp & 0x3F)); }
+            }
             else err("unknown entity &" + ent + ";");
             k = e;
         }
         return o;
     }
+    // Recursion depth of element(): a model file nested deeper than this is refused (CANOPY_E_IO) instead of overflowing
+    // the stack, which no exception handler could turn into a status code.
+    static constexpr int kMaxDepth = 512;
+    int depth_ = 0;
+    struct DepthGuard { int& d; explicit DepthGuard(int& x) : d(x) { ++d; } ~DepthGuard() { --d; } };
     std::unique_ptr<XNode> element() {
         if (i_ >= s_.size() || s_[i_] != '<') err("expected '<'");
+        DepthGuard dg(depth_);
+        if (depth_ > kMaxDepth) err("elements nested deeper than " + std::to_string(kMaxDepth) + " levels");
         auto n = std::make_unique<XNode>();
         n->line = line_;
         adv();

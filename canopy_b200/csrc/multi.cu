@@ -1,13 +1,17 @@
 // Single-process multi-GPU run: contiguous Philox counter ranges per device, one host
 // thread per device, then ONE ncclAllReduce(ncclUint64, ncclSum) over the final tallies on NVLink.
-// The tallies buffer the engine finalises into is the buffer NCCL reduces in place on the same stream:
-// no staging copy and no host synchronisation sits between the last gate kernel and the collective.
+// The tallies buffer the engine finalises into is the buffer NCCL reduces in place on the same stream: no staging
+// copy, and the per-device runs are enqueued without a report, so nothing synchronises the host between the last
+// gate kernel and the collective (device times come from events read after the collective has been enqueued).
+// Communicators are created once per device list and kept for the life of the process (never destroyed: NCCL
+// teardown at exit is unsafe once the CUDA context is going away); a per-list mutex serialises the group calls.
 //
 // NCCL is bound lazily with dlopen("libnccl.so.2") so that libcanopy has no load-time dependency on it
 // (the torchrun path lets torch.distributed own the communicator and only needs canopy_mc_run_device).
 #include <dlfcn.h>
 #include <nccl.h>  // types only; no symbol is linked
 
+#include <chrono>
 #include <cstring>
 #include <map>
 #include <mutex>
@@ -58,7 +62,7 @@ void nccl_check(ncclResult_t r, const char* what) {
     }
 }
 
-struct CommSet { std::vector<ncclComm_t> comms; };
+struct CommSet { std::vector<ncclComm_t> comms; std::mutex mu; };
 std::mutex g_comm_mu;
 std::map<std::vector<int>, CommSet> g_comms;  // communicators are cached per device list for the process lifetime
 
@@ -66,9 +70,12 @@ CommSet& get_comms(const std::vector<int>& devs) {
     std::lock_guard<std::mutex> lock(g_comm_mu);
     auto it = g_comms.find(devs);
     if (it != g_comms.end()) return it->second;
-    CommSet cs; cs.comms.resize(devs.size());
-    nccl_check(nccl().CommInitAll(cs.comms.data(), (int)devs.size(), devs.data()), "ncclCommInitAll");
-    return g_comms.emplace(devs, std::move(cs)).first->second;
+    CommSet& cs = g_comms[devs];   // std::map: the reference stays valid for the life of the process
+    cs.comms.resize(devs.size());
+    try {
+        nccl_check(nccl().CommInitAll(cs.comms.data(), (int)devs.size(), devs.data()), "ncclCommInitAll");
+    } catch (...) { g_comms.erase(devs); throw; }
+    return cs;
 }
 
 #define CU(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) throw Error(CANOPY_E_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); } while (0)
@@ -77,6 +84,7 @@ CommSet& get_comms(const std::vector<int>& devs) {
 
 void mc_run_multi(canopy_plan* plan, const canopy_mc_opts& o, const int32_t* devices, int32_t n_devices,
                   uint64_t* tallies_host, canopy_mc_report* rep) {
+    const auto t_begin = std::chrono::steady_clock::now();
     const size_t nt = plan->low.tally_kind.size();
     std::vector<int> devs(devices, devices + n_devices);
     if (n_devices == 1) {  // degenerate: no collective
@@ -87,7 +95,6 @@ void mc_run_multi(canopy_plan* plan, const canopy_mc_opts& o, const int32_t* dev
     CommSet& cs = get_comms(devs);
     std::vector<unsigned long long*> d_t(n_devices, nullptr);
     std::vector<cudaStream_t> st(n_devices, nullptr);
-    std::vector<canopy_mc_report> reps(n_devices);
     std::vector<std::string> errs(n_devices);
     std::vector<canopy_status> codes(n_devices, CANOPY_OK);
     std::vector<std::thread> th;
@@ -100,8 +107,10 @@ void mc_run_multi(canopy_plan* plan, const canopy_mc_opts& o, const int32_t* dev
                 canopy_mc_opts oi = o;
                 oi.device = devs[i]; oi.stream = st[i];
                 shard_range(o.sample_begin, o.n_samples, i, n_devices, &oi.sample_begin, &oi.n_samples);
-                mc_run(plan, oi, nullptr, (uint64_t*)d_t[i], &reps[i]);
+                mc_run(plan, oi, nullptr, (uint64_t*)d_t[i], nullptr);   // no report: returns with the kernels in flight
             } catch (const Error& e) { codes[i] = e.code; errs[i] = e.what(); }
+            catch (const std::exception& e) { codes[i] = CANOPY_E_OOM; errs[i] = e.what(); }   // bad_alloc, system_error: never std::terminate
+            catch (...) { codes[i] = CANOPY_E_INVALID; errs[i] = "unknown error in a device worker"; }
         });
     }
     for (auto& t : th) t.join();
@@ -116,6 +125,7 @@ void mc_run_multi(canopy_plan* plan, const canopy_mc_opts& o, const int32_t* dev
         if (codes[i] != CANOPY_OK) { cleanup(); throw Error(codes[i], "device " + std::to_string(devs[i]) + ": " + errs[i]); }
     try {
         if (nt) {
+            std::lock_guard<std::mutex> comm_lock(cs.mu);   // two concurrent runs on one device list must not interleave their groups
             nccl_check(nccl().GroupStart(), "ncclGroupStart");
             for (int i = 0; i < n_devices; ++i)
                 nccl_check(nccl().AllReduce(d_t[i], d_t[i], nt, ncclUint64, ncclSum, cs.comms[i], st[i]), "ncclAllReduce");
@@ -126,14 +136,9 @@ void mc_run_multi(canopy_plan* plan, const canopy_mc_opts& o, const int32_t* dev
         for (int i = 0; i < n_devices; ++i) { CU(cudaSetDevice(devs[i])); CU(cudaStreamSynchronize(st[i])); }
     } catch (...) { cleanup(); throw; }
     cleanup();
-    if (rep) {
-        *rep = reps[0];
-        for (int i = 1; i < n_devices; ++i) {
-            rep->total_ms = std::max(rep->total_ms, reps[i].total_ms);
-            rep->sampler_launches += reps[i].sampler_launches; rep->gate_launches += reps[i].gate_launches;
-            rep->other_launches += reps[i].other_launches; rep->n_batches += reps[i].n_batches;
-            rep->h2d_bytes += reps[i].h2d_bytes;
-        }
+    if (rep) {   // wall-clock of the whole call on the host; per-kernel times need a single-device run with profile = 1
+        *rep = canopy_mc_report{};
+        rep->total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count();
         rep->d2h_bytes = nt * 8;
     }
 }

@@ -87,6 +87,8 @@ struct Lowered {
 };
 
 void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lowered& out);
+void lower_graph_cached(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lowered& out);  // through the plan cache
+void plan_cache_clear();
 // Re-quantise the thresholds of the live events from new probabilities (canopy_plan_update_p); throws if the
 // constant folding of the existing lowering would no longer hold.
 void requantise(Lowered& L, const double* p, uint32_t n_basic);

@@ -79,13 +79,15 @@ def _arr(ptr, n, dtype):
 class Plan:
     """Lowered DAG (host) + lazily created per-device state (owned by libcanopy)."""
 
-    def __init__(self, graph: Graph, tally_all_gates: bool = False, threshold_bits: int = 32, sampler: int = 0):
+    def __init__(self, graph: Graph, tally_all_gates: bool = False, threshold_bits: int = 32, sampler: int = 0,
+                 plan_cache: bool = True):
         self._h = C.c_void_p()
         self.graph = graph
         self.tally_all_gates = bool(tally_all_gates)
         self.threshold_bits = threshold_bits
         desc = graph.c_desc()
-        opts = _lib.CPlanOpts(tally_all_gates=int(tally_all_gates), threshold_bits=threshold_bits, sampler=int(sampler))
+        opts = _lib.CPlanOpts(tally_all_gates=int(tally_all_gates), threshold_bits=threshold_bits, sampler=int(sampler),
+                              no_plan_cache=int(not plan_cache))
         _lib.check(_lib.lib().canopy_plan_create(C.byref(desc), C.byref(opts), C.byref(self._h)))
         st = _lib.CPlanStats()
         _lib.check(_lib.lib().canopy_plan_info(self._h, C.byref(st)))
@@ -278,6 +280,11 @@ def shard_range(sample_begin: int, n_samples: int, rank: int, world: int):
     b, n = C.c_uint64(), C.c_uint64()
     _lib.check(_lib.lib().canopy_shard_range(sample_begin, n_samples, rank, world, C.byref(b), C.byref(n)))
     return int(b.value), int(n.value)
+
+
+def plan_cache_clear() -> None:
+    """Empty the process-wide cache of lowered plans (canopy_plan_cache_clear)."""
+    _lib.check(_lib.lib().canopy_plan_cache_clear())
 
 
 def trim_device_cache(device: int = -1) -> None:

@@ -144,7 +144,8 @@ typedef struct canopy_plan_opts {
     int32_t tally_all_gates;   /* 0: tallies = [n_roots]; 1: tallies = [n_roots] ++ [n_gates] (descriptor order) */
     int32_t threshold_bits;    /* 32 (default) or 64: width of the variate / threshold comparison                */
     int32_t sampler;           /* CANOPY_SAMPLER_*: which sampling spec the plan's tallies follow (0 = default)   */
-    int32_t reserved[5];
+    int32_t no_plan_cache;     /* 1: lower from scratch and do not keep the result (see canopy_plan_create)       */
+    int32_t reserved[4];
 } canopy_plan_opts;
 
 /* Lowering statistics, reported before and after dead-code elimination / folding. */
@@ -163,16 +164,21 @@ typedef struct canopy_plan_stats {
     uint32_t n_const_nodes;    /* roots/gates folded to constants                                */
     uint32_t n_alias_nodes;    /* gates folded to (possibly complemented) aliases                */
     uint32_t spec_version;     /* the spec this plan samples with (1 direct, 2 sliced, 4 classed sparse) */
+    uint32_t plan_cache_hit;   /* 1: the lowered form came from the plan cache                    */
 } canopy_plan_stats;
 
 typedef struct canopy_plan canopy_plan; /* opaque; immutable lowered graph + lazily created per-device state */
 
 /* Host lowering: validate (reference event.cpp:140-204 arity/min/max/nesting rules), fold constants
- * and NOT/NULL aliases, eliminate dead nodes, levelise, emit CSR. No GPU needed. */
+ * and NOT/NULL aliases, eliminate dead nodes, levelise, emit CSR. No GPU needed.
+ * The last few lowered forms are kept in a process-wide cache keyed by a hash of the descriptor and verified by
+ * comparing the arrays, so creating a plan for a model that was lowered before costs one pass over the descriptor
+ * instead of the lowering (c4: 42 ms); opts->no_plan_cache = 1 bypasses it, canopy_plan_cache_clear() empties it. */
 CANOPY_API canopy_status canopy_plan_create(const canopy_graph_desc* desc, const canopy_plan_opts* opts,
                                             canopy_plan** out_plan);
 CANOPY_API void          canopy_plan_destroy(canopy_plan* plan);
 CANOPY_API canopy_status canopy_plan_info(const canopy_plan* plan, canopy_plan_stats* out);
+CANOPY_API canopy_status canopy_plan_cache_clear(void);
 
 /* Introspection of the lowered form (used by the host-logic tests; all pointers stay valid until
  * canopy_plan_destroy). Device node ids: [0,n_basic_live) events, then gates in layer order. */

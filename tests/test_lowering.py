@@ -166,3 +166,34 @@ def test_no_cpu_fallback_without_gpu():
         with pytest.raises(_lib.CanopyError) as ei:
             plan.run(1000)
     assert ei.value.status == _lib.E_CUDA
+
+
+def test_plan_cache_hits_are_verified_by_content():
+    """canopy_plan_create keeps the last lowered forms keyed by a hash of the descriptor; a hit must be the same plan as a
+    fresh lowering, and any change of an array or an option must miss."""
+    from canopy_b200.engine import plan_cache_clear
+    from canopy_b200 import synth
+    plan_cache_clear()
+    g = synth.generate(n_basic=400, n_gates=250, n_layers=7, max_fanin=9, seed=5)
+    with Plan(g, True) as a, Plan(g, True) as b, Plan(g, True, plan_cache=False) as c:
+        assert (a.stats["plan_cache_hit"], b.stats["plan_cache_hit"], c.stats["plan_cache_hit"]) == (0, 1, 0)
+        fp = a.fingerprint()
+        assert fp == b.fingerprint() == c.fingerprint()
+        va, vb = a.view(), b.view()
+        assert all(np.array_equal(va[k], vb[k]) for k in va)
+        b.update_p(np.clip(g.p * 1.5, 0, 0.9))                  # a plan owns its copy: the cached form stays untouched
+        assert b.fingerprint() != a.fingerprint()
+    with Plan(g, True) as d:
+        assert d.stats["plan_cache_hit"] == 1 and d.fingerprint() == fp
+    with Plan(g, False) as e, Plan(g, True, threshold_bits=64) as f, Plan(g, True, sampler=2) as h:
+        assert (e.stats["plan_cache_hit"], f.stats["plan_cache_hit"], h.stats["plan_cache_hit"]) == (0, 0, 0)
+    g2 = G.Graph(p=g.p.copy(), op=g.op, kmin=g.kmin, kmax=g.kmax, child_off=g.child_off, child=g.child.copy(), roots=g.roots)
+    g2.child[7] ^= 0x80000000
+    with Plan(g2, True) as x:
+        assert x.stats["plan_cache_hit"] == 0
+    for i in range(6):                                          # more graphs than the cache holds: the oldest entry goes
+        with Plan(synth.generate(50 + i, 30, 4, 5, seed=i)) as y:
+            assert y.stats["plan_cache_hit"] == 0
+    with Plan(g, True) as z:
+        assert z.stats["plan_cache_hit"] == 0
+    plan_cache_clear()

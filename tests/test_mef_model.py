@@ -268,3 +268,25 @@ def test_event_tree_errors(patch, status, msg):
     with pytest.raises(_lib.CanopyError) as ei:
         load_mef(text=ET_XML.replace(patch[0], patch[1], 1))
     assert ei.value.status == status and msg in ei.value.message
+
+
+# ---- reader robustness ------------------------------------------------------------------------------------
+def test_xml_nesting_depth_is_capped_and_reported():
+    deep = "<a>" * 600 + "</a>" * 600
+    with pytest.raises(_lib.CanopyError) as ei:
+        load_mef(text=f"<?xml version='1.0'?><opsa-mef>{deep}</opsa-mef>")
+    assert ei.value.status == _lib.E_IO and "nested deeper" in ei.value.message
+    # a very deep input must come back as a status too, not as a stack overflow of the process
+    with pytest.raises(_lib.CanopyError):
+        load_mef(text="<?xml version='1.0'?><opsa-mef>" + "<x>" * 200000)
+
+
+def test_numeric_character_references_are_utf8():
+    xml = model("<define-fault-tree name='ft'><define-gate name='top'><or><basic-event name='pump&#xE9;'/>"
+                "<basic-event name='&#26085;&#x672C;'/></or></define-gate></define-fault-tree><model-data>"
+                + be("pump&#233;", fl(0.1)) + be("日本", fl(0.2)) + "</model-data>")
+    g = load_mef(text=xml)
+    assert g.basic_names == ["pumpé", "日本"] and g.n_gates == 1
+    with pytest.raises(_lib.CanopyError) as ei:
+        load_mef(text=model("<define-fault-tree name='f&#x110000;'/>"))
+    assert ei.value.status == _lib.E_IO
