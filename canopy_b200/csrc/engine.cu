@@ -293,6 +293,19 @@ static DeviceInfo device_info(int device) {
     // function attributes are per device (context): set once
     CUDA_CHECK(cudaFuncSetAttribute(gate_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmemBytes));
     CUDA_CHECK(cudaFuncSetAttribute(gate_ring_kernel_g4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmemBytes));
+#ifndef CANOPY_CARVEOUT
+#define CANOPY_CARVEOUT 100
+#endif
+    // Kernels that are to share an SM (the walk of batch b and the sampler of batch b+1) must ask for the same shared-memory
+    // carve-out: an SM cannot change its L1 / shared split while a CTA of the other kernel is resident on it.
+    if (CANOPY_CARVEOUT >= 0) {
+        CUDA_CHECK(cudaFuncSetAttribute(gate_ring_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, CANOPY_CARVEOUT));
+        CUDA_CHECK(cudaFuncSetAttribute(gate_ring_kernel_g4, cudaFuncAttributePreferredSharedMemoryCarveout, CANOPY_CARVEOUT));
+        CUDA_CHECK(cudaFuncSetAttribute(sampler_classed_kernel<32>, cudaFuncAttributePreferredSharedMemoryCarveout, CANOPY_CARVEOUT));
+        CUDA_CHECK(cudaFuncSetAttribute(sampler_classed_kernel<64>, cudaFuncAttributePreferredSharedMemoryCarveout, CANOPY_CARVEOUT));
+        CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<32>, cudaFuncAttributePreferredSharedMemoryCarveout, CANOPY_CARVEOUT));
+        CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<64>, cudaFuncAttributePreferredSharedMemoryCarveout, CANOPY_CARVEOUT));
+    }
     CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&I.ring_ctas_per_sm, gate_ring_kernel, kGateThreads, kRingSmemBytes));
     if (I.ring_ctas_per_sm < 1) throw Error(CANOPY_E_CUDA, "gate_ring_kernel does not fit on an SM");
     I.ready = true;
@@ -437,6 +450,12 @@ static void launch_sampler(const DeviceState* s, const Lowered& L, uint4* vals, 
                                   first_slab, n_slabs, K));
 }
 
+#ifndef CANOPY_WALK_SHARED_CTAS
+#define CANOPY_WALK_SHARED_CTAS 1   // walk CTAs per SM while the sampler of the next batch shares the GPU
+#endif
+#ifndef CANOPY_WALK_ALONE_CTAS
+#define CANOPY_WALK_ALONE_CTAS 8    // ... and when the walk has the GPU to itself (capped by its occupancy)
+#endif
 // Returns the number of CTAs launched (what the next walk waits for in walk_done[parity]).
 static uint32_t launch_gates(const DeviceState* s, const Lowered& L, uint4* vals, uint64_t first_slab, uint32_t n_slabs,
                              uint64_t begin, uint64_t end, cudaStream_t st, bool shared_sm = false, uint32_t parity = 0,
@@ -444,7 +463,7 @@ static uint32_t launch_gates(const DeviceState* s, const Lowered& L, uint4* vals
     if (L.n_gates() == 0 || n_slabs == 0) return 0;
     // persistent: one CTA per resident slot, each walks slabs blockIdx.x, +gridDim.x, ...; beside the sampler of the
     // next batch the walk keeps one CTA per SM (64 KB of row rings in flight), which measured best on B200
-    const int per_sm = std::min(shared_sm ? 1 : s->ring_ctas_per_sm, s->ring_ctas_per_sm);
+    const int per_sm = std::min(shared_sm ? CANOPY_WALK_SHARED_CTAS : CANOPY_WALK_ALONE_CTAS, s->ring_ctas_per_sm);
     const uint32_t grid = std::min<uint32_t>(n_slabs, (uint32_t)(s->sm_count * per_sm));
     const int b = vals == s->vals[1] ? 1 : 0;
     if (vals == s->vals[b] && s->vmap_ok[b] && kGroupRows == 4)

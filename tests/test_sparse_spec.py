@@ -24,7 +24,7 @@ TABLE_CASES = [(1, 13), (5 << 32, 13), (429496 << 32, 13), ((1 << 52) - 1, 13), 
                (3 << 53, 11), (12345678 << 32, 10), (1 << 57, 8), ((1 << 58) - 1, 8), (1 << 58, 7), ((1 << 59) - 1, 7),
                (0x0123456789ABCDEF >> 4, 13), (0x0123456789ABCDEF << 1, 8)]
 # probabilities covering dense, the boundary, and every class k = 7 .. 13
-CLASS_PS = [1e-9, 3e-5, 1.1e-4, 2.0 ** -12, 4e-4, 2.0 ** -11, 9e-4, 0.0018, 2.0 ** -8, 0.0039, 0.0078, 0.02, P_SPARSE - 2.0 ** -31,
+CLASS_PS = [1e-9, 3e-5, 1.1e-4, 2.0 ** -12, 4e-4, 2.0 ** -11, 9e-4, 0.0018, 2.0 ** -8, 0.0039, 0.0078, 0.011, 0.02, P_SPARSE - 2.0 ** -31,
             P_SPARSE, 0.1, 0.5, 2.0 ** -31]
 
 
