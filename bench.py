@@ -103,7 +103,7 @@ def build_tag() -> str:
     from a capture of ANOTHER build is reported as null instead of silently going stale."""
     import hashlib
     h = hashlib.sha1()
-    for f in ("engine.cu", "kernels.cuh", "plan.h", "lowering.cpp"):
+    for f in ("engine.cu", "kernels.cuh", "sampler.cuh", "walk.cuh", "sparse_table.h", "plan.h", "lowering.cpp"):
         with open(os.path.join(ROOT, "canopy_b200", "csrc", f), "rb") as fh:
             h.update(fh.read())
     return h.hexdigest()[:12]
@@ -122,7 +122,7 @@ def captured(workload_name: str):
         return None, None, "no capture for this workload in profiles/captures.json"
     if c.get("build_tag") != build_tag():
         return None, None, f"capture is of build {c.get('build_tag')}, this build is {build_tag()}: not quoted"
-    return c.get("gate_dram_bytes_per_launch"), c.get("sampler_executed_int_ops_per_bit"), f"ncu capture of build {c['build_tag']}"
+    return c.get("gate_dram_bytes_per_launch"), c.get("sampler_executed_int_ops_per_bit_x_events"), f"ncu capture {c.get('capture')} of build {c['build_tag']}"
 
 
 # samples per step per GPU where the configuration's full count makes a step too long for 25 timed steps per arm
@@ -191,8 +191,13 @@ def cpu_arm(graph, n_samples_hint: int, tally_all: bool, seconds_target: float =
     from oracle import oracle as O
     spec = spec or O.SPEC
     cores = len(os.sched_getaffinity(0))
-    probe = 1 << 12
-    t0 = time.perf_counter(); O.mc_packed(graph, 1, 0, probe, tally_all, nthreads=cores, spec=spec); dt = time.perf_counter() - t0
+    # size the sample from probes that are long enough to mean something (thread start-up dominates a 4096-sample call)
+    probe, dt = 1 << 12, 0.0
+    while True:
+        t0 = time.perf_counter(); O.mc_packed(graph, 1, 0, probe, tally_all, nthreads=cores, spec=spec); dt = time.perf_counter() - t0
+        if dt >= 0.5 or probe >= n_samples_hint:
+            break
+        probe *= 4
     n = int(min(n_samples_hint, max(probe, probe * seconds_target / max(dt, 1e-6))))
     n = max(64, n // 64 * 64)
     t0 = time.perf_counter(); t = O.mc_packed(graph, 1, 0, n, tally_all, nthreads=cores, spec=spec); dt = time.perf_counter() - t0
@@ -211,8 +216,12 @@ def run_reference(args):
     from oracle import oracle as O
     spec = args.sampler or O.SPEC
     # bounded sample per step, sized from a probe so K+W steps end within a few minutes
-    probe = 1 << 12
-    t0 = time.perf_counter(); O.mc_packed(g, 1, 0, probe, tally_all, nthreads=cores, spec=spec); dt = time.perf_counter() - t0
+    probe, dt = 1 << 12, 0.0
+    while True:
+        t0 = time.perf_counter(); O.mc_packed(g, 1, 0, probe, tally_all, nthreads=cores, spec=spec); dt = time.perf_counter() - t0
+        if dt >= 0.5 or probe >= S:
+            break
+        probe *= 4
     budget = float(os.environ.get("CANOPY_BENCH_REF_BUDGET_S", "60")) / max(1, args.steps + args.warmup)  # seconds of CPU work per step
     n = int(max(probe, min(S, probe * budget / max(dt, 1e-6)))) // 64 * 64
     for w in range(args.warmup):
@@ -286,14 +295,17 @@ def sampler_algorithmic_ops(plan, spec):
     if spec == 2:
         return 2.580, None
     view = plan.view()
-    thr = view["event_thr32"].astype(np.float64)
-    sparse = thr < 2.0 ** 27
-    # per 128-sample group (one lane): a plane event 330.2; a sparse event one Philox call (19 IMAD.WIDE + 20 LOP3) + a
-    # 64-bit compare (2) per table entry inspected (N + 1) + 4 per placed one: 41 + 6 * 128 p
-    per_group = np.where(sparse, 41.0 + 6.0 * 128.0 * thr / 2.0 ** 32, 330.2)
+    thr = view["event_thr64"].astype(np.float64) / 2.0 ** 64
+    k = view["event_k"].astype(np.int64)      # 0 = dense (planes), 7..13 = sparse with 2^k-sample groups
+    sparse = k > 0
+    grp = np.where(sparse, 2.0 ** k, 128.0)
+    # per group (one lane): a dense event 330.2 per 128 samples; a sparse event one Philox call
+    # (19 IMAD.WIDE + 20 LOP3) + a 64-bit compare (2) per table entry inspected (N + 1) + 4 per placed one: 41 + 6 * 2^k p
+    per_group = np.where(sparse, 41.0 + 6.0 * grp * thr, 330.2)
     mix = {"sparse_events": int(sparse.sum()), "plane_events": int((~sparse).sum()),
-           "mean_ones_per_group_sparse": float((128.0 * thr[sparse] / 2.0 ** 32).mean()) if sparse.any() else 0.0}
-    return (float(per_group.mean() / 128.0) if len(thr) else 0.0), mix
+           "events_per_class_k7_to_k13": [int((k == c).sum()) for c in range(7, 14)],
+           "mean_ones_per_group_sparse": float((grp[sparse] * thr[sparse]).mean()) if sparse.any() else 0.0}
+    return (float((per_group / grp).mean()) if len(thr) else 0.0), mix
 
 
 def side_line(name, local, stream, sampler, steps=2):
@@ -428,17 +440,28 @@ def main():
     e2e_steps = max(1, min(args.steps, 5))
     host_out = torch.zeros(max(nt, 1), dtype=torch.int64).pin_memory()
 
+    e2e_parts = {"plan_create_ms": 0.0, "run_ms": 0.0, "run_device_ms": 0.0, "allreduce_d2h_ms": 0.0, "plan_destroy_ms": 0.0}
+
     def e2e_step(k):
+        t0 = time.perf_counter()
         p2 = Plan(g, tally_all, sampler=args.sampler)  # canopy_plan_create from HOST arrays
+        t1 = time.perf_counter()
         r = p2.run_device(tallies.data_ptr(), S, seed=0xB200, sample_begin=(k * world + rank) * S, device=local,
                           stream=stream, want_report=True)   # uploads the lowered arrays (h2d) and runs
+        t2 = time.perf_counter()
         if world > 1:
             dist.all_reduce(tallies)
         host_out.copy_(tallies, non_blocking=False)   # d2h of the step's result
+        t3 = time.perf_counter()
         p2.close()
+        t4 = time.perf_counter()
+        for key, v in zip(e2e_parts, (t1 - t0, t2 - t1, r.total_ms * 1e-3, t3 - t2, t4 - t3)):
+            e2e_parts[key] += v * 1e3
         return r
     e2e_step(0)
     barrier()
+    for key in e2e_parts:
+        e2e_parts[key] = 0.0
     t0 = time.perf_counter()
     for k in range(e2e_steps):
         r_e2e = e2e_step(100 + k)
@@ -463,8 +486,9 @@ def main():
         # Integer roofline of the sampler.  Measured on sm_100 (canopy_microbench_int): LOP3, IMAD.WIDE.U32 and
         # any mix of the two issue at ONE shared rate of 64 lanes/clk/SM, so the bound is the integer instruction count.
         int_peak, _ = microbench_int(0, local)
-        kernel_name = {1: "sampler_kernel<32,1>", 2: "sampler_sliced_kernel<32,false>", 3: "sampler_sliced_kernel<32,true>"}.get(spec, "sampler")
-        traffic, exec_ops_per_bit, cap_note = captured(args.workload)
+        kernel_name = {1: "sampler_direct_kernel<32>", 2: "sampler_sliced_kernel<32>", 4: "sampler_classed_kernel<32>"}.get(spec, "sampler")
+        traffic, exec_x_events, cap_note = captured(args.workload)
+        exec_ops_per_bit = exec_x_events / stats["n_basic_live"] if exec_x_events and stats["n_basic_live"] else None
         step_ms = ms / args.steps
         step_bytes = (gate_bytes_per_sample + sampler_bytes_per_sample) * S
         line = {
@@ -476,6 +500,7 @@ def main():
             "clocks": clk,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(r_e2e.h2d_bytes),
                     "d2h_bytes_per_step": int(nt * 8), "steps": e2e_steps,
+                    "host_ms_per_step": {k2: v / e2e_steps for k2, v in e2e_parts.items()},
                     "what": "canopy_plan_create from host arrays + upload + run + allreduce + tallies to host, wall clock"},
             "gpu_launches": int(launches_per_step * args.steps),
             "roofline": {"kernel": "gate_ring_kernel", "bound": "hbm", "achieved": gate_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",

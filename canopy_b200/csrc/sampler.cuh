@@ -219,12 +219,14 @@ __device__ __forceinline__ void sparse_unit(uint4* __restrict__ vals, const uint
                                             uint32_t unit, const SparseClasses& C, uint32_t n_nodes, uint64_t first_slab,
                                             uint32_t n_slabs, const PhiloxKeys& K, uint32_t img) {
     const uint32_t lane = threadIdx.x & 31;
-    uint32_t c = 0;
+    // class of this unit (warp-uniform); constant indices only, so that the parameter struct stays in the constant bank
+    uint32_t c = 0, u_lo = C.unit_off[0], e_lo = C.ev_off[0], e_hi = C.ev_off[1];
 #pragma unroll
-    for (uint32_t i = 1; i < 7; ++i) c += unit >= C.unit_off[i] ? 1u : 0u;      // class of this unit (warp-uniform)
+    for (uint32_t i = 1; i < 7; ++i)
+        if (unit >= C.unit_off[i]) { c = i; u_lo = C.unit_off[i]; e_lo = C.ev_off[i]; e_hi = C.ev_off[i + 1]; }
     const uint32_t k = 7u + c;
-    const uint32_t first = C.ev_off[c] + (unit - C.unit_off[c]) * kUnitRows;
-    const uint32_t n_rows = min(kUnitRows, C.ev_off[c + 1] - first);
+    const uint32_t first = e_lo + (unit - u_lo) * kUnitRows;
+    const uint32_t n_rows = min(kUnitRows, e_hi - first);
     // lane r < n_rows keeps the device id and the original index of event r of the unit
     uint32_t my_ev = 0, my_e = 0;
     if (lane < n_rows) { my_ev = __ldg(ev_perm + first + lane); my_e = __ldg(ev_orig + my_ev); }
