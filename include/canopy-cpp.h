@@ -11,7 +11,8 @@
  *   canopy::McSettings     Monte Carlo subset of reference Settings (settings.h:118-187,324-327)
  *   canopy::lower_model()  adapter from reference mef::openpsa::Model objects; only compiled when the caller
  *                          defines CANOPY_WITH_MEF_OPENPSA and has the reference headers (+ Boost) on its include
- *                          path -- neither exists in this repository's build environment.
+ *                          path.  This repository compiles and runs it against tests/cpp/mef_shim/ (stand-ins with
+ *                          the reference's signatures; Boost is not in this image): tests/test_mef_adapter.py.
  */
 #pragma once
 
@@ -63,9 +64,13 @@ struct Arg {
 
 class GraphBuilder {
   public:
+    /// Gate handles carry this tag; basic-event handles are plain indices, so events and gates may be added in any order
+    /// (the adapter meets CCF events only while it walks the gates).  desc() resolves handles to descriptor node ids.
+    static constexpr std::uint32_t kGateTag = 0x40000000u;
+
     /// @returns handle of a new basic event with mean probability p (BasicEvent::p(), event.h:93-96).
     std::uint32_t basic_event(double p) {
-        if (!gates_op_.empty()) throw Error(CANOPY_E_INVALID, "add all basic events before the first gate");
+        if (p_.size() >= kGateTag) throw Error(CANOPY_E_INVALID, "too many basic events");
         p_.push_back(p);
         return static_cast<std::uint32_t>(p_.size() - 1);
     }
@@ -76,23 +81,37 @@ class GraphBuilder {
 
     /// @returns handle of a new gate with formula (connective, args, min_number, max_number).
     std::uint32_t gate(Connective c, const std::vector<Arg>& args, int min_number = 0, int max_number = 0) {
+        if (gates_op_.size() >= kGateTag - 2u) throw Error(CANOPY_E_INVALID, "too many gates");
         gates_op_.push_back(c);
         kmin_.push_back(static_cast<std::uint16_t>(min_number));
         kmax_.push_back(static_cast<std::uint16_t>(max_number));
         for (const Arg& a : args) child_.push_back(a.node | (a.complement ? CANOPY_CHILD_COMPLEMENT : 0u));
         child_off_.push_back(child_.size());
-        return static_cast<std::uint32_t>(p_.size() + gates_op_.size() - 1);
+        return kGateTag | static_cast<std::uint32_t>(gates_op_.size() - 1);
     }
     void root(std::uint32_t node) { roots_.push_back(node); }
+    std::size_t n_basic() const noexcept { return p_.size(); }
+    std::size_t n_gates() const noexcept { return gates_op_.size(); }
 
+    /// The flat descriptor; valid until the builder is modified or destroyed.
     canopy_graph_desc desc() const {
+        const std::uint32_t nb = static_cast<std::uint32_t>(p_.size());
+        auto resolve = [nb](std::uint32_t h) {
+            const std::uint32_t id = h & ~CANOPY_CHILD_COMPLEMENT, c = h & CANOPY_CHILD_COMPLEMENT;
+            if (id == CANOPY_CONST_TRUE || id == CANOPY_CONST_FALSE || !(id & kGateTag)) return h;
+            return (nb + (id & ~kGateTag)) | c;
+        };
+        child_out_.resize(child_.size());
+        for (std::size_t i = 0; i < child_.size(); ++i) child_out_[i] = resolve(child_[i]);
+        roots_out_.resize(roots_.size());
+        for (std::size_t i = 0; i < roots_.size(); ++i) roots_out_[i] = resolve(roots_[i]);
         canopy_graph_desc d{};
-        d.n_basic = static_cast<std::uint32_t>(p_.size());
+        d.n_basic = nb;
         d.n_gates = static_cast<std::uint32_t>(gates_op_.size());
         d.n_roots = static_cast<std::uint32_t>(roots_.size());
         d.n_edges = child_.size();
         d.p = p_.data(); d.op = gates_op_.data(); d.kmin = kmin_.data(); d.kmax = kmax_.data();
-        d.child_off = child_off_.data(); d.child = child_.data(); d.roots = roots_.data();
+        d.child_off = child_off_.data(); d.child = child_out_.data(); d.roots = roots_out_.data();
         return d;
     }
 
@@ -101,7 +120,8 @@ class GraphBuilder {
     std::vector<std::uint8_t> gates_op_;
     std::vector<std::uint16_t> kmin_, kmax_;
     std::vector<std::uint64_t> child_off_{0};
-    std::vector<std::uint32_t> child_, roots_;
+    std::vector<std::uint32_t> child_, roots_;                 // handles
+    mutable std::vector<std::uint32_t> child_out_, roots_out_; // descriptor node ids, filled by desc()
 };
 
 /// Monte Carlo knobs of reference Settings, widened from int to 64 bit.
@@ -213,16 +233,28 @@ inline Result quantify(const canopy_graph_desc& d, const McSettings& s) {
 namespace canopy {
 
 /// Flattens Model -> FaultTree::top_events() -> Gate::formula().args() into a GraphBuilder.
-/// Follows BasicEvent::ccf_gate() when settings.ccf_analysis() (event.h:108-114, settings.h:298).
+/// Basic events: the rows of Model::basic_events() first, in table order (model.h:89), so that an event's Philox stream
+/// (keyed by its descriptor index) does not depend on which gates use it.  With settings.ccf_analysis() (settings.h:298) a
+/// member of a CCF group is replaced by its proxy gate BasicEvent::ccf_gate() (event.h:108-114), whose arguments are
+/// CcfEvent objects owned by the group (ccf_group.h:215-260), NOT rows of Model::basic_events(): those are added when the
+/// walk first meets them, in walk order (top events in fault-tree order, arguments left to right, depth first).
 /// Must run on the thread that owns the model: MEF objects are not thread-safe (model.h:74-76).
 inline GraphBuilder lower_model(const mef::openpsa::Model& model, const mef::openpsa::Settings& settings) {
     using namespace mef::openpsa;
     GraphBuilder b;
-    std::unordered_map<const BasicEvent*, std::uint32_t> ev;
-    for (const BasicEvent& e : model.basic_events()) ev.emplace(&e, b.basic_event(e.p()));
-    std::unordered_map<const Gate*, std::uint32_t> done;
+    using EventIds = std::unordered_map<const BasicEvent*, std::uint32_t>;
+    using GateIds = std::unordered_map<const Gate*, std::uint32_t>;
+    EventIds events;
+    for (const BasicEvent& e : model.basic_events()) events.emplace(&e, b.basic_event(e.p()));
+    GateIds gates;
     struct Walk {
-        GraphBuilder& b; decltype(ev)& ev; decltype(done)& done; bool ccf;
+        GraphBuilder& b; EventIds& ev; GateIds& done; bool ccf;
+        std::uint32_t basic(const BasicEvent* e) {
+            if (ccf && e->HasCcf()) return gate(e->ccf_gate());
+            auto it = ev.find(e);
+            if (it != ev.end()) return it->second;
+            return ev.emplace(e, b.basic_event(e->p())).first->second;   // a CcfEvent (or an event outside the model's table)
+        }
         std::uint32_t gate(const Gate& g) {
             auto it = done.find(&g);
             if (it != done.end()) return it->second;
@@ -232,7 +264,7 @@ inline GraphBuilder lower_model(const mef::openpsa::Model& model, const mef::ope
                 std::uint32_t node = std::visit([&](auto* e) -> std::uint32_t {
                     using T = std::decay_t<decltype(*e)>;
                     if constexpr (std::is_same_v<T, Gate>) return gate(*e);
-                    else if constexpr (std::is_same_v<T, BasicEvent>) return ccf && e->HasCcf() ? gate(e->ccf_gate()) : ev.at(e);
+                    else if constexpr (std::is_same_v<T, BasicEvent>) return basic(e);
                     else return GraphBuilder::house_event(e->state());
                 }, a.event);
                 args.push_back({node, a.complement});
@@ -242,7 +274,7 @@ inline GraphBuilder lower_model(const mef::openpsa::Model& model, const mef::ope
             done.emplace(&g, h);
             return h;
         }
-    } walk{b, ev, done, settings.ccf_analysis()};
+    } walk{b, events, gates, settings.ccf_analysis()};
     for (const FaultTree& ft : model.fault_trees())
         for (const Gate* top : ft.top_events()) b.root(walk.gate(*top));
     return b;
