@@ -74,6 +74,21 @@ class CMefOpts(C.Structure):
                 ("reserved", C.c_int32 * 4)]
 
 
+class CDeviate(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("n_bins", C.c_uint32), ("a", C.c_double), ("b", C.c_double), ("c", C.c_double),
+                ("bounds", C.POINTER(C.c_double)), ("weights", C.POINTER(C.c_double))]
+
+
+class CUncertaintyOpts(C.Structure):
+    _fields_ = [("n_trials", C.c_uint64), ("first_trial", C.c_uint64), ("seed", C.c_uint64),
+                ("num_quantiles", C.c_uint32), ("num_bins", C.c_uint32), ("reserved", C.c_int32 * 4)]
+
+
+class CUncertaintyStats(C.Structure):
+    _fields_ = [("mean", C.c_double), ("sigma", C.c_double), ("ci_lo", C.c_double), ("ci_hi", C.c_double),
+                ("error_factor", C.c_double), ("min", C.c_double), ("max", C.c_double)]
+
+
 class CEstimate(C.Structure):
     _fields_ = [("p", C.c_double), ("sigma", C.c_double), ("ci_lo", C.c_double), ("ci_hi", C.c_double)]
 
@@ -109,6 +124,15 @@ SYMBOLS = {
     "canopy_model_basic_name": (C.c_char_p, [C.c_void_p, C.c_uint32]),
     "canopy_model_gate_name": (C.c_char_p, [C.c_void_p, C.c_uint32]),
     "canopy_model_destroy": (None, [C.c_void_p]),
+    "canopy_psource_from_model": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "canopy_psource_from_deviates": (C.c_int, [C.POINTER(CDeviate), C.c_uint32, C.POINTER(C.c_void_p)]),
+    "canopy_psource_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    "canopy_psource_mean": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
+    "canopy_psource_sample": (C.c_int, [C.c_void_p, C.c_uint64, C.c_uint64, C.POINTER(C.c_double)]),
+    "canopy_psource_destroy": (None, [C.c_void_p]),
+    "canopy_uncertainty_run": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(CMcOpts), C.POINTER(CUncertaintyOpts),
+                                         C.POINTER(CUncertaintyStats), C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                         _u64p, C.POINTER(C.c_double)]),
     "canopy_last_error": (C.c_char_p, []),
     "canopy_status_string": (C.c_char_p, [C.c_int]),
     "canopy_version": (C.c_uint32, []),

@@ -20,7 +20,7 @@
 //     paths; along a path collect-formula instructions are conjoined, collect-expression instructions multiply
 //     into one extra basic event, set-house-event overrides apply to the formulas collected after them.
 // Not covered (CANOPY_E_UNSUPPORTED): nested formulas (the reference's Formula::Arg cannot hold them either,
-// formula.h:9-15), periodic-test, extern functions, alignments/substitutions, XInclude, private roles
+// formula.h:9-15), the 11-argument periodic-test, extern functions, alignments/substitutions, XInclude, private roles
 // (every name is looked up as written; a dotted reference falls back to its last segment).
 #include <algorithm>
 #include <cmath>
@@ -30,16 +30,8 @@
 #include <sstream>
 
 #include "mef_xml.h"
+#include "model.h"
 
-struct canopy_model {
-    std::vector<double> p;
-    std::vector<uint8_t> op;
-    std::vector<uint16_t> kmin, kmax;
-    std::vector<uint64_t> child_off{0};
-    std::vector<uint32_t> child;
-    std::vector<uint32_t> roots;
-    std::vector<std::string> basic_names, gate_names, root_names;
-};
 
 namespace canopy {
 namespace {
@@ -59,9 +51,9 @@ struct GateDef {
     int tree = -1;               // fault-tree ordinal, -1 for synthetic gates
     const XNode* body = nullptr; // <define-gate>, null for synthetic gates
 };
-struct BasicDef { std::string name; const XNode* body = nullptr; double p = 0.0; bool has_p = false; int proxy_gate = -1; };
+struct BasicDef { std::string name; const XNode* body = nullptr; double p = 0.0; bool has_p = false; int proxy_gate = -1; uint32_t node = 0; };  // node: tape node of p
 struct HouseDef { std::string name; bool state = false; };
-struct ParamDef { std::string name; const XNode* body = nullptr; double value = 0.0; int mark = 0; };
+struct ParamDef { std::string name; const XNode* body = nullptr; double value = 0.0; int mark = 0; uint32_t node = 0; };
 struct CcfDef { std::string name, model; const XNode* node = nullptr; std::vector<uint32_t> members; };
 struct EventTreeDef {
     std::string name;
@@ -237,134 +229,168 @@ struct Builder {
         }
     }
 
-    // ---- expressions: Expression::value(), i.e. the mean (expression.h:74; expr/*.h) -----------------
-    double parameter_value(const XNode& at, const std::string& name) {
+    // ---- expressions (expression.h:74-117; expr/*.h) -----------------------------------------------------
+    // Every expression is compiled onto the model's tape (expr_tape.h) while its mean value -- Expression::value() -- is
+    // computed for validation, so that the same probabilities can later be re-evaluated with sampled deviates
+    // (Expression::Sample(), canopy_model_sample_p).  Ex = (mean value, tape node).
+    struct Ex { double v; uint32_t id; };
+    Ex emit(uint16_t op, const std::vector<Ex>& a, double v) {
+        std::vector<uint32_t> ids;
+        for (const Ex& x : a) ids.push_back(x.id);
+        return Ex{v, m.tape.add(op, ids)};
+    }
+    Ex konst(double c) { return Ex{c, m.tape.constant(c)}; }
+    Ex parameter_value(const XNode& at, const std::string& name) {
         auto it = param_idx.find(name);
         if (it == param_idx.end()) it = param_idx.find(last_segment(name));
         if (it == param_idx.end()) bad(CANOPY_E_VALIDITY, at, "Undefined Element Error: parameter " + name);
         ParamDef& p = params[it->second];
-        if (p.mark == 2) return p.value;
+        if (p.mark == 2) return Ex{p.value, p.node};   // one node per parameter: sampled once per trial, shared by its users
         if (p.mark == 1) bad(CANOPY_E_CYCLE, at, "Cycle Error: parameter " + name + " refers to itself");  // cycle.h:219-229
         p.mark = 1;
-        p.value = eval(*p.body, EvalCtx{});
+        const Ex x = ev(*p.body, EvalCtx{});
+        p.value = x.v; p.node = x.id;
         p.mark = 2;
-        return p.value;
+        return x;
     }
-    std::vector<double> eval_args(const XNode& e, const EvalCtx& cx, size_t lo, size_t hi) {
-        std::vector<double> v;
-        for (const XNode* k : kids_of(e)) v.push_back(eval(*k, cx));
+    std::vector<Ex> eval_args(const XNode& e, const EvalCtx& cx, size_t lo, size_t hi) {
+        std::vector<Ex> v;
+        for (const XNode* k : kids_of(e)) v.push_back(ev(*k, cx));
         if (v.size() < lo || v.size() > hi)
             bad(CANOPY_E_VALIDITY, e, "<" + e.name + "> takes " + (lo == hi ? std::to_string(lo) : std::to_string(lo) + "+") +
                                           " argument(s), got " + std::to_string(v.size()));
         return v;
     }
-    double eval(const XNode& e, const EvalCtx& cx) {
+    double eval(const XNode& e, const EvalCtx& cx) { return ev(e, cx).v; }
+    Ex ev(const XNode& e, const EvalCtx& cx) {
         const std::string& t = e.name;
         constexpr size_t kMany = 1u << 20;
-        if (t == "float" || t == "int") return parse_number(e, need_attr(e, "value"));
-        if (t == "bool") return parse_bool(e, need_attr(e, "value")) ? 1.0 : 0.0;
+        if (t == "float" || t == "int") return konst(parse_number(e, need_attr(e, "value")));
+        if (t == "bool") return konst(parse_bool(e, need_attr(e, "value")) ? 1.0 : 0.0);
         if (t == "parameter") return parameter_value(e, need_name(e));
-        if (t == "system-mission-time") return opts.mission_time;
-        if (t == "pi") return 3.14159265358979323846;
+        if (t == "system-mission-time") return konst(opts.mission_time);
+        if (t == "pi") return konst(3.14159265358979323846);
         if (t == "test-initiating-event") {  // test_event.h: true iff the walk started from this initiating event
             if (!cx.initiating_event) bad(CANOPY_E_VALIDITY, e, "<test-initiating-event> outside an event-tree walk");
-            return *cx.initiating_event == need_name(e) ? 1.0 : 0.0;
+            return konst(*cx.initiating_event == need_name(e) ? 1.0 : 0.0);
         }
         if (t == "test-functional-event") {  // test_event.h: true iff the functional event is in the given state on this path
             if (!cx.functional_states) bad(CANOPY_E_VALIDITY, e, "<test-functional-event> outside an event-tree walk");
             auto it = cx.functional_states->find(need_name(e));
-            return it != cx.functional_states->end() && it->second == need_attr(e, "state") ? 1.0 : 0.0;
+            return konst(it != cx.functional_states->end() && it->second == need_attr(e, "state") ? 1.0 : 0.0);
         }
-        if (t == "neg") return -eval_args(e, cx, 1, 1)[0];
+        if (t == "neg") { const auto v = eval_args(e, cx, 1, 1); return emit(X_NEG, v, -v[0].v); }
         if (t == "add" || t == "sub" || t == "mul" || t == "div") {
             const auto v = eval_args(e, cx, t == "add" || t == "mul" ? 1 : 2, kMany);
-            double r = v[0];
+            double r = v[0].v;
             for (size_t i = 1; i < v.size(); ++i) {
-                if (t == "add") r += v[i]; else if (t == "sub") r -= v[i]; else if (t == "mul") r *= v[i];
-                else { if (v[i] == 0.0) bad(CANOPY_E_DOMAIN, e, "Division by 0."); r /= v[i]; }  // numerical.h: Div::Validate
+                if (t == "add") r += v[i].v; else if (t == "sub") r -= v[i].v; else if (t == "mul") r *= v[i].v;
+                else { if (v[i].v == 0.0) bad(CANOPY_E_DOMAIN, e, "Division by 0."); r /= v[i].v; }  // numerical.h: Div::Validate
             }
-            return r;
+            return emit(t == "add" ? X_ADD : t == "sub" ? X_SUB : t == "mul" ? X_MUL : X_DIV, v, r);
         }
-        static const std::map<std::string, double (*)(double)> kUnary = {
-            {"abs", [](double x) { return std::fabs(x); }}, {"acos", [](double x) { return std::acos(x); }},
-            {"asin", [](double x) { return std::asin(x); }}, {"atan", [](double x) { return std::atan(x); }},
-            {"cos", [](double x) { return std::cos(x); }}, {"sin", [](double x) { return std::sin(x); }},
-            {"tan", [](double x) { return std::tan(x); }}, {"cosh", [](double x) { return std::cosh(x); }},
-            {"sinh", [](double x) { return std::sinh(x); }}, {"tanh", [](double x) { return std::tanh(x); }},
-            {"exp", [](double x) { return std::exp(x); }}, {"log", [](double x) { return std::log(x); }},
-            {"log10", [](double x) { return std::log10(x); }}, {"sqrt", [](double x) { return std::sqrt(x); }},
-            {"ceil", [](double x) { return std::ceil(x); }}, {"floor", [](double x) { return std::floor(x); }}};
+        struct Unary { uint16_t op; double (*f)(double); };
+        static const std::map<std::string, Unary> kUnary = {
+            {"abs", {X_ABS, [](double x) { return std::fabs(x); }}}, {"acos", {X_ACOS, [](double x) { return std::acos(x); }}},
+            {"asin", {X_ASIN, [](double x) { return std::asin(x); }}}, {"atan", {X_ATAN, [](double x) { return std::atan(x); }}},
+            {"cos", {X_COS, [](double x) { return std::cos(x); }}}, {"sin", {X_SIN, [](double x) { return std::sin(x); }}},
+            {"tan", {X_TAN, [](double x) { return std::tan(x); }}}, {"cosh", {X_COSH, [](double x) { return std::cosh(x); }}},
+            {"sinh", {X_SINH, [](double x) { return std::sinh(x); }}}, {"tanh", {X_TANH, [](double x) { return std::tanh(x); }}},
+            {"exp", {X_EXP, [](double x) { return std::exp(x); }}}, {"log", {X_LOG, [](double x) { return std::log(x); }}},
+            {"log10", {X_LOG10, [](double x) { return std::log10(x); }}}, {"sqrt", {X_SQRT, [](double x) { return std::sqrt(x); }}},
+            {"ceil", {X_CEIL, [](double x) { return std::ceil(x); }}}, {"floor", {X_FLOOR, [](double x) { return std::floor(x); }}}};
         if (auto it = kUnary.find(t); it != kUnary.end()) {
-            const double x = eval_args(e, cx, 1, 1)[0];
+            const auto v = eval_args(e, cx, 1, 1);
+            const double x = v[0].v;
             if ((t == "acos" || t == "asin") && (x < -1 || x > 1)) bad(CANOPY_E_DOMAIN, e, "argument of " + t + " outside [-1, 1]");
             if ((t == "log" || t == "log10") && x <= 0) bad(CANOPY_E_DOMAIN, e, "argument of " + t + " is not positive");
             if (t == "sqrt" && x < 0) bad(CANOPY_E_DOMAIN, e, "argument of sqrt is negative");
-            return it->second(x);
+            return emit(it->second.op, v, it->second.f(x));
         }
-        if (t == "mod") { const auto v = eval_args(e, cx, 2, 2); if ((long long)v[1] == 0) bad(CANOPY_E_DOMAIN, e, "Modulo second operand must not be 0."); return (double)((long long)v[0] % (long long)v[1]); }
-        if (t == "pow") { const auto v = eval_args(e, cx, 2, 2); return std::pow(v[0], v[1]); }
-        if (t == "min") { const auto v = eval_args(e, cx, 1, kMany); return *std::min_element(v.begin(), v.end()); }
-        if (t == "max") { const auto v = eval_args(e, cx, 1, kMany); return *std::max_element(v.begin(), v.end()); }
-        if (t == "mean") { const auto v = eval_args(e, cx, 1, kMany); double s = 0; for (double x : v) s += x; return s / (double)v.size(); }
-        if (t == "not") return eval_args(e, cx, 1, 1)[0] != 0.0 ? 0.0 : 1.0;
-        if (t == "and") { for (double x : eval_args(e, cx, 2, kMany)) if (x == 0.0) return 0.0; return 1.0; }
-        if (t == "or") { for (double x : eval_args(e, cx, 2, kMany)) if (x != 0.0) return 1.0; return 0.0; }
+        if (t == "mod") { const auto v = eval_args(e, cx, 2, 2); if ((long long)v[1].v == 0) bad(CANOPY_E_DOMAIN, e, "Modulo second operand must not be 0."); return emit(X_MOD, v, (double)((long long)v[0].v % (long long)v[1].v)); }
+        if (t == "pow") { const auto v = eval_args(e, cx, 2, 2); return emit(X_POW, v, std::pow(v[0].v, v[1].v)); }
+        if (t == "min" || t == "max" || t == "mean") {
+            const auto v = eval_args(e, cx, 1, kMany);
+            double r = v[0].v, s = 0;
+            for (const Ex& x : v) { r = t == "min" ? std::fmin(r, x.v) : std::fmax(r, x.v); s += x.v; }
+            return t == "mean" ? emit(X_MEAN, v, s / (double)v.size()) : emit(t == "min" ? X_MIN : X_MAX, v, r);
+        }
+        if (t == "not") { const auto v = eval_args(e, cx, 1, 1); return emit(X_NOT, v, v[0].v != 0.0 ? 0.0 : 1.0); }
+        if (t == "and") { const auto v = eval_args(e, cx, 2, kMany); double r = 1.0; for (const Ex& x : v) if (x.v == 0.0) r = 0.0; return emit(X_AND, v, r); }
+        if (t == "or") { const auto v = eval_args(e, cx, 2, kMany); double r = 0.0; for (const Ex& x : v) if (x.v != 0.0) r = 1.0; return emit(X_OR, v, r); }
         if (t == "eq" || t == "df" || t == "lt" || t == "gt" || t == "leq" || t == "geq") {
             const auto v = eval_args(e, cx, 2, 2);
-            const bool r = t == "eq" ? v[0] == v[1] : t == "df" ? v[0] != v[1] : t == "lt" ? v[0] < v[1] : t == "gt" ? v[0] > v[1]
-                         : t == "leq" ? v[0] <= v[1] : v[0] >= v[1];
-            return r ? 1.0 : 0.0;
+            const double a = v[0].v, b = v[1].v;
+            const bool r = t == "eq" ? a == b : t == "df" ? a != b : t == "lt" ? a < b : t == "gt" ? a > b : t == "leq" ? a <= b : a >= b;
+            return emit(t == "eq" ? X_EQ : t == "df" ? X_DF : t == "lt" ? X_LT : t == "gt" ? X_GT : t == "leq" ? X_LEQ : X_GEQ, v, r ? 1.0 : 0.0);
         }
-        if (t == "ite") { const auto v = eval_args(e, cx, 3, 3); return v[0] != 0.0 ? v[1] : v[2]; }
-        if (t == "switch") {  // conditional.h: the first <case> whose condition holds, else the trailing default
+        if (t == "ite") { const auto v = eval_args(e, cx, 3, 3); return emit(X_ITE, v, v[0].v != 0.0 ? v[1].v : v[2].v); }
+        if (t == "switch") {  // conditional.h: the first <case> whose condition holds, else the trailing default; = nested ite
             const auto ks = kids_of(e);
             if (ks.empty()) bad(CANOPY_E_VALIDITY, e, "<switch> needs a default value");
-            for (size_t i = 0; i + 1 < ks.size(); ++i) {
+            Ex r = ev(*ks.back(), cx);
+            for (size_t i = ks.size() - 1; i-- > 0;) {
                 const auto cs = kids_of(*ks[i]);
                 if (ks[i]->name != "case" || cs.size() != 2) bad(CANOPY_E_VALIDITY, *ks[i], "<switch> takes <case> elements with 2 arguments, then a default");
-                if (eval(*cs[0], cx) != 0.0) return eval(*cs[1], cx);
+                const Ex c = ev(*cs[0], cx), x = ev(*cs[1], cx);
+                r = emit(X_ITE, {c, x, r}, c.v != 0.0 ? x.v : r.v);
             }
-            return eval(*ks.back(), cx);
+            return r;
         }
         if (t == "exponential") {  // exponential.h:15-41: 1 - exp(-lambda t)
             const auto v = eval_args(e, cx, 2, 2);
-            if (v[0] < 0) bad(CANOPY_E_DOMAIN, e, "The rate of failure cannot be negative.");
-            if (v[1] < 0) bad(CANOPY_E_DOMAIN, e, "The mission time cannot be negative.");
-            return 1.0 - std::exp(-v[0] * v[1]);
+            if (v[0].v < 0) bad(CANOPY_E_DOMAIN, e, "The rate of failure cannot be negative.");
+            if (v[1].v < 0) bad(CANOPY_E_DOMAIN, e, "The mission time cannot be negative.");
+            return emit(X_EXPONENTIAL, v, 1.0 - std::exp(-v[0].v * v[1].v));
         }
         if (t == "GLM") {  // exponential.h:43-72: (lambda - (lambda - gamma r) exp(-r t)) / r, r = lambda + mu
             const auto v = eval_args(e, cx, 4, 4);
-            const double gamma = v[0], lambda = v[1], mu = v[2], time = v[3], r = lambda + mu;
+            const double gamma = v[0].v, lambda = v[1].v, mu = v[2].v, time = v[3].v, r = lambda + mu;
             if (gamma < 0 || gamma > 1) bad(CANOPY_E_DOMAIN, e, "Invalid value for probability on demand.");
             if (lambda < 0 || mu < 0) bad(CANOPY_E_DOMAIN, e, "The rate of failure or repair cannot be negative.");
             if (time < 0) bad(CANOPY_E_DOMAIN, e, "The mission time cannot be negative.");
-            if (r == 0) return gamma;
-            return (lambda - (lambda - gamma * r) * std::exp(-r * time)) / r;
+            return emit(X_GLM, v, r == 0 ? gamma : (lambda - (lambda - gamma * r) * std::exp(-r * time)) / r);
         }
         if (t == "Weibull") {  // exponential.h:74-103: 1 - exp(-((t - t0) / alpha)^beta)
             const auto v = eval_args(e, cx, 4, 4);
-            if (v[0] <= 0) bad(CANOPY_E_DOMAIN, e, "The scale parameter for Weibull distribution must be positive.");
-            if (v[1] <= 0) bad(CANOPY_E_DOMAIN, e, "The shape parameter for Weibull distribution must be positive.");
-            if (v[2] < 0) bad(CANOPY_E_DOMAIN, e, "Invalid value for time shift.");
-            if (v[3] < 0) bad(CANOPY_E_DOMAIN, e, "The mission time cannot be negative.");
-            return v[3] <= v[2] ? 0.0 : 1.0 - std::exp(-std::pow((v[3] - v[2]) / v[0], v[1]));
+            if (v[0].v <= 0) bad(CANOPY_E_DOMAIN, e, "The scale parameter for Weibull distribution must be positive.");
+            if (v[1].v <= 0) bad(CANOPY_E_DOMAIN, e, "The shape parameter for Weibull distribution must be positive.");
+            if (v[2].v < 0) bad(CANOPY_E_DOMAIN, e, "Invalid value for time shift.");
+            if (v[3].v < 0) bad(CANOPY_E_DOMAIN, e, "The mission time cannot be negative.");
+            return emit(X_WEIBULL, v, v[3].v <= v[2].v ? 0.0 : 1.0 - std::exp(-std::pow((v[3].v - v[2].v) / v[0].v, v[1].v)));
         }
-        // random deviates: value() is the mean of the distribution (random_deviate.h:44-264)
-        if (t == "uniform-deviate") { const auto v = eval_args(e, cx, 2, 2); if (v[0] >= v[1]) bad(CANOPY_E_VALIDITY, e, "Min value is more than max for Uniform distribution."); return (v[0] + v[1]) / 2; }
-        if (t == "normal-deviate") { const auto v = eval_args(e, cx, 2, 2); if (v[1] <= 0) bad(CANOPY_E_DOMAIN, e, "Standard deviation cannot be negative or zero."); return v[0]; }
+        if (t == "periodic-test") {  // exponential.h:105-245, initializer.cpp:1128-1141 (4, 5 or 11 arguments)
+            const auto ks = kids_of(e);
+            if (ks.size() != 4 && ks.size() != 5 && ks.size() != 11) bad(CANOPY_E_VALIDITY, e, "Invalid number of arguments for Periodic Test.");
+            if (ks.size() == 11) bad(CANOPY_E_UNSUPPORTED, e, "the 11-argument <periodic-test> is not supported by this loader");
+            const auto v = eval_args(e, cx, 4, 5);
+            const bool five = v.size() == 5;
+            const double lambda = v[0].v, tau = v[five ? 2 : 1].v, theta = v[five ? 3 : 2].v, time = v[five ? 4 : 3].v;
+            if (lambda < 0) bad(CANOPY_E_DOMAIN, e, "The rate of failure cannot be negative.");
+            if (five && v[1].v < 0) bad(CANOPY_E_DOMAIN, e, "The rate of repair cannot be negative.");
+            if (tau <= 0) bad(CANOPY_E_DOMAIN, e, "The time between tests must be positive.");
+            if (theta < 0) bad(CANOPY_E_DOMAIN, e, "The time before the first test cannot be negative.");
+            if (time < 0) bad(CANOPY_E_DOMAIN, e, "The mission time cannot be negative.");
+            if ((time - theta) / tau > 1e7) bad(CANOPY_E_DOMAIN, e, "periodic-test: more than 1e7 test intervals in the mission time");
+            return five ? emit(X_PERIODIC5, v, periodic_test5(lambda, v[1].v, tau, theta, time)) : emit(X_PERIODIC4, v, periodic_test4(lambda, tau, theta, time));
+        }
+        // random deviates: value() is the mean of the distribution (random_deviate.h:44-264); sampling: expr_tape.h
+        if (t == "uniform-deviate") { const auto v = eval_args(e, cx, 2, 2); if (v[0].v >= v[1].v) bad(CANOPY_E_VALIDITY, e, "Min value is more than max for Uniform distribution."); return emit(X_UNIFORM, v, (v[0].v + v[1].v) / 2); }
+        if (t == "normal-deviate") { const auto v = eval_args(e, cx, 2, 2); if (v[1].v <= 0) bad(CANOPY_E_DOMAIN, e, "Standard deviation cannot be negative or zero."); return emit(X_NORMAL, v, v[0].v); }
         if (t == "lognormal-deviate") {
             const auto v = eval_args(e, cx, 2, 3);
             if (v.size() == 3) {  // (mean, error factor, confidence level)
-                if (v[0] <= 0) bad(CANOPY_E_DOMAIN, e, "The mean of Log-Normal distribution cannot be negative or zero.");
-                if (v[1] <= 1) bad(CANOPY_E_DOMAIN, e, "The Error Factor for Log-Normal distribution cannot be less than 1.");
-                if (v[2] <= 0 || v[2] >= 1) bad(CANOPY_E_DOMAIN, e, "The confidence level is not within (0, 1).");
-                return v[0];
+                if (v[0].v <= 0) bad(CANOPY_E_DOMAIN, e, "The mean of Log-Normal distribution cannot be negative or zero.");
+                if (v[1].v <= 1) bad(CANOPY_E_DOMAIN, e, "The Error Factor for Log-Normal distribution cannot be less than 1.");
+                if (v[2].v <= 0 || v[2].v >= 1) bad(CANOPY_E_DOMAIN, e, "The confidence level is not within (0, 1).");
+                if (v[2].v == 0.5) bad(CANOPY_E_DOMAIN, e, "The confidence level 0.5 leaves the Log-Normal scale undefined.");
+                return emit(X_LOGNORMAL3, v, v[0].v);
             }
-            if (v[1] <= 0) bad(CANOPY_E_DOMAIN, e, "Standard deviation cannot be negative or zero.");
-            return std::exp(v[0] + v[1] * v[1] / 2);  // (mu, sigma) of the underlying normal
+            if (v[1].v <= 0) bad(CANOPY_E_DOMAIN, e, "Standard deviation cannot be negative or zero.");
+            return emit(X_LOGNORMAL2, v, std::exp(v[0].v + v[1].v * v[1].v / 2));  // (mu, sigma) of the underlying normal
         }
-        if (t == "gamma-deviate") { const auto v = eval_args(e, cx, 2, 2); if (v[0] <= 0 || v[1] <= 0) bad(CANOPY_E_DOMAIN, e, "The k and theta parameters of Gamma distribution must be positive."); return v[0] * v[1]; }
-        if (t == "beta-deviate") { const auto v = eval_args(e, cx, 2, 2); if (v[0] <= 0 || v[1] <= 0) bad(CANOPY_E_DOMAIN, e, "The alpha and beta parameters of Beta distribution must be positive."); return v[0] / (v[0] + v[1]); }
+        if (t == "gamma-deviate") { const auto v = eval_args(e, cx, 2, 2); if (v[0].v <= 0 || v[1].v <= 0) bad(CANOPY_E_DOMAIN, e, "The k and theta parameters of Gamma distribution must be positive."); return emit(X_GAMMA, v, v[0].v * v[1].v); }
+        if (t == "beta-deviate") { const auto v = eval_args(e, cx, 2, 2); if (v[0].v <= 0 || v[1].v <= 0) bad(CANOPY_E_DOMAIN, e, "The alpha and beta parameters of Beta distribution must be positive."); return emit(X_BETA, v, v[0].v / (v[0].v + v[1].v)); }
         if (t == "histogram") {
             // <histogram> lower-bound <bin> upper-bound weight </bin>... (initializer.cpp:1094-1112); validation as
             // random_deviate.h:240-247: boundaries strictly increasing, weights not negative.  value() has no body in
@@ -372,17 +398,19 @@ struct Builder {
             // w_i / sum(w) (random_deviate.h:234-238 "weights of intervals") is sum_i w_i (b_{i-1} + b_i) / (2 sum w).
             const auto kids = kids_of(e);
             if (kids.size() < 2) bad(CANOPY_E_VALIDITY, e, "<histogram> needs a lower boundary and at least one <bin>");
-            double prev = eval(*kids[0], cx), sum_w = 0, sum_wm = 0;
+            std::vector<Ex> v{ev(*kids[0], cx)};
+            double prev = v[0].v, sum_w = 0, sum_wm = 0;
             for (size_t i = 1; i < kids.size(); ++i) {
                 const auto bin = kids_of(*kids[i]);
                 if (kids[i]->name != "bin" || bin.size() != 2) bad(CANOPY_E_VALIDITY, *kids[i], "<bin> takes an upper boundary and a weight");
-                const double b = eval(*bin[0], cx), w = eval(*bin[1], cx);
-                if (!(b > prev)) bad(CANOPY_E_VALIDITY, e, "Histogram upper boundaries are not strictly increasing.");
-                if (w < 0) bad(CANOPY_E_VALIDITY, e, "Histogram weights cannot be negative.");
-                sum_w += w; sum_wm += w * (prev + b); prev = b;
+                const Ex b = ev(*bin[0], cx), w = ev(*bin[1], cx);
+                if (!(b.v > prev)) bad(CANOPY_E_VALIDITY, e, "Histogram upper boundaries are not strictly increasing.");
+                if (w.v < 0) bad(CANOPY_E_VALIDITY, e, "Histogram weights cannot be negative.");
+                sum_w += w.v; sum_wm += w.v * (prev + b.v); prev = b.v;
+                v.push_back(b); v.push_back(w);
             }
             if (sum_w <= 0) bad(CANOPY_E_VALIDITY, e, "Histogram weights sum to zero.");
-            return sum_wm / (2 * sum_w);
+            return emit(X_HISTOGRAM, v, sum_wm / (2 * sum_w));
         }
         bad(CANOPY_E_UNSUPPORTED, e, "expression <" + t + "> is not supported by this loader");
     }
@@ -401,12 +429,13 @@ struct Builder {
                 else if (k->name == "factors") for (auto& f : k->kids) if (f->name == "factor") factor_nodes.push_back(f.get());
             }
             if (!distr || !first_kid(*distr)) bad(CANOPY_E_VALIDITY, n, "CCF group " + c.name + " has no distribution");
-            const double q = eval(*first_kid(*distr), EvalCtx{});
+            const Ex qx = ev(*first_kid(*distr), EvalCtx{});
+            const double q = qx.v;
             if (!(q >= 0 && q <= 1)) bad(CANOPY_E_DOMAIN, *distr, "Invalid probability value for CCF group distribution " + c.name);
-            for (uint32_t b : c.members) { basics[b].p = q; basics[b].has_p = true; }  // AddDistribution, ccf_group.h:127-130
+            for (uint32_t b : c.members) { basics[b].p = q; basics[b].node = qx.id; basics[b].has_p = true; }  // AddDistribution, ccf_group.h:127-130
             // AddFactor, ccf_group.h:144-175
             const int min_level = c.model == "beta-factor" ? n_mem : c.model == "MGL" ? 2 : 1;
-            std::vector<std::pair<int, double>> factors;  // index = level - min_level; level 0 = missing
+            std::vector<std::pair<int, Ex>> factors;  // index = level - min_level; level 0 = missing
             int prev_level = 0;
             for (const XNode* f : factor_nodes) {
                 int level = prev_level ? prev_level + 1 : min_level;
@@ -416,39 +445,44 @@ struct Builder {
                 if (level > n_mem) bad(CANOPY_E_VALIDITY, *f, "The CCF factor level " + std::to_string(level) + " is more than the number of members (" + std::to_string(n_mem) + ") in " + c.name);
                 const size_t idx = (size_t)(level - min_level);
                 if (idx < factors.size() && factors[idx].first) bad(CANOPY_E_VALIDITY, *f, "Redefinition of CCF factor for level " + std::to_string(level) + " in " + c.name);
-                if (idx >= factors.size()) factors.resize(idx + 1, {0, 0.0});
+                if (idx >= factors.size()) factors.resize(idx + 1, {0, Ex{0.0, 0u}});
                 if (!first_kid(*f)) bad(CANOPY_E_VALIDITY, *f, "CCF factor without an expression");
-                const double v = eval(*first_kid(*f), EvalCtx{});
-                if (!(v >= 0 && v <= 1)) bad(CANOPY_E_DOMAIN, *f, "Invalid probability value for CCF group factor in " + c.name);
+                const Ex v = ev(*first_kid(*f), EvalCtx{});
+                if (!(v.v >= 0 && v.v <= 1)) bad(CANOPY_E_DOMAIN, *f, "Invalid probability value for CCF group factor in " + c.name);
                 factors[idx] = {level, v};
                 prev_level = level;
             }
             if (factors.empty()) bad(CANOPY_E_VALIDITY, n, "CCF group " + c.name + " has no factors");
             for (auto& f : factors) if (!f.first) bad(CANOPY_E_VALIDITY, n, "Missing some CCF factors in " + c.name);  // ccf_group.h:195-197
-            // CalculateProbabilities of the four models: (level, probability of ONE event of that level)
-            std::vector<std::pair<int, double>> probs;
+            // CalculateProbabilities of the four models: (level, probability of ONE event of that level), built as tape
+            // expressions over the distribution and the factors so that sampled deviates flow through them
+            auto mul = [&](Ex a, Ex b) { return emit(X_MUL, {a, b}, a.v * b.v); };
+            auto one_minus = [&](Ex a) { return emit(X_SUB, {konst(1.0), a}, 1.0 - a.v); };
+            std::vector<std::pair<int, Ex>> probs;
             const int max_level = factors.back().first;
             if (c.model == "beta-factor") {  // ccf_group.h:330-350
-                probs.emplace_back(1, (1.0 - factors[0].second) * q);
-                probs.emplace_back(factors[0].first, factors[0].second * q);
+                probs.emplace_back(1, mul(one_minus(factors[0].second), qx));
+                probs.emplace_back(factors[0].first, mul(factors[0].second, qx));
             } else if (c.model == "MGL") {  // ccf_group.h:357-381
                 for (int i = 0; i < max_level; ++i) {
-                    double v = combination_reciprocal(n_mem - 1, i);
-                    for (int j = 0; j < i; ++j) v *= factors[j].second;
-                    if (i < max_level - 1) v *= 1.0 - factors[i].second;
-                    probs.emplace_back(i + 1, v * q);
+                    Ex v = konst(combination_reciprocal(n_mem - 1, i));
+                    for (int j = 0; j < i; ++j) v = mul(v, factors[j].second);
+                    if (i < max_level - 1) v = mul(v, one_minus(factors[i].second));
+                    probs.emplace_back(i + 1, mul(v, qx));
                 }
             } else if (c.model == "alpha-factor") {  // ccf_group.h:388-416
-                double sum = 0;
-                for (auto& f : factors) sum += f.first * f.second;
-                if (sum == 0) bad(CANOPY_E_DOMAIN, n, "alpha factors of " + c.name + " sum to 0");
-                for (int i = 0; i < max_level; ++i)
-                    probs.emplace_back(i + 1, (i + 1) * combination_reciprocal(n_mem - 1, i) * (factors[i].second / sum) * q);
+                Ex sum = konst(0.0);
+                for (auto& f : factors) sum = emit(X_ADD, {sum, mul(konst((double)f.first), f.second)}, sum.v + f.first * f.second.v);
+                if (sum.v == 0) bad(CANOPY_E_DOMAIN, n, "alpha factors of " + c.name + " sum to 0");
+                for (int i = 0; i < max_level; ++i) {
+                    const Ex frac = emit(X_DIV, {factors[i].second, sum}, factors[i].second.v / sum.v);
+                    probs.emplace_back(i + 1, mul(mul(konst((i + 1) * combination_reciprocal(n_mem - 1, i)), frac), qx));
+                }
             } else {  // phi-factor, ccf_group.h:422-455
                 double sum = 0;
-                for (auto& f : factors) sum += f.second;
+                for (auto& f : factors) sum += f.second.v;
                 if (std::fabs(sum - 1.0) > 1e-4) bad(CANOPY_E_VALIDITY, n, "The factors for Phi model CCF must sum to 1.");
-                for (auto& f : factors) probs.emplace_back(f.first, f.second * q);
+                for (auto& f : factors) probs.emplace_back(f.first, mul(f.second, qx));
             }
             if (!opts.ccf_analysis) continue;
             // ApplyModel, ccf_group.h:215-260: proxy OR gate per member over the CCF events that contain it
@@ -461,7 +495,7 @@ struct Builder {
             }
             for (auto& lp : probs) {
                 const int level = lp.first;
-                if (!(lp.second >= 0 && lp.second <= 1)) bad(CANOPY_E_DOMAIN, n, "CCF event probability outside [0, 1] in " + c.name);
+                if (!(lp.second.v >= 0 && lp.second.v <= 1)) bad(CANOPY_E_DOMAIN, n, "CCF event probability outside [0, 1] in " + c.name);
                 std::vector<int> comb(level);
                 for (int i = 0; i < level; ++i) comb[i] = i;
                 for (;;) {  // combinations in lexicographic order (algorithm.h:214-221 for_each_combination)
@@ -469,7 +503,7 @@ struct Builder {
                     for (int i = 0; i < level; ++i) nm += (i ? " " : "") + basics[c.members[comb[i]]].name;
                     nm += "]";
                     if (sym.count(nm)) bad(CANOPY_E_VALIDITY, n, "Duplicate Element Error: Redefinition of event: " + nm);
-                    BasicDef b; b.name = nm; b.p = lp.second; b.has_p = true;
+                    BasicDef b; b.name = nm; b.p = lp.second.v; b.node = lp.second.id; b.has_p = true;
                     const uint32_t bi = (uint32_t)basics.size();
                     basics.push_back(b);
                     for (int i = 0; i < level; ++i) gates[proxy[comb[i]]].args.push_back(ArgRef{ArgRef::kBasic, false, bi});
@@ -561,7 +595,8 @@ struct Builder {
     using HouseCtx = std::map<uint32_t, bool>;  // set-house-event overrides in force on the path
     struct PathCollector {
         std::vector<ArgRef> formulas;  // gates collected along the path (conjoined)
-        double expr = 1.0;             // product of the collected expressions
+        double expr = 1.0;             // product of the collected expressions ...
+        uint32_t expr_node = 0;        // ... and its tape node (valid iff has_expr)
         bool has_expr = false;
         HouseCtx house;
     };
@@ -644,7 +679,9 @@ struct Builder {
         } else if (t == "collect-expression") {
             const XNode* e = first_kid(ins);
             if (!e) bad(CANOPY_E_VALIDITY, ins, "<collect-expression> needs an expression");
-            pc.expr *= eval(*e, cx); pc.has_expr = true;
+            const Ex x = ev(*e, cx);
+            if (pc.has_expr) { const Ex prod = emit(X_MUL, {Ex{pc.expr, pc.expr_node}, x}, pc.expr * x.v); pc.expr = prod.v; pc.expr_node = prod.id; }
+            else { pc.expr = x.v; pc.expr_node = x.id; pc.has_expr = true; }
         } else if (t == "collect-formula") {
             const XNode* f = first_kid(ins);
             if (!f) bad(CANOPY_E_VALIDITY, ins, "<collect-formula> needs a formula");
@@ -736,7 +773,7 @@ struct Builder {
                     const std::string tag = ie.first + "." + sq + "#" + std::to_string(pi++);
                     if (pc.has_expr) {  // the product of the collected expressions becomes one more basic event
                         if (!(pc.expr >= 0 && pc.expr <= 1)) throw Error(CANOPY_E_DOMAIN, "Invalid probability value " + std::to_string(pc.expr) + " collected on a path to sequence " + sq);
-                        BasicDef b; b.name = "__expr_" + tag; b.p = pc.expr; b.has_p = true;
+                        BasicDef b; b.name = "__expr_" + tag; b.p = pc.expr; b.node = pc.expr_node; b.has_p = true;
                         basics.push_back(b);
                         conj.push_back(ArgRef{ArgRef::kBasic, false, (uint32_t)basics.size() - 1});
                     }
@@ -755,7 +792,7 @@ struct Builder {
         check_cycles();
         walk_event_trees();
         const uint32_t B = (uint32_t)basics.size(), G = (uint32_t)gates.size();
-        m.p.resize(B); m.basic_names.resize(B);
+        m.p.resize(B); m.p_node.resize(B); m.basic_names.resize(B);
         for (uint32_t e = 0; e < B; ++e) {
             BasicDef& b = basics[e];
             m.basic_names[e] = b.name;
@@ -763,10 +800,11 @@ struct Builder {
                 // a basic event never given an expression cannot be quantified; the reference reports it when
                 // the probability analysis asks for p() (event.h:93-96 asserts the expression)
                 if (!b.body) throw Error(CANOPY_E_VALIDITY, "basic event " + b.name + " has no expression");
-                b.p = eval(*b.body, EvalCtx{});
+                const Ex x = ev(*b.body, EvalCtx{});
+                b.p = x.v; b.node = x.id;
             }
             if (!(b.p >= 0.0 && b.p <= 1.0)) throw Error(CANOPY_E_DOMAIN, "Invalid probability value for " + b.name);  // event.cpp:27-33
-            m.p[e] = b.p;
+            m.p[e] = b.p; m.p_node[e] = b.node;
         }
         m.op.resize(G); m.kmin.resize(G); m.kmax.resize(G); m.gate_names.resize(G);
         m.child_off.assign(1, 0);

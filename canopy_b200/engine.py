@@ -240,16 +240,101 @@ class Session:
         return s
 
 
-def uncertainty(graph: Graph, settings: Settings, sample_p, n_outer: int, device: int = 0):
-    """Parameter-uncertainty outer loop (SURVEY.md 8f-4; reference Settings::uncertainty_analysis, settings.h:281-295):
-    for each epistemic trial k draw basic-event probabilities with `sample_p(k) -> float64[n_basic]`, re-quantise the
-    thresholds of ONE lowered plan (canopy_plan_update_p) and rerun the inner Monte Carlo on a disjoint counter
-    range.  Returns dict(p=[n_outer, n_tallies], mean, std, quantiles 5/50/95 per output)."""
+# canopy_deviate_kind (include/canopy.h)
+DEV_CONSTANT, DEV_UNIFORM, DEV_NORMAL, DEV_LOGNORMAL, DEV_LOGNORMAL_EF, DEV_GAMMA, DEV_BETA, DEV_HISTOGRAM = range(8)
+
+
+class PSource:
+    """Probability source of the uncertainty loop (canopy_psource): BasicEvent::p() of every event as the mean
+    (Expression::value()) or as the trial-th joint draw of all random deviates (Expression::Sample()/Reset(),
+    reference expression.h:98-117, expr/random_deviate.h).  Built from a loaded MEF model (`load_mef` leaves one in
+    Graph.meta["psource"]) or from one distribution per event: tuples (kind, a, b[, c]) or
+    (DEV_HISTOGRAM, bounds, weights)."""
+
+    def __init__(self, handle):
+        self._h = handle
+        nb, nd = C.c_uint32(), C.c_uint32()
+        _lib.check(_lib.lib().canopy_psource_info(self._h, C.byref(nb), C.byref(nd)))
+        self.n_basic, self.n_deviates = int(nb.value), int(nd.value)
+
+    @classmethod
+    def from_deviates(cls, dists) -> "PSource":
+        arr = (_lib.CDeviate * max(len(dists), 1))()
+        keep = []
+        for i, d in enumerate(dists):
+            arr[i].kind = int(d[0])
+            if d[0] == DEV_HISTOGRAM:
+                bounds = np.ascontiguousarray(d[1], dtype=np.float64)
+                weights = np.ascontiguousarray(d[2], dtype=np.float64)
+                if bounds.shape[0] != weights.shape[0] + 1:
+                    raise ValueError("histogram: need len(bounds) == len(weights) + 1")
+                keep += [bounds, weights]
+                arr[i].n_bins = weights.shape[0]
+                arr[i].bounds = bounds.ctypes.data_as(C.POINTER(C.c_double))
+                arr[i].weights = weights.ctypes.data_as(C.POINTER(C.c_double))
+            else:
+                vals = list(d[1:]) + [0.0, 0.0, 0.0]
+                arr[i].a, arr[i].b, arr[i].c = float(vals[0]), float(vals[1]), float(vals[2])
+        h = C.c_void_p()
+        _lib.check(_lib.lib().canopy_psource_from_deviates(arr, len(dists), C.byref(h)))
+        return cls(h)
+
+    def mean(self) -> np.ndarray:
+        out = np.zeros(max(self.n_basic, 1), dtype=np.float64)
+        _lib.check(_lib.lib().canopy_psource_mean(self._h, out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out[: self.n_basic]
+
+    def sample(self, seed: int, trial: int) -> np.ndarray:
+        out = np.zeros(max(self.n_basic, 1), dtype=np.float64)
+        _lib.check(_lib.lib().canopy_psource_sample(self._h, int(seed), int(trial), out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out[: self.n_basic]
+
+    def close(self):
+        if self._h:
+            _lib.lib().canopy_psource_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def uncertainty(graph: Graph, settings: Settings, source, n_outer: int, device: int = 0, deviate_seed: int | None = None,
+                num_quantiles: int = 20, num_bins: int = 20):
+    """Parameter-uncertainty outer loop (SURVEY.md 8f-4; reference Settings::uncertainty_analysis, settings.h:281-295).
+    `source` is a PSource: every trial draws all deviates (counter-based, canopy_psource_sample), re-quantises the
+    thresholds of ONE lowered plan on the device and reruns the inner Monte Carlo of settings.num_trials samples on a
+    disjoint counter range, all inside canopy_uncertainty_run.  A callable `source(k) -> float64[n_basic]` is also
+    accepted (probabilities drawn by the caller; same loop through canopy_plan_update_p).
+    Returns dict(p=[n_outer, n_tallies], mean, std, ci_lo, ci_hi, error_factor, quantiles=[n_tallies, num_quantiles],
+    bin_edges, bin_counts, q05, q50, q95)."""
     settings.validate()
-    out = []
     with Plan(graph, settings.tally_all_gates, settings.threshold_bits, settings.sampler) as plan:
+        nt = plan.n_tallies
+        if isinstance(source, PSource):
+            o = plan._opts(settings.seed, settings.sample_begin, settings.num_trials, device, settings.batch_size, None,
+                           settings.overlap, False)
+            u = _lib.CUncertaintyOpts()
+            u.n_trials, u.first_trial = int(n_outer), 0
+            u.seed = int(settings.seed if deviate_seed is None else deviate_seed)
+            u.num_quantiles, u.num_bins = int(num_quantiles), int(num_bins)
+            stats = (_lib.CUncertaintyStats * max(nt, 1))()
+            quant = np.zeros((max(nt, 1), num_quantiles)); edges = np.zeros((max(nt, 1), num_bins + 1))
+            counts = np.zeros((max(nt, 1), num_bins), dtype=np.uint64); p = np.zeros((n_outer, max(nt, 1)))
+            dp = C.POINTER(C.c_double)
+            _lib.check(_lib.lib().canopy_uncertainty_run(plan._h, source._h, C.byref(o), C.byref(u), stats,
+                                                         quant.ctypes.data_as(dp), edges.ctypes.data_as(dp),
+                                                         counts.ctypes.data_as(C.POINTER(C.c_uint64)), p.ctypes.data_as(dp)))
+            p = p[:, :nt]
+            f = lambda name: np.array([getattr(stats[i], name) for i in range(nt)])
+            return dict(p=p, mean=f("mean"), std=f("sigma"), ci_lo=f("ci_lo"), ci_hi=f("ci_hi"), error_factor=f("error_factor"),
+                        quantiles=quant[:nt], bin_edges=edges[:nt], bin_counts=counts[:nt],
+                        q05=np.quantile(p, 0.05, axis=0), q50=np.quantile(p, 0.5, axis=0), q95=np.quantile(p, 0.95, axis=0))
+        out = []
         for k in range(n_outer):
-            plan.update_p(sample_p(k))
+            plan.update_p(source(k))
             t, _ = plan.run(settings.num_trials, settings.seed, settings.sample_begin + k * settings.num_trials, device,
                             settings.batch_size, overlap=settings.overlap)
             out.append(t.astype(np.float64) / settings.num_trials)
@@ -328,6 +413,9 @@ def load_mef(paths=None, text: str | None = None, ccf_analysis: bool = False, mi
                   basic_names=[L.canopy_model_basic_name(h, i).decode() for i in range(d.n_basic)],
                   gate_names=[L.canopy_model_gate_name(h, i).decode() for i in range(d.n_gates)])
         g.meta["root_names"] = [L.canopy_model_root_name(h, i).decode() for i in range(d.n_roots)]
+        ps = C.c_void_p()
+        _lib.check(L.canopy_psource_from_model(h, C.byref(ps)))
+        g.meta["psource"] = PSource(ps)   # the model's expressions: mean and sampled probabilities (uncertainty loop)
         return g
     finally:
         L.canopy_model_destroy(h)

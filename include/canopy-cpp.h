@@ -187,6 +187,64 @@ class Plan {
     canopy_plan_stats stats_{};
 };
 
+/// Probability source of the parameter-uncertainty loop (canopy_psource): BasicEvent::p() of every event as the mean
+/// (Expression::value()) or as one joint draw of all random deviates (Expression::Sample()/Reset(), reference
+/// expression.h:98-117; the deviates of expr/random_deviate.h).
+class ProbabilitySource {
+  public:
+    explicit ProbabilitySource(const std::vector<canopy_deviate>& dist) {
+        canopy_psource* s = nullptr;
+        check(canopy_psource_from_deviates(dist.data(), (std::uint32_t)dist.size(), &s));
+        src_.reset(s);
+    }
+    explicit ProbabilitySource(const canopy_model* model) {
+        canopy_psource* s = nullptr;
+        check(canopy_psource_from_model(model, &s));
+        src_.reset(s);
+    }
+    std::uint32_t n_basic() const { std::uint32_t n = 0; check(canopy_psource_info(src_.get(), &n, nullptr)); return n; }
+    std::uint32_t n_deviates() const { std::uint32_t n = 0; check(canopy_psource_info(src_.get(), nullptr, &n)); return n; }
+    std::vector<double> mean() const { std::vector<double> p(n_basic()); check(canopy_psource_mean(src_.get(), p.data())); return p; }
+    std::vector<double> sample(std::uint64_t seed, std::uint64_t trial) const {
+        std::vector<double> p(n_basic());
+        check(canopy_psource_sample(src_.get(), seed, trial, p.data()));
+        return p;
+    }
+    const canopy_psource* get() const noexcept { return src_.get(); }
+
+  private:
+    struct Deleter { void operator()(canopy_psource* p) const noexcept { canopy_psource_destroy(p); } };
+    std::unique_ptr<canopy_psource, Deleter> src_;
+};
+
+/// Result of the uncertainty analysis (reference Settings::uncertainty_analysis / num_quantiles / num_bins,
+/// settings.h:154-175,281-295), per output.
+struct UncertaintyResult {
+    std::uint32_t num_quantiles = 0, num_bins = 0;
+    std::vector<canopy_uncertainty_stats> stats;   ///< [n_tallies]
+    std::vector<double> quantiles;                 ///< [n_tallies][num_quantiles]
+    std::vector<double> bin_edges;                 ///< [n_tallies][num_bins + 1]
+    std::vector<std::uint64_t> bin_counts;         ///< [n_tallies][num_bins]
+    std::vector<double> p_hat;                     ///< [n_trials][n_tallies]
+};
+/// `n_outer` epistemic trials of `s.num_trials` samples each on one lowered plan (canopy_uncertainty_run).
+inline UncertaintyResult uncertainty(Plan& plan, const ProbabilitySource& src, const McSettings& s, std::uint64_t n_outer,
+                                     std::uint64_t deviate_seed, std::uint32_t num_quantiles = 20, std::uint32_t num_bins = 20) {
+    canopy_mc_opts o;
+    canopy_mc_opts_default(&o);
+    o.seed = s.seed; o.sample_begin = s.sample_begin; o.n_samples = s.num_trials; o.device = s.device; o.batch_slabs = s.batch_size;
+    canopy_uncertainty_opts u{};
+    u.n_trials = n_outer; u.seed = deviate_seed; u.num_quantiles = num_quantiles; u.num_bins = num_bins;
+    const std::size_t nt = plan.stats().n_tallies;
+    UncertaintyResult r;
+    r.num_quantiles = num_quantiles; r.num_bins = num_bins;
+    r.stats.resize(nt); r.quantiles.resize(nt * num_quantiles); r.bin_edges.resize(nt * (num_bins + 1));
+    r.bin_counts.resize(nt * num_bins); r.p_hat.resize(n_outer * nt);
+    check(canopy_uncertainty_run(plan.get(), src.get(), &o, &u, r.stats.data(), r.quantiles.data(), r.bin_edges.data(),
+                                 r.bin_counts.data(), r.p_hat.data()));
+    return r;
+}
+
 /// Restartable run: (seed, next sample index, tallies) -- canopy_checkpoint + canopy_mc_run_resume.
 /// `record` and `tallies` are plain data and may be written to disk between calls.
 class Session {

@@ -330,6 +330,69 @@ CANOPY_API const char*   canopy_model_gate_name(const canopy_model* model, uint3
 CANOPY_API const char*   canopy_model_root_name(const canopy_model* model, uint32_t i);
 CANOPY_API void          canopy_model_destroy(canopy_model* model);
 
+/* ---- Parameter uncertainty ---------------------------------------------------------------------
+ * A probability source yields BasicEvent::p() of every event either as the mean (Expression::value(), expression.h:74)
+ * or as one joint draw of all random deviates (Expression::Sample()/Reset(), expression.h:98-117: each deviate is drawn
+ * once per trial and shared by every expression that refers to it, e.g. one <parameter> used by many events).  The six
+ * deviates of the reference (expr/random_deviate.h:25-264; DoSample has no body there) are drawn from counter-based
+ * Philox streams: draw j of deviate d in trial t is a pure function of (seed, t, d, j) -- csrc/expr_tape.h states the
+ * mapping and the algorithms.  From a loaded model the source carries every expression of the MEF file (parameters,
+ * arithmetic, exponential/GLM/Weibull/periodic-test, CCF factor models, collected event-tree expressions); from a flat
+ * list it is one independent distribution per basic event. */
+typedef enum canopy_deviate_kind {
+    CANOPY_DEV_CONSTANT = 0,     /* a = value                                                                    */
+    CANOPY_DEV_UNIFORM = 1,      /* a = min, b = max                         (UniformDeviate, random_deviate.h:46) */
+    CANOPY_DEV_NORMAL = 2,       /* a = mean, b = sigma                      (NormalDeviate, :70)                  */
+    CANOPY_DEV_LOGNORMAL = 3,    /* a = mu, b = sigma of the underlying normal (LognormalDeviate::Normal, :150)    */
+    CANOPY_DEV_LOGNORMAL_EF = 4, /* a = mean, b = error factor, c = confidence level (LognormalDeviate::Logarithmic, :133) */
+    CANOPY_DEV_GAMMA = 5,        /* a = k (shape), b = theta (scale)         (GammaDeviate, :171)                  */
+    CANOPY_DEV_BETA = 6,         /* a = alpha, b = beta                      (BetaDeviate, :195)                   */
+    CANOPY_DEV_HISTOGRAM = 7     /* bounds[n_bins + 1] strictly increasing, weights[n_bins] >= 0 (Histogram, :222) */
+} canopy_deviate_kind;
+typedef struct canopy_deviate {
+    int32_t  kind;               /* canopy_deviate_kind */
+    uint32_t n_bins;             /* histogram only */
+    double   a, b, c;
+    const double* bounds;        /* histogram only; read during the call */
+    const double* weights;
+} canopy_deviate;
+typedef struct canopy_psource canopy_psource;
+CANOPY_API canopy_status canopy_psource_from_model(const canopy_model* model, canopy_psource** out);
+CANOPY_API canopy_status canopy_psource_from_deviates(const canopy_deviate* dist, uint32_t n_basic, canopy_psource** out);
+CANOPY_API canopy_status canopy_psource_info(const canopy_psource* src, uint32_t* n_basic, uint32_t* n_deviates);
+CANOPY_API canopy_status canopy_psource_mean(const canopy_psource* src, double* p_out /* [n_basic] */);
+/* The trial-th joint draw, each probability clamped to [0, 1] (a deviate may leave it). */
+CANOPY_API canopy_status canopy_psource_sample(const canopy_psource* src, uint64_t seed, uint64_t trial,
+                                               double* p_out /* [n_basic] */);
+CANOPY_API void          canopy_psource_destroy(canopy_psource* src);
+
+/* Outer loop (Settings::uncertainty_analysis, settings.h:281-295): for trial t in [first_trial, first_trial + n_trials)
+ * draw every p, re-quantise the thresholds of `plan` on its device (canopy_plan_update_p: same lowering, new thresholds
+ * and count tables, no new plan), run mc->n_samples samples [mc->sample_begin + (t - first_trial) n_samples, ...) so that
+ * the aleatory streams of different trials are disjoint, and record p_hat_t = tally / n_samples of every output.  A drawn
+ * probability is clamped into the sampled range (2^-threshold_bits, 1 - 2^-53) when the event is sampled at the mean, and
+ * ignored when the event is a constant at the mean (the lowering folded it).  The plan is left at the mean probabilities.
+ * Per output: mean and standard deviation over the trials, a 95 % normal interval of the mean, the error factor
+ * q95 / q50, num_quantiles quantiles (levels i / num_quantiles, i = 1 .. num_quantiles, as order statistics;
+ * Settings::num_quantiles, settings.h:154-163) and a histogram of num_bins equal bins over [min, max]
+ * (Settings::num_bins, settings.h:166-175). */
+typedef struct canopy_uncertainty_opts {
+    uint64_t n_trials;
+    uint64_t first_trial;
+    uint64_t seed;            /* of the deviates; the sample-level seed is mc->seed */
+    uint32_t num_quantiles;   /* 0 = 20, the reference default (settings.h:328) */
+    uint32_t num_bins;        /* 0 = 20 (settings.h:329) */
+    int32_t  reserved[4];
+} canopy_uncertainty_opts;
+typedef struct canopy_uncertainty_stats { double mean, sigma, ci_lo, ci_hi, error_factor, min, max; } canopy_uncertainty_stats;
+CANOPY_API canopy_status canopy_uncertainty_run(canopy_plan* plan, const canopy_psource* src, const canopy_mc_opts* mc,
+                                                const canopy_uncertainty_opts* opts,
+                                                canopy_uncertainty_stats* stats /* [n_tallies] */,
+                                                double* quantiles    /* [n_tallies][num_quantiles] or NULL */,
+                                                double* bin_edges    /* [n_tallies][num_bins + 1] or NULL */,
+                                                uint64_t* bin_counts /* [n_tallies][num_bins] or NULL */,
+                                                double* p_hat        /* [n_trials][n_tallies] or NULL */);
+
 CANOPY_API const char* canopy_last_error(void);   /* thread-local; valid until the next call on this thread */
 CANOPY_API const char* canopy_status_string(canopy_status s);
 CANOPY_API uint32_t    canopy_version(void);      /* major<<16 | minor */

@@ -14,5 +14,17 @@ int main() {
     std::printf("session: fingerprint %d done=%llu tallies=%zu\n", sess.record.plan_fingerprint == plan.fingerprint(),
                 (unsigned long long)sess.done(), sess.tallies.size());
     try { plan.update_p({0.1, 0.2, 1.0}); } catch (const canopy::Error& e) { std::printf("update_p: status %d\n", e.status()); }
+    {   // probability source of the uncertainty loop: host only up to the inner run
+        std::vector<canopy_deviate> d(3);
+        d[0].kind = CANOPY_DEV_UNIFORM; d[0].a = 0.05; d[0].b = 0.15;
+        d[1].kind = CANOPY_DEV_LOGNORMAL_EF; d[1].a = 0.2; d[1].b = 2.0; d[1].c = 0.95;
+        d[2].kind = CANOPY_DEV_CONSTANT; d[2].a = 0.3;
+        canopy::ProbabilitySource src(d);
+        const auto m = src.mean(), x = src.sample(1, 0), y = src.sample(1, 0), z = src.sample(1, 1);
+        std::printf("psource: n=%u deviates=%u mean_ok=%d repeat=%d fresh=%d\n", src.n_basic(), src.n_deviates(),
+                    m[0] == 0.1 && m[1] == 0.2 && m[2] == 0.3, x == y, x != z && z[2] == 0.3);
+        try { canopy::McSettings s; s.num_trials = 1000; canopy::uncertainty(plan, src, s, 2, 9); }
+        catch (const canopy::Error& e) { std::printf("uncertainty: status %d\n", e.status()); }
+    }
     return 0;
 }

@@ -20,8 +20,10 @@ def test_cpp_header_smoke(tmp_path):
     assert "validity: status 2" in out
     assert "session: fingerprint 1 done=0 tallies=2" in out
     assert "update_p: status 1" in out      # an event cannot turn constant without a new lowering
+    assert "psource: n=3 deviates=2 mean_ok=1 repeat=1 fresh=1" in out
     if not torch.cuda.is_available():
         assert "run: status 5" in out and "no CPU fallback" in out
+        assert "uncertainty: status 5" in out
 
 
 def test_c_header_is_plain_c(tmp_path):

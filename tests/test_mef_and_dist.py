@@ -98,7 +98,7 @@ BAD_XML = [
      "<define-basic-event name='a'><float value='0.2'/></define-basic-event></model-data></opsa-mef>", _lib.E_VALIDITY, "Duplicate"),
     ("<opsa-mef><model-data><define-basic-event name='a'><float value='1.5'/></define-basic-event></model-data></opsa-mef>",
      _lib.E_DOMAIN, "probability"),
-    ("<opsa-mef><model-data><define-basic-event name='a'><periodic-test/></define-basic-event></model-data></opsa-mef>",
+    ("<opsa-mef><model-data><define-basic-event name='a'><extern-function name='f'/></define-basic-event></model-data></opsa-mef>",
      _lib.E_UNSUPPORTED, "not supported"),
     ("<opsa-mef><define-fault-tree name='t'></opsa-mef>", _lib.E_IO, "mismatched"),
     ("<other/>", _lib.E_IO, "opsa-mef"),

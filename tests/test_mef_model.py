@@ -70,7 +70,8 @@ def test_expression_means_and_parameters():
     ("<div><float value='1'/><float value='0'/></div>", _lib.E_DOMAIN, "Division by 0"),
     ("<exponential><float value='-1'/><float value='1'/></exponential>", _lib.E_DOMAIN, "rate of failure"),
     ("<exponential/>", _lib.E_VALIDITY, "takes 2"),
-    ("<periodic-test/>", _lib.E_UNSUPPORTED, "not supported"),
+    ("<periodic-test/>", _lib.E_VALIDITY, "Invalid number of arguments for Periodic Test"),
+    ("<periodic-test>" + "<float value=\"1\"/>" * 11 + "</periodic-test>", _lib.E_UNSUPPORTED, "not supported"),
     ("<histogram><float value='0.2'/><bin><float value='0.1'/><float value='1'/></bin></histogram>", _lib.E_VALIDITY, "strictly increasing"),
     ("<histogram><float value='0'/><bin><float value='0.1'/><float value='-1'/></bin></histogram>", _lib.E_VALIDITY, "negative"),
     ("<add><float value='0.8'/><float value='0.8'/></add>", _lib.E_DOMAIN, "probability"),
