@@ -20,8 +20,9 @@
 //     paths; along a path collect-formula instructions are conjoined, collect-expression instructions multiply
 //     into one extra basic event, set-house-event overrides apply to the formulas collected after them.
 // Not covered (CANOPY_E_UNSUPPORTED): nested formulas (the reference's Formula::Arg cannot hold them either,
-// formula.h:9-15), the 11-argument periodic-test, extern functions, alignments/substitutions, XInclude, private roles
-// (every name is looked up as written; a dotted reference falls back to its last segment).
+// formula.h:9-15), the 11-argument periodic-test, extern functions, alignments/substitutions, XInclude.
+// Roles: public / private elements, base paths of fault trees and nested components, and the reference's lookup order
+// (local scope, public id, full path) are followed (element.h:300-379, initializer.cpp:42-57,1378-1437).
 #include <algorithm>
 #include <cmath>
 #include <fstream>
@@ -50,11 +51,12 @@ struct GateDef {
     std::vector<ArgRef> args;
     int tree = -1;               // fault-tree ordinal, -1 for synthetic gates
     const XNode* body = nullptr; // <define-gate>, null for synthetic gates
+    std::string base_path;       // scope its formula's references are resolved in (initializer.cpp:483)
 };
-struct BasicDef { std::string name; const XNode* body = nullptr; double p = 0.0; bool has_p = false; int proxy_gate = -1; uint32_t node = 0; };  // node: tape node of p
+struct BasicDef { std::string name, base_path; const XNode* body = nullptr; double p = 0.0; bool has_p = false; int proxy_gate = -1; uint32_t node = 0; };  // node: tape node of p
 struct HouseDef { std::string name; bool state = false; };
-struct ParamDef { std::string name; const XNode* body = nullptr; double value = 0.0; int mark = 0; uint32_t node = 0; };
-struct CcfDef { std::string name, model; const XNode* node = nullptr; std::vector<uint32_t> members; };
+struct ParamDef { std::string name, base_path; const XNode* body = nullptr; double value = 0.0; int mark = 0; uint32_t node = 0; };
+struct CcfDef { std::string name, model, base_path; const XNode* node = nullptr; std::vector<uint32_t> members; };
 struct EventTreeDef {
     std::string name;
     const XNode* node = nullptr;
@@ -101,10 +103,6 @@ double parse_number(const XNode& n, const std::string& v) {
     if (end == v.c_str() || *end) bad(CANOPY_E_VALIDITY, n, "bad number '" + v + "'");
     return x;
 }
-std::string last_segment(const std::string& s) {
-    const size_t p = s.rfind('.');
-    return p == std::string::npos ? s : s.substr(p + 1);
-}
 double combination_reciprocal(int n, int k) {  // 1 / C(n, k), algorithm.h:230-241
     if (n - k > k) k = n - k;
     double r = 1;
@@ -121,6 +119,12 @@ struct Builder {
     std::vector<HouseDef> houses;
     std::vector<ParamDef> params;
     std::map<std::string, uint32_t> param_idx;
+    // Roles (element.h:300-379, initializer.cpp:42-57,98-106): an element's id is its name when public and
+    // base_path.name when private; `sym` / `param_idx` are the id tables (Model::table<T>), `path_sym` / `param_path`
+    // the full-path tables (Initializer::path_gates_ ...), which hold public and private elements alike.
+    std::map<std::string, Sym> path_sym;
+    std::map<std::string, uint32_t> param_path;
+    std::string cur_base;   // base path of the element whose body is being read (scope of its references)
     std::vector<CcfDef> ccfs;
     std::vector<EventTreeDef> trees;
     std::map<std::string, uint32_t> tree_idx;
@@ -132,18 +136,35 @@ struct Builder {
     explicit Builder(canopy_model& model, const MefOpts& o) : m(model), opts(o) {}
 
     // ---- pass 1: register names ---------------------------------------------------------------------
-    void reg(const XNode& n, const std::string& nm, Kind k, uint32_t idx) {
-        if (!sym.emplace(nm, Sym{k, idx}).second)
-            bad(CANOPY_E_VALIDITY, n, "Duplicate Element Error: Redefinition of event: " + nm);  // model.h:151-155
+    static bool role_of(const XNode& n, bool container_public) {  // GetRole, initializer.cpp:42-57
+        const std::string* r = n.attr("role");
+        if (!r || r->empty()) return container_public;
+        if (*r != "public" && *r != "private") bad(CANOPY_E_VALIDITY, n, "bad role '" + *r + "'");
+        return *r == "public";
     }
-    uint32_t add_basic(const XNode& n, const std::string& nm, const XNode* body) {
-        reg(n, nm, Kind::kBasic, (uint32_t)basics.size());
-        BasicDef b; b.name = nm; b.body = body;
+    static std::string make_id(const std::string& nm, const std::string& base, bool is_public) {  // Id::id(), element.h:341-344
+        return is_public ? nm : base + "." + nm;
+    }
+    // Returns the id.  `in_path_table`: CCF members are added to the model only (initializer.cpp:1324-1339).
+    std::string reg(const XNode& n, const std::string& nm, Kind k, uint32_t idx, const std::string& base, bool is_public,
+                    bool in_path_table = true) {
+        if (!is_public && base.empty()) bad(CANOPY_E_VALIDITY, n, "Elements cannot be private at model scope: " + nm);  // element.h: Role ctor
+        const std::string id = make_id(nm, base, is_public);
+        if (!sym.emplace(id, Sym{k, idx}).second)
+            bad(CANOPY_E_VALIDITY, n, "Duplicate Element Error: Redefinition of event: " + id);  // model.h:151-155
+        if (in_path_table && !base.empty()) path_sym.emplace(base + "." + nm, Sym{k, idx});
+        return id;
+    }
+    uint32_t add_basic(const XNode& n, const std::string& nm, const XNode* body, const std::string& base, bool is_public,
+                       bool in_path_table = true) {
+        BasicDef b; b.body = body; b.base_path = base;
+        b.name = reg(n, nm, Kind::kBasic, (uint32_t)basics.size(), base, is_public, in_path_table);
         basics.push_back(b);
         return (uint32_t)basics.size() - 1;
     }
-    void register_ccf(const XNode& n) {  // initializer.cpp:375-401, 1324-1339
-        CcfDef c; c.name = need_name(n); c.model = need_attr(n, "model"); c.node = &n;
+    void register_ccf(const XNode& n, const std::string& base, bool container_public) {  // initializer.cpp:375-401, 1324-1339
+        const bool is_public = role_of(n, container_public);
+        CcfDef c; c.name = make_id(need_name(n), base, is_public); c.model = need_attr(n, "model"); c.node = &n; c.base_path = base;
         if (c.model != "beta-factor" && c.model != "MGL" && c.model != "alpha-factor" && c.model != "phi-factor")
             bad(CANOPY_E_VALIDITY, n, "unknown CCF model '" + c.model + "'");
         for (auto& g : ccfs) if (g.name == c.name) bad(CANOPY_E_VALIDITY, n, "Duplicate Element Error: Redefinition of CCF group: " + c.name);
@@ -152,39 +173,42 @@ struct Builder {
         if (!mem) bad(CANOPY_E_VALIDITY, n, "CCF group " + c.name + " has no <members>");
         for (auto& e : mem->kids) {
             if (e->name != "basic-event") bad(CANOPY_E_VALIDITY, *e, "CCF members must be <basic-event>");
-            c.members.push_back(add_basic(*e, need_name(*e), nullptr));
+            c.members.push_back(add_basic(*e, need_name(*e), nullptr, base, is_public, false));  // the group's base path and role
         }
         ccfs.push_back(c);
     }
-    void register_container(const XNode& c, int tree) {  // initializer.cpp:712-770
+    void register_container(const XNode& c, int tree, const std::string& base, bool container_public) {  // initializer.cpp:712-770
         for (auto& k : c.kids) {
             const std::string& t = k->name;
             if (t == "define-gate") {
-                reg(*k, need_name(*k), Kind::kGate, (uint32_t)gates.size());
-                GateDef g; g.name = need_name(*k); g.body = k.get(); g.tree = tree;
+                GateDef g; g.body = k.get(); g.tree = tree; g.base_path = base;
+                g.name = reg(*k, need_name(*k), Kind::kGate, (uint32_t)gates.size(), base, role_of(*k, container_public));
                 gates.push_back(g);
             } else if (t == "define-basic-event") {
-                add_basic(*k, need_name(*k), first_kid(*k));
+                add_basic(*k, need_name(*k), first_kid(*k), base, role_of(*k, container_public));
             } else if (t == "define-house-event") {
-                reg(*k, need_name(*k), Kind::kHouse, (uint32_t)houses.size());
-                HouseDef h; h.name = need_name(*k);
+                HouseDef h;
+                h.name = reg(*k, need_name(*k), Kind::kHouse, (uint32_t)houses.size(), base, role_of(*k, container_public));
                 if (const XNode* b = first_kid(*k)) {
                     if (b->name != "constant" || !b->attr("value")) bad(CANOPY_E_VALIDITY, *b, "house event body must be <constant value=.../>");
                     h.state = parse_bool(*b, *b->attr("value"));
                 }
                 houses.push_back(h);
             } else if (t == "define-parameter") {
-                const std::string& nm = need_name(*k);
+                const bool is_public = role_of(*k, container_public);
+                if (!is_public && base.empty()) bad(CANOPY_E_VALIDITY, *k, "Elements cannot be private at model scope: " + need_name(*k));
+                const std::string nm = make_id(need_name(*k), base, is_public);
                 if (!param_idx.emplace(nm, (uint32_t)params.size()).second)
                     bad(CANOPY_E_VALIDITY, *k, "Duplicate Element Error: Redefinition of parameter: " + nm);
-                ParamDef p; p.name = nm; p.body = first_kid(*k);
+                if (!base.empty()) param_path.emplace(base + "." + need_name(*k), (uint32_t)params.size());
+                ParamDef p; p.name = nm; p.base_path = base; p.body = first_kid(*k);
                 if (!p.body) bad(CANOPY_E_VALIDITY, *k, "parameter " + nm + " has no expression");
                 params.push_back(p);
             } else if (t == "define-CCF-group") {
-                register_ccf(*k);
-            } else if (t == "define-component") {
-                need_name(*k);
-                register_container(*k, tree);
+                register_ccf(*k, base, container_public);
+            } else if (t == "define-component") {  // DefineComponent, initializer.cpp:718-726: nested scope, inherited role
+                if (base.empty()) bad(CANOPY_E_VALIDITY, *k, "<define-component> outside a fault tree");
+                register_container(*k, tree, base + "." + need_name(*k), role_of(*k, container_public));
             } else if (is_meta(*k)) {
             } else {
                 bad(CANOPY_E_UNSUPPORTED, *k, "unexpected element <" + t + ">");
@@ -213,9 +237,9 @@ struct Builder {
         if (root.name != "opsa-mef") bad(CANOPY_E_IO, root, "document element must be <opsa-mef>");
         for (auto& k : root.kids) {
             const std::string& t = k->name;
-            if (t == "define-fault-tree") { need_name(*k); register_container(*k, n_fault_trees++); }
-            else if (t == "model-data") register_container(*k, -1);
-            else if (t == "define-CCF-group") register_ccf(*k);
+            if (t == "define-fault-tree") register_container(*k, n_fault_trees++, need_name(*k), true);  // a fault tree is public; its name opens the scope
+            else if (t == "model-data") register_container(*k, -1, "", true);
+            else if (t == "define-CCF-group") register_ccf(*k, "", true);
             else if (t == "define-event-tree") register_event_tree(*k);
             else if (t == "define-initiating-event") {
                 const std::string& nm = need_name(*k);
@@ -241,14 +265,22 @@ struct Builder {
     }
     Ex konst(double c) { return Ex{c, m.tape.constant(c)}; }
     Ex parameter_value(const XNode& at, const std::string& name) {
-        auto it = param_idx.find(name);
-        if (it == param_idx.end()) it = param_idx.find(last_segment(name));
+        // GetEntity, initializer.cpp:1378-1403: the local scope first, then the public id, or the full path as written
+        auto it = param_idx.end();
+        if (!cur_base.empty()) { it = param_path.find(cur_base + "." + name); if (it == param_path.end()) it = param_idx.end(); }
+        if (it == param_idx.end()) {
+            if (name.find('.') == std::string::npos) it = param_idx.find(name);
+            else { it = param_path.find(name); if (it == param_path.end()) it = param_idx.end(); }
+        }
         if (it == param_idx.end()) bad(CANOPY_E_VALIDITY, at, "Undefined Element Error: parameter " + name);
         ParamDef& p = params[it->second];
         if (p.mark == 2) return Ex{p.value, p.node};   // one node per parameter: sampled once per trial, shared by its users
         if (p.mark == 1) bad(CANOPY_E_CYCLE, at, "Cycle Error: parameter " + name + " refers to itself");  // cycle.h:219-229
         p.mark = 1;
+        const std::string saved = cur_base;
+        cur_base = p.base_path;   // a parameter's own references resolve in ITS scope (initializer.cpp:499-503)
         const Ex x = ev(*p.body, EvalCtx{});
+        cur_base = saved;
         p.value = x.v; p.node = x.id;
         p.mark = 2;
         return x;
@@ -419,6 +451,7 @@ struct Builder {
     void apply_ccf() {
         for (CcfDef& c : ccfs) {
             const XNode& n = *c.node;
+            cur_base = c.base_path;   // distribution and factors resolve in the group's scope (initializer.cpp:1341-1352)
             const int n_mem = (int)c.members.size();
             if (n_mem < 2) bad(CANOPY_E_VALIDITY, n, "CCF group must have at least 2 members: " + c.name);  // ccf_group.h:123-125
             const XNode* distr = nullptr;
@@ -484,6 +517,7 @@ struct Builder {
                 if (std::fabs(sum - 1.0) > 1e-4) bad(CANOPY_E_VALIDITY, n, "The factors for Phi model CCF must sum to 1.");
                 for (auto& f : factors) probs.emplace_back(f.first, mul(f.second, qx));
             }
+            cur_base.clear();
             if (!opts.ccf_analysis) continue;
             // ApplyModel, ccf_group.h:215-260: proxy OR gate per member over the CCF events that contain it
             std::vector<uint32_t> proxy(n_mem);
@@ -518,16 +552,30 @@ struct Builder {
     }
 
     // ---- formulas (initializer.cpp:772-851) --------------------------------------------------------------
+    // GetEvent, initializer.cpp:1416-1437: base_path.reference in the full-path table; else a reference without a dot is a
+    // public id, one with dots a full path.  (A typed reference -- <gate name=...> -- that finds an event of another
+    // kind is reported by the caller.)
+    const Sym* find_event(const std::string& ref) const {
+        if (!cur_base.empty()) {
+            auto it = path_sym.find(cur_base + "." + ref);
+            if (it != path_sym.end()) return &it->second;
+        }
+        if (ref.find('.') == std::string::npos) {
+            auto it = sym.find(ref);
+            return it == sym.end() ? nullptr : &it->second;
+        }
+        auto it = path_sym.find(ref);
+        return it == path_sym.end() ? nullptr : &it->second;
+    }
     ArgRef event_ref(const XNode& a, bool complement) {
         const std::string* type = a.attr("type");
         const std::string et = type && !type->empty() ? *type : a.name;
         if (et != "event" && et != "gate" && et != "basic-event" && et != "house-event")
             bad(CANOPY_E_UNSUPPORTED, a, "formula argument <" + a.name + "> is not an event reference (nested formulas are not supported)");
         const std::string& nm = need_name(a);
-        auto it = sym.find(nm);
-        if (it == sym.end()) it = sym.find(last_segment(nm));
-        if (it == sym.end()) bad(CANOPY_E_VALIDITY, a, "Undefined Element Error: " + nm);
-        const Sym s = it->second;
+        const Sym* found = find_event(nm);
+        if (!found) bad(CANOPY_E_VALIDITY, a, "Undefined Element Error: " + nm);
+        const Sym s = *found;
         if ((et == "gate" && s.kind != Kind::kGate) || (et == "basic-event" && s.kind != Kind::kBasic) ||
             (et == "house-event" && s.kind != Kind::kHouse))
             bad(CANOPY_E_VALIDITY, a, "Undefined Element Error: " + nm + " is not a " + et);
@@ -571,7 +619,9 @@ struct Builder {
         for (uint32_t g = 0; g < n_xml_gates; ++g) {
             const XNode* f = first_kid(*gates[g].body);
             if (!f) bad(CANOPY_E_VALIDITY, *gates[g].body, "gate " + gates[g].name + " has no formula");
+            cur_base = gates[g].base_path;
             parse_formula(*f, gates[g]);
+            cur_base.clear();
         }
     }
     void check_cycles() {  // cycle.h:114-131 (DFS marks); the event-tree walk below recurses over the gate graph
@@ -694,11 +744,11 @@ struct Builder {
         } else if (t == "block") {
             for (const XNode* k : kids_of(ins)) exec(*k, pc, w, in_sequence, linked);
         } else if (t == "set-house-event") {
-            auto it = sym.find(need_name(ins));
-            if (it == sym.end() || it->second.kind != Kind::kHouse) bad(CANOPY_E_VALIDITY, ins, "Undefined Element Error: house event " + need_name(ins));
+            const Sym* it = find_event(need_name(ins));   // event-tree instructions are read at model scope (initializer.cpp:950)
+            if (!it || it->kind != Kind::kHouse) bad(CANOPY_E_VALIDITY, ins, "Undefined Element Error: house event " + need_name(ins));
             const XNode* c = first_kid(ins);
             if (!c || c->name != "constant") bad(CANOPY_E_VALIDITY, ins, "<set-house-event> needs <constant value=.../>");
-            pc.house[it->second.idx] = parse_bool(*c, need_attr(*c, "value"));
+            pc.house[it->idx] = parse_bool(*c, need_attr(*c, "value"));
         } else bad(CANOPY_E_UNSUPPORTED, ins, "unknown instruction <" + t + ">");
     }
     void walk_branch(const EventTreeDef& et, const std::vector<const XNode*>& nodes, PathCollector pc, Walk& w, const XNode& at) {
@@ -800,7 +850,9 @@ struct Builder {
                 // a basic event never given an expression cannot be quantified; the reference reports it when
                 // the probability analysis asks for p() (event.h:93-96 asserts the expression)
                 if (!b.body) throw Error(CANOPY_E_VALIDITY, "basic event " + b.name + " has no expression");
+                cur_base = b.base_path;
                 const Ex x = ev(*b.body, EvalCtx{});
+                cur_base.clear();
                 b.p = x.v; b.node = x.id;
             }
             if (!(b.p >= 0.0 && b.p <= 1.0)) throw Error(CANOPY_E_DOMAIN, "Invalid probability value for " + b.name);  // event.cpp:27-33

@@ -291,3 +291,50 @@ def test_numeric_character_references_are_utf8():
     with pytest.raises(_lib.CanopyError) as ei:
         load_mef(text=model("<define-fault-tree name='f&#x110000;'/>"))
     assert ei.value.status == _lib.E_IO
+
+
+# ---- roles and scopes (element.h:300-379; initializer.cpp:42-57, 712-758, 1378-1437) -----------------------------------
+def test_private_roles_and_scoped_lookup():
+    """Two private events of the same name in different components are two nodes; a reference resolves in its local scope
+    first, then as a public id, then as a full path; a private element is not visible by its bare name elsewhere."""
+    xml = model(
+        "<define-fault-tree name='FT'>"
+        "<define-gate name='top'><and><gate name='A.g'/><gate name='B.g'/><basic-event name='shared'/></and></define-gate>"
+        "<define-component name='A' role='private'>"
+        "  <define-gate name='g'><or><basic-event name='pump'/><basic-event name='shared'/></or></define-gate>"
+        "  <define-basic-event name='pump'><parameter name='rate'/></define-basic-event>"
+        "  <define-parameter name='rate'><float value='0.125'/></define-parameter>"
+        "</define-component>"
+        "<define-component name='B' role='private'>"
+        "  <define-gate name='g'><or><basic-event name='pump'/><basic-event name='FT.A.pump'/></or></define-gate>"
+        "  <define-basic-event name='pump'><parameter name='rate'/></define-basic-event>"
+        "  <define-parameter name='rate'><float value='0.25'/></define-parameter>"
+        "</define-component>"
+        "<define-basic-event name='shared'><float value='0.5'/></define-basic-event>"
+        "</define-fault-tree>")
+    g = load_mef(text=xml)
+    assert sorted(g.basic_names) == ["FT.A.pump", "FT.B.pump", "shared"]          # ids: private = full path
+    assert sorted(g.gate_names) == ["FT.A.g", "FT.B.g", "top"]
+    p = dict(zip(g.basic_names, g.p))
+    assert p == {"FT.A.pump": 0.125, "FT.B.pump": 0.25, "shared": 0.5}           # each pump reads the rate of ITS scope
+    assert g.meta["root_names"] == ["top"]
+    # top = (pa | s) & (pb | pa) & s = s & (pa | pb)
+    ex = O.exact(g, False, 32)[0]
+    assert ex == pytest.approx(Q(0.5) * (1 - (1 - Q(0.125)) * (1 - Q(0.25))), rel=1e-12)
+    # a private element is not reachable by its bare name from another scope
+    bad = xml.replace("<basic-event name='FT.A.pump'/>", "<basic-event name='nosuch'/>").replace(
+        "<gate name='A.g'/>", "<gate name='g'/>")
+    with pytest.raises(_lib.CanopyError) as ei:
+        load_mef(text=bad)
+    assert ei.value.status == _lib.E_VALIDITY and "Undefined Element" in ei.value.message
+    # role attribute on a single element overrides the container's; public elements collide across components
+    dup = model("<define-fault-tree name='FT'><define-gate name='top'><or><basic-event name='e'/><basic-event name='C.e'/></or></define-gate>"
+                "<define-basic-event name='e'><float value='0.1'/></define-basic-event>"
+                "<define-component name='C'><define-basic-event name='e'><float value='0.2'/></define-basic-event></define-component>"
+                "</define-fault-tree>")
+    with pytest.raises(_lib.CanopyError) as ei:
+        load_mef(text=dup)
+    assert "Duplicate Element" in ei.value.message
+    ok = dup.replace("<define-basic-event name='e'><float value='0.2'/>", "<define-basic-event name='e' role='private'><float value='0.2'/>")
+    g2 = load_mef(text=ok)
+    assert sorted(g2.basic_names) == ["FT.C.e", "e"]
