@@ -186,7 +186,7 @@ def config_block(name, g, S, S_full, stats=None, n_step=None):
     return c
 
 
-def cpu_arm(graph, n_samples_hint: int, tally_all: bool, seconds_target: float = 12.0, spec: int = 0):
+def cpu_arm(graph, n_samples_hint: int, tally_all: bool, seconds_target: float = 12.0, spec: int = 0, bits: int = 32):
     """Bit-packed multi-threaded CPU port (oracle/) on a bounded sample of the same workload."""
     from oracle import oracle as O
     spec = spec or O.SPEC
@@ -194,13 +194,13 @@ def cpu_arm(graph, n_samples_hint: int, tally_all: bool, seconds_target: float =
     # size the sample from probes that are long enough to mean something (thread start-up dominates a 4096-sample call)
     probe, dt = 1 << 12, 0.0
     while True:
-        t0 = time.perf_counter(); O.mc_packed(graph, 1, 0, probe, tally_all, nthreads=cores, spec=spec); dt = time.perf_counter() - t0
+        t0 = time.perf_counter(); O.mc_packed(graph, 1, 0, probe, tally_all, bits=bits, nthreads=cores, spec=spec); dt = time.perf_counter() - t0
         if dt >= 0.5 or probe >= n_samples_hint:
             break
         probe *= 4
     n = int(min(n_samples_hint, max(probe, probe * seconds_target / max(dt, 1e-6))))
     n = max(64, n // 64 * 64)
-    t0 = time.perf_counter(); t = O.mc_packed(graph, 1, 0, n, tally_all, nthreads=cores, spec=spec); dt = time.perf_counter() - t0
+    t0 = time.perf_counter(); t = O.mc_packed(graph, 1, 0, n, tally_all, bits=bits, nthreads=cores, spec=spec); dt = time.perf_counter() - t0
     return n / dt, cores, n, dt, t
 
 
@@ -215,26 +215,27 @@ def run_reference(args):
     cores = len(os.sched_getaffinity(0))
     from oracle import oracle as O
     spec = args.sampler or O.SPEC
+    bits = args.threshold_bits
     # bounded sample per step, sized from a probe so K+W steps end within a few minutes
     probe, dt = 1 << 12, 0.0
     while True:
-        t0 = time.perf_counter(); O.mc_packed(g, 1, 0, probe, tally_all, nthreads=cores, spec=spec); dt = time.perf_counter() - t0
+        t0 = time.perf_counter(); O.mc_packed(g, 1, 0, probe, tally_all, bits=bits, nthreads=cores, spec=spec); dt = time.perf_counter() - t0
         if dt >= 0.5 or probe >= S:
             break
         probe *= 4
     budget = float(os.environ.get("CANOPY_BENCH_REF_BUDGET_S", "60")) / max(1, args.steps + args.warmup)  # seconds of CPU work per step
     n = int(max(probe, min(S, probe * budget / max(dt, 1e-6)))) // 64 * 64
     for w in range(args.warmup):
-        O.mc_packed(g, 1, 0, n, tally_all, nthreads=cores, spec=spec)
+        O.mc_packed(g, 1, 0, n, tally_all, bits=bits, nthreads=cores, spec=spec)
     t0 = time.perf_counter()
     for k in range(args.steps):
-        O.mc_packed(g, 1, (k + 1) * n, n, tally_all, nthreads=cores, spec=spec)
+        O.mc_packed(g, 1, (k + 1) * n, n, tally_all, bits=bits, nthreads=cores, spec=spec)
     dt = time.perf_counter() - t0
     v = n * args.steps / dt
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-            "config": config_block(args.workload, g, S, S_full, n_step=n),
+            "vs_baseline": None, "dtype": f"u{bits}", "data": "synthetic",
+            "config": dict(config_block(args.workload, g, S, S_full, n_step=n), threshold_bits=bits),
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": f"{n} samples/step of {args.workload} (bit-packed pthreads port in oracle/, spec {spec}; the reference has no CPU path)"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -246,7 +247,7 @@ def run_reference(args):
 CHECK_SEED = 0x7A11
 
 
-def tally_check(g, world, rank, local, dev, stream, sampler, n_fixed=1 << 24, n_prefix=1 << 14):
+def tally_check(g, world, rank, local, dev, stream, sampler, n_fixed=1 << 24, n_prefix=1 << 14, bits=32):
     """In-run parity evidence on the driver's clock, every gate tallied:
        (i)  the fixed range [0, n_fixed) cut over the N ranks by canopy_shard_range + ONE all-reduce == the same range on
             one GPU (at N = 1: three ragged pieces summed == the whole);
@@ -256,7 +257,7 @@ def tally_check(g, world, rank, local, dev, stream, sampler, n_fixed=1 << 24, n_
     import torch.distributed as dist
     from canopy_b200.engine import Plan, shard_range
     res = {"range": [0, n_fixed], "ranks": world, "prefix": n_prefix, "tallies": 0}
-    with Plan(g, tally_all_gates=True, sampler=sampler) as plan:
+    with Plan(g, tally_all_gates=True, threshold_bits=bits, sampler=sampler) as plan:
         nt = plan.n_tallies
         res["tallies"] = nt
         buf = torch.zeros(max(nt, 1), dtype=torch.int64, device=dev)
@@ -275,7 +276,7 @@ def tally_check(g, world, rank, local, dev, stream, sampler, n_fixed=1 << 24, n_
             flags[1] = int(np.array_equal(one, pieces))
             from oracle import oracle as O
             pre, _ = plan.run(n_prefix, seed=CHECK_SEED, sample_begin=0, device=local)
-            want = O.mc_packed(g, CHECK_SEED, 0, n_prefix, True, nthreads=len(os.sched_getaffinity(0)), spec=plan.spec)
+            want = O.mc_packed(g, CHECK_SEED, 0, n_prefix, True, bits=bits, nthreads=len(os.sched_getaffinity(0)), spec=plan.spec)
             flags[2] = int(np.array_equal(pre, want))
             res["top_event_tally"] = int(one[0]) if nt else 0
             res["nonzero_tallies"] = int((one > 0).sum())
@@ -308,13 +309,14 @@ def sampler_algorithmic_ops(plan, spec):
     return (float((per_group / grp).mean()) if len(thr) else 0.0), mix
 
 
-def side_line(name, local, stream, sampler, steps=2):
+def side_line(name, local, stream, sampler, steps=2, bits=32, samples=None):
     """A short device-timed line of another BASELINE config on rank 0 (extra key, not the headline)."""
     import torch
     from canopy_b200.engine import Plan
     g, S, S_full = workload(name)
+    S = samples or S
     tally_all = name == "c3"
-    with Plan(g, tally_all, sampler=sampler) as plan:
+    with Plan(g, tally_all, threshold_bits=bits, sampler=sampler) as plan:
         nt = plan.n_tallies
         out = torch.zeros(max(nt, 1), dtype=torch.int64, device=torch.device("cuda", local))
         for w in range(2):
@@ -328,7 +330,7 @@ def side_line(name, local, stream, sampler, steps=2):
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / steps
         st = plan.stats
-    return {"workload": config_block(name, g, S, S_full)["workload"], "samples_per_s": S / (ms * 1e-3), "ms_per_step": ms, "steps": steps,
+    return {"workload": config_block(name, g, S, S_full)["workload"], "threshold_bits": bits, "samples_per_s": S / (ms * 1e-3), "ms_per_step": ms, "steps": steps,
             "gate_evals_per_s": S / (ms * 1e-3) * st["n_gates_live"], "tallies": nt, "G_live": st["n_gates_live"],
             "alg_bytes_per_sample": (st["n_edges_live"] + st["n_gates_stored"] + st["n_basic_live"]) / 8.0}
 
@@ -342,6 +344,8 @@ def main():
     ap.add_argument("--workload", default="c4", choices=["c1", "c2", "c3", "c4"])
     ap.add_argument("--sampler", type=int, default=0,
                     help="sampling spec of the plan (0 = build default; include/canopy.h CANOPY_SAMPLER_*)")
+    ap.add_argument("--threshold-bits", type=int, default=32, choices=[32, 64],
+                    help="width of the variate / threshold comparison (canopy_plan_opts.threshold_bits)")
     ap.add_argument("--no-study", action="store_true", help="skip the short c2 / c3 side lines on rank 0")
     ap.add_argument("--no-check", action="store_true", help="skip tally_check (kernel-tuning runs only; the line says so)")
     ap.add_argument("--samples", type=int, default=0,
@@ -381,7 +385,7 @@ def main():
     # ---- parity evidence before anything is timed ------------------------------------------------------
     check = None
     if not args.no_check:
-        check = tally_check(g, world, rank, local, dev, stream, args.sampler)
+        check = tally_check(g, world, rank, local, dev, stream, args.sampler, bits=args.threshold_bits)
         if not (check["n_way_equals_1_way"] and check["pieces_equal_whole"] and check["prefix_equals_oracle"]):
             if rank == 0:
                 print(json.dumps({"metric": METRIC, "error": "tally_check failed", "tally_check": check}), flush=True)
@@ -389,7 +393,7 @@ def main():
                 dist.destroy_process_group()
             return 3
 
-    plan = Plan(g, tally_all, sampler=args.sampler)
+    plan = Plan(g, tally_all, threshold_bits=args.threshold_bits, sampler=args.sampler)
     stats = plan.stats
     spec = stats["spec_version"]
     nt = plan.n_tallies
@@ -444,7 +448,7 @@ def main():
 
     def e2e_step(k):
         t0 = time.perf_counter()
-        p2 = Plan(g, tally_all, sampler=args.sampler)  # canopy_plan_create from HOST arrays
+        p2 = Plan(g, tally_all, threshold_bits=args.threshold_bits, sampler=args.sampler)  # canopy_plan_create from HOST arrays
         t1 = time.perf_counter()
         r = p2.run_device(tallies.data_ptr(), S, seed=0xB200, sample_begin=(k * world + rank) * S, device=local,
                           stream=stream, want_report=True)   # uploads the lowered arrays (h2d) and runs
@@ -486,7 +490,7 @@ def main():
         # Integer roofline of the sampler.  Measured on sm_100 (canopy_microbench_int): LOP3, IMAD.WIDE.U32 and
         # any mix of the two issue at ONE shared rate of 64 lanes/clk/SM, so the bound is the integer instruction count.
         int_peak, _ = microbench_int(0, local)
-        kernel_name = {1: "sampler_direct_kernel<32>", 2: "sampler_sliced_kernel<32>", 4: "sampler_classed_kernel<32>"}.get(spec, "sampler")
+        kernel_name = {1: "sampler_direct_kernel", 2: "sampler_sliced_kernel", 4: "sampler_classed_kernel"}.get(spec, "sampler") + f"<{args.threshold_bits}>"
         traffic, exec_x_events, cap_note = captured(args.workload)
         exec_ops_per_bit = exec_x_events / stats["n_basic_live"] if exec_x_events and stats["n_basic_live"] else None
         step_ms = ms / args.steps
@@ -494,8 +498,8 @@ def main():
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "u32", "data": "synthetic",
-            "config": config_block(args.workload, g, S, S_full, stats),
+            "dtype": f"u{args.threshold_bits}", "data": "synthetic",
+            "config": dict(config_block(args.workload, g, S, S_full, stats), threshold_bits=args.threshold_bits),
             "gate_evals_per_sec": value * stats["n_gates_live"],
             "clocks": clk,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(r_e2e.h2d_bytes),
@@ -534,11 +538,14 @@ def main():
             "build_tag": build_tag(),
         }
     if world == 1 and rank == 0:
-        cpu_v, cores, n_cpu, dt_cpu, _ = cpu_arm(g, S, tally_all, spec=spec)
+        cpu_v, cores, n_cpu, dt_cpu, _ = cpu_arm(g, S, tally_all, spec=spec, bits=args.threshold_bits)
         line["cpu_baseline"] = {"value": cpu_v, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": f"{n_cpu} samples of {args.workload} in {dt_cpu:.1f} s (bit-packed pthreads port in oracle/)"}
         if not args.no_study:
-            line["other_configs"] = {n: side_line(n, local, stream, args.sampler) for n in ("c2", "c3") if n != args.workload}
+            line["other_configs"] = {n: side_line(n, local, stream, args.sampler, bits=args.threshold_bits) for n in ("c2", "c3") if n != args.workload}
+            # the same workload under the other threshold width (64-bit thresholds are what p below 1e-8 needs), a quarter step
+            ob = 96 - args.threshold_bits
+            line["other_configs"][f"{args.workload}_u{ob}"] = side_line(args.workload, local, stream, args.sampler, steps=1, bits=ob, samples=max(S // 4, 1 << 20))
     if rank == 0:
         if args.samples:
             line["config"]["reduced"] = f"--samples {args.samples}: side study, NOT the workload's sample count"

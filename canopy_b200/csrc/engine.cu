@@ -141,7 +141,7 @@ struct DeviceState {
     cudaEvent_t ev_done = nullptr;
     cudaStream_t last_stream = nullptr;
     bool ran = false;
-    uint32_t* walk_done = nullptr;   // 2 counters: walk CTAs of even / odd batches that have finished (pipeline hazard guard)
+    uint32_t* walk_done = nullptr;   // [0..1] walk CTAs of even / odd batches that have finished (pipeline hazard guard); [2..3] slab queues
 };
 
 // Order `st` after the last run on this state, if that run was on another stream.
@@ -336,7 +336,7 @@ static DeviceState* get_state(canopy_plan* plan, int device) {
         A.add(s->tally_kind, L.tally_kind); A.add(s->grec, L.gate_rec);
         A.add(s->ev_perm, L.event_perm);
         if (!L.event_perm.empty()) A.reserve(s->ev_cdf, (size_t)L.n_events() * CANOPY_SPARSE_CDF_LEN * 8);
-        A.reserve(s->gate_tallies, (std::max<size_t>(L.n_gates(), 1) + 1) * 8);  // + the two walk_done counters
+        A.reserve(s->gate_tallies, (std::max<size_t>(L.n_gates(), 1) + 2) * 8);  // + walk_done[4]
         A.reserve(s->out_tallies, std::max<size_t>(L.tally_kind.size(), 1) * 8);
         if (cudaMalloc(&s->arena, A.total) != cudaSuccess) { cudaGetLastError(); throw Error(CANOPY_E_OOM, "cudaMalloc failed for plan arrays"); }
         {   // one staged upload of all plan arrays instead of a dozen small synchronous copies
@@ -456,12 +456,13 @@ static void launch_sampler(const DeviceState* s, const Lowered& L, uint4* vals, 
 #ifndef CANOPY_WALK_ALONE_CTAS
 #define CANOPY_WALK_ALONE_CTAS 8    // ... and when the walk has the GPU to itself (capped by its occupancy)
 #endif
-// Returns the number of CTAs launched (what the next walk waits for in walk_done[parity]).
+// Returns the number of CTAs launched (what the next walk waits for in walk_done[parity]).  `qsel`: slab queue of this
+// batch (batch index & 1).
 static uint32_t launch_gates(const DeviceState* s, const Lowered& L, uint4* vals, uint64_t first_slab, uint32_t n_slabs,
                              uint64_t begin, uint64_t end, cudaStream_t st, bool shared_sm = false, uint32_t parity = 0,
-                             uint32_t wait_val = 0) {
+                             uint32_t wait_val = 0, uint32_t qsel = 0) {
     if (L.n_gates() == 0 || n_slabs == 0) return 0;
-    // persistent: one CTA per resident slot, each walks slabs blockIdx.x, +gridDim.x, ...; beside the sampler of the
+    // persistent: one CTA per resident slot, each takes slabs from the batch's queue; beside the sampler of the
     // next batch the walk keeps one CTA per SM (64 KB of row rings in flight), which measured best on B200
     const int per_sm = std::min(shared_sm ? CANOPY_WALK_SHARED_CTAS : CANOPY_WALK_ALONE_CTAS, s->ring_ctas_per_sm);
     const uint32_t grid = std::min<uint32_t>(n_slabs, (uint32_t)(s->sm_count * per_sm));
@@ -469,11 +470,11 @@ static uint32_t launch_gates(const DeviceState* s, const Lowered& L, uint4* vals
     if (vals == s->vals[b] && s->vmap_ok[b] && kGroupRows == 4)
         gate_ring_kernel_g4<<<grid, kGateThreads, kRingSmemBytes, st>>>(
             s->vmap[b], vals, s->grec, s->child, s->layer_off, s->wide_off, s->split, s->split_child, L.n_layers(), L.n_nodes(),
-            L.n_events(), s->gate_tallies, first_slab, n_slabs, begin, end, s->walk_done, parity, wait_val);
+            L.n_events(), s->gate_tallies, first_slab, n_slabs, begin, end, s->walk_done, parity, wait_val, qsel);
     else   // value buffers of more than 2^31 rows: one bulk copy per row instead of tile::gather4
         gate_ring_kernel<<<grid, kGateThreads, kRingSmemBytes, st>>>(
             s->vmap[0], vals, s->grec, s->child, s->layer_off, s->wide_off, s->split, s->split_child, L.n_layers(), L.n_nodes(),
-            L.n_events(), s->gate_tallies, first_slab, n_slabs, begin, end, s->walk_done, parity, wait_val);
+            L.n_events(), s->gate_tallies, first_slab, n_slabs, begin, end, s->walk_done, parity, wait_val, qsel);
     CUDA_CHECK(cudaGetLastError());
     return grid;
 }
@@ -531,7 +532,7 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
 
     order_after_last_run(s, user);
     CUDA_CHECK(cudaEventRecord(s->ev_t0, user));
-    CUDA_CHECK(cudaMemsetAsync(s->gate_tallies, 0, (std::max<size_t>(L.n_gates(), 1) + 1) * 8, user));  // tallies + walk_done
+    CUDA_CHECK(cudaMemsetAsync(s->gate_tallies, 0, (std::max<size_t>(L.n_gates(), 1) + 2) * 8, user));  // tallies + walk_done[4]
     R.other_launches += 1;
     struct EventList {  // profile events, 3 per batch; destroyed on every path out of this function
         std::vector<cudaEvent_t> v;
@@ -547,7 +548,7 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
             if (profile) { cudaEvent_t e[3]; for (auto& x : e) { CUDA_CHECK(cudaEventCreate(&x)); pe.push_back(x); } CUDA_CHECK(cudaEventRecord(e[0], user)); }
             launch_sampler(s, L, s->vals[0], fs, ns, K, user);
             if (profile) CUDA_CHECK(cudaEventRecord(pe[pe.size() - 2], user));
-            launch_gates(s, L, s->vals[0], fs, ns, begin, end, user);
+            launch_gates(s, L, s->vals[0], fs, ns, begin, end, user, false, 0, 0, (uint32_t)(b & 1));
             if (profile) CUDA_CHECK(cudaEventRecord(pe[pe.size() - 1], user));
             R.sampler_launches += L.n_events() ? 1 : 0; R.gate_launches += 1;
         }
@@ -566,7 +567,7 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
             const int buf = (int)(b & 1);
             launch_sampler(s, L, s->vals[buf], fs, sched[b], K, user, b > 0);
             done[buf] += launch_gates(s, L, s->vals[buf], fs, sched[b], begin, end, user, b + 1 < n_batches, (uint32_t)buf,
-                                      done[buf ^ 1]);
+                                      done[buf ^ 1], (uint32_t)buf);
             R.sampler_launches += L.n_events() ? 1 : 0; R.gate_launches += 1;
         }
     }

@@ -353,7 +353,7 @@ gate_ring_kernel_t(const __grid_constant__ CUtensorMap vmap, uint4* __restrict__
                    const uint32_t* __restrict__ split, const uint32_t* __restrict__ split_child,
                    uint32_t n_layers, uint32_t n_nodes, uint32_t n_ev, unsigned long long* __restrict__ tallies,
                    uint64_t first_slab, uint32_t n_slabs, uint64_t begin, uint64_t end,
-                   uint32_t* __restrict__ walk_done, uint32_t parity, uint32_t wait_val) {
+                   uint32_t* __restrict__ walk_done, uint32_t parity, uint32_t wait_val, uint32_t qsel) {
     extern __shared__ __align__(128) unsigned char smem[];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = __shfl_sync(0xFFFFFFFFu, threadIdx.x >> 5, 0);  // broadcast: provably warp-uniform
@@ -371,6 +371,12 @@ gate_ring_kernel_t(const __grid_constant__ CUtensorMap vmap, uint4* __restrict__
         while (*prev < wait_val) __nanosleep(64);
         __threadfence();
     }
+    // Slabs are dealt from a queue (walk_done[2 + qsel]: the next slab of this batch; qsel = batch index & 1): CTAs that draw
+    // cheap slabs or start early take more of them.  This walk clears the other queue for the batch after it: the walk
+    // that used it has finished (this launch is an ordinary one), and its next user starts after this kernel.
+    uint32_t* queue = walk_done + 2 + (qsel & 1u);
+    __shared__ uint32_t s_slab;
+    if (threadIdx.x == 0 && blockIdx.x == 0) walk_done[2 + ((qsel & 1u) ^ 1u)] = 0u;
     __syncthreads();
     // Pipelined run: the sampler of the next batch is launched as a programmatic dependent of this walk and needs
     // nothing from it, so it may start as soon as every CTA of this (persistent, single-wave) grid is resident.
@@ -381,7 +387,12 @@ gate_ring_kernel_t(const __grid_constant__ CUtensorMap vmap, uint4* __restrict__
     R.ring = smem_u32(smem) + warp * (kRingSlots * kRowBytes);
     R.bars = smem_u32(bars) + warp * (kRingGroups * 8u);
 
-    for (uint32_t slab = blockIdx.x; slab < n_slabs; slab += gridDim.x) {
+    for (;;) {
+        if (threadIdx.x == 0) s_slab = atomicAdd(queue, 1u);
+        __syncthreads();
+        const uint32_t slab = s_slab;
+        __syncthreads();
+        if (slab >= n_slabs) break;
         uint4* base = vals + (size_t)slab * n_nodes * kRowVec;
         R.row0 = slab * n_nodes;
         Row mask;

@@ -9,5 +9,5 @@ for f in engine multi; do
   nvcc $ARCH -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-fvisibility=hidden -DCANOPY_BUILD -DCANOPY_SHARED -I../../include -I. $defs -c $f.cu -o build/$name/$f.o &
 done
 wait
-nvcc $ARCH -shared -o build/variants/libcanopy_$name.so build/$name/engine.o build/$name/multi.o build/lowering.o build/capi.o build/mef_model.o -ldl -lpthread
+nvcc $ARCH -shared -o build/variants/libcanopy_$name.so build/$name/engine.o build/$name/multi.o build/lowering.o build/capi.o build/mef_model.o build/uncertainty.o -ldl -lpthread
 echo built $name

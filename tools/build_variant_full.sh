@@ -9,9 +9,9 @@ ARCH="-gencode arch=compute_100a,code=sm_100a"
 for f in engine multi; do
   nvcc $ARCH -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-fvisibility=hidden -DCANOPY_BUILD -DCANOPY_SHARED -I../../include -I. $defs -c $f.cu -o build/$name/$f.o &
 done
-for f in lowering capi mef_model; do
+for f in lowering capi mef_model uncertainty; do
   g++ -O2 -std=c++17 -fPIC -fvisibility=hidden -DCANOPY_BUILD -DCANOPY_SHARED -I../../include -I. -I/usr/local/cuda/include $defs -c $f.cpp -o build/$name/$f.o &
 done
 wait
-nvcc $ARCH -shared -o build/variants/libcanopy_$name.so build/$name/engine.o build/$name/multi.o build/$name/lowering.o build/$name/capi.o build/$name/mef_model.o -ldl -lpthread
+nvcc $ARCH -shared -o build/variants/libcanopy_$name.so build/$name/engine.o build/$name/multi.o build/$name/lowering.o build/$name/capi.o build/$name/mef_model.o build/$name/uncertainty.o -ldl -lpthread
 echo built $name
