@@ -41,7 +41,10 @@ constexpr uint32_t kShardAlign = 4096;               // canopy_shard_range cuts 
 static_assert(kRowHalves == 1 || kRowHalves == 2, "CANOPY_ROW_HALVES must be 1 or 2");
 
 // Gate kernel geometry fixed at lowering time.
-constexpr uint32_t kGateWarps = 8;     // warps of the CTA that walks one slab; the per-layer split is cut for this
+#ifndef CANOPY_GATE_WARPS
+#define CANOPY_GATE_WARPS 8
+#endif
+constexpr uint32_t kGateWarps = CANOPY_GATE_WARPS;     // warps of the CTA that walks one slab; the per-layer split is cut for this
 constexpr uint32_t kWideFanin = 512;   // count gates with at least this fan-in take the multi-pass register path
 
 struct GateRec {           // 16 bytes, loaded as one uint4 by the gate kernel

@@ -310,7 +310,10 @@ __device__ __forceinline__ void sparse_unit(uint4* __restrict__ vals, const uint
 // grid.x = dense CTAs (one warp per dense event) ++ sparse CTAs (one warp per unit); the dense ones come first: they are
 // the expensive ones, so the CTAs still running when a launch drains are the cheap units.
 template <int BITS>
-__global__ void __launch_bounds__(kClassedWarps * 32, 8)
+#ifndef CANOPY_CLASSED_MIN_BLOCKS
+#define CANOPY_CLASSED_MIN_BLOCKS 8
+#endif
+__global__ void __launch_bounds__(kClassedWarps * 32, CANOPY_CLASSED_MIN_BLOCKS)
 sampler_classed_kernel(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_orig,
                        const uint32_t* __restrict__ thr32, const uint64_t* __restrict__ thr64,
                        const uint32_t* __restrict__ ev_perm, const uint64_t* __restrict__ cdf, const SparseClasses C,

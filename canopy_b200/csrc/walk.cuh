@@ -112,7 +112,7 @@ __device__ __forceinline__ uint32_t valid_mask32(uint64_t s, uint64_t begin, uin
     return m;
 }
 
-constexpr int kGateThreads = 256;
+constexpr int kGateThreads = kGateWarps * 32;
 
 // ================================================================================================
 // Ring gate kernel (slab walker, TMA-bulk staging).
