@@ -507,7 +507,7 @@ def main():
                     "host_ms_per_step": {k2: v / e2e_steps for k2, v in e2e_parts.items()},
                     "what": "canopy_plan_create from host arrays + upload + run + allreduce + tallies to host, wall clock"},
             "gpu_launches": int(launches_per_step * args.steps),
-            "roofline": {"kernel": "gate_ring_kernel", "bound": "hbm", "achieved": gate_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+            "roofline": {"kernel": "gate_ring_kernel" if prof.sampler_launches else "small_model_kernel (sampler + walk fused over shared-memory rows: the HBM figure is nominal, nothing but tallies leaves the SM)", "bound": "hbm", "achieved": gate_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": gate_gbs / peaks["hbm_gbs"], "traffic": traffic,
                          "traffic_note": "DRAM read+write bytes of one full launch, " + cap_note + "; "
                                          "frac can read a little above 1: the peak is a 1:1 read:write copy, this kernel's traffic is about 5:1 reads",

@@ -26,7 +26,7 @@ class CanopyError(RuntimeError):
 
 class CPlanOpts(C.Structure):
     _fields_ = [("tally_all_gates", C.c_int32), ("threshold_bits", C.c_int32), ("sampler", C.c_int32),
-                ("no_plan_cache", C.c_int32), ("reserved", C.c_int32 * 4)]
+                ("no_plan_cache", C.c_int32), ("engine", C.c_int32), ("reserved", C.c_int32 * 3)]
 
 
 class CPlanStats(C.Structure):

@@ -51,7 +51,11 @@ canopy_status canopy_plan_create(const canopy_graph_desc* desc, const canopy_pla
         if (o.sampler == CANOPY_SAMPLER_DEFAULT) o.sampler = CANOPY_SPEC_VERSION;
         auto* p = new canopy_plan();
         try {
+            require(o.engine >= CANOPY_ENGINE_AUTO && o.engine <= CANOPY_ENGINE_FUSED, "canopy_plan_create: bad engine option");
             canopy::lower_graph_cached(*desc, o, p->low);
+            if (o.engine == CANOPY_ENGINE_FUSED && !canopy::small_eligible(p->low))
+                throw canopy::Error(CANOPY_E_UNSUPPORTED, "the fused engine needs a model whose node rows of one slab fit in shared memory "
+                                                          "(about 200 live nodes) and a sliced or classed sampler");
         } catch (...) { delete p; throw; }
         *out_plan = p;
     });

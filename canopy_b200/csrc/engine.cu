@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "sampler.cuh"
+#include "small.cuh"
 #include "walk.cuh"
 
 namespace canopy {
@@ -141,6 +142,7 @@ struct DeviceState {
     cudaEvent_t ev_done = nullptr;
     cudaStream_t last_stream = nullptr;
     bool ran = false;
+    uint32_t* child_small = nullptr; // fused path only: Lowered::child with node ids replaced by shared-memory row indices (small.cuh)
     uint32_t* walk_done = nullptr;   // [0..1] walk CTAs of even / odd batches that have finished (pipeline hazard guard); [2..3] slab queues
 };
 
@@ -306,10 +308,33 @@ static DeviceInfo device_info(int device) {
         CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<32>, cudaFuncAttributePreferredSharedMemoryCarveout, CANOPY_CARVEOUT));
         CUDA_CHECK(cudaFuncSetAttribute(sampler_sliced_kernel<64>, cudaFuncAttributePreferredSharedMemoryCarveout, CANOPY_CARVEOUT));
     }
+    CUDA_CHECK(cudaFuncSetAttribute(small_model_kernel<32, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmallMaxBytes));
+    CUDA_CHECK(cudaFuncSetAttribute(small_model_kernel<64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmallMaxBytes));
+    CUDA_CHECK(cudaFuncSetAttribute(small_model_kernel<32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmallMaxBytes));
+    CUDA_CHECK(cudaFuncSetAttribute(small_model_kernel<64, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmallMaxBytes));
     CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&I.ring_ctas_per_sm, gate_ring_kernel, kGateThreads, kRingSmemBytes));
     if (I.ring_ctas_per_sm < 1) throw Error(CANOPY_E_CUDA, "gate_ring_kernel does not fit on an SM");
     I.ready = true;
     return I;
+}
+
+// Fused path (small.cuh): may runs of this plan use it, and do they?
+bool small_eligible(const Lowered& L) {
+    return L.n_gates() > 0 && (size_t)L.n_nodes() * kRowBytes <= kSmallMaxBytes && L.opts.sampler != CANOPY_SAMPLER_DIRECT;
+}
+static bool use_small(const Lowered& L) { return small_eligible(L) && L.opts.engine != CANOPY_ENGINE_STREAMED; }
+// Child codes of the fused kernel: an event's row index is its position in the sampler's order (spec 4), a gate keeps its
+// device node id.  Follows the thresholds (the order does), so it is rebuilt with them.
+static std::vector<uint32_t> small_children(const Lowered& L) {
+    const uint32_t n_ev = L.n_events();
+    std::vector<uint32_t> pos(n_ev);
+    for (uint32_t i = 0; i < n_ev; ++i) pos[L.event_perm.empty() ? i : L.event_perm[i]] = i;
+    std::vector<uint32_t> out(L.child.size());
+    for (size_t c = 0; c < L.child.size(); ++c) {
+        const uint32_t code = L.child[c], node = code & 0x7FFFFFFFu;
+        out[c] = (node < n_ev ? pos[node] : node) | (code & 0x80000000u);
+    }
+    return out;
 }
 
 // Spec 4: (re)build the count tables of the sparse events on the device from the thresholds already uploaded.
@@ -335,6 +360,8 @@ static DeviceState* get_state(canopy_plan* plan, int device) {
         A.add(s->wide_off, L.wide_off); A.add(s->split, L.split); A.add(s->split_child, L.split_child);
         A.add(s->tally_kind, L.tally_kind); A.add(s->grec, L.gate_rec);
         A.add(s->ev_perm, L.event_perm);
+        const std::vector<uint32_t> csmall = small_eligible(L) ? small_children(L) : std::vector<uint32_t>();
+        A.add(s->child_small, csmall);
         if (!L.event_perm.empty()) A.reserve(s->ev_cdf, (size_t)L.n_events() * CANOPY_SPARSE_CDF_LEN * 8);
         A.reserve(s->gate_tallies, (std::max<size_t>(L.n_gates(), 1) + 2) * 8);  // + walk_done[4]
         A.reserve(s->out_tallies, std::max<size_t>(L.tally_kind.size(), 1) * 8);
@@ -479,6 +506,33 @@ static uint32_t launch_gates(const DeviceState* s, const Lowered& L, uint4* vals
     return grid;
 }
 
+// Fused path: the whole sample range in one launch, one CTA per resident slot striding over the slabs.
+static void launch_small(const DeviceState* s, const Lowered& L, uint64_t first_slab, uint64_t n_slabs, uint64_t begin, uint64_t end,
+                         const PhiloxKeys& K, cudaStream_t st) {
+    if (n_slabs > 0xFFFFFFFFull) throw Error(CANOPY_E_INVALID, "too many slabs for one run; split the sample range");
+    const bool classed = L.opts.sampler == CANOPY_SAMPLER_SPARSE, wide = L.opts.threshold_bits == 64;
+    SparseClasses C{};
+    uint32_t units = 0;
+    if (classed) {
+        C.n_dense = L.n_dense;
+        for (int c = 0; c < 8; ++c) {
+            C.ev_off[c] = L.class_off[c];
+            C.unit_off[c] = units;
+            if (c < 7) units += (L.class_off[c + 1] - L.class_off[c] + kUnitRows - 1) / kUnitRows;
+        }
+    }
+    const uint32_t smem = L.n_nodes() * kRowBytes;
+    auto kern = classed ? (wide ? small_model_kernel<64, true> : small_model_kernel<32, true>)
+                        : (wide ? small_model_kernel<64, false> : small_model_kernel<32, false>);
+    int per_sm = 1;
+    CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, (int)kSmallThreads, smem));
+    const uint32_t grid = (uint32_t)std::min<uint64_t>(n_slabs, (uint64_t)s->sm_count * std::max(per_sm, 1));
+    kern<<<grid, kSmallThreads, smem, st>>>(s->grec, s->child_small, s->layer_off, s->ev_orig, s->thr32, s->thr64, s->ev_perm, s->ev_cdf,
+                                           C, units, L.n_events(), L.n_layers(), s->gate_tallies, first_slab, (uint32_t)n_slabs,
+                                           begin, end, K);
+    CUDA_CHECK(cudaGetLastError());
+}
+
 static uint32_t pick_batch_slabs(const DeviceState* s, const Lowered& L, const canopy_mc_opts& o, uint64_t total_slabs, int n_bufs) {
     uint64_t want = o.batch_slabs > 0 ? (uint64_t)o.batch_slabs : (uint64_t)s->sm_count * (4 / kRowHalves);  // 16384 samples per SM
     want = std::min<uint64_t>(want, 65535 / kRowHalves);  // gridDim.y of the direct sampler
@@ -517,9 +571,11 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
     const uint32_t n_tallies = (uint32_t)L.tally_kind.size();
     unsigned long long* d_out = tallies_dev ? (unsigned long long*)tallies_dev : s->out_tallies;
 
+    const bool fused = use_small(L);
     uint32_t batch = 1; uint64_t n_batches = 0;
     std::vector<uint32_t> sched;  // slabs per batch, in order
-    if (total_slabs && L.n_gates()) {
+    if (fused) { overlap = false; batch = (uint32_t)std::min<uint64_t>(total_slabs, 0xFFFFFFFFull); n_batches = total_slabs ? 1 : 0; }
+    else if (total_slabs && L.n_gates()) {
         batch = pick_batch_slabs(s, L, o, total_slabs, overlap ? 2 : 1);
         if ((total_slabs + batch - 1) / batch < 2) overlap = false;
         for (uint64_t done = 0; done < total_slabs; done += batch) sched.push_back((uint32_t)std::min<uint64_t>(batch, total_slabs - done));
@@ -541,7 +597,12 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
         cudaEvent_t operator[](size_t i) const { return v[i]; }
         void push_back(cudaEvent_t e) { v.push_back(e); }
     } pe;
-    if (!overlap) {
+    if (fused) {   // sampler, walk and tallies of the whole range in one kernel over shared-memory rows (small.cuh)
+        cudaEvent_t e[2] = {nullptr, nullptr};
+        if (profile) { for (auto& x : e) { CUDA_CHECK(cudaEventCreate(&x)); pe.push_back(x); } CUDA_CHECK(cudaEventRecord(e[0], user)); }
+        if (total_slabs) { launch_small(s, L, slab0, total_slabs, begin, end, K, user); R.gate_launches += 1; }
+        if (profile) CUDA_CHECK(cudaEventRecord(e[1], user));
+    } else if (!overlap) {
         uint64_t fs = slab0;
         for (uint64_t b = 0; b < n_batches; fs += sched[b], ++b) {
             const uint32_t ns = sched[b];
@@ -585,7 +646,8 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
     if (tallies_host || rep || profile) {
         CUDA_CHECK(cudaStreamSynchronize(user));
         float ms = 0; CUDA_CHECK(cudaEventElapsedTime(&ms, s->ev_t0, s->ev_t1)); R.total_ms = ms;
-        for (size_t i = 0; i + 3 <= pe.size(); i += 3) {
+        if (fused && pe.size() == 2) { float a = 0; CUDA_CHECK(cudaEventElapsedTime(&a, pe[0], pe[1])); R.gate_ms = a; }   // one fused kernel: reported as the walk
+        for (size_t i = 0; !fused && i + 3 <= pe.size(); i += 3) {
             float a = 0, b2 = 0;
             CUDA_CHECK(cudaEventElapsedTime(&a, pe[i], pe[i + 1]));
             CUDA_CHECK(cudaEventElapsedTime(&b2, pe[i + 1], pe[i + 2]));
@@ -637,6 +699,10 @@ void refresh_thresholds(canopy_plan* plan) {
         }
         if (!L.event_perm.empty()) {   // spec 4: sampler order and tables follow the thresholds (sizes do not change)
             CUDA_CHECK(cudaMemcpy(s->ev_perm, L.event_perm.data(), L.event_perm.size() * 4, cudaMemcpyHostToDevice));
+            if (small_eligible(L) && !L.child.empty()) {   // the fused path's row indices follow the sampler's order
+                const std::vector<uint32_t> cs = small_children(L);
+                CUDA_CHECK(cudaMemcpy(s->child_small, cs.data(), cs.size() * 4, cudaMemcpyHostToDevice));
+            }
             build_tables(s, L);
         }
     }

@@ -118,6 +118,7 @@ void mc_sample_words(canopy_plan* plan, const canopy_mc_opts& o, uint64_t first_
 void mc_run_multi(canopy_plan* plan, const canopy_mc_opts& o, const int32_t* devices, int32_t n_devices,
                   uint64_t* tallies_host, canopy_mc_report* rep);
 void microbench_int(int device, int kind, double* lane_ops_per_s, double* ms);
+bool small_eligible(const Lowered& L);        // may runs of this plan take the fused shared-memory path (small.cuh)
 void trim_device_cache(int device);           // free the value buffers parked by destroyed plans (-1: all devices)
 void refresh_thresholds(canopy_plan* plan);  // re-upload thresholds and sampler order to every device the plan is resident on; rebuild the tables
 void debug_set_sparse_table(canopy_plan* plan, uint32_t live_event, const uint64_t* cdf);  // canopy-testing.h hook

@@ -107,64 +107,82 @@ template <> struct TailQueue<64> {
     __device__ __forceinline__ bool pop_lt(uint32_t, uint64_t tail64) { const bool lt = q0 < tail64; q0 = q1; return lt; }
 };
 
-// All 4096-sample blocks blockIdx.y, +gridDim.y, ... of the batch for one event.  Everything that depends on the event only
-// is warp-uniform (loaded once and broadcast), so the compiler keeps it in uniform registers.
+// The threshold of a plane event as the group code needs it: everything here is warp-uniform (loaded once and broadcast),
+// so the compiler keeps it in uniform registers.
+struct PlaneThr {
+    uint32_t head;                 // top H bits of the threshold, left-aligned in a 32-bit word
+    uint32_t trans;                // bit k (MSB first) set iff threshold bits k and k-1 differ
+    uint32_t tail32; uint64_t tail64;  // (thr mod 2^(BITS-H)) << H: compared with the raw tail variate
+};
+template <int BITS>
+__device__ __forceinline__ PlaneThr plane_thr(uint32_t t32, uint64_t t64) {
+    PlaneThr T; T.tail32 = 0; T.tail64 = 0;
+    if (BITS == 32) { T.head = t32; T.tail32 = t32 << kHeadBits; }
+    else {
+        const uint32_t lo = bcast0((uint32_t)t64), hi = bcast0((uint32_t)(t64 >> 32));
+        T.head = hi; T.tail64 = (((uint64_t)hi << 32) | lo) << kHeadBits;
+    }
+    T.trans = T.head ^ (T.head >> 1);
+    return T;
+}
+
+// The 128 samples of group g of event e (original index): four 32-sample words.  Called by a whole warp (the tail call is
+// issued warp-wide), each lane with its own group.
+template <int BITS>
+__device__ __forceinline__ uint4 plane_group(uint64_t g, uint32_t e, const PlaneThr& T, const PhiloxKeys& K) {
+    const uint32_t g_lo = (uint32_t)g, g_hi = (uint32_t)(g >> 32);
+    const uint32_t head = T.head, trans = T.trans;
+    // Branch-free head, two LOP3 per word and plane.  With m_k = all-ones iff bit k (MSB first) of the
+    // threshold is set:   u_{k+1} = u_k & ~(x_k ^ m_k)   (stay undecided where the variate bit equals the
+    // threshold bit), and a sample decided at plane k is "less" iff m_k.  The decided sets u_k ^ u_{k+1}
+    // are disjoint, so   r = XOR_k m_k & (u_k ^ u_{k+1}) = XOR_k (m_k ^ m_{k-1}) & u_k  ^  m_{H-1} & u_H
+    // (m_{-1} = 0): one LOP3 on (r, u_k, c_k) with the warp-uniform transition mask c_k.
+    uint32_t u[4] = {~0u, ~0u, ~0u, ~0u};  // undecided samples
+    uint32_t r[4] = {0, 0, 0, 0};          // decided "u < thr"
+#pragma unroll
+    for (int k = 0; k < kHeadBits; ++k) {
+        const uint4 x = philox4x32_10(g_lo, g_hi, e, 0x100u + k, K);
+        const uint32_t m = (uint32_t)((int32_t)(head << k) >> 31);
+        const uint32_t c = (uint32_t)((int32_t)(trans << k) >> 31);
+        r[0] ^= c & u[0]; r[1] ^= c & u[1]; r[2] ^= c & u[2]; r[3] ^= c & u[3];
+        u[0] &= ~(x.x ^ m); u[1] &= ~(x.y ^ m); u[2] &= ~(x.z ^ m); u[3] &= ~(x.w ^ m);
+    }
+    {   // closing term m_{H-1} & u_H (r is then exactly the decided-less set, disjoint from u)
+        const uint32_t m = (uint32_t)((int32_t)(head << (kHeadBits - 1)) >> 31);
+        r[0] ^= m & u[0]; r[1] ^= m & u[1]; r[2] ^= m & u[2]; r[3] ^= m & u[3];
+    }
+    if (__any_sync(0xFFFFFFFFu, (u[0] | u[1] | u[2] | u[3]) != 0u)) {
+        TailQueue<BITS> Q;
+        Q.fill(philox4x32_10(g_lo, g_hi, e, TailQueue<BITS>::kCtr, K));  // tail call 0, whole warp
+        uint32_t left = TailQueue<BITS>::kPerCall, call = 0;
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+#pragma unroll 1
+            while (u[w]) {
+                const uint32_t b = u[w] & (0u - u[w]);  // lowest undecided sample of word w
+                u[w] ^= b;
+                if (left == 0) {  // more undecided samples than one call serves: rare (3.5e-3 per group)
+                    Q.fill(philox4x32_10(g_lo, g_hi, e, TailQueue<BITS>::kCtr + (++call), K));
+                    left = TailQueue<BITS>::kPerCall;
+                }
+                --left;
+                if (Q.pop_lt(T.tail32, T.tail64)) r[w] |= b;
+            }
+        }
+    }
+    return make_uint4(r[0], r[1], r[2], r[3]);
+}
+
+// All 4096-sample blocks blockIdx.y, +gridDim.y, ... of the batch for one event; lane r owns group block * 32 + r.
 template <int BITS>
 __device__ __forceinline__ void plane_rows(uint4* __restrict__ vals, uint32_t ev, uint32_t e, uint32_t t32, uint64_t t64,
                                            uint32_t n_nodes, uint64_t first_slab, uint32_t n_slabs, const PhiloxKeys& K) {
     const uint32_t lane = threadIdx.x & 31;
-    uint32_t head;                 // top H bits of the threshold, left-aligned in a 32-bit word
-    uint32_t tail32 = 0; uint64_t tail64 = 0;  // (thr mod 2^(BITS-H)) << H: compared with the raw tail variate
-    if (BITS == 32) { head = t32; tail32 = t32 << kHeadBits; }
-    else {
-        const uint32_t lo = bcast0((uint32_t)t64), hi = bcast0((uint32_t)(t64 >> 32));
-        head = hi; tail64 = (((uint64_t)hi << 32) | lo) << kHeadBits;
-    }
-    const uint32_t trans = head ^ (head >> 1);  // bit k (MSB first) set iff threshold bits k and k-1 differ
+    const PlaneThr T = plane_thr<BITS>(t32, t64);
     const uint32_t n_blk = n_slabs * kRowHalves;
     for (uint32_t blk = blockIdx.y; blk < n_blk; blk += gridDim.y) {
         uint4* row = vals + ((size_t)(blk / kRowHalves) * n_nodes + ev) * kRowVec + (blk % kRowHalves) * 32u + lane;
-        const uint64_t g = (first_slab * kRowHalves + blk) * 32u + lane;  // 128-sample group of this lane
-        const uint32_t g_lo = (uint32_t)g, g_hi = (uint32_t)(g >> 32);
-        // Branch-free head, two LOP3 per word and plane.  With m_k = all-ones iff bit k (MSB first) of the
-        // threshold is set:   u_{k+1} = u_k & ~(x_k ^ m_k)   (stay undecided where the variate bit equals the
-        // threshold bit), and a sample decided at plane k is "less" iff m_k.  The decided sets u_k ^ u_{k+1}
-        // are disjoint, so   r = XOR_k m_k & (u_k ^ u_{k+1}) = XOR_k (m_k ^ m_{k-1}) & u_k  ^  m_{H-1} & u_H
-        // (m_{-1} = 0): one LOP3 on (r, u_k, c_k) with the warp-uniform transition mask c_k.
-        uint32_t u[4] = {~0u, ~0u, ~0u, ~0u};  // undecided samples
-        uint32_t r[4] = {0, 0, 0, 0};          // decided "u < thr"
-#pragma unroll
-        for (int k = 0; k < kHeadBits; ++k) {
-            const uint4 x = philox4x32_10(g_lo, g_hi, e, 0x100u + k, K);
-            const uint32_t m = (uint32_t)((int32_t)(head << k) >> 31);
-            const uint32_t c = (uint32_t)((int32_t)(trans << k) >> 31);
-            r[0] ^= c & u[0]; r[1] ^= c & u[1]; r[2] ^= c & u[2]; r[3] ^= c & u[3];
-            u[0] &= ~(x.x ^ m); u[1] &= ~(x.y ^ m); u[2] &= ~(x.z ^ m); u[3] &= ~(x.w ^ m);
-        }
-        {   // closing term m_{H-1} & u_H (r is then exactly the decided-less set, disjoint from u)
-            const uint32_t m = (uint32_t)((int32_t)(head << (kHeadBits - 1)) >> 31);
-            r[0] ^= m & u[0]; r[1] ^= m & u[1]; r[2] ^= m & u[2]; r[3] ^= m & u[3];
-        }
-        if (__any_sync(0xFFFFFFFFu, (u[0] | u[1] | u[2] | u[3]) != 0u)) {
-            TailQueue<BITS> Q;
-            Q.fill(philox4x32_10(g_lo, g_hi, e, TailQueue<BITS>::kCtr, K));  // tail call 0, whole warp
-            uint32_t left = TailQueue<BITS>::kPerCall, call = 0;
-#pragma unroll
-            for (int w = 0; w < 4; ++w) {
-#pragma unroll 1
-                while (u[w]) {
-                    const uint32_t b = u[w] & (0u - u[w]);  // lowest undecided sample of word w
-                    u[w] ^= b;
-                    if (left == 0) {  // more undecided samples than one call serves: rare (3.5e-3 per group)
-                        Q.fill(philox4x32_10(g_lo, g_hi, e, TailQueue<BITS>::kCtr + (++call), K));
-                        left = TailQueue<BITS>::kPerCall;
-                    }
-                    --left;
-                    if (Q.pop_lt(tail32, tail64)) r[w] |= b;
-                }
-            }
-        }
-        st_cg(row, make_uint4(r[0], r[1], r[2], r[3]));
+        st_cg(row, plane_group<BITS>((first_slab * kRowHalves + blk) * 32u + lane, e, T, K));
     }
 }
 
@@ -212,85 +230,107 @@ __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.comm
 __device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ uint32_t ge64(uint64_t a, uint64_t b) { return a >= b ? 1u : 0u; }
 
-// One unit = up to four events of one class x the slabs blockIdx.y, +gridDim.y, ... of the batch.  Lane = one 2^k-sample
-// group of the unit's 4-KB image (k = 7: eight groups per lane, one after the other; k >= 11: some lanes idle).
-__device__ __forceinline__ void sparse_unit(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_orig,
-                                            const uint32_t* __restrict__ ev_perm, const uint64_t* __restrict__ cdf,
-                                            uint32_t unit, const SparseClasses& C, uint32_t n_nodes, uint64_t first_slab,
-                                            uint32_t n_slabs, const PhiloxKeys& K, uint32_t img) {
+// One unit = up to four events of one class; lane = one 2^k-sample group of the unit's 4-KB image (k = 7: eight groups per
+// lane, one after the other; k >= 11: some lanes idle).
+struct SparseUnit {
+    uint32_t k, n_rows, rows_log, n_groups;
+    uint32_t first;         // position in ev_perm of the unit's first event
+    uint32_t my_ev, my_e;   // lane r < n_rows: device id and original index of event r of the unit
+};
+__device__ __forceinline__ SparseUnit sparse_unit_setup(const uint32_t* __restrict__ ev_orig, const uint32_t* __restrict__ ev_perm,
+                                                        uint32_t unit, const SparseClasses& C) {
     const uint32_t lane = threadIdx.x & 31;
     // class of this unit (warp-uniform); constant indices only, so that the parameter struct stays in the constant bank
     uint32_t c = 0, u_lo = C.unit_off[0], e_lo = C.ev_off[0], e_hi = C.ev_off[1];
 #pragma unroll
     for (uint32_t i = 1; i < 7; ++i)
         if (unit >= C.unit_off[i]) { c = i; u_lo = C.unit_off[i]; e_lo = C.ev_off[i]; e_hi = C.ev_off[i + 1]; }
-    const uint32_t k = 7u + c;
+    SparseUnit U;
+    U.k = 7u + c;
     const uint32_t first = e_lo + (unit - u_lo) * kUnitRows;
-    const uint32_t n_rows = min(kUnitRows, e_hi - first);
-    // lane r < n_rows keeps the device id and the original index of event r of the unit
-    uint32_t my_ev = 0, my_e = 0;
-    if (lane < n_rows) { my_ev = __ldg(ev_perm + first + lane); my_e = __ldg(ev_orig + my_ev); }
-    const uint32_t rows_log = 13u - k;                       // log2(groups per row)
-    const uint32_t n_groups = n_rows << rows_log;
+    U.first = first;
+    U.n_rows = min(kUnitRows, e_hi - first);
+    U.my_ev = 0; U.my_e = 0;
+    if (lane < U.n_rows) { U.my_ev = __ldg(ev_perm + first + lane); U.my_e = __ldg(ev_orig + U.my_ev); }
+    U.rows_log = 13u - U.k;                       // log2(groups per row)
+    U.n_groups = U.n_rows << U.rows_log;
+    return U;
+}
+// The unit's rows of one slab (global slab index `gslab`) as bitmaps in the shared-memory image `img` (n_rows x 1 KB,
+// cleared here).  Ends with the image complete and visible to the whole warp.
+__device__ __forceinline__ void sparse_unit_fill(const SparseUnit& U, const uint64_t* __restrict__ cdf, uint64_t gslab,
+                                                 const PhiloxKeys& K, uint32_t img) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t k = U.k, rows_log = U.rows_log;
     const uint32_t fpw = 32u / k, kmask = (1u << k) - 1u;
+    for (uint32_t i = lane; i < U.n_rows * (kRowBytes / 16u); i += 32u) sts128_zero(img + i * 16u);
+    __syncwarp();
+    const uint64_t gbase = gslab << rows_log;
+    for (uint32_t u0 = 0; u0 < U.n_groups; u0 += 32u) {
+        const uint32_t uu = u0 + lane;
+        const bool active = uu < U.n_groups;
+        const uint32_t r = active ? uu >> rows_log : 0u, gr = uu & ((1u << rows_log) - 1u);
+        const uint32_t ev = __shfl_sync(0xFFFFFFFFu, U.my_ev, r), e = __shfl_sync(0xFFFFFFFFu, U.my_e, r);
+        const uint64_t g = gbase + gr;
+        const uint32_t g_lo = (uint32_t)g, g_hi = (uint32_t)(g >> 32);
+        const uint4 x = philox4x32_10(g_lo, g_hi, e, 0x400u, K);
+        const uint64_t Uv = active ? ((uint64_t)x.y << 32) | x.x : 0ull;   // an idle lane draws no ones
+        // count: N = #{j : U >= cdf_j}, four table entries per trip, while some lane still exceeds the last one
+        const ulonglong2* tab = reinterpret_cast<const ulonglong2*>(cdf + (size_t)ev * CANOPY_SPARSE_CDF_LEN);
+        uint32_t n;
+        {
+            const ulonglong2 a = __ldg(tab), b = __ldg(tab + 1);
+            n = ge64(Uv, a.x) + ge64(Uv, a.y) + ge64(Uv, b.x) + ge64(Uv, b.y);
+            if (__any_sync(0xFFFFFFFFu, Uv >= b.y)) {
+#pragma unroll 1
+                for (uint32_t j = 2; j < CANOPY_SPARSE_CDF_LEN / 2; j += 2) {
+                    const ulonglong2 p = __ldg(tab + j), q = __ldg(tab + j + 1);
+                    n += ge64(Uv, p.x) + ge64(Uv, p.y) + ge64(Uv, q.x) + ge64(Uv, q.y);
+                    if (!__any_sync(0xFFFFFFFFu, Uv >= q.y)) break;
+                }
+            }
+        }
+        // placement: the first n distinct k-bit fields.  The lane owns the group's words of the image outright, so a
+        // plain read-modify-write does; the old value tells whether the position was taken already.
+        const uint32_t wbase = img + r * kRowBytes + (gr << (k - 3u));
+        uint32_t f = x.z, avail = fpw, fw = 0;
+        uint4 ext = x;
+#pragma unroll 1
+        while (n) {
+            if (avail == 0) {   // field word fw: 0, 1 = words 2, 3 of call 0x400; then word (fw-2)&3 of call 0x401 + ((fw-2)>>2)
+                avail = fpw; ++fw;
+                if (fw == 1u) f = x.w;
+                else {
+                    const uint32_t kx = fw - 2u;
+                    if ((kx & 3u) == 0u) ext = philox4x32_10(g_lo, g_hi, e, 0x401u + (kx >> 2), K);
+                    f = (kx & 3u) == 0u ? ext.x : (kx & 3u) == 1u ? ext.y : (kx & 3u) == 2u ? ext.z : ext.w;
+                }
+            }
+            const uint32_t pos = f & kmask;
+            f >>= k; --avail;
+            const uint32_t addr = wbase + ((pos >> 5) << 2), bit = 1u << (pos & 31u);
+            const uint32_t old = lds32(addr);
+            sts32(addr, old | bit);
+            n -= (old & bit) ? 0u : 1u;
+        }
+    }
+    __syncwarp();
+}
+
+// The unit x the slabs blockIdx.y, +gridDim.y, ... of the batch, into the value buffer.
+__device__ __forceinline__ void sparse_unit(uint4* __restrict__ vals, const uint32_t* __restrict__ ev_orig,
+                                            const uint32_t* __restrict__ ev_perm, const uint64_t* __restrict__ cdf,
+                                            uint32_t unit, const SparseClasses& C, uint32_t n_nodes, uint64_t first_slab,
+                                            uint32_t n_slabs, const PhiloxKeys& K, uint32_t img) {
+    const uint32_t lane = threadIdx.x & 31;
+    const SparseUnit U = sparse_unit_setup(ev_orig, ev_perm, unit, C);
     uint4* row_ptr[kUnitRows];
 #pragma unroll
-    for (uint32_t r = 0; r < kUnitRows; ++r) row_ptr[r] = vals + (size_t)__shfl_sync(0xFFFFFFFFu, my_ev, r) * kRowVec;
-
+    for (uint32_t r = 0; r < kUnitRows; ++r) row_ptr[r] = vals + (size_t)__shfl_sync(0xFFFFFFFFu, U.my_ev, r) * kRowVec;
     for (uint32_t slab = blockIdx.y; slab < n_slabs; slab += gridDim.y) {
         if (lane == 0) bulk_wait_read_all();                 // the stores of the previous slab (lane 0's bulk group) have read the image
         __syncwarp();
-        for (uint32_t i = lane; i < n_rows * (kRowBytes / 16u); i += 32u) sts128_zero(img + i * 16u);
-        __syncwarp();
-        const uint64_t gbase = (first_slab + slab) << rows_log;
-        for (uint32_t u0 = 0; u0 < n_groups; u0 += 32u) {
-            const uint32_t uu = u0 + lane;
-            const bool active = uu < n_groups;
-            const uint32_t r = active ? uu >> rows_log : 0u, gr = uu & ((1u << rows_log) - 1u);
-            const uint32_t ev = __shfl_sync(0xFFFFFFFFu, my_ev, r), e = __shfl_sync(0xFFFFFFFFu, my_e, r);
-            const uint64_t g = gbase + gr;
-            const uint32_t g_lo = (uint32_t)g, g_hi = (uint32_t)(g >> 32);
-            const uint4 x = philox4x32_10(g_lo, g_hi, e, 0x400u, K);
-            const uint64_t U = active ? ((uint64_t)x.y << 32) | x.x : 0ull;   // an idle lane draws no ones
-            // count: N = #{j : U >= cdf_j}, four table entries per trip, while some lane still exceeds the last one
-            const ulonglong2* tab = reinterpret_cast<const ulonglong2*>(cdf + (size_t)ev * CANOPY_SPARSE_CDF_LEN);
-            uint32_t n;
-            {
-                const ulonglong2 a = __ldg(tab), b = __ldg(tab + 1);
-                n = ge64(U, a.x) + ge64(U, a.y) + ge64(U, b.x) + ge64(U, b.y);
-                if (__any_sync(0xFFFFFFFFu, U >= b.y)) {
-#pragma unroll 1
-                    for (uint32_t j = 2; j < CANOPY_SPARSE_CDF_LEN / 2; j += 2) {
-                        const ulonglong2 p = __ldg(tab + j), q = __ldg(tab + j + 1);
-                        n += ge64(U, p.x) + ge64(U, p.y) + ge64(U, q.x) + ge64(U, q.y);
-                        if (!__any_sync(0xFFFFFFFFu, U >= q.y)) break;
-                    }
-                }
-            }
-            // placement: the first n distinct k-bit fields.  The lane owns the group's words of the image outright, so a
-            // plain read-modify-write does; the old value tells whether the position was taken already.
-            const uint32_t wbase = img + r * kRowBytes + (gr << (k - 3u));
-            uint32_t f = x.z, avail = fpw, fw = 0;
-            uint4 ext = x;
-#pragma unroll 1
-            while (n) {
-                if (avail == 0) {   // field word fw: 0, 1 = words 2, 3 of call 0x400; then word (fw-2)&3 of call 0x401 + ((fw-2)>>2)
-                    avail = fpw; ++fw;
-                    if (fw == 1u) f = x.w;
-                    else {
-                        const uint32_t kx = fw - 2u;
-                        if ((kx & 3u) == 0u) ext = philox4x32_10(g_lo, g_hi, e, 0x401u + (kx >> 2), K);
-                        f = (kx & 3u) == 0u ? ext.x : (kx & 3u) == 1u ? ext.y : (kx & 3u) == 2u ? ext.z : ext.w;
-                    }
-                }
-                const uint32_t pos = f & kmask;
-                f >>= k; --avail;
-                const uint32_t addr = wbase + ((pos >> 5) << 2), bit = 1u << (pos & 31u);
-                const uint32_t old = lds32(addr);
-                sts32(addr, old | bit);
-                n -= (old & bit) ? 0u : 1u;
-            }
-        }
+        sparse_unit_fill(U, cdf, first_slab + slab, K, img);
         // image -> global: one bulk store per row (the rows of a unit's events are not adjacent in the value buffer)
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
@@ -298,7 +338,7 @@ __device__ __forceinline__ void sparse_unit(uint4* __restrict__ vals, const uint
             const size_t slab_off = (size_t)slab * n_nodes * kRowVec;
 #pragma unroll
             for (uint32_t r = 0; r < kUnitRows; ++r)
-                if (r < n_rows) bulk_s2g(row_ptr[r] + slab_off, img + r * kRowBytes, kRowBytes);
+                if (r < U.n_rows) bulk_s2g(row_ptr[r] + slab_off, img + r * kRowBytes, kRowBytes);
             bulk_commit();
         }
         __syncwarp();

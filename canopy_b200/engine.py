@@ -76,18 +76,24 @@ def _arr(ptr, n, dtype):
     return np.ctypeslib.as_array(ptr, shape=(n,)).astype(dtype, copy=True)
 
 
+ENGINE_AUTO, ENGINE_STREAMED, ENGINE_FUSED = 0, 1, 2   # CANOPY_ENGINE_* (include/canopy.h)
+DEFAULT_ENGINE = ENGINE_AUTO   # what Plan(engine=None) asks for; the GPU tests run under both AUTO and STREAMED (tests/conftest.py)
+
+
 class Plan:
     """Lowered DAG (host) + lazily created per-device state (owned by libcanopy)."""
 
     def __init__(self, graph: Graph, tally_all_gates: bool = False, threshold_bits: int = 32, sampler: int = 0,
-                 plan_cache: bool = True):
+                 plan_cache: bool = True, engine: int | None = None):
+        """engine: ENGINE_AUTO (fused kernel for models whose rows fit in shared memory), ENGINE_STREAMED, ENGINE_FUSED."""
+        engine = DEFAULT_ENGINE if engine is None else engine
         self._h = C.c_void_p()
         self.graph = graph
         self.tally_all_gates = bool(tally_all_gates)
         self.threshold_bits = threshold_bits
         desc = graph.c_desc()
         opts = _lib.CPlanOpts(tally_all_gates=int(tally_all_gates), threshold_bits=threshold_bits, sampler=int(sampler),
-                              no_plan_cache=int(not plan_cache))
+                              no_plan_cache=int(not plan_cache), engine=int(engine))
         _lib.check(_lib.lib().canopy_plan_create(C.byref(desc), C.byref(opts), C.byref(self._h)))
         st = _lib.CPlanStats()
         _lib.check(_lib.lib().canopy_plan_info(self._h, C.byref(st)))

@@ -145,8 +145,16 @@ typedef struct canopy_plan_opts {
     int32_t threshold_bits;    /* 32 (default) or 64: width of the variate / threshold comparison                */
     int32_t sampler;           /* CANOPY_SAMPLER_*: which sampling spec the plan's tallies follow (0 = default)   */
     int32_t no_plan_cache;     /* 1: lower from scratch and do not keep the result (see canopy_plan_create)       */
-    int32_t reserved[4];
+    int32_t engine;            /* CANOPY_ENGINE_*: how runs of this plan are executed (same tallies either way)   */
+    int32_t reserved[3];
 } canopy_plan_opts;
+/* AUTO: the fused kernel when the node rows of one slab fit in shared memory (about 200 live nodes; sampler, gate walk and
+ * tallies in one launch, nothing but tallies leaves the SM), else the streamed pair of kernels over the value buffer in HBM.
+ * STREAMED forces the latter; FUSED fails at plan creation (CANOPY_E_UNSUPPORTED) when the model is too large or the plan
+ * uses the direct sampler (spec 1). */
+#define CANOPY_ENGINE_AUTO     0
+#define CANOPY_ENGINE_STREAMED 1
+#define CANOPY_ENGINE_FUSED    2
 
 /* Lowering statistics, reported before and after dead-code elimination / folding. */
 typedef struct canopy_plan_stats {

@@ -18,3 +18,21 @@ def _built():
     """Build libcanopy.so and the oracle once per session (no-op when up to date)."""
     import __graft_entry__ as ge
     ge.build()
+
+
+def pytest_generate_tests(metafunc):
+    """Every GPU test runs twice: with the engine chosen by the library (the fused shared-memory kernel for models of up to
+    about 200 live nodes, which most test graphs are) and with the streamed sampler + gate-walk pair forced, so that
+    neither path hides behind the other."""
+    if metafunc.definition.get_closest_marker("gpu") is not None:
+        metafunc.fixturenames.append("_engine_mode")
+        metafunc.parametrize("_engine_mode", ["auto", "streamed"], indirect=True)
+
+
+@pytest.fixture
+def _engine_mode(request):
+    from canopy_b200 import engine
+    old = engine.DEFAULT_ENGINE
+    engine.DEFAULT_ENGINE = {"auto": engine.ENGINE_AUTO, "streamed": engine.ENGINE_STREAMED}[request.param]
+    yield request.param
+    engine.DEFAULT_ENGINE = old

@@ -248,3 +248,47 @@ def test_pipeline_hazard_on_a_gate_bound_graph():
         for rep in range(12):
             got, r = plan.run(n, seed=7, batch_slabs=4, overlap=True)
             assert r.n_batches >= 24 and np.array_equal(got, want), rep
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("spec,bits", [(4, 32), (4, 64), (2, 32), (2, 64)])
+def test_fused_engine_equals_streamed_and_oracle(spec, bits):
+    """The fused small-model kernel (csrc/small.cuh) against the streamed pair and the scalar oracle: all connectives,
+    constants, complements, ragged sample ranges, every class of spec 4."""
+    from canopy_b200.engine import ENGINE_FUSED, ENGINE_STREAMED
+    from helpers import random_graph
+    rng = np.random.default_rng(5)
+    for seed in range(6):
+        g = random_graph(100 + seed, n_basic=40, n_gates=60, max_fanin=9)
+        g.p[:] = np.where(g.p > 0, 10.0 ** rng.uniform(-4.5, -0.3, g.n_basic), 0.0) * (g.p < 1) + (g.p >= 1)   # spread over the classes, keep p = 0 / 1
+        n, begin = 2 * 8192 + 777 + seed, 4096 * seed + 13
+        with Plan(g, tally_all_gates=True, threshold_bits=bits, sampler=spec, engine=ENGINE_FUSED) as pf, \
+             Plan(g, tally_all_gates=True, threshold_bits=bits, sampler=spec, engine=ENGINE_STREAMED) as ps:
+            tf, rf = pf.run(n, seed=21, sample_begin=begin)
+            ts, rs = ps.run(n, seed=21, sample_begin=begin)
+            assert rf.sampler_launches == 0 and rf.gate_launches == 1 and rs.sampler_launches >= 1
+        assert np.array_equal(tf, ts)
+        assert np.array_equal(tf, O.mc_scalar(g, 21, begin, n, True, bits=bits, spec=spec))
+
+
+@pytest.mark.gpu
+def test_fused_engine_limits_and_update_p():
+    from canopy_b200 import _lib
+    from canopy_b200.engine import ENGINE_FUSED
+    big = synth.generate(n_basic=300, n_gates=160, n_layers=6, max_fanin=12, seed=3)
+    with pytest.raises(_lib.CanopyError) as ei:
+        Plan(big, engine=ENGINE_FUSED)
+    assert ei.value.status == _lib.E_UNSUPPORTED
+    g = synth.generate(n_basic=120, n_gates=70, n_layers=5, max_fanin=8, seed=4)
+    with pytest.raises(_lib.CanopyError):
+        Plan(g, sampler=1, engine=ENGINE_FUSED)                     # the direct sampler has no fused form
+    rng = np.random.default_rng(1)
+    with Plan(g, tally_all_gates=True, engine=ENGINE_FUSED) as plan:
+        plan.run(4096, seed=1)
+        for k in range(3):                                          # classes (hence the row order) change with p
+            p = np.clip(g.p * rng.lognormal(0.0, 1.5, g.n_basic), 1e-7, 0.9)
+            plan.update_p(p)
+            got, rep = plan.run(8192 + 5, seed=3, sample_begin=k * 50000)
+            assert rep.sampler_launches == 0
+            g2 = G.Graph(p=p, op=g.op, kmin=g.kmin, kmax=g.kmax, child_off=g.child_off, child=g.child, roots=g.roots)
+            assert np.array_equal(got, O.mc_scalar(g2, 3, k * 50000, 8192 + 5, True))
