@@ -103,7 +103,7 @@ def build_tag() -> str:
     from a capture of ANOTHER build is reported as null instead of silently going stale."""
     import hashlib
     h = hashlib.sha1()
-    for f in ("engine.cu", "kernels.cuh", "sampler.cuh", "walk.cuh", "sparse_table.h", "plan.h", "lowering.cpp"):
+    for f in ("engine.cu", "kernels.cuh", "sampler.cuh", "walk.cuh", "small.cuh", "sparse_table.h", "plan.h", "lowering.cpp"):
         with open(os.path.join(ROOT, "canopy_b200", "csrc", f), "rb") as fh:
             h.update(fh.read())
     return h.hexdigest()[:12]

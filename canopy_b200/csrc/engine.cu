@@ -128,6 +128,7 @@ struct DeviceState {
     unsigned long long* gate_tallies = nullptr;
     unsigned long long* out_tallies = nullptr;   // used when the caller wants host output
     void* arena = nullptr;                       // one allocation holding every plan array above
+    size_t arena_bytes = 0;
     uint4* vals[2] = {nullptr, nullptr};
     size_t vals_bytes[2] = {0, 0};  // capacity of each value buffer
     size_t vals_slabs = 0;  // capacity of each buffer in slabs
@@ -169,7 +170,8 @@ struct ValPool {
     struct Entry { int device; void* ptr; size_t bytes; };
     std::mutex mu;
     std::vector<Entry> parked;
-    static constexpr size_t kMaxParkedPerDevice = 2;
+    size_t kMaxParkedPerDevice;
+    explicit ValPool(size_t max_parked) : kMaxParkedPerDevice(max_parked) {}
 
     void* acquire(int device, size_t bytes, size_t* got) {
         {
@@ -233,15 +235,19 @@ struct ValPool {
         if (cur >= 0) cudaSetDevice(cur);
     }
 };
-static ValPool g_val_pool;
+static ValPool g_val_pool(2);
+// The plan arrays of destroyed plans are parked the same way: cudaFree synchronises the device and was measured at anything
+// between 0.6 and 250 ms per call next to 90 GB of live value buffers (it dominated the end-to-end time of a one-shot
+// quantification), cudaMalloc at a few ms.
+static ValPool g_arena_pool(4);
 
-void trim_device_cache(int device) { g_val_pool.trim(device); }
+void trim_device_cache(int device) { g_val_pool.trim(device); g_arena_pool.trim(device); }
 
 void destroy_device_state(DeviceState* s) {
     if (!s) return;
     cudaSetDevice(s->device);
     cudaDeviceSynchronize();  // nothing of this plan (on its own or on a caller's stream) may still run on a parked buffer
-    cudaFree(s->arena);
+    g_arena_pool.release(s->device, s->arena, s->arena_bytes);
     for (int b = 0; b < 2; ++b) g_val_pool.release(s->device, s->vals[b], s->vals_bytes[b]);
     if (s->main) cudaStreamDestroy(s->main);
     for (cudaEvent_t e : {s->ev_t0, s->ev_t1, s->ev_done})
@@ -255,12 +261,14 @@ struct ArenaPlan {
     struct Piece { void** dst; const void* src; size_t bytes, off; };
     std::vector<Piece> pieces;
     size_t total = 0;
+    size_t upload = 0;   // the arrays with host data come first: only [0, upload) is staged and copied
     template <class P, class T>
     void add(P*& dst, const std::vector<T>& v, size_t min_elems = 1) {
         const size_t bytes = std::max(v.size(), min_elems) * sizeof(T);
         pieces.push_back({reinterpret_cast<void**>(&dst), v.empty() ? nullptr : v.data(), bytes, total});
         pieces.back().bytes = v.size() * sizeof(T);  // bytes to copy; the reservation below may be larger
         total += (bytes + 255) & ~size_t(255);
+        upload = total;
     }
     template <class P>
     void reserve(P*& dst, size_t bytes) {
@@ -365,15 +373,16 @@ static DeviceState* get_state(canopy_plan* plan, int device) {
         if (!L.event_perm.empty()) A.reserve(s->ev_cdf, (size_t)L.n_events() * CANOPY_SPARSE_CDF_LEN * 8);
         A.reserve(s->gate_tallies, (std::max<size_t>(L.n_gates(), 1) + 2) * 8);  // + walk_done[4]
         A.reserve(s->out_tallies, std::max<size_t>(L.tally_kind.size(), 1) * 8);
-        if (cudaMalloc(&s->arena, A.total) != cudaSuccess) { cudaGetLastError(); throw Error(CANOPY_E_OOM, "cudaMalloc failed for plan arrays"); }
+        s->arena = g_arena_pool.acquire(device, A.total, &s->arena_bytes);
+        if (!s->arena) throw Error(CANOPY_E_OOM, "cudaMalloc failed for plan arrays");
         {   // one staged upload of all plan arrays instead of a dozen small synchronous copies
-            std::vector<char> stage(A.total);
+            std::vector<char> stage(A.upload);
             for (auto& p : A.pieces) {
                 *p.dst = static_cast<char*>(s->arena) + p.off;
                 if (p.bytes) std::memcpy(stage.data() + p.off, p.src, p.bytes);
                 s->h2d_bytes += p.bytes;
             }
-            CUDA_CHECK(cudaMemcpy(s->arena, stage.data(), A.total, cudaMemcpyHostToDevice));
+            CUDA_CHECK(cudaMemcpy(s->arena, stage.data(), A.upload, cudaMemcpyHostToDevice));
         }
         CUDA_CHECK(cudaStreamCreateWithFlags(&s->main, cudaStreamNonBlocking));
         CUDA_CHECK(cudaEventCreateWithFlags(&s->ev_done, cudaEventDisableTiming));
