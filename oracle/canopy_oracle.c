@@ -52,6 +52,30 @@ void oracle_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2], uint32_t
     out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 
+/* Eight Philox calls that share counter words 0-2 and differ in word 3, lane-wise (structure of arrays) so that the
+ * compiler vectorises the rounds (AVX2 where the host has it: the function is compiled twice and dispatched at load time).
+ * Only the timed CPU port uses it; the values are those of oracle_philox4x32_10, which the tests compare it with. */
+#if defined(__x86_64__) && defined(__GNUC__)
+__attribute__((target_clones("avx2", "default")))
+#endif
+static void philox_batch8(uint32_t a0, uint32_t a1, uint32_t a2, const uint32_t c3[8], const uint32_t key[2], uint32_t out[4][8]) {
+    uint32_t c0[8], c1[8], c2[8], cc3[8];
+    for (int i = 0; i < 8; ++i) { c0[i] = a0; c1[i] = a1; c2[i] = a2; cc3[i] = c3[i]; }
+    uint32_t k0 = key[0], k1 = key[1];
+    for (int r = 0; r < 10; ++r) {
+        for (int i = 0; i < 8; ++i) {
+            const uint64_t p0 = (uint64_t)PHILOX_M0 * c0[i], p1 = (uint64_t)PHILOX_M1 * c2[i];
+            const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1[i] ^ k0, n2 = (uint32_t)(p0 >> 32) ^ cc3[i] ^ k1;
+            c1[i] = (uint32_t)p1; cc3[i] = (uint32_t)p0; c0[i] = n0; c2[i] = n2;
+        }
+        k0 += PHILOX_W0; k1 += PHILOX_W1;
+    }
+    for (int i = 0; i < 8; ++i) { out[0][i] = c0[i]; out[1][i] = c1[i]; out[2][i] = c2[i]; out[3][i] = cc3[i]; }
+}
+void oracle_philox_batch8(uint32_t a0, uint32_t a1, uint32_t a2, const uint32_t c3[8], const uint32_t key[2], uint32_t out[32]) {
+    philox_batch8(a0, a1, a2, c3, key, (uint32_t(*)[8])out);   /* test entry: out[w * 8 + lane] */
+}
+
 /* ------------------------------------------------------------------------------------------------
  * SPEC v1 "Threshold quantisation".  kind: 0 = always false (p <= 0), 1 = always true (p >= 1),
  * 2 = sampled with thr = floor(p * 2^bits).  Returns -1 for NaN / out of [0,1].
@@ -247,9 +271,17 @@ static void sliced_group_words(uint64_t seed, uint32_t e, uint64_t g, int kind, 
     uint32_t ctr[4], x[4];
     uint32_t und[4] = {~0u, ~0u, ~0u, ~0u}, res[4] = {0, 0, 0, 0};
     unsigned head = (unsigned)(thr >> (bits - H));
+    /* the H <= 7 head calls and tail call 0 in one batch of eight (they differ in counter word 3 only) */
+    uint32_t c3[8], y[4][8];
+    for (unsigned k = 0; k < 8; ++k) c3[k] = k < H ? 0x100u + k : (bits == 32 ? 0x200u : 0x300u);
+    const int batched = H <= 7;
+    if (batched) philox_batch8((uint32_t)g, (uint32_t)(g >> 32), e, c3, key, y);
     for (unsigned k = 0; k < H; ++k) {
-        ctr[0] = (uint32_t)g; ctr[1] = (uint32_t)(g >> 32); ctr[2] = e; ctr[3] = 0x100u + k;
-        oracle_philox4x32_10(ctr, key, x);
+        if (batched) { x[0] = y[0][k]; x[1] = y[1][k]; x[2] = y[2][k]; x[3] = y[3][k]; }
+        else {
+            ctr[0] = (uint32_t)g; ctr[1] = (uint32_t)(g >> 32); ctr[2] = e; ctr[3] = 0x100u + k;
+            oracle_philox4x32_10(ctr, key, x);
+        }
         int tb = (head >> (H - 1 - k)) & 1;
         for (int j = 0; j < 4; ++j) {
             if (tb) { res[j] |= und[j] & ~x[j]; und[j] &= x[j]; }
@@ -259,9 +291,12 @@ static void sliced_group_words(uint64_t seed, uint32_t e, uint64_t g, int kind, 
     /* tail: the r-th undecided sample of the group (ascending sample index) takes output word r&3 of tail
      * call r>>2 (32-bit thresholds), or words 2(r&1)+1 : 2(r&1) of tail call r>>1 (64-bit thresholds) */
     unsigned rank = 0, have = ~0u;
-    for (unsigned j = 0; j < 4; ++j)
-        for (unsigned t = 0; t < 32; ++t) {
-            if (!((und[j] >> t) & 1u)) continue;
+    if (batched) { x[0] = y[0][7]; x[1] = y[1][7]; x[2] = y[2][7]; x[3] = y[3][7]; have = 0; }
+    for (unsigned j = 0; j < 4; ++j) {
+        uint32_t u = und[j];
+        while (u) {
+            const unsigned t = (unsigned)__builtin_ctz(u);
+            u &= u - 1;
             unsigned call = bits == 32 ? rank >> 2 : rank >> 1;
             if (call != have) {
                 ctr[0] = (uint32_t)g; ctr[1] = (uint32_t)(g >> 32); ctr[2] = e; ctr[3] = (bits == 32 ? 0x200u : 0x300u) + call;
@@ -274,6 +309,7 @@ static void sliced_group_words(uint64_t seed, uint32_t e, uint64_t g, int kind, 
             if (lt) res[j] |= 1u << t;
             ++rank;
         }
+    }
     out2[0] = ((uint64_t)res[1] << 32) | res[0];
     out2[1] = ((uint64_t)res[3] << 32) | res[2];
 }
@@ -567,6 +603,7 @@ typedef struct {
     const uint32_t* order;
     const int* kind; const uint64_t* thr; const unsigned char* used;
     const uint64_t* tab; /* spec 4 count tables, or NULL */
+    const uint32_t* edge_idx; const uint64_t* edge_mask; /* per argument: slot in val[] (constants have their own two), complement mask */
     uint64_t seed, begin, n; int tally_all, bits, spec;
     uint64_t first_group, n_groups; /* global 128-sample group range covering [begin, begin+n) */
     int tid, nthreads;
@@ -605,10 +642,12 @@ static void* packed_worker(void* arg) {
     packed_job* J = (packed_job*)arg;
     const canopy_graph_desc* d = J->d;
     uint32_t B = d->n_basic, G = d->n_gates;
-    uint64_t* val = (uint64_t*)malloc(sizeof(uint64_t) * 2 * ((size_t)B + G + 1));
+    uint64_t* val = (uint64_t*)malloc(sizeof(uint64_t) * 2 * ((size_t)B + G + 2));
+    val[2 * ((size_t)B + G)] = val[2 * ((size_t)B + G) + 1] = 0;              /* slot B+G: constant false */
+    val[2 * ((size_t)B + G + 1)] = val[2 * ((size_t)B + G + 1) + 1] = ~0ull;  /* slot B+G+1: constant true */
     uint32_t maxf = 1;
     for (uint32_t g = 0; g < G; ++g) { uint64_t f = d->child_off[g + 1] - d->child_off[g]; if (f > maxf) maxf = (uint32_t)f; }
-    uint64_t* x = (uint64_t*)malloc(sizeof(uint64_t) * maxf);
+    uint64_t* x = (uint64_t*)malloc(sizeof(uint64_t) * 2 * maxf);
     /* per sparse event: the positions of the 2^k-group the thread is currently inside */
     unsigned char* ev_k = (unsigned char*)calloc(B ? B : 1, 1);
     unsigned char* cache_n = (unsigned char*)calloc(B ? B : 1, 1);
@@ -642,33 +681,42 @@ static void* packed_worker(void* arg) {
                 if (q < 128u) v[q >> 6] |= 1ull << (q & 63u);
             }
         }
+        /* both 64-sample halves of the window at once: every gate is two words wide */
+        for (uint32_t i = 0; i < G; ++i) {
+            const uint32_t g = J->order[i];
+            const uint64_t o = d->child_off[g]; const uint32_t f = (uint32_t)(d->child_off[g + 1] - o);
+            const uint32_t* idx = J->edge_idx + o; const uint64_t* cm = J->edge_mask + o;
+            uint64_t r0 = 0, r1 = 0;
+#define ARG0(j) (val[2 * (size_t)idx[j]] ^ cm[j])
+#define ARG1(j) (val[2 * (size_t)idx[j] + 1] ^ cm[j])
+            switch (d->op[g]) {
+                case CANOPY_AND: case CANOPY_NAND:
+                    r0 = r1 = ~0ull; for (uint32_t j = 0; j < f; ++j) { r0 &= ARG0(j); r1 &= ARG1(j); }
+                    if (d->op[g] == CANOPY_NAND) { r0 = ~r0; r1 = ~r1; }
+                    break;
+                case CANOPY_OR: case CANOPY_NOR:
+                    for (uint32_t j = 0; j < f; ++j) { r0 |= ARG0(j); r1 |= ARG1(j); }
+                    if (d->op[g] == CANOPY_NOR) { r0 = ~r0; r1 = ~r1; }
+                    break;
+                case CANOPY_XOR:  r0 = ARG0(0) ^ ARG0(1); r1 = ARG1(0) ^ ARG1(1); break;
+                case CANOPY_IFF:  r0 = ~(ARG0(0) ^ ARG0(1)); r1 = ~(ARG1(0) ^ ARG1(1)); break;
+                case CANOPY_IMPLY: r0 = ~ARG0(0) | ARG0(1); r1 = ~ARG1(0) | ARG1(1); break;
+                case CANOPY_NOT:  r0 = ~ARG0(0); r1 = ~ARG1(0); break;
+                case CANOPY_NULL: r0 = ARG0(0); r1 = ARG1(0); break;
+                case CANOPY_ATLEAST: case CANOPY_CARDINALITY: {
+                    for (uint32_t j = 0; j < f; ++j) { x[j] = ARG0(j); x[maxf + j] = ARG1(j); }
+                    const unsigned hi = d->op[g] == CANOPY_ATLEAST ? 0xFFFFu : d->kmax[g];
+                    r0 = packed_count_range(x, f, d->kmin[g], hi); r1 = packed_count_range(x + maxf, f, d->kmin[g], hi);
+                    break;
+                }
+                default: break;
+            }
+#undef ARG0
+#undef ARG1
+            val[2 * ((size_t)B + g)] = r0; val[2 * ((size_t)B + g) + 1] = r1;
+        }
         for (int h = 0; h < 2; ++h) {
             if (!mask[h]) continue;
-            for (uint32_t i = 0; i < G; ++i) {
-                uint32_t g = J->order[i];
-                uint64_t o = d->child_off[g]; uint32_t f = (uint32_t)(d->child_off[g + 1] - o);
-                for (uint32_t j = 0; j < f; ++j) {
-                    uint32_t c = d->child[o + j]; uint32_t id = c & CANOPY_CHILD_ID_MASK;
-                    uint64_t v = id == CANOPY_CONST_TRUE ? ~0ull : id == CANOPY_CONST_FALSE ? 0 : val[2 * (size_t)id + h];
-                    x[j] = (c & CANOPY_CHILD_COMPLEMENT) ? ~v : v;
-                }
-                uint64_t r = 0;
-                switch (d->op[g]) {
-                    case CANOPY_AND:  r = ~0ull; for (uint32_t j = 0; j < f; ++j) r &= x[j]; break;
-                    case CANOPY_NAND: r = ~0ull; for (uint32_t j = 0; j < f; ++j) r &= x[j]; r = ~r; break;
-                    case CANOPY_OR:   r = 0; for (uint32_t j = 0; j < f; ++j) r |= x[j]; break;
-                    case CANOPY_NOR:  r = 0; for (uint32_t j = 0; j < f; ++j) r |= x[j]; r = ~r; break;
-                    case CANOPY_XOR:  r = x[0] ^ x[1]; break;
-                    case CANOPY_IFF:  r = ~(x[0] ^ x[1]); break;
-                    case CANOPY_IMPLY: r = ~x[0] | x[1]; break;
-                    case CANOPY_NOT:  r = ~x[0]; break;
-                    case CANOPY_NULL: r = x[0]; break;
-                    case CANOPY_ATLEAST: r = packed_count_range(x, f, d->kmin[g], 0xFFFFu); break;
-                    case CANOPY_CARDINALITY: r = packed_count_range(x, f, d->kmin[g], d->kmax[g]); break;
-                    default: r = 0;
-                }
-                val[2 * ((size_t)B + g) + h] = r;
-            }
             for (uint32_t r = 0; r < d->n_roots; ++r)
                 J->tallies[r] += (uint64_t)__builtin_popcountll(val[2 * (size_t)d->roots[r] + h] & mask[h]);
             if (J->tally_all)
@@ -702,11 +750,19 @@ int oracle_mc_packed(const canopy_graph_desc* d, uint64_t seed, uint64_t begin, 
     if (n == 0) { free(order); free(kind); free(thr); free(used); return 0; }
     uint64_t first_group = begin / 128, last_group = (begin + n - 1) / 128;
     uint64_t* tab = sparse_tables(spec, bits, B, kind, thr);
+    uint32_t* edge_idx = (uint32_t*)malloc(sizeof(uint32_t) * (d->n_edges ? d->n_edges : 1));
+    uint64_t* edge_mask = (uint64_t*)malloc(sizeof(uint64_t) * (d->n_edges ? d->n_edges : 1));
+    for (uint64_t i = 0; i < d->n_edges; ++i) {
+        const uint32_t c = d->child[i], id = c & CANOPY_CHILD_ID_MASK;
+        edge_idx[i] = id == CANOPY_CONST_TRUE ? B + G + 1 : id == CANOPY_CONST_FALSE ? B + G : id;
+        edge_mask[i] = (c & CANOPY_CHILD_COMPLEMENT) ? ~0ull : 0ull;
+    }
     packed_job* jobs = (packed_job*)calloc((size_t)nthreads, sizeof(packed_job));
     pthread_t* th = (pthread_t*)malloc(sizeof(pthread_t) * (size_t)nthreads);
     for (int t = 0; t < nthreads; ++t) {
         packed_job* J = &jobs[t];
         J->d = d; J->order = order; J->kind = kind; J->thr = thr; J->used = used; J->tab = tab;
+        J->edge_idx = edge_idx; J->edge_mask = edge_mask;
         J->seed = seed; J->begin = begin; J->n = n; J->tally_all = tally_all; J->bits = bits; J->spec = spec;
         J->first_group = first_group; J->n_groups = last_group - first_group + 1;
         J->tid = t; J->nthreads = nthreads;
@@ -718,7 +774,7 @@ int oracle_mc_packed(const canopy_graph_desc* d, uint64_t seed, uint64_t begin, 
         for (size_t i = 0; i < nt; ++i) tallies[i] += jobs[t].tallies[i];
         free(jobs[t].tallies);
     }
-    free(jobs); free(th); free(order); free(kind); free(thr); free(used); free(tab);
+    free(jobs); free(th); free(order); free(kind); free(thr); free(used); free(tab); free(edge_idx); free(edge_mask);
     return 0;
 }
 

@@ -61,6 +61,15 @@ def philox4x32_10(ctr, key):
     return [int(x) for x in o]
 
 
+def philox_batch8(a0: int, a1: int, a2: int, c3, key):
+    """The eight-lane Philox of the timed CPU port: calls (a0, a1, a2, c3[i]); returns eight 4-word outputs."""
+    c = (C.c_uint32 * 8)(*[int(x) & 0xFFFFFFFF for x in c3])
+    k = (C.c_uint32 * 2)(*[int(x) & 0xFFFFFFFF for x in key])
+    o = (C.c_uint32 * 32)()
+    lib().oracle_philox_batch8(C.c_uint32(a0), C.c_uint32(a1), C.c_uint32(a2), c, k, o)
+    return [[int(o[w * 8 + i]) for w in range(4)] for i in range(8)]
+
+
 def threshold(p: float, bits: int = 32):
     t = C.c_uint64()
     kind = lib().oracle_threshold(p, bits, C.byref(t))

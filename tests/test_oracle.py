@@ -144,3 +144,15 @@ def test_cycle_is_reported():
     b.root(g1)
     with pytest.raises(ValueError, match="cycle"):
         O.mc_scalar(b.build(), 0, 0, 10)
+
+
+def test_vectorised_philox_of_the_cpu_port_equals_the_scalar_one():
+    import random
+    rng = random.Random(3)
+    for _ in range(50):
+        a = [rng.getrandbits(32) for _ in range(3)]
+        c3 = [rng.getrandbits(32) for _ in range(8)]
+        key = [rng.getrandbits(32), rng.getrandbits(32)]
+        got = O.philox_batch8(a[0], a[1], a[2], c3, key)
+        for i in range(8):
+            assert got[i] == O.philox4x32_10([a[0], a[1], a[2], c3[i]], key)
