@@ -337,9 +337,9 @@ static std::vector<uint32_t> small_children(const Lowered& L) {
     const uint32_t n_ev = L.n_events();
     std::vector<uint32_t> pos(n_ev);
     for (uint32_t i = 0; i < n_ev; ++i) pos[L.event_perm.empty() ? i : L.event_perm[i]] = i;
-    std::vector<uint32_t> out(L.child.size());
-    for (size_t c = 0; c < L.child.size(); ++c) {
-        const uint32_t code = L.child[c], node = code & 0x7FFFFFFFu;
+    std::vector<uint32_t> out(L.dev_child.size());   // same offsets as dev_rec.child_off
+    for (size_t c = 0; c < L.dev_child.size(); ++c) {
+        const uint32_t code = L.dev_child[c], node = code & 0x7FFFFFFFu;
         out[c] = (node < n_ev ? pos[node] : node) | (code & 0x80000000u);
     }
     return out;
@@ -364,9 +364,9 @@ static DeviceState* get_state(canopy_plan* plan, int device) {
         static_assert(sizeof(GateRec) == sizeof(uint4), "GateRec must be 16 bytes");
         ArenaPlan A;
         A.add(s->ev_orig, L.event_orig); A.add(s->thr32, L.event_thr32); A.add(s->thr64, L.event_thr64);
-        A.add(s->child, L.child); A.add(s->layer_off, L.layer_off); A.add(s->tally_gate, L.tally_gate);
+        A.add(s->child, L.dev_child); A.add(s->layer_off, L.layer_off); A.add(s->tally_gate, L.tally_gate);
         A.add(s->wide_off, L.wide_off); A.add(s->split, L.split); A.add(s->split_child, L.split_child);
-        A.add(s->tally_kind, L.tally_kind); A.add(s->grec, L.gate_rec);
+        A.add(s->tally_kind, L.tally_kind); A.add(s->grec, L.dev_rec);
         A.add(s->ev_perm, L.event_perm);
         const std::vector<uint32_t> csmall = small_eligible(L) ? small_children(L) : std::vector<uint32_t>();
         A.add(s->child_small, csmall);
@@ -708,7 +708,7 @@ void refresh_thresholds(canopy_plan* plan) {
         }
         if (!L.event_perm.empty()) {   // spec 4: sampler order and tables follow the thresholds (sizes do not change)
             CUDA_CHECK(cudaMemcpy(s->ev_perm, L.event_perm.data(), L.event_perm.size() * 4, cudaMemcpyHostToDevice));
-            if (small_eligible(L) && !L.child.empty()) {   // the fused path's row indices follow the sampler's order
+            if (small_eligible(L) && !L.dev_child.empty()) {   // the fused path's row indices follow the sampler's order
                 const std::vector<uint32_t> cs = small_children(L);
                 CUDA_CHECK(cudaMemcpy(s->child_small, cs.data(), cs.size() * 4, cudaMemcpyHostToDevice));
             }

@@ -376,6 +376,8 @@ void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lower
         const uint32_t nl = max_level;
         L.wide_off.resize(nl); L.split.assign((size_t)nl * (kGateWarps + 1), 0);
         L.split_child.assign((size_t)nl * (kGateWarps + 1), 0);
+        L.dev_rec = L.gate_rec;
+        L.dev_child.clear(); L.dev_child.reserve(L.child.size() + (size_t)nl * 4 * (kGateWarps + 1));
         for (uint32_t l = 0; l < nl; ++l) {
             const uint32_t a = L.layer_off[l], b = L.layer_off[l + 1];
             uint32_t wv = b;
@@ -389,8 +391,25 @@ void lower_graph(const canopy_graph_desc& d, const canopy_plan_opts& opts, Lower
                 sp[w] = a + (uint32_t)(std::lower_bound(cost.begin(), cost.end(), target) - cost.begin());
             }
             sp[0] = a; sp[kGateWarps] = wv;
+            // Device child stream of the layer: the runs of the kGateWarps warps one after the other, each padded to a whole
+            // number of four-row groups (the pad repeats the run's first row: fetched with its group, never read), then
+            // the arguments of the layer's wide gates.  Every run therefore starts on a 16-byte boundary of dev_child[]
+            // and the walk reads the four codes of a group with one 128-bit load.
             uint32_t* sc = &L.split_child[(size_t)l * (kGateWarps + 1)];
-            for (uint32_t w = 0; w <= kGateWarps; ++w) sc[w] = L.gate_child_off[sp[w]];
+            for (uint32_t w = 0; w < kGateWarps; ++w) {
+                sc[w] = (uint32_t)L.dev_child.size();
+                for (uint32_t g = sp[w]; g < sp[w + 1]; ++g) {
+                    L.dev_rec[g].child_off = (uint32_t)L.dev_child.size();
+                    L.dev_child.insert(L.dev_child.end(), L.child.begin() + L.gate_child_off[g], L.child.begin() + L.gate_child_off[g + 1]);
+                }
+                while ((L.dev_child.size() - sc[w]) % 4u) L.dev_child.push_back(L.dev_child[sc[w]] & 0x7FFFFFFFu);
+            }
+            sc[kGateWarps] = (uint32_t)L.dev_child.size();
+            for (uint32_t g = wv; g < b; ++g) {
+                L.dev_rec[g].child_off = (uint32_t)L.dev_child.size();
+                L.dev_child.insert(L.dev_child.end(), L.child.begin() + L.gate_child_off[g], L.child.begin() + L.gate_child_off[g + 1]);
+            }
+            while (L.dev_child.size() % 4u) L.dev_child.push_back(0u);
         }
     }
     // ---- tally mapping -------------------------------------------------------------------------------

@@ -79,7 +79,12 @@ struct Lowered {
     std::vector<uint32_t> layer_off;       // [n_layers+1]
     std::vector<uint32_t> wide_off;        // [n_layers] first wide count gate of the layer (== layer end if none)
     std::vector<uint32_t> split;           // [n_layers][kGateWarps+1] equal-cost chunks of the ring-path gates
-    std::vector<uint32_t> split_child;     // [n_layers][kGateWarps+1] offsets into child[] at the same cut points
+    std::vector<uint32_t> split_child;     // [n_layers][kGateWarps+1] run w of the layer is dev_child[split_child[w], split_child[w+1])
+    // What the kernels read: gate_rec with child_off pointing into dev_child, and the child codes laid out per layer and
+    // per warp run, every run padded to a multiple of four codes (lowering.cpp).  `child` / `gate_rec` above stay the
+    // canonical form (plan view, fingerprint).
+    std::vector<GateRec> dev_rec;
+    std::vector<uint32_t> dev_child;
     // output mapping: user-visible tallies -> device gate tallies
     std::vector<uint8_t> tally_kind;
     std::vector<uint32_t> tally_gate;

@@ -219,67 +219,56 @@ struct RowRing {
     const uint4* base;          // this slab's rows
     const CUtensorMap* tmap;    // G4: tensor map of the value buffer, rows of kRowBytes
     uint32_t row0;              // G4: tensor row of node 0 of this slab
-    const uint32_t* ids;        // child + c0: the warp's run of child codes for this layer
+    const uint4* ids;           // the warp's run of child codes for this layer, four per group (the lowering pads every run)
     uint32_t ring;              // shared address of slot 0 of this warp's ring
     uint32_t bars;              // shared address of mbarrier 0 of this warp's ring
     uint32_t lane_off;          // lane * 16
-    uint32_t lane;
-    uint32_t total;             // rows in the run
     uint32_t n_groups;          // groups in the run
     uint32_t k_cur;             // groups of the run handed to the consumer so far
-    uint32_t gi_next;           // ring group the next consumed group sits in
-    uint32_t phase;             // bit g = parity of the phase the consumer waits for next on ring group g
+    uint32_t n_used;            // ring groups consumed since the kernel started: group gi = n_used & (kRingGroups-1), phase parity from the rest
     uint32_t cur;               // shared address of this lane's 16 bytes of the next row to read
     uint32_t in_group;          // rows of the current group not read yet
-    uint32_t idreg, idnext;     // child codes of rows [32k, 32k+32) of the run (and of the next 32), one per lane
+    uint4 codes;                // child codes of the group that will be requested next (loaded one request ahead)
 
     __device__ __forceinline__ void issue_group(uint32_t k, uint32_t gi) {  // request rows [4k, 4k+4) of the run into ring group gi
-        const uint32_t i = k * kGroupRows;
-        if ((i & 31u) == 8u) idnext = (i + 24u + lane < total) ? __ldg(ids + i + 24u + lane) : 0u;  // codes of the next 32 rows
-        if ((i & 31u) == 0u && i) idreg = idnext;
-        const uint32_t cnt = min(kGroupRows, total - i);
-        uint32_t code[kGroupRows];
-#pragma unroll
-        for (uint32_t r = 0; r < kGroupRows; ++r) code[r] = __shfl_sync(0xFFFFFFFFu, idreg, (i + r) & 31u);
+        static_assert(kGroupRows == 4, "a group is the four codes of one 128-bit load");
+        const uint4 c = codes;
+        if (k + 1 < n_groups) codes = __ldg(ids + k + 1);   // warp-uniform address: one broadcast load, needed one request later
+        const uint32_t bar = bars + gi * 8u;
+        const uint32_t dst = ring + gi * (kGroupRows * kRowBytes);
         if (G4) {
             // one tensor copy gathers the four rows of the group (tile::gather4: a column offset and four row
-            // coordinates; rows land back to back).  A short last group repeats its first row: always 4 rows, 4 KB.
-            static_assert(!G4 || kGroupRows == 4, "tile::gather4 moves four rows");
-            uint32_t row[4];
-#pragma unroll
-            for (uint32_t r = 0; r < 4; ++r) row[r] = row0 + ((r < cnt ? code[r] : code[0]) & 0x7FFFFFFFu);
+            // coordinates; rows land back to back)
             if (elect_one()) {
-                const uint32_t bar = bars + gi * 8u;
-                const uint32_t dst = ring + gi * (kGroupRows * kRowBytes);
                 mbar_expect_tx(bar, kGroupRows * kRowBytes);
                 asm volatile("cp.async.bulk.tensor.2d.shared::cta.global.tile::gather4.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5, %6}], [%7];"
-                             ::"r"(dst), "l"(tmap), "r"(0), "r"(row[0]), "r"(row[1]), "r"(row[2]), "r"(row[3]), "r"(bar) : "memory");
+                             ::"r"(dst), "l"(tmap), "r"(0), "r"(row0 + (c.x & 0x7FFFFFFFu)), "r"(row0 + (c.y & 0x7FFFFFFFu)),
+                               "r"(row0 + (c.z & 0x7FFFFFFFu)), "r"(row0 + (c.w & 0x7FFFFFFFu)), "r"(bar) : "memory");
             }
         } else if (elect_one()) {
-            const uint32_t bar = bars + gi * 8u;
-            const uint32_t dst = ring + gi * (kGroupRows * kRowBytes);
-            mbar_expect_tx(bar, cnt * kRowBytes);
-#pragma unroll
-            for (uint32_t r = 0; r < kGroupRows; ++r)
-                if (r < cnt) bulk_g2s(dst + r * kRowBytes, base + (size_t)(code[r] & 0x7FFFFFFFu) * kRowVec, kRowBytes, bar);
+            mbar_expect_tx(bar, kGroupRows * kRowBytes);
+            bulk_g2s(dst, base + (size_t)(c.x & 0x7FFFFFFFu) * kRowVec, kRowBytes, bar);
+            bulk_g2s(dst + kRowBytes, base + (size_t)(c.y & 0x7FFFFFFFu) * kRowVec, kRowBytes, bar);
+            bulk_g2s(dst + 2 * kRowBytes, base + (size_t)(c.z & 0x7FFFFFFFu) * kRowVec, kRowBytes, bar);
+            bulk_g2s(dst + 3 * kRowBytes, base + (size_t)(c.w & 0x7FFFFFFFu) * kRowVec, kRowBytes, bar);
         }
     }
-    __device__ __forceinline__ void begin(const uint4* base_, const uint32_t* ids_, uint32_t total_) {
-        base = base_; ids = ids_; total = total_; k_cur = 0; in_group = 0;
-        n_groups = (total + kGroupRows - 1) / kGroupRows;
-        idreg = lane < total ? __ldg(ids + lane) : 0u; idnext = 0u;
+    __device__ __forceinline__ void begin(const uint4* base_, const uint32_t* ids_, uint32_t total_) {   // total_: multiple of 4
+        base = base_; ids = reinterpret_cast<const uint4*>(ids_); k_cur = 0; in_group = 0;
+        n_groups = total_ / kGroupRows;
+        if (n_groups) codes = __ldg(ids);
         const uint32_t ng = min(n_groups, kRingGroups);
-        for (uint32_t k = 0; k < ng; ++k) issue_group(k, (gi_next + k) & (kRingGroups - 1));
+        for (uint32_t k = 0; k < ng; ++k) issue_group(k, (n_used + k) & (kRingGroups - 1));
     }
     __device__ __forceinline__ void advance() {  // current group exhausted: recycle it, wait for the next one
-        const uint32_t gi = gi_next;
-        gi_next = (gi_next + 1) & (kRingGroups - 1);
+        const uint32_t gi = n_used & (kRingGroups - 1);
         // the group read before this one is free now (its values have been consumed by the ALU): refill it
         if (k_cur && k_cur - 1 + kRingGroups < n_groups) issue_group(k_cur - 1 + kRingGroups, (gi - 1) & (kRingGroups - 1));
-        mbar_wait(bars + gi * 8u, (phase >> gi) & 1u);
-        phase ^= 1u << gi;
+        static_assert((kRingGroups & (kRingGroups - 1)) == 0, "ring groups: a power of two");
+        mbar_wait(bars + gi * 8u, (n_used / kRingGroups) & 1u);   // ring group gi is on its (n_used / kRingGroups)-th use
+        ++n_used;
         cur = ring + gi * (kGroupRows * kRowBytes) + lane_off;
-        in_group = min(kGroupRows, total - k_cur * kGroupRows);
+        in_group = kGroupRows;
         ++k_cur;
     }
     __device__ __forceinline__ Row pop() {
@@ -290,14 +279,28 @@ struct RowRing {
         cur += kRowBytes; --in_group;
         return v;
     }
+    __device__ __forceinline__ void pop2(Row& a, Row& b) {   // two rows of the current group (in_group >= 2): one bookkeeping step
+#pragma unroll
+        for (uint32_t h = 0; h < kRowHalves; ++h) { a.h[h] = lds128(cur + h * 512u); b.h[h] = lds128(cur + kRowBytes + h * 512u); }
+        cur += 2 * kRowBytes; in_group -= 2;
+    }
 };
 
 template <int OP, class RR>
 __device__ __forceinline__ Row ring_simple(RR& R, uint32_t n_plain, uint32_t n_comp) {
     Row acc = splat<Row>(OP == kDevAnd ? 0xFFFFFFFFu : 0u);
-    for (uint32_t j = 0; j < n_plain; ++j) {
-        const Row v = R.pop();
-        acc = OP == kDevAnd ? and4(acc, v) : OP == kDevOr ? or4(acc, v) : xor4(acc, v);
+    uint32_t j = 0;
+    while (j < n_plain) {
+        if (R.in_group >= 2u && j + 2u <= n_plain) {   // two rows per trip while the group and the gate both have them
+            Row a, b;
+            R.pop2(a, b);
+            acc = OP == kDevAnd ? and4(acc, and4(a, b)) : OP == kDevOr ? or4(acc, or4(a, b)) : xor4(acc, xor4(a, b));
+            j += 2u;
+        } else {
+            const Row v = R.pop();
+            acc = OP == kDevAnd ? and4(acc, v) : OP == kDevOr ? or4(acc, v) : xor4(acc, v);
+            ++j;
+        }
     }
     for (uint32_t j = 0; j < n_comp; ++j) {
         const Row v = xors4(R.pop(), 0xFFFFFFFFu);
@@ -306,14 +309,43 @@ __device__ __forceinline__ Row ring_simple(RR& R, uint32_t n_plain, uint32_t n_c
     return acc;
 }
 
+// sum and carry of a full adder on every bit lane: one LOP3 each (0x96, 0xE8)
+__device__ __forceinline__ uint4 xor3(uint4 a, uint4 b, uint4 c) { return make_uint4(a.x ^ b.x ^ c.x, a.y ^ b.y ^ c.y, a.z ^ b.z ^ c.z, a.w ^ b.w ^ c.w); }
+__device__ __forceinline__ uint32_t maj1(uint32_t a, uint32_t b, uint32_t c) { return (a & b) | (c & (a | b)); }
+__device__ __forceinline__ uint4 maj3(uint4 a, uint4 b, uint4 c) { return make_uint4(maj1(a.x, b.x, c.x), maj1(a.y, b.y, c.y), maj1(a.z, b.z, c.z), maj1(a.w, b.w, c.w)); }
+__device__ __forceinline__ Row xor3(Row a, Row b, Row c) { Row r; _Pragma("unroll") for (uint32_t i = 0; i < kRowHalves; ++i) r.h[i] = xor3(a.h[i], b.h[i], c.h[i]); return r; }
+__device__ __forceinline__ Row maj3(Row a, Row b, Row c) { Row r; _Pragma("unroll") for (uint32_t i = 0; i < kRowHalves; ++i) r.h[i] = maj3(a.h[i], b.h[i], c.h[i]); return r; }
+
+// count-in-range over the next n rows of the ring with a bit-sliced counter of P planes.  Inputs are absorbed four at a time
+// through carry-save adders -- two full adders into plane 0, one into plane 1, and only their carry ripples through planes
+// 2 .. P-1 -- which costs 6 + 2 (P - 2) LOP3 per word for four inputs instead of 8 P with a ripple counter per input
+// (P = 9: 5 instead of 18 per input); the up to three inputs left over ripple one by one.
 template <int P, class RR>
 __device__ __forceinline__ Row ring_range(RR& R, uint32_t n_plain, uint32_t n_comp, uint32_t lo, uint32_t hi) {
     Row pl[P];
 #pragma unroll
     for (int p = 0; p < P; ++p) pl[p] = splat<Row>(0u);
     const uint32_t n = n_plain + n_comp;
-    for (uint32_t j = 0; j < n; ++j) {
-        Row carry = xors4(R.pop(), j < n_plain ? 0u : 0xFFFFFFFFu);
+    uint32_t j = 0;
+    auto next = [&]() { const Row v = xors4(R.pop(), j < n_plain ? 0u : 0xFFFFFFFFu); ++j; return v; };
+    while (j + 4u <= n) {
+        Row a = next(), b = next();
+        const Row tA = maj3(pl[0], a, b);
+        pl[0] = xor3(pl[0], a, b);
+        a = next(); b = next();
+        const Row tB = maj3(pl[0], a, b);
+        pl[0] = xor3(pl[0], a, b);
+        Row carry = maj3(pl[1], tA, tB);
+        pl[1] = xor3(pl[1], tA, tB);
+#pragma unroll
+        for (int p = 2; p < P; ++p) {
+            const Row t = and4(pl[p], carry);
+            pl[p] = xor4(pl[p], carry);
+            carry = t;
+        }
+    }
+    while (j < n) {
+        Row carry = next();
 #pragma unroll
         for (int p = 0; p < P; ++p) {
             const Row t = and4(pl[p], carry);
@@ -383,7 +415,7 @@ gate_ring_kernel_t(const __grid_constant__ CUtensorMap vmap, uint4* __restrict__
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     RowRing<G4> R;
     R.tmap = &vmap; R.row0 = 0;
-    R.lane = lane; R.lane_off = lane * 16u; R.gi_next = 0; R.phase = 0;
+    R.lane_off = lane * 16u; R.n_used = 0;
     R.ring = smem_u32(smem) + warp * (kRingSlots * kRowBytes);
     R.bars = smem_u32(bars) + warp * (kRingGroups * 8u);
 
