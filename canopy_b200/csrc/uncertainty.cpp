@@ -3,6 +3,7 @@
 // Boundary: the canopy_psource_* / canopy_uncertainty_run entries of include/canopy.h.
 #include <algorithm>
 #include <cmath>
+#include <future>
 #include <memory>
 #include <new>
 #include <string>
@@ -161,8 +162,15 @@ canopy_status canopy_uncertainty_run(canopy_plan* plan, const canopy_psource* sr
             canopy_plan* plan; const std::vector<double>& p;
             ~Restore() { try { std::lock_guard<std::mutex> lock(plan->mu); requantise(plan->low, p.data(), (uint32_t)p.size()); refresh_thresholds(plan); } catch (...) {} }
         } restore{plan, mean_p};
+        // the draws of trial t + 1 are made on a helper thread while the device runs trial t (100k lognormal draws cost 9 ms
+        // of host time, an inner run of 2^22 samples of c4 50 ms)
+        std::vector<double> p_next(nb), scratch_next;
+        auto draw = [&](uint64_t t, std::vector<double>& sc, std::vector<double>& out) { source_p(*src, true, opts->seed, opts->first_trial + t, sc, out.data()); };
+        std::future<void> pending = std::async(std::launch::async, draw, (uint64_t)0, std::ref(scratch_next), std::ref(p_next));
         for (uint64_t t = 0; t < T; ++t) {
-            source_p(*src, true, opts->seed, opts->first_trial + t, scratch, p.data());
+            pending.get();   // rethrows what the draw threw
+            p.swap(p_next);
+            if (t + 1 < T) pending = std::async(std::launch::async, draw, t + 1, std::ref(scratch_next), std::ref(p_next));
             for (uint32_t i = 0; i < nb; ++i)
                 p[i] = L.event_class[i] == 2 ? std::fmin(p_hi, std::fmax(p_lo, p[i])) : mean_p[i];
             {
