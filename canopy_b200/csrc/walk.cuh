@@ -115,21 +115,20 @@ __device__ __forceinline__ uint32_t valid_mask32(uint64_t s, uint64_t begin, uin
 constexpr int kGateThreads = kGateWarps * 32;
 
 // ================================================================================================
-// Ring gate kernel (slab walker, TMA-bulk staging).
+// Ring gate kernel (slab walker, TMA staging).
 //
-// Same decomposition as gate_kernel -- one CTA walks every layer of one slab, __syncthreads() between
-// layers -- but child rows are no longer loaded into registers.  Each warp owns a ring of kRingSlots
-// 512-byte row slots in shared memory and streams the child rows of its share of the layer through it with
-// `cp.async.bulk.shared::cluster.global` (SASS UBLKCP), one copy per row, each completing on the slot's
-// own mbarrier.  The lowering cuts every layer into kGateWarps contiguous runs of equal cost
-// (Lowered::split / split_child), so the rows a warp needs are simply child[c0..c1) in order, independent
-// of gate boundaries: the producer side is a linear stream, the consumer side walks the gates and pops rows.
-// A row is re-requested into a slot one pop after the slot was read, so kRingSlots-1 rows (7.5 KB per warp,
-// 180 KB per SM at 3 CTAs) are in flight without holding a single register.
-// Arguments of a gate come plain-first, complemented-last (GateRec::n_children >> 16 = #complemented), so
-// the consumer needs no per-row flag.  Count gates use uint4 bit planes straight from shared memory
-// (3/6/9 planes, one pass); fan-in >= kWideFanin count gates sit at the end of the layer and take the
-// multi-pass register path of gate_kernel.
+// One CTA walks every layer of one slab, __syncthreads() between layers; child rows are never loaded into registers by
+// address.  Each warp owns a ring of kRingSlots 1-KB row slots in shared memory (kRingGroups groups of kGroupRows rows)
+// and streams the child rows of its share of the layer through it, one group per copy: a tile::gather4 tensor copy
+// (SASS UTMALDG.2D.GATHER4: four row coordinates, rows land back to back) or, for buffers of more than 2^31 rows, one
+// cp.async.bulk per row (UBLKCP), completing on the group's mbarrier.  The lowering cuts every layer into kGateWarps
+// contiguous runs of equal cost and lays their child codes out run by run, every run padded to whole groups
+// (Lowered::split / split_child / dev_child), so the producer side is a linear stream of 128-bit code loads independent
+// of gate boundaries, and the consumer side walks the gates and pops rows.  A group is re-requested one group after it
+// was read, so kRingSlots - kGroupRows rows per warp (64 KB per CTA in all) are in flight without holding a register.
+// Arguments of a gate come plain-first, complemented-last (GateRec::n_children >> 16 = #complemented), so the consumer
+// needs no per-row flag.  Count gates keep uint4 bit planes in registers (3/6/9 planes, carry-save adders); count gates
+// with fan-in >= kWideFanin sit at the end of the layer and take a multi-pass register path (eval_range).
 // ================================================================================================
 #ifndef CANOPY_RING_GROUPS
 #define CANOPY_RING_GROUPS 2
@@ -208,12 +207,10 @@ __device__ __forceinline__ uint32_t popc_masked(Row r, Row m) {
     return c;
 }
 
-// Per-warp stream of child rows through the shared-memory ring.  Rows travel in groups of kGroupRows
-// consecutive rows of the run: one mbarrier phase (one expect_tx, one try_wait) per group, so the
-// ~90-cycle mbarrier round trip and the copy-issue sequence are paid once per 2 KB, not once per row.
-// Every member except `lane_off`/`idreg`/`idnext` is warp-uniform and derived from values the compiler can
-// prove uniform (kernel parameters, blockIdx, loop counters, shuffles from a uniform lane), so the copy
-// operands live in uniform registers and UBLKCP issues without a per-lane serialisation loop.
+// Per-warp stream of child rows through the shared-memory ring.  Rows travel in groups of kGroupRows consecutive rows of
+// the run: one mbarrier phase (one expect_tx, one try_wait) and one copy instruction per group, so the mbarrier round trip
+// and the copy-issue sequence are paid once per 4 KB.  Everything but `lane_off` is warp-uniform (kernel parameters,
+// blockIdx, loop counters, broadcast loads), so the copy operands live in uniform registers; one elected lane issues.
 template <bool G4>
 struct RowRing {
     const uint4* base;          // this slab's rows
