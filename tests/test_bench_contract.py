@@ -46,3 +46,11 @@ def test_reference_arm_loads_no_native_code_of_the_product():
     b = load_mef(os.path.join(ROOT, "examples", "c1_small_ft.xml"))
     for f in ("p", "op", "child_off", "child", "roots"):
         assert np.array_equal(getattr(a, f), getattr(b, f)), f
+
+
+def test_reference_arm_with_64_bit_thresholds():
+    env = dict(os.environ, CANOPY_BENCH_REF_BUDGET_S="1")
+    out = subprocess.check_output([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--workload", "c1",
+                                   "--steps", "1", "--warmup", "0", "--threshold-bits", "64"], env=env, text=True, timeout=300)
+    d = json.loads([l for l in out.splitlines() if l.startswith("{")][0])
+    assert d["dtype"] == "u64" and d["config"]["threshold_bits"] == 64 and d["value"] > 0
