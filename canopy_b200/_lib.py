@@ -89,6 +89,12 @@ class CUncertaintyStats(C.Structure):
                 ("error_factor", C.c_double), ("min", C.c_double), ("max", C.c_double)]
 
 
+class CPlanStreams(C.Structure):
+    _fields_ = [("n_dev_child", C.c_uint32), ("warps", C.c_uint32), ("n_layers", C.c_uint32), ("reserved", C.c_uint32),
+                ("dev_child", C.POINTER(C.c_uint32)), ("gate_child_off", C.POINTER(C.c_uint32)),
+                ("split", C.POINTER(C.c_uint32)), ("split_child", C.POINTER(C.c_uint32))]
+
+
 class CEstimate(C.Structure):
     _fields_ = [("p", C.c_double), ("sigma", C.c_double), ("ci_lo", C.c_double), ("ci_hi", C.c_double)]
 
@@ -139,6 +145,7 @@ SYMBOLS = {
     "canopy_spec_version": (C.c_uint32, []),
     "canopy_sparse_class": (C.c_int, [C.c_uint64, C.POINTER(C.c_uint32)]),
     "canopy_sparse_cdf": (C.c_int, [C.c_uint64, C.c_uint32, C.POINTER(C.c_uint64)]),
+    "canopy_plan_debug_streams": (C.c_int, [C.c_void_p, C.POINTER(CPlanStreams)]),
     "canopy_plan_debug_set_sparse_table": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint64)]),
 }
 

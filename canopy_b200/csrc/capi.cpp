@@ -192,6 +192,19 @@ canopy_status canopy_plan_debug_set_sparse_table(canopy_plan* plan, uint32_t liv
     });
 }
 
+canopy_status canopy_plan_debug_streams(const canopy_plan* plan, canopy_plan_streams* out) {
+    return guard([&] {
+        require(plan && out, "canopy_plan_debug_streams: null argument");
+        const canopy::Lowered& L = plan->low;
+        static thread_local std::vector<uint32_t> off;   // valid until the next call on this thread
+        off.resize(L.dev_rec.size());
+        for (size_t g = 0; g < L.dev_rec.size(); ++g) off[g] = L.dev_rec[g].child_off;
+        out->n_dev_child = (uint32_t)L.dev_child.size(); out->warps = canopy::kGateWarps; out->n_layers = L.n_layers(); out->reserved = 0;
+        out->dev_child = L.dev_child.data(); out->gate_child_off = off.data();
+        out->split = L.split.data(); out->split_child = L.split_child.data();
+    });
+}
+
 canopy_status canopy_mc_sample_words(canopy_plan* plan, const canopy_mc_opts* opts, uint64_t first_word, uint64_t n_words,
                                      uint64_t* words_host) {
     return guard([&] {

@@ -17,6 +17,21 @@ extern "C" {
  * CANOPY_E_INVALID unless the plan samples with spec 4 and the event takes the sparse path. */
 CANOPY_API canopy_status canopy_plan_debug_set_sparse_table(canopy_plan* plan, uint32_t live_event, const uint64_t* cdf);
 
+/* The child stream the gate walk reads (host only; pointers stay valid until canopy_plan_destroy, gate_child_off until the
+ * next call of this function on the same thread): per layer the runs of the
+ * walk's warps one after the other, each padded to a multiple of four codes, then the arguments of the layer's wide gates.
+ * gate_child_off[g] = where gate g's arguments start in dev_child (same order as canopy_plan_view.gate_child);
+ * split / split_child: [n_layers][warps + 1] gate and dev_child offsets of the runs.  Lets the host-logic tests check the
+ * layout without a GPU. */
+typedef struct canopy_plan_streams {
+    uint32_t n_dev_child, warps, n_layers, reserved;
+    const uint32_t* dev_child;
+    const uint32_t* gate_child_off;   /* [n_gates] */
+    const uint32_t* split;
+    const uint32_t* split_child;
+} canopy_plan_streams;
+CANOPY_API canopy_status canopy_plan_debug_streams(const canopy_plan* plan, canopy_plan_streams* out);
+
 #ifdef __cplusplus
 }
 #endif

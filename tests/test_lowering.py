@@ -197,3 +197,40 @@ def test_plan_cache_hits_are_verified_by_content():
     with Plan(g, True) as z:
         assert z.stats["plan_cache_hit"] == 0
     plan_cache_clear()
+
+
+def test_device_child_stream_layout():
+    """The child stream the gate walk reads (csrc/lowering.cpp): per layer the runs of the walk's warps, each a whole number of
+    four-code groups (the pad repeats the run's first row), gate arguments in canonical order inside their run."""
+    import ctypes as C
+    from canopy_b200 import _lib, synth
+    from canopy_b200.engine import Plan
+    for g in (synth.generate(n_basic=300, n_gates=200, n_layers=7, max_fanin=12, seed=5), random_graph(7, n_basic=30, n_gates=80, max_fanin=9)):
+        with Plan(g, tally_all_gates=True) as plan:
+            v = plan.view()
+            st = _lib.CPlanStreams()
+            _lib.check(_lib.lib().canopy_plan_debug_streams(plan._h, C.byref(st)))
+            W, nl, ng = st.warps, st.n_layers, int(v["n_gates"]) if "n_gates" in v else len(v["gate_op"])
+            dev = np.ctypeslib.as_array(st.dev_child, shape=(st.n_dev_child,)).copy()
+            off = np.ctypeslib.as_array(st.gate_child_off, shape=(ng,)).copy()
+            split = np.ctypeslib.as_array(st.split, shape=(nl, W + 1)).copy()
+            sc = np.ctypeslib.as_array(st.split_child, shape=(nl, W + 1)).copy()
+            canon, coff = v["gate_child"], v["gate_child_off"]
+            n_nodes = len(v["event_orig"]) + ng
+            assert st.n_dev_child % 4 == 0 and np.all((dev & 0x7FFFFFFF) < max(n_nodes, 1))
+            for g_i in range(ng):   # every gate's arguments, contiguous and in canonical order
+                n = int(coff[g_i + 1] - coff[g_i])
+                assert np.array_equal(dev[off[g_i]: off[g_i] + n], canon[coff[g_i]: coff[g_i + 1]])
+            for l in range(nl):
+                assert np.all(np.diff(split[l]) >= 0) and split[l, 0] == v["layer_off"][l]
+                for w in range(W):
+                    a, b = int(sc[l, w]), int(sc[l, w + 1])
+                    assert a % 4 == 0 and (b - a) % 4 == 0
+                    gates = range(int(split[l, w]), int(split[l, w + 1]))
+                    real = sum(int(coff[x + 1] - coff[x]) for x in gates)
+                    assert 0 <= (b - a) - real < 4
+                    if gates:
+                        assert off[gates[0]] == a
+                        assert np.all(dev[a + real: b] == (dev[a] & 0x7FFFFFFF))   # the pad: a row that exists, plain
+                    else:
+                        assert a == b
