@@ -545,7 +545,7 @@ def main():
             line["other_configs"] = {n: side_line(n, local, stream, args.sampler, bits=args.threshold_bits) for n in ("c2", "c3") if n != args.workload}
             # the same workload under the other threshold width (64-bit thresholds are what p below 1e-8 needs), a quarter step
             ob = 96 - args.threshold_bits
-            line["other_configs"][f"{args.workload}_u{ob}"] = side_line(args.workload, local, stream, args.sampler, steps=1, bits=ob, samples=max(S // 4, 1 << 20))
+            line["other_configs"][f"{args.workload}_u{ob}"] = side_line(args.workload, local, stream, args.sampler, steps=2, bits=ob, samples=max(S // 4, 1 << 20))
     if rank == 0:
         if args.samples:
             line["config"]["reduced"] = f"--samples {args.samples}: side study, NOT the workload's sample count"
