@@ -338,3 +338,35 @@ def test_private_roles_and_scoped_lookup():
     ok = dup.replace("<define-basic-event name='e'><float value='0.2'/>", "<define-basic-event name='e' role='private'><float value='0.2'/>")
     g2 = load_mef(text=ok)
     assert sorted(g2.basic_names) == ["FT.C.e", "e"]
+
+
+def test_scoped_parameters_and_ccf_group_in_a_component():
+    """Parameters resolve like events (local scope, public id, full path); a CCF group declared in a private component
+    resolves its distribution / factors in the component's scope.  Its members are added to the model only, not to the
+    full-path table (reference initializer.cpp:1324-1339), so members of a PRIVATE group cannot be referred to at all --
+    kept as the reference has it."""
+    def xml(group_role):
+        return model(
+            "<define-fault-tree name='FT'>"
+            "<define-gate name='top'><or><basic-event name='x'/><basic-event name='y'/><gate name='C.two'/></or></define-gate>"
+            "<define-basic-event name='x'><parameter name='FT.C.q'/></define-basic-event>"          # full path into a private scope
+            "<define-basic-event name='y'><parameter name='q'/></define-basic-event>"               # the public q of model-data
+            "<define-component name='C' role='private'>"
+            "  <define-parameter name='q'><float value='0.125'/></define-parameter>"
+            "  <define-parameter name='beta'><float value='0.25'/></define-parameter>"
+            "  <define-gate name='two'><and><basic-event name='m1'/><basic-event name='m2'/></and></define-gate>"
+            f"  <define-CCF-group name='grp' model='beta-factor'{group_role}><members><basic-event name='m1'/><basic-event name='m2'/></members>"
+            "    <distribution><parameter name='q'/></distribution><factor level='2'><parameter name='beta'/></factor></define-CCF-group>"
+            "</define-component></define-fault-tree>"
+            "<model-data><define-parameter name='q'><float value='0.5'/></define-parameter></model-data>")
+    g = load_mef(text=xml(" role='public'"), ccf_analysis=True)
+    p = dict(zip(g.basic_names, g.p))
+    assert p["x"] == 0.125 and p["y"] == 0.5
+    # the group's q and beta are the component's (0.125, 0.25), not the public q
+    assert p["[m1]"] == pytest.approx(0.75 * 0.125) and p["[m2]"] == pytest.approx(0.75 * 0.125)
+    assert p["[m1 m2]"] == pytest.approx(0.25 * 0.125)
+    assert "FT.C.two" in g.gate_names and "m1" in g.gate_names            # the members' proxy OR gates
+    assert np.array_equal(g.meta["psource"].mean(), g.p)                  # the sampled source sees the same scoping
+    with pytest.raises(_lib.CanopyError) as ei:                           # private group: its members have no reachable name
+        load_mef(text=xml(""), ccf_analysis=True)
+    assert ei.value.status == _lib.E_VALIDITY and "Undefined Element" in ei.value.message
