@@ -459,7 +459,7 @@ struct Builder {
             for (auto& k : n.kids) {
                 if (k->name == "distribution") distr = k.get();
                 else if (k->name == "factor") factor_nodes.push_back(k.get());
-                else if (k->name == "factors") for (auto& f : k->kids) if (f->name == "factor") factor_nodes.push_back(f.get());
+                else if (k->name == "factors") { for (auto& f : k->kids) if (f->name == "factor") factor_nodes.push_back(f.get()); }
                 else if (k->name != "members" && !is_meta(*k)) bad(CANOPY_E_UNSUPPORTED, *k, "unexpected element <" + k->name + "> in CCF group " + c.name);
             }
             if (!distr || !first_kid(*distr)) bad(CANOPY_E_VALIDITY, n, "CCF group " + c.name + " has no distribution");
