@@ -109,6 +109,7 @@ SYMBOLS = {
     "canopy_mc_opts_default": (None, [C.POINTER(CMcOpts)]),
     "canopy_mc_run": (C.c_int, [C.c_void_p, C.POINTER(CMcOpts), _u64p, C.POINTER(CMcReport)]),
     "canopy_mc_run_device": (C.c_int, [C.c_void_p, C.POINTER(CMcOpts), C.c_void_p, C.POINTER(CMcReport)]),
+    "canopy_mc_run_static": (C.c_int, [C.c_void_p, C.POINTER(CMcOpts), _u64p, C.c_void_p]),
     "canopy_mc_run_multi": (C.c_int, [C.c_void_p, C.POINTER(CMcOpts), C.POINTER(C.c_int32), C.c_int32, _u64p, C.POINTER(CMcReport)]),
     "canopy_trim_device_cache": (C.c_int, [C.c_int32]),
     "canopy_plan_cache_clear": (C.c_int, []),

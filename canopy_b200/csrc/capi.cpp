@@ -112,6 +112,14 @@ canopy_status canopy_mc_run_device(canopy_plan* plan, const canopy_mc_opts* opts
     });
 }
 
+canopy_status canopy_mc_run_static(canopy_plan* plan, const canopy_mc_opts* opts, uint64_t* tallies_host, uint64_t* tallies_device) {
+    return guard([&] {
+        require(plan && opts, "canopy_mc_run_static: null argument");
+        require(tallies_host || tallies_device || plan->low.tally_kind.empty(), "canopy_mc_run_static: both output pointers are null");
+        canopy::mc_run_static(plan, *opts, tallies_host, tallies_device);
+    });
+}
+
 canopy_status canopy_mc_run_multi(canopy_plan* plan, const canopy_mc_opts* opts, const int32_t* devices, int32_t n_devices,
                                   uint64_t* tallies_host, canopy_mc_report* report) {
     return guard([&] {

@@ -729,4 +729,106 @@ void debug_set_sparse_table(canopy_plan* plan, uint32_t live_event, const uint64
     }
 }
 
+// ================================================================================================
+// canopy_mc_run_static (include/canopy.h): the fused path for callers that must not allocate device memory.
+//
+// Who that is: a library like this one is often loaded INTO somebody else's process -- a plant-monitoring service, a
+// solver, a framework with its own caching allocator -- that claimed the GPU's memory for its own pool at start-up, or
+// that runs under a memory quota (MIG slice, container limit) it has already committed.  A cudaMalloc from a plug-in then
+// fails or eats into a budget it was never given.  Others simply forbid cudaMalloc / cudaFree in their steady-state loop,
+// because both synchronise the whole device and stall every other stream for the duration.  canopy_mc_run() is no use to
+// them on its first run of a plan: that is when it makes the plan resident (cudaMalloc of the plan arena, stream and events).
+//
+// What this path does instead: everything the fused kernel needs in global memory beyond the caller's output -- the device
+// copy of the plan arrays, the count tables of spec 4, the per-gate tally counters, the mapped tallies -- lives in ONE
+// file-scope array that is part of the library's device image.  Every GPU that loads libcanopy holds those
+// CANOPY_STATIC_SCRATCH_BYTES until the process exits, whether or not this entry point is ever called.  Nothing here calls
+// cudaMalloc, cudaFree, cudaStreamCreate or cudaEventCreate.
+//
+// Consequences the caller has to know (repeated in canopy.h):
+//   - one array per device, shared by every call and every plan: a call overwrites what the previous one left, so the plan
+//     image is uploaded and the counters are cleared on EVERY call, and two calls whose GPU work overlaps (different
+//     streams, or device-output calls from two threads) corrupt each other.  The host side is serialised by a mutex per
+//     device; ordering the GPU work is the caller's job.
+//   - the first call on a device resolves the array's device address (below) and sets the kernels' attributes; make that
+//     call before starting any stream capture.
+// ================================================================================================
+static __device__ __align__(256) unsigned char g_static_scratch[CANOPY_STATIC_SCRATCH_BYTES];
+
+struct StaticDev {
+    std::mutex mu;                    // serialises the host side of canopy_mc_run_static per device
+    bool ready = false;
+    unsigned char* base = nullptr;    // DEVICE address of g_static_scratch on this device
+};
+static StaticDev g_static_dev[64];
+
+void mc_run_static(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, uint64_t* tallies_dev) {
+    const DeviceInfo info = device_info(o.device);   // ordinal and sm_100 checks; kernel attributes, once per device
+    CUDA_CHECK(cudaSetDevice(o.device));
+    StaticDev& D = g_static_dev[o.device];
+    std::lock_guard<std::mutex> dev_lock(D.mu);
+    if (!D.ready) {
+        // In host code `g_static_scratch` is only a handle for the symbol, not somewhere a kernel can write: ask the
+        // runtime where the array lives on the device that is current now.
+        void* p = nullptr;
+        CUDA_CHECK(cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p || (reinterpret_cast<uintptr_t>(p) & 255u)) throw Error(CANOPY_E_CUDA, "static scratch array has no usable device address");
+        D.base = static_cast<unsigned char*>(p);
+        D.ready = true;
+    }
+    if (o.sample_begin + o.n_samples < o.sample_begin) throw Error(CANOPY_E_INVALID, "sample range overflows 64 bits");
+    const uint64_t begin = o.sample_begin, end = o.sample_begin + o.n_samples;
+    const uint64_t slab0 = begin / kSlabSamples;
+    const uint64_t total_slabs = o.n_samples ? (end - 1) / kSlabSamples - slab0 + 1 : 0;
+    cudaStream_t st = o.stream ? (cudaStream_t)o.stream : cudaStreamPerThread;   // no library-owned stream: that would be a create
+
+    std::lock_guard<std::mutex> plan_lock(plan->mu);   // the thresholds may be re-quantised by canopy_plan_update_p
+    const Lowered& L = plan->low;
+    if (!small_eligible(L))
+        throw Error(CANOPY_E_UNSUPPORTED, "canopy_mc_run_static runs the fused kernel only: the plan needs at least one live gate, at most " +
+                                              std::to_string(kSmallMaxBytes / kRowBytes) + " live nodes (it has " + std::to_string(L.n_nodes()) +
+                                              ") and a sliced or classed sampler");
+    // Same pieces, same order and alignment as the arena of get_state(), laid over the static array.
+    DeviceState v;   // a view: pointers into the static array, nothing owned
+    v.device = o.device; v.sm_count = info.sm_count;
+    ArenaPlan A;
+    A.add(v.ev_orig, L.event_orig); A.add(v.thr32, L.event_thr32); A.add(v.thr64, L.event_thr64);
+    A.add(v.layer_off, L.layer_off); A.add(v.tally_gate, L.tally_gate); A.add(v.tally_kind, L.tally_kind);
+    A.add(v.grec, L.dev_rec); A.add(v.ev_perm, L.event_perm);
+    const std::vector<uint32_t> csmall = small_children(L);
+    A.add(v.child_small, csmall);
+    if (!L.event_perm.empty()) A.reserve(v.ev_cdf, (size_t)L.n_events() * CANOPY_SPARSE_CDF_LEN * 8);
+    const size_t tally_bytes = (size_t)L.n_gates() * 8;
+    A.reserve(v.gate_tallies, tally_bytes);
+    A.reserve(v.out_tallies, std::max<size_t>(L.tally_kind.size(), 1) * 8);
+    if (A.total > (size_t)CANOPY_STATIC_SCRATCH_BYTES)
+        throw Error(CANOPY_E_UNSUPPORTED, "canopy_mc_run_static: this plan needs " + std::to_string(A.total) + " bytes of device scratch, the static "
+                                              "array holds CANOPY_STATIC_SCRATCH_BYTES = " + std::to_string((size_t)CANOPY_STATIC_SCRATCH_BYTES) +
+                                              "; use canopy_mc_run");
+    std::vector<char> stage(A.upload);
+    for (auto& p : A.pieces) {
+        *p.dst = D.base + p.off;
+        if (p.bytes) std::memcpy(stage.data() + p.off, p.src, p.bytes);
+    }
+    // Pageable source: the call returns once the bytes are in the driver's staging buffer, so `stage` may go out of scope.
+    CUDA_CHECK(cudaMemcpyAsync(D.base, stage.data(), A.upload, cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemsetAsync(v.gate_tallies, 0, tally_bytes, st));   // the kernel adds into these; the last call's counts are still there
+    if (!L.event_perm.empty() && L.n_events()) {
+        sparse_table_kernel<<<(L.n_events() + 127) / 128, 128, 0, st>>>(v.thr64, L.n_events(), v.ev_cdf);
+        CUDA_CHECK(cudaGetLastError());
+    }
+    if (total_slabs) launch_small(&v, L, slab0, total_slabs, begin, end, make_keys(o.seed), st);
+    const uint32_t n_tallies = (uint32_t)L.tally_kind.size();
+    unsigned long long* d_out = tallies_dev ? (unsigned long long*)tallies_dev : v.out_tallies;
+    if (n_tallies) {
+        finalize_kernel<<<(n_tallies + 255) / 256, 256, 0, st>>>(d_out, v.gate_tallies, v.tally_kind, v.tally_gate, n_tallies,
+                                                                (unsigned long long)o.n_samples);
+        CUDA_CHECK(cudaGetLastError());
+    }
+    if (tallies_host) {
+        if (n_tallies) CUDA_CHECK(cudaMemcpyAsync(tallies_host, d_out, (size_t)n_tallies * 8, cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+    }
+}
+
 }  // namespace canopy

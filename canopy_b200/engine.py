@@ -166,6 +166,19 @@ class Plan:
                                                    C.byref(rep) if want_report else None))
         return _report(rep) if want_report else None
 
+    def run_static(self, n_samples: int, seed: int = 0, sample_begin: int = 0, device: int = 0, stream=None,
+                   tallies_ptr: int | None = None, host: bool = True):
+        """canopy_mc_run_static: the fused engine over the library's built-in scratch array, for hosts that cannot let a
+        plug-in allocate device memory (see include/canopy.h for who that is and for the sharing rules: one array per GPU,
+        calls must not overlap on the GPU).  Returns uint64[n_tallies] when `host`, else None (tallies are then left at the
+        caller-owned device address `tallies_ptr`, ordered on `stream`)."""
+        o = self._opts(seed, sample_begin, n_samples, device, 0, stream, False, False)
+        out = np.zeros(max(self.n_tallies, 1), dtype=np.uint64) if host else None
+        _lib.check(_lib.lib().canopy_mc_run_static(
+            self._h, C.byref(o), out.ctypes.data_as(C.POINTER(C.c_uint64)) if host else None,
+            C.c_void_p(tallies_ptr) if tallies_ptr else None))
+        return out[: self.n_tallies] if host else None
+
     def run_multi(self, devices, n_samples: int, seed: int = 0, sample_begin: int = 0, batch_slabs: int = 0,
                   overlap: bool = True):
         """Single-process multi-GPU with one NCCL all-reduce of the tallies (canopy_mc_run_multi)."""

@@ -249,6 +249,45 @@ CANOPY_API canopy_status canopy_mc_run(canopy_plan* plan, const canopy_mc_opts* 
  * ordered on opts->stream: the buffer a collective (NCCL all-reduce) consumes with no host hop. */
 CANOPY_API canopy_status canopy_mc_run_device(canopy_plan* plan, const canopy_mc_opts* opts,
                                               uint64_t* tallies_device, canopy_mc_report* report);
+/* The same tallies as canopy_mc_run / canopy_mc_run_device, computed WITHOUT allocating anything on the device.
+ * (This entry point has no counterpart in the reference, which has no device code at all.)
+ *
+ * Who needs it.  This library gets loaded into other people's processes: a monitoring service or a solver whose own
+ * allocator took the GPU's memory at start-up, a job inside a MIG slice or container quota that is already spoken for, a
+ * control loop that bans cudaMalloc / cudaFree after initialisation because both stall every stream on the device while
+ * they run.  For such a host the first canopy_mc_run of a plan is a problem: that is when the plan is made resident
+ * (cudaMalloc for the plan arrays, a stream, events).  This call never does any of that -- no cudaMalloc, cudaFree,
+ * stream or event creation, on any call, including the first.
+ *
+ * How.  It runs the fused engine (CANOPY_ENGINE_FUSED: sampler, gate walk and tallies in one kernel over shared-memory
+ * rows).  The little global memory that engine needs besides the caller's output -- a device copy of the plan arrays,
+ * the spec-4 count tables, one counter per gate -- sits in a fixed array of CANOPY_STATIC_SCRATCH_BYTES compiled into the
+ * library.  Every GPU on which the library's device code is loaded carries that array until the process exits.
+ *
+ * Limits.  Only plans the fused engine can run: at least one live gate, at most about 200 live nodes (the rows of one slab
+ * must fit in shared memory), sampler spec 2 or 4; and the plan's device image must fit in the array (every plan within
+ * the node limit seen so far does, with room to spare).  Anything larger is refused with CANOPY_E_UNSUPPORTED and a
+ * message that names the size and the limit; use canopy_mc_run for it.  The plan's own `engine` option is not consulted:
+ * tallies do not depend on the engine.
+ *
+ * Arguments.  opts->seed / sample_begin / n_samples / device as for canopy_mc_run.  opts->stream orders the work; NULL means
+ * the calling thread's cudaStreamPerThread (there is no library-owned stream here, creating one would allocate).
+ * batch_slabs / overlap / profile are ignored.  Outputs: tallies_host (uint64[n_tallies], any host memory; the call then
+ * returns after the stream has drained) and/or tallies_device (uint64[n_tallies] in memory the CALLER already owns on
+ * opts->device; with tallies_host == NULL the call returns with the work still queued on the stream).  At least one of
+ * the two must be given unless the plan has no tallies.
+ *
+ * Sharing.  There is ONE array per GPU, used by every call, every plan and every thread, and it keeps whatever the last
+ * call left in it.  The call therefore re-uploads the plan image and zeroes the counters every time (a few tens of KB),
+ * and two calls whose GPU work overlaps in time -- different streams, or device-output calls issued back to back from two
+ * threads -- overwrite each other's counters and give wrong tallies.  Host-side entry is serialised per device; keeping
+ * the GPU work of successive calls in order (same stream, or an event between streams) is up to the caller.
+ *
+ * First call.  The first call on each device looks up the array's device address and sets kernel attributes for that
+ * device.  Make it during initialisation, before any stream capture is begun. */
+#define CANOPY_STATIC_SCRATCH_BYTES (128u * 1024u)
+CANOPY_API canopy_status canopy_mc_run_static(canopy_plan* plan, const canopy_mc_opts* opts,
+                                              uint64_t* tallies_host, uint64_t* tallies_device);
 /* Single-process multi-GPU: shards [sample_begin, +n_samples) into n_devices contiguous counter
  * ranges, one host thread per device, then one ncclAllReduce(ncclUint64, ncclSum) over the tallies. */
 CANOPY_API canopy_status canopy_mc_run_multi(canopy_plan* plan, const canopy_mc_opts* opts,
