@@ -264,26 +264,45 @@ struct Builder {
         return Ex{v, m.tape.add(op, ids)};
     }
     Ex konst(double c) { return Ex{c, m.tape.constant(c)}; }
-    Ex parameter_value(const XNode& at, const std::string& name) {
-        // GetEntity, initializer.cpp:1378-1403: the local scope first, then the public id, or the full path as written
-        auto it = param_idx.end();
-        if (!cur_base.empty()) { it = param_path.find(cur_base + "." + name); if (it == param_path.end()) it = param_idx.end(); }
-        if (it == param_idx.end()) {
-            if (name.find('.') == std::string::npos) it = param_idx.find(name);
-            else { it = param_path.find(name); if (it == param_path.end()) it = param_idx.end(); }
+    // GetEntity, initializer.cpp:1378-1403: the local scope first, then the public id, or the full path as written.
+    const uint32_t* find_parameter(const std::string& name) const {
+        if (!cur_base.empty()) {
+            auto it = param_path.find(cur_base + "." + name);
+            if (it != param_path.end()) return &it->second;
         }
-        if (it == param_idx.end()) bad(CANOPY_E_VALIDITY, at, "Undefined Element Error: parameter " + name);
-        ParamDef& p = params[it->second];
+        if (name.find('.') == std::string::npos) {
+            auto it = param_idx.find(name);
+            return it == param_idx.end() ? nullptr : &it->second;
+        }
+        auto it = param_path.find(name);
+        return it == param_path.end() ? nullptr : &it->second;
+    }
+    Ex define_parameter(uint32_t idx, const XNode& at) {
+        ParamDef& p = params[idx];
         if (p.mark == 2) return Ex{p.value, p.node};   // one node per parameter: sampled once per trial, shared by its users
-        if (p.mark == 1) bad(CANOPY_E_CYCLE, at, "Cycle Error: parameter " + name + " refers to itself");  // cycle.h:219-229
+        if (p.mark == 1) bad(CANOPY_E_CYCLE, at, "Cycle Error: parameter " + p.name + " refers to itself");  // cycle.h:219-229
         p.mark = 1;
         const std::string saved = cur_base;
         cur_base = p.base_path;   // a parameter's own references resolve in ITS scope (initializer.cpp:499-503)
         const Ex x = ev(*p.body, EvalCtx{});
         cur_base = saved;
-        p.value = x.v; p.node = x.id;
-        p.mark = 2;
+        params[idx].value = x.v; params[idx].node = x.id;
+        params[idx].mark = 2;
         return x;
+    }
+    Ex parameter_value(const XNode& at, const std::string& name) {
+        const uint32_t* idx = find_parameter(name);
+        if (!idx) bad(CANOPY_E_VALIDITY, at, "Undefined Element Error: parameter " + name);
+        return define_parameter(*idx, at);
+    }
+    // The reference defines EVERY registered parameter (tbd_, initializer.cpp:668-681), cycle-checks the whole parameter
+    // table and validates every expression (initializer.cpp:1860-1874), used or not.  Those no event reached are compiled
+    // here, after everything else, so that the tape nodes (and with them the deviate streams) of the used ones keep their
+    // numbers.
+    void define_unused_parameters() {
+        for (uint32_t i = 0; i < params.size(); ++i)
+            if (params[i].mark != 2) define_parameter(i, *params[i].body);
+        cur_base.clear();
     }
     std::vector<Ex> eval_args(const XNode& e, const EvalCtx& cx, size_t lo, size_t hi) {
         std::vector<Ex> v;
@@ -843,6 +862,7 @@ struct Builder {
         check_cycles();
         walk_event_trees();
         const uint32_t B = (uint32_t)basics.size(), G = (uint32_t)gates.size();
+
         m.p.resize(B); m.p_node.resize(B); m.basic_names.resize(B);
         for (uint32_t e = 0; e < B; ++e) {
             BasicDef& b = basics[e];
@@ -859,6 +879,7 @@ struct Builder {
             if (!(b.p >= 0.0 && b.p <= 1.0)) throw Error(CANOPY_E_DOMAIN, "Invalid probability value for " + b.name);  // event.cpp:27-33
             m.p[e] = b.p; m.p_node[e] = b.node;
         }
+        define_unused_parameters();
         m.op.resize(G); m.kmin.resize(G); m.kmax.resize(G); m.gate_names.resize(G);
         m.child_off.assign(1, 0);
         for (uint32_t g = 0; g < G; ++g) {

@@ -370,3 +370,34 @@ def test_scoped_parameters_and_ccf_group_in_a_component():
     with pytest.raises(_lib.CanopyError) as ei:                           # private group: its members have no reachable name
         load_mef(text=xml(""), ccf_analysis=True)
     assert ei.value.status == _lib.E_VALIDITY and "Undefined Element" in ei.value.message
+
+
+_UNUSED_PARAM_MODEL = """<opsa-mef>
+<define-fault-tree name="FT"><define-gate name="top"><or><basic-event name="a"/><basic-event name="b"/></or></define-gate></define-fault-tree>
+<model-data>
+  <define-basic-event name="a"><float value="0.1"/></define-basic-event>
+  <define-basic-event name="b"><parameter name="ok"/></define-basic-event>
+  <define-parameter name="ok"><float value="0.2"/></define-parameter>
+  %s
+</model-data></opsa-mef>"""
+
+
+@pytest.mark.parametrize("extra,status,msg", [
+    ('<define-parameter name="u"><parameter name="nope"/></define-parameter>', _lib.E_VALIDITY, "Undefined Element Error"),
+    ('<define-parameter name="u"><parameter name="v"/></define-parameter>'
+     '<define-parameter name="v"><parameter name="u"/></define-parameter>', _lib.E_CYCLE, "Cycle Error"),
+    ('<define-parameter name="u"><div><float value="1"/><float value="0"/></div></define-parameter>', _lib.E_DOMAIN, "Division by 0"),
+])
+def test_parameters_nothing_refers_to_are_still_defined_and_validated(extra, status, msg):
+    """The reference defines every registered parameter, cycle-checks the whole table and validates every expression
+    (initializer.cpp:668-681, 1860-1874): an invalid parameter is an error even when no event uses it."""
+    with pytest.raises(_lib.CanopyError) as e:
+        load_mef(text=_UNUSED_PARAM_MODEL % extra)
+    assert e.value.status == status and msg in e.value.message
+
+
+def test_a_valid_unused_parameter_changes_nothing():
+    g0 = load_mef(text=_UNUSED_PARAM_MODEL % "")
+    g1 = load_mef(text=_UNUSED_PARAM_MODEL % '<define-parameter name="u"><add><parameter name="ok"/><float value="1"/></add></define-parameter>')
+    assert np.array_equal(g0.p, g1.p) and np.array_equal(g0.child, g1.child)
+    assert np.array_equal(g0.meta["psource"].sample(3, 5), g1.meta["psource"].sample(3, 5))
