@@ -4,6 +4,7 @@
 #include <cmath>
 #include <cstring>
 #include <new>
+#include <shared_mutex>
 #include <string>
 #include <vector>
 
@@ -182,6 +183,7 @@ canopy_status canopy_mc_run_resume(canopy_plan* plan, const canopy_mc_opts* opts
 canopy_status canopy_plan_update_p(canopy_plan* plan, const double* p, uint32_t n_basic) {
     return guard([&] {
         require(plan && (p || n_basic == 0), "canopy_plan_update_p: null argument");
+        std::unique_lock<std::shared_mutex> low_lock(plan->low_mu);   // waits for the host side of runs in progress
         std::lock_guard<std::mutex> lock(plan->mu);
         canopy::requantise(plan->low, p, n_basic);
         canopy::refresh_thresholds(plan);

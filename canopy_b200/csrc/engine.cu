@@ -566,6 +566,7 @@ static uint32_t pick_batch_slabs(const DeviceState* s, const Lowered& L, const c
 }
 
 void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, uint64_t* tallies_dev, canopy_mc_report* rep) {
+    std::shared_lock<std::shared_mutex> low_lock(plan->low_mu);   // no re-quantising while this run reads the plan (plan.h)
     const Lowered& L = plan->low;
     DeviceState* s = nullptr;
     { std::lock_guard<std::mutex> lock(plan->mu); s = get_state(plan, o.device); }
@@ -669,6 +670,7 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
 }
 
 void mc_sample_words(canopy_plan* plan, const canopy_mc_opts& o, uint64_t first_word, uint64_t n_words, uint64_t* words_host) {
+    std::shared_lock<std::shared_mutex> low_lock(plan->low_mu);
     const Lowered& L = plan->low;
     DeviceState* s = nullptr;
     { std::lock_guard<std::mutex> lock(plan->mu); s = get_state(plan, o.device); }
@@ -782,7 +784,7 @@ void mc_run_static(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies
     const uint64_t total_slabs = o.n_samples ? (end - 1) / kSlabSamples - slab0 + 1 : 0;
     cudaStream_t st = o.stream ? (cudaStream_t)o.stream : cudaStreamPerThread;   // no library-owned stream: that would be a create
 
-    std::lock_guard<std::mutex> plan_lock(plan->mu);   // the thresholds may be re-quantised by canopy_plan_update_p
+    std::shared_lock<std::shared_mutex> low_lock(plan->low_mu);   // the thresholds may be re-quantised by canopy_plan_update_p
     const Lowered& L = plan->low;
     if (!small_eligible(L))
         throw Error(CANOPY_E_UNSUPPORTED, "canopy_mc_run_static runs the fused kernel only: the plan needs at least one live gate, at most " +

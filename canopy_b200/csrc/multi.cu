@@ -127,8 +127,10 @@ void mc_run_multi(canopy_plan* plan, const canopy_mc_opts& o, const int32_t* dev
         if (nt) {
             std::lock_guard<std::mutex> comm_lock(cs.mu);   // two concurrent runs on one device list must not interleave their groups
             nccl_check(nccl().GroupStart(), "ncclGroupStart");
-            for (int i = 0; i < n_devices; ++i)
-                nccl_check(nccl().AllReduce(d_t[i], d_t[i], nt, ncclUint64, ncclSum, cs.comms[i], st[i]), "ncclAllReduce");
+            try {
+                for (int i = 0; i < n_devices; ++i)
+                    nccl_check(nccl().AllReduce(d_t[i], d_t[i], nt, ncclUint64, ncclSum, cs.comms[i], st[i]), "ncclAllReduce");
+            } catch (...) { nccl().GroupEnd(); throw; }   // never leave the group open: the next NCCL call of this thread would join it
             nccl_check(nccl().GroupEnd(), "ncclGroupEnd");
             CU(cudaSetDevice(devs[0]));
             CU(cudaMemcpyAsync(tallies_host, d_t[0], nt * 8, cudaMemcpyDeviceToHost, st[0]));

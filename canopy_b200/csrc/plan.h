@@ -3,6 +3,7 @@
 #pragma once
 #include <cstdint>
 #include <mutex>
+#include <shared_mutex>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -111,6 +112,10 @@ void destroy_device_state(DeviceState*);
 struct canopy_plan {
     canopy::Lowered low;
     std::mutex mu;  // serialises runs on one plan (per-device scratch is owned by the plan)
+    // Guards the parts of `low` that canopy_plan_update_p / canopy_uncertainty_run rewrite (thresholds, classes, sampler
+    // order): re-quantising holds it exclusively, a run holds it shared for as long as its host side reads `low`, so a run
+    // sees the old thresholds or the new ones, never a vector in mid-resize.  Lock order: low_mu, then mu, then a device's run_mu.
+    std::shared_mutex low_mu;
     std::vector<canopy::DeviceState*> dev;  // lazily created, one per CUDA ordinal used
 };
 

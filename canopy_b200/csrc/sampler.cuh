@@ -290,6 +290,7 @@ __device__ __forceinline__ void sparse_unit_fill(const SparseUnit& U, const uint
                 }
             }
         }
+        n = active ? n : 0u;   // Uv = 0 keeps an idle lane at zero only while cdf_0 > 0 (every real table; not the test hook's all-zero one)
         // placement: the first n distinct k-bit fields.  The lane owns the group's words of the image outright, so a
         // plain read-modify-write does; the old value tells whether the position was taken already.
         const uint32_t wbase = img + r * kRowBytes + (gr << (k - 3u));

@@ -160,7 +160,7 @@ canopy_status canopy_uncertainty_run(canopy_plan* plan, const canopy_psource* sr
         std::vector<uint64_t> tallies(nt);
         struct Restore {  // leave the plan at the mean probabilities on every path out
             canopy_plan* plan; const std::vector<double>& p;
-            ~Restore() { try { std::lock_guard<std::mutex> lock(plan->mu); requantise(plan->low, p.data(), (uint32_t)p.size()); refresh_thresholds(plan); } catch (...) {} }
+            ~Restore() { try { std::unique_lock<std::shared_mutex> low_lock(plan->low_mu); std::lock_guard<std::mutex> lock(plan->mu); requantise(plan->low, p.data(), (uint32_t)p.size()); refresh_thresholds(plan); } catch (...) {} }
         } restore{plan, mean_p};
         // the draws of trial t + 1 are made on a helper thread while the device runs trial t (100k lognormal draws cost 9 ms
         // of host time, an inner run of 2^22 samples of c4 50 ms)
@@ -174,6 +174,7 @@ canopy_status canopy_uncertainty_run(canopy_plan* plan, const canopy_psource* sr
             for (uint32_t i = 0; i < nb; ++i)
                 p[i] = L.event_class[i] == 2 ? std::fmin(p_hi, std::fmax(p_lo, p[i])) : mean_p[i];
             {
+                std::unique_lock<std::shared_mutex> low_lock(plan->low_mu);
                 std::lock_guard<std::mutex> lock(plan->mu);
                 requantise(L, p.data(), nb);
                 refresh_thresholds(plan);

@@ -326,7 +326,10 @@ CANOPY_API canopy_status canopy_mc_run_resume(canopy_plan* plan, const canopy_mc
  * (same graph, same lowering) and re-quantise the thresholds; the next run uses them.  p[n_basic] in descriptor
  * order.  The constant folding done at lowering must stay valid: an event that was folded to a constant
  * (p <= 0, p >= 1, or a threshold of 0) must fold to the same constant, and a sampled event must stay sampled;
- * otherwise CANOPY_E_INVALID (create a new plan).  Changes canopy_plan_fingerprint(). */
+ * otherwise CANOPY_E_INVALID (create a new plan).  Changes canopy_plan_fingerprint().
+ * May be called while other threads run the same plan: it waits for the host side of every run in progress (and for
+ * kernels a device-output run left in flight), and a run started meanwhile waits for it, so each run samples with the
+ * old probabilities or with the new ones, never with a mixture. */
 CANOPY_API canopy_status canopy_plan_update_p(canopy_plan* plan, const double* p, uint32_t n_basic);
 
 /* Parity hook: run only the sampler kernel and return the packed words of the live basic events,

@@ -292,3 +292,45 @@ def test_fused_engine_limits_and_update_p():
             assert rep.sampler_launches == 0
             g2 = G.Graph(p=p, op=g.op, kmin=g.kmin, kmax=g.kmax, child_off=g.child_off, child=g.child, roots=g.roots)
             assert np.array_equal(got, O.mc_scalar(g2, 3, k * 50000, 8192 + 5, True))
+
+
+def test_update_p_from_another_thread_while_the_plan_runs():
+    """canopy_plan_update_p and runs of the same plan from different host threads (include/canopy.h): the update waits for
+    the host side of a run, a run waits for the update, so every run's tallies are those of one of the two probability
+    sets, whole -- never thresholds of one set with the sampler order or count tables of the other."""
+    import threading
+    g = synth.config_graph("c2", 0.05)
+    p0 = np.array(g.p, dtype=np.float64)
+    p1 = np.where((p0 > 0) & (p0 < 1), np.clip(p0 * 3.0, 0.0, 0.9), p0)      # moves many events across class boundaries (dense <-> sparse, k <-> k - 1)
+    n, seed = 40_000, 11
+    with Plan(g, tally_all_gates=True, sampler=4) as plan:
+        want = []
+        for p in (p0, p1):
+            plan.update_p(p)
+            want.append(plan.run(n, seed=seed)[0].copy())
+        assert not np.array_equal(want[0], want[1])
+        stop = threading.Event()
+        errors = []
+
+        def updater():
+            i = 0
+            try:
+                while not stop.is_set():
+                    plan.update_p(p0 if i & 1 else p1)
+                    i += 1
+            except Exception as e:   # noqa: BLE001
+                errors.append(e)
+
+        t = threading.Thread(target=updater)
+        t.start()
+        try:
+            seen = [0, 0]
+            for _ in range(60):
+                got = plan.run(n, seed=seed)[0]
+                which = [np.array_equal(got, w) for w in want]
+                assert any(which), "a run mixed two probability sets"
+                seen[which.index(True)] += 1
+        finally:
+            stop.set()
+            t.join()
+        assert not errors, errors

@@ -358,3 +358,28 @@ def test_gpu_update_p_moves_events_across_classes():
     g2 = G.from_lists([0.02, 0.0005, 0.004, 0.006], [(G.OR, [0, 1], 0, 0), (G.ATLEAST, [0, 1, 2, 3], 2, 0)], [4, 5])
     assert np.array_equal(first, O.mc_packed(g, 11, 0, n, True, nthreads=CORES, spec=4))
     assert np.array_equal(second, O.mc_packed(g2, 11, 0, n, True, nthreads=CORES, spec=4))
+
+
+@pytest.mark.gpu
+def test_gpu_forced_counts_in_partly_filled_units():
+    """Units whose groups do not fill the warp (three k = 13 events: 3 of 32 lanes busy; two k = 11 events: 8 of 32) with an
+    all-zero count table: the idle lanes compare U = 0 with cdf_0 = 0 and would draw 32 ones into row 0 if the kernel did
+    not switch them off explicitly.  Every row must equal the oracle's for that event alone."""
+    tab = _forced_tables()["all32"]
+    ps = (0.5, 0.0001, 0.00011, 0.00012, 0.001, 0.0015, 0.02)
+    b = G.GraphBuilder()
+    ev = [b.basic_event(p) for p in ps]
+    b.root(b.gate(G.OR, ev))
+    g = b.build()
+    n_words = 128 * 64
+    with Plan(g, sampler=4) as plan:
+        orig = [int(x) for x in plan.view()["event_orig"]]
+        ks = {int(e): int(k) for e, k in zip(plan.view()["event_orig"], plan.view()["event_k"])}
+        assert [ks[e] for e in range(1, 7)] == [13, 13, 13, 11, 11, 7]
+        for e in range(1, 7):
+            plan.debug_set_sparse_table(orig.index(e), tab)
+        got = plan.sample_words(seed=77, first_word=128 * 3, n_words=n_words)
+    want = O.sample_words(g, 77, orig, 128 * 3, n_words, 32, 4, fast=True)
+    for e in range(1, 7):
+        want[orig.index(e)] = O.sparse_words_with_table(77, e, ks[e], tab, 128 * 3, n_words, stream=True)
+    assert np.array_equal(got, want)
