@@ -122,7 +122,7 @@ struct Builder {
     // Roles (element.h:300-379, initializer.cpp:42-57,98-106): an element's id is its name when public and
     // base_path.name when private; `sym` / `param_idx` are the id tables (Model::table<T>), `path_sym` / `param_path`
     // the full-path tables (Initializer::path_gates_ ...), which hold public and private elements alike.
-    std::map<std::string, Sym> path_sym;
+    std::map<std::string, Sym> path_sym[3];   // one full-path table per Kind (path_gates_, path_basic_events_, path_house_events_)
     std::map<std::string, uint32_t> param_path;
     std::string cur_base;   // base path of the element whose body is being read (scope of its references)
     std::vector<CcfDef> ccfs;
@@ -152,7 +152,7 @@ struct Builder {
         const std::string id = make_id(nm, base, is_public);
         if (!sym.emplace(id, Sym{k, idx}).second)
             bad(CANOPY_E_VALIDITY, n, "Duplicate Element Error: Redefinition of event: " + id);  // model.h:151-155
-        if (in_path_table && !base.empty()) path_sym.emplace(base + "." + nm, Sym{k, idx});
+        if (in_path_table && !base.empty()) path_sym[(int)k].emplace(base + "." + nm, Sym{k, idx});
         return id;
     }
     uint32_t add_basic(const XNode& n, const std::string& nm, const XNode* body, const std::string& base, bool is_public,
@@ -572,20 +572,26 @@ struct Builder {
     }
 
     // ---- formulas (initializer.cpp:772-851) --------------------------------------------------------------
-    // GetEvent, initializer.cpp:1416-1437: base_path.reference in the full-path table; else a reference without a dot is a
-    // public id, one with dots a full path.  (A typed reference -- <gate name=...> -- that finds an event of another
-    // kind is reported by the caller.)
-    const Sym* find_event(const std::string& ref) const {
-        if (!cur_base.empty()) {
-            auto it = path_sym.find(cur_base + "." + ref);
-            if (it != path_sym.end()) return &it->second;
+    // An untyped reference (GetEvent, initializer.cpp:1416-1437) looks through the gates, the basic events and the house
+    // events in that order; a typed one (GetGate / GetBasicEvent / GetHouseEvent -> GetEntity, :1372-1403) only through the
+    // tables of its kind, so that an element of another kind with the same local name does not shadow it.  Either way:
+    // base_path.reference in the full-path table(s); else a reference without a dot is a public id, one with dots a full path.
+    const Sym* find_in_paths(const std::string& path, int kind) const {
+        for (int k = 0; k < 3; ++k) {
+            if (kind >= 0 && k != kind) continue;
+            auto it = path_sym[k].find(path);
+            if (it != path_sym[k].end()) return &it->second;
         }
+        return nullptr;
+    }
+    const Sym* find_event(const std::string& ref, int kind = -1) const {
+        if (!cur_base.empty())
+            if (const Sym* s = find_in_paths(cur_base + "." + ref, kind)) return s;
         if (ref.find('.') == std::string::npos) {
-            auto it = sym.find(ref);
-            return it == sym.end() ? nullptr : &it->second;
+            auto it = sym.find(ref);   // ids are unique across the three kinds (model.h:151-155)
+            return it == sym.end() || (kind >= 0 && (int)it->second.kind != kind) ? nullptr : &it->second;
         }
-        auto it = path_sym.find(ref);
-        return it == path_sym.end() ? nullptr : &it->second;
+        return find_in_paths(ref, kind);
     }
     ArgRef event_ref(const XNode& a, bool complement) {
         const std::string* type = a.attr("type");
@@ -593,12 +599,10 @@ struct Builder {
         if (et != "event" && et != "gate" && et != "basic-event" && et != "house-event")
             bad(CANOPY_E_UNSUPPORTED, a, "formula argument <" + a.name + "> is not an event reference (nested formulas are not supported)");
         const std::string& nm = need_name(a);
-        const Sym* found = find_event(nm);
-        if (!found) bad(CANOPY_E_VALIDITY, a, "Undefined Element Error: " + nm);
+        const int want = et == "gate" ? (int)Kind::kGate : et == "basic-event" ? (int)Kind::kBasic : et == "house-event" ? (int)Kind::kHouse : -1;
+        const Sym* found = find_event(nm, want);
+        if (!found) bad(CANOPY_E_VALIDITY, a, "Undefined Element Error: " + nm + (want >= 0 && find_event(nm) ? " is not a " + et : std::string()));
         const Sym s = *found;
-        if ((et == "gate" && s.kind != Kind::kGate) || (et == "basic-event" && s.kind != Kind::kBasic) ||
-            (et == "house-event" && s.kind != Kind::kHouse))
-            bad(CANOPY_E_VALIDITY, a, "Undefined Element Error: " + nm + " is not a " + et);
         if (s.kind == Kind::kGate) return ArgRef{ArgRef::kGate, complement, s.idx};
         if (s.kind == Kind::kHouse) return ArgRef{ArgRef::kHouse, complement, s.idx};
         if (basics[s.idx].proxy_gate >= 0) return ArgRef{ArgRef::kGate, complement, (uint32_t)basics[s.idx].proxy_gate};  // event.h:108-114

@@ -401,3 +401,27 @@ def test_a_valid_unused_parameter_changes_nothing():
     g1 = load_mef(text=_UNUSED_PARAM_MODEL % '<define-parameter name="u"><add><parameter name="ok"/><float value="1"/></add></define-parameter>')
     assert np.array_equal(g0.p, g1.p) and np.array_equal(g0.child, g1.child)
     assert np.array_equal(g0.meta["psource"].sample(3, 5), g1.meta["psource"].sample(3, 5))
+
+
+def test_typed_reference_is_not_shadowed_by_a_local_element_of_another_kind():
+    """<gate name='x'/> is looked up in the gate tables only (GetGate -> GetEntity, initializer.cpp:1372-1403): a private
+    basic event FT.x in the referring scope does not hide the public gate x of another tree.  The untyped <event name='x'/>
+    takes the local element (GetEvent, :1416-1437)."""
+    xml = model(
+        "<define-fault-tree name='Other'><define-gate name='x'><and><basic-event name='a'/><basic-event name='b'/></and></define-gate>"
+        "<define-basic-event name='a'><float value='0.5'/></define-basic-event>"
+        "<define-basic-event name='b'><float value='0.25'/></define-basic-event></define-fault-tree>"
+        "<define-fault-tree name='FT'>"
+        "<define-gate name='top'><or><gate name='x'/><basic-event name='c'/></or></define-gate>"
+        "<define-basic-event name='x' role='private'><float value='0.0625'/></define-basic-event>"
+        "<define-basic-event name='c'><float value='0.125'/></define-basic-event>"
+        "</define-fault-tree>")
+    g = load_mef(text=xml)
+    top = g.meta["root_names"].index("top")
+    assert O.exact(g, False, 32)[top] == pytest.approx(1 - (1 - Q(0.5) * Q(0.25)) * (1 - Q(0.125)), rel=1e-12)
+    g = load_mef(text=xml.replace("<gate name='x'/>", "<event name='x'/>"))       # untyped: the local basic event FT.x
+    top = g.meta["root_names"].index("top")
+    assert O.exact(g, False, 32)[top] == pytest.approx(1 - (1 - Q(0.0625)) * (1 - Q(0.125)), rel=1e-12)
+    with pytest.raises(_lib.CanopyError) as ei:                                   # typed and of the wrong kind everywhere
+        load_mef(text=xml.replace("<gate name='x'/>", "<house-event name='x'/>"))
+    assert ei.value.status == _lib.E_VALIDITY and "is not a house-event" in ei.value.message
