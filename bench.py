@@ -247,15 +247,19 @@ def run_reference(args):
 CHECK_SEED = 0x7A11
 
 
-def tally_check(g, world, rank, local, dev, stream, sampler, n_fixed=1 << 24, n_prefix=1 << 14, bits=32):
+def tally_check(g, world, rank, local, dev, stream, sampler, n_fixed=1 << 24, n_prefix=None, bits=32):
     """In-run parity evidence on the driver's clock, every gate tallied:
        (i)  the fixed range [0, n_fixed) cut over the N ranks by canopy_shard_range + ONE all-reduce == the same range on
             one GPU (at N = 1: three ragged pieces summed == the whole);
-       (ii) its first n_prefix samples on the GPU == oracle.mc_packed on the host."""
+       (ii) its first n_prefix samples on the GPU == oracle.mc_packed on the host; by default one full batch of the
+            default pipeline (two slabs per SM) plus a slab and a ragged tail, so that the run the oracle checks crosses a
+            swap of the two value buffers (c4: 2.4e6 samples, about 10 s of host time)."""
     import numpy as np
     import torch
     import torch.distributed as dist
     from canopy_b200.engine import Plan, shard_range
+    if n_prefix is None:
+        n_prefix = (2 * torch.cuda.get_device_properties(local).multi_processor_count + 1) * 8192 + 77
     res = {"range": [0, n_fixed], "ranks": world, "prefix": n_prefix, "tallies": 0}
     with Plan(g, tally_all_gates=True, threshold_bits=bits, sampler=sampler) as plan:
         nt = plan.n_tallies

@@ -6,6 +6,7 @@ import os
 
 import numpy as np
 import pytest
+import torch
 
 from helpers import G, O, ROOT, random_graph
 from canopy_b200 import synth
@@ -142,3 +143,32 @@ def test_high_fanin_count_gates(fanin, lo, hi):
     want = O.mc_packed(g, fanin, 0, n, nthreads=CORES)
     assert np.array_equal(got, want)
     assert 0 < int(got[0]) < n          # the threshold sits inside the count distribution: the gate is exercised
+
+
+_ORACLE_CACHE = {}   # the two engine modes of conftest.py both take the streamed path at these sizes: ask the oracle once
+
+
+def _oracle_cached(name, g, seed, begin, n, bits):
+    key = (name, seed, begin, n, bits)
+    if key not in _ORACLE_CACHE:
+        _ORACLE_CACHE[key] = O.mc_packed(g, seed, begin, n, True, bits=bits, nthreads=CORES)
+    return _ORACLE_CACHE[key]
+
+
+@pytest.mark.parametrize("name,bits", [("c4", 32), ("c4", 64), ("c3", 32)])
+def test_full_graphs_pipelined_over_several_batches_per_gate(name, bits):
+    """The benched configuration on the path that produces the bench number: FULL c4 (and c3) graph, every gate tallied,
+    default batch size (two slabs per SM) and the default overlapped pipeline -- sampler of batch b+1 beside the walk of
+    batch b on two value buffers, each buffer rewritten at least twice -- over a range that starts inside a slab and ends
+    with a ragged tail, against the oracle (about 30 s of host time per case on 16 cores)."""
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    g = synth.config_graph(name)
+    begin = (1 << 40) + 8192 * 3 + 4001
+    n = 4 * (2 * sms) * 8192 + 8192 + 1234
+    with Plan(g, tally_all_gates=True, threshold_bits=bits) as plan:
+        got, rep = plan.run(n, seed=0xFACADE, sample_begin=begin)
+    # the default batch is two slabs per SM, less when two value buffers of that size exceed half the free memory (c4: 293 of 296)
+    assert rep.n_batches >= 5 and sms <= rep.batch_slabs <= 2 * sms and rep.sampler_launches == rep.n_batches
+    want = _oracle_cached(name, g, 0xFACADE, begin, n, bits)
+    assert want[:g.n_roots].sum() > 0
+    assert np.array_equal(got, want)
