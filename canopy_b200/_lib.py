@@ -146,9 +146,26 @@ SYMBOLS = {
     "canopy_spec_version": (C.c_uint32, []),
     "canopy_sparse_class": (C.c_int, [C.c_uint64, C.POINTER(C.c_uint32)]),
     "canopy_sparse_cdf": (C.c_int, [C.c_uint64, C.c_uint32, C.POINTER(C.c_uint64)]),
+}
+# include/canopy-testing.h: exported by libcanopy_testing.so only (the product library plus csrc/capi_testing.cpp)
+TESTING_SYMBOLS = {
     "canopy_plan_debug_streams": (C.c_int, [C.c_void_p, C.POINTER(CPlanStreams)]),
     "canopy_plan_debug_set_sparse_table": (C.c_int, [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint64)]),
+    "canopy_debug_force_row_copies": (C.c_int, [C.c_int32]),
 }
+TESTING_LIB_PATH = os.path.join(_HERE, "libcanopy_testing.so")
+_TESTING = False
+
+
+def use_testing_library():
+    """Called by tests/conftest.py before anything is loaded: bind libcanopy_testing.so, which adds the test hooks of
+    include/canopy-testing.h to the very same objects libcanopy.so is linked from.  Product code never calls this."""
+    global LIB_PATH, _TESTING
+    if _LIB is not None and not _TESTING:
+        raise RuntimeError("libcanopy.so is already loaded; use_testing_library() must come first")
+    if not os.environ.get("CANOPY_LIB"):
+        LIB_PATH = TESTING_LIB_PATH
+    _TESTING = True
 
 _LIB = None
 
@@ -161,7 +178,7 @@ def lib():
                 f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
                 "or `make -C canopy_b200/csrc`. canopy_b200 has no CPU or pure-Python fallback.")
         L = C.CDLL(LIB_PATH)
-        for name, (res, args) in SYMBOLS.items():
+        for name, (res, args) in list(SYMBOLS.items()) + (list(TESTING_SYMBOLS.items()) if _TESTING else []):
             fn = getattr(L, name)  # AttributeError here means the .so does not match include/canopy.h
             fn.restype = res
             fn.argtypes = args

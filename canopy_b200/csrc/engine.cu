@@ -1,6 +1,7 @@
 // Monte Carlo engine, host side: per-device state, the value-buffer pool and the batch loop.  sm_100a only, no CPU
 // fallback.  Kernels: sampler.cuh (subsystem 2), walk.cuh (subsystem 3); layout, spec and roofline accounting: DESIGN.md.
 #include <algorithm>
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -486,6 +487,12 @@ static void launch_sampler(const DeviceState* s, const Lowered& L, uint4* vals, 
                                   first_slab, n_slabs, K));
 }
 
+// Test hook (canopy-testing.h, exported by libcanopy_testing.so only): take the fallback the walk uses when no tensor map
+// can be had (value buffers of more than 2^31 rows, or a driver without cuTensorMapEncodeTiled) on buffers of any size, so
+// that the parity tests reach gate_ring_kernel_t<false>.
+static std::atomic<bool> g_force_row_copies{false};
+void debug_force_row_copies(bool on) { g_force_row_copies.store(on); }
+
 #ifndef CANOPY_WALK_SHARED_CTAS
 #define CANOPY_WALK_SHARED_CTAS 1   // walk CTAs per SM while the sampler of the next batch shares the GPU
 #endif
@@ -503,7 +510,7 @@ static uint32_t launch_gates(const DeviceState* s, const Lowered& L, uint4* vals
     const int per_sm = std::min(shared_sm ? CANOPY_WALK_SHARED_CTAS : CANOPY_WALK_ALONE_CTAS, s->ring_ctas_per_sm);
     const uint32_t grid = std::min<uint32_t>(n_slabs, (uint32_t)(s->sm_count * per_sm));
     const int b = vals == s->vals[1] ? 1 : 0;
-    if (vals == s->vals[b] && s->vmap_ok[b] && kGroupRows == 4)
+    if (vals == s->vals[b] && s->vmap_ok[b] && kGroupRows == 4 && !g_force_row_copies.load(std::memory_order_relaxed))
         gate_ring_kernel_g4<<<grid, kGateThreads, kRingSmemBytes, st>>>(
             s->vmap[b], vals, s->grec, s->child, s->layer_off, s->wide_off, s->split, s->split_child, L.n_layers(), L.n_nodes(),
             L.n_events(), s->gate_tallies, first_slab, n_slabs, begin, end, s->walk_done, parity, wait_val, qsel);

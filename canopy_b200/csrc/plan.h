@@ -133,5 +133,6 @@ bool small_eligible(const Lowered& L);        // may runs of this plan take the 
 void trim_device_cache(int device);           // free the value buffers parked by destroyed plans (-1: all devices)
 void refresh_thresholds(canopy_plan* plan);  // re-upload thresholds and sampler order to every device the plan is resident on; rebuild the tables
 void debug_set_sparse_table(canopy_plan* plan, uint32_t live_event, const uint64_t* cdf);  // canopy-testing.h hook
+void debug_force_row_copies(bool on);   // canopy-testing.h hook: the gate walk fills its ring with one bulk copy per row instead of tile::gather4
 void shard_range(uint64_t begin, uint64_t n, int rank, int world, uint64_t* ob, uint64_t* on);
 }  // namespace canopy

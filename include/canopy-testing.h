@@ -1,7 +1,8 @@
 /*
- * canopy-testing.h -- test-only entry points of libcanopy.  NOT part of the public boundary (include/canopy.h): nothing a
- * caller of the engine needs is declared here, and the installed package does not ship this header.  The symbols are
- * exported so that the parity tests can drive paths a real probability never reaches.
+ * canopy-testing.h -- test-only entry points.  NOT part of the public boundary (include/canopy.h): nothing a caller of
+ * the engine needs is declared here, the installed package does not ship this header, and libcanopy.so does not export
+ * these symbols.  They exist in libcanopy_testing.so only -- the same objects as libcanopy.so plus csrc/capi_testing.cpp
+ * (csrc/Makefile) -- which the test suite loads, so that the parity tests can drive paths that real inputs never reach.
  */
 #ifndef CANOPY_TESTING_H
 #define CANOPY_TESTING_H
@@ -31,6 +32,12 @@ typedef struct canopy_plan_streams {
     const uint32_t* split_child;
 } canopy_plan_streams;
 CANOPY_API canopy_status canopy_plan_debug_streams(const canopy_plan* plan, canopy_plan_streams* out);
+
+/* Process-wide switch: with on != 0 every later gate walk fills its shared-memory ring with one bulk copy per row
+ * (gate_ring_kernel_t<false>) instead of four-row tile::gather4 tensor copies -- the path the engine otherwise takes only
+ * for value buffers of more than 2^31 rows or when the driver offers no tensor-map encoder, neither of which a 180 GB part
+ * can produce.  Tallies must not change. */
+CANOPY_API canopy_status canopy_debug_force_row_copies(int32_t on);
 
 #ifdef __cplusplus
 }

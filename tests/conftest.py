@@ -9,6 +9,11 @@ for p in (ROOT, os.path.join(ROOT, "tests")):
         sys.path.insert(0, p)
 
 
+from canopy_b200 import _lib as _canopy_lib  # noqa: E402
+
+_canopy_lib.use_testing_library()   # the suite drives the test hooks of include/canopy-testing.h; the product library has none
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a B200 (run with -m gpu on the GPU box)")
 

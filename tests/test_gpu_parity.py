@@ -172,3 +172,40 @@ def test_full_graphs_pipelined_over_several_batches_per_gate(name, bits):
     want = _oracle_cached(name, g, 0xFACADE, begin, n, bits)
     assert want[:g.n_roots].sum() > 0
     assert np.array_equal(got, want)
+
+
+@pytest.fixture
+def row_copies():
+    """include/canopy-testing.h: make every gate walk take gate_ring_kernel_t<false> (one bulk copy per row), the path the
+    engine itself only chooses for value buffers beyond 2^31 rows or without a tensor-map encoder."""
+    from canopy_b200 import _lib
+    _lib.check(_lib.lib().canopy_debug_force_row_copies(1))
+    yield
+    _lib.check(_lib.lib().canopy_debug_force_row_copies(0))
+
+
+@pytest.mark.parametrize("name,scale,n,batch", [("c2", 0.1, 1 << 15, 0), ("c3", 0.05, 1 << 15, 0), ("c4", 0.02, 1 << 14, 0),
+                                                ("c4", 0.05, 8192 * 50 + 99, 8), ("c2", 1.0, 8192 * 40 + 5, 6)])
+def test_walk_with_one_bulk_copy_per_row(row_copies, name, scale, n, batch):
+    """The walk's fallback instantiation against the oracle: scaled configs (k-of-n, wide gates, fan-in up to 245), and two
+    pipelined runs of 7 batches on two value buffers; then the same run on the default (gather4) path gives the same tallies."""
+    from canopy_b200 import _lib
+    from canopy_b200.engine import ENGINE_STREAMED
+    g = synth.config_graph(name, scale)
+    begin = 4096 * 9 + 13
+    with Plan(g, tally_all_gates=True, engine=ENGINE_STREAMED) as plan:
+        got, rep = plan.run(n, seed=77, sample_begin=begin, batch_slabs=batch)
+        assert rep.gate_launches >= (7 if batch else 1)
+        _lib.check(_lib.lib().canopy_debug_force_row_copies(0))
+        again, _ = plan.run(n, seed=77, sample_begin=begin, batch_slabs=batch)
+    assert np.array_equal(got, O.mc_packed(g, 77, begin, n, True, nthreads=CORES))
+    assert np.array_equal(got, again)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_walk_with_one_bulk_copy_per_row_all_connectives(row_copies, seed):
+    from canopy_b200.engine import ENGINE_STREAMED
+    g = random_graph(500 + seed, n_basic=16, n_gates=48, max_fanin=9, n_roots=4)
+    with Plan(g, tally_all_gates=True, engine=ENGINE_STREAMED) as plan:
+        got, _ = plan.run(20_000, seed=seed, sample_begin=1000 * seed + 7)
+    assert np.array_equal(got, O.mc_scalar(g, seed, 1000 * seed + 7, 20_000, True))

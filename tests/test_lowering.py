@@ -14,13 +14,21 @@ from canopy_b200.engine import Plan, Settings, SettingsError, estimate, shard_ra
 
 
 def test_library_exports_every_declared_symbol():
-    hdr = open(os.path.join(ROOT, "include", "canopy.h")).read() + open(os.path.join(ROOT, "include", "canopy-testing.h")).read()
-    assert "debug" not in open(os.path.join(ROOT, "include", "canopy.h")).read()     # test hooks live in canopy-testing.h only
-    declared = set(re.findall(r"CANOPY_API\s+[\w\s\*]+?\b(canopy_\w+)\s*\(", hdr))
+    """libcanopy.so exports exactly what include/canopy.h declares -- no test hook; libcanopy_testing.so adds exactly what
+    include/canopy-testing.h declares."""
+    pub = open(os.path.join(ROOT, "include", "canopy.h")).read()
+    tst = open(os.path.join(ROOT, "include", "canopy-testing.h")).read()
+    assert "debug" not in pub     # test hooks live in canopy-testing.h only
+    rx = r"CANOPY_API\s+[\w\s\*]+?\b(canopy_\w+)\s*\("
+    declared, hooks = set(re.findall(rx, pub)), set(re.findall(rx, tst))
     assert declared == set(_lib.SYMBOLS), (declared ^ set(_lib.SYMBOLS))
-    L = C.CDLL(_lib.LIB_PATH)
+    assert hooks == set(_lib.TESTING_SYMBOLS), (hooks ^ set(_lib.TESTING_SYMBOLS))
+    product = C.CDLL(os.path.join(os.path.dirname(_lib.TESTING_LIB_PATH), "libcanopy.so"))
+    testing = C.CDLL(_lib.TESTING_LIB_PATH)
     for name in declared:
-        assert hasattr(L, name), name
+        assert hasattr(product, name) and hasattr(testing, name), name
+    for name in hooks:
+        assert hasattr(testing, name) and not hasattr(product, name), name
     assert _lib.lib().canopy_spec_version() == 4
     assert _lib.lib().canopy_status_string(3) == b"cycle error"
 

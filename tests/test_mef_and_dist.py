@@ -1,4 +1,5 @@
 """MEF XML loader (C++ in libcanopy) and the world_size-2 sharding logic over gloo.  CPU only."""
+import ctypes as C
 import os
 
 import numpy as np
@@ -126,10 +127,16 @@ def _worker(rank, world, port, q):
     g = random_graph(3, n_basic=12, n_gates=30, n_roots=2)
     seen = []
 
-    def local_run(begin, n, out):   # the CUDA engine refuses to run on CPU; the oracle stands in for ONE rank's shard
-        seen.append((begin, n))
-        out[: g.n_tallies(True)] = torch.from_numpy(O.mc_packed(g, 11, begin, n, True).astype(np.int64))
-    total = run_sharded(None, 3 * 4096 + 100, seed=11, sample_begin=50, local_run=local_run, n_tallies=g.n_tallies(True))
+    class OracleShard:
+        """Stands in for a Plan on this CPU-only box (the CUDA engine refuses to run here): same run_device signature, the
+        oracle computes ONE rank's shard into the tensor run_sharded hands to the all-reduce."""
+        n_tallies = g.n_tallies(True)
+
+        def run_device(self, tallies_ptr, n, seed=0, sample_begin=0, device=0, stream=None):
+            seen.append((sample_begin, n))
+            out = np.ctypeslib.as_array(C.cast(tallies_ptr, C.POINTER(C.c_int64)), shape=(self.n_tallies,))
+            out[:] = O.mc_packed(g, seed, sample_begin, n, True).astype(np.int64)
+    total = run_sharded(OracleShard(), 3 * 4096 + 100, seed=11, sample_begin=50, device="cpu")
     q.put((rank, seen[0], total.tolist()))
     dist.destroy_process_group()
 
