@@ -247,7 +247,7 @@ def run_reference(args):
 CHECK_SEED = 0x7A11
 
 
-def tally_check(g, world, rank, local, dev, stream, sampler, n_fixed=1 << 24, n_prefix=None, bits=32):
+def tally_check(g, world, rank, local, dev, stream, sampler, n_fixed=1 << 24, n_prefix=None, bits=32, host_group=None):
     """In-run parity evidence on the driver's clock, every gate tallied:
        (i)  the fixed range [0, n_fixed) cut over the N ranks by canopy_shard_range + ONE all-reduce == the same range on
             one GPU (at N = 1: three ragged pieces summed == the whole);
@@ -289,6 +289,25 @@ def tally_check(g, world, rank, local, dev, stream, sampler, n_fixed=1 << 24, n_
         f = [bool(x) for x in flags.cpu().tolist()]
     res.update({"n_way_equals_1_way": f[0], "pieces_equal_whole": f[1], "prefix_equals_oracle": f[2],
                 "allreduce_bytes": nt * 8 if world > 1 else 0})
+    if world > 1 and host_group is not None:
+        # (iii) the library's own collective: canopy_mc_run_multi (csrc/multi.cu: ncclCommInitAll + one
+        # ncclAllReduce(ncclUint64, ncclSum)) driven from rank 0's process over all `world` GPUs, against the same range on
+        # one GPU.  Every rank has closed its check plan; the others wait on a HOST (gloo) barrier, so that no kernel of
+        # theirs spins on the GPUs rank 0 is about to use.
+        torch.cuda.synchronize()
+        multi = torch.ones(1, dtype=torch.int64, device=dev)
+        if rank == 0:
+            n_multi = 1 << 22
+            t0 = time.perf_counter()
+            with Plan(g, tally_all_gates=True, threshold_bits=bits, sampler=sampler) as plan:
+                many, _ = plan.run_multi(list(range(world)), n_multi, seed=CHECK_SEED, sample_begin=12345, batch_slabs=32)
+                one, _ = plan.run(n_multi, seed=CHECK_SEED, sample_begin=12345, device=local, batch_slabs=32)
+            multi[0] = int(np.array_equal(many, one))
+            res["run_multi"] = {"devices": world, "samples": n_multi, "seconds": round(time.perf_counter() - t0, 2),
+                                "what": "canopy_mc_run_multi from rank 0's process (own ncclCommInitAll + ncclAllReduce) == one GPU"}
+        dist.barrier(group=host_group)
+        dist.broadcast(multi, 0)
+        res["run_multi_equals_1_way"] = bool(multi.item())
     return res
 
 
@@ -313,7 +332,7 @@ def sampler_algorithmic_ops(plan, spec):
     return (float((per_group / grp).mean()) if len(thr) else 0.0), mix
 
 
-def side_line(name, local, stream, sampler, steps=2, bits=32, samples=None):
+def side_line(name, local, stream, sampler, steps=2, bits=32, samples=None, warmups=2):
     """A short device-timed line of another BASELINE config on rank 0 (extra key, not the headline)."""
     import torch
     from canopy_b200.engine import Plan
@@ -323,7 +342,7 @@ def side_line(name, local, stream, sampler, steps=2, bits=32, samples=None):
     with Plan(g, tally_all, threshold_bits=bits, sampler=sampler) as plan:
         nt = plan.n_tallies
         out = torch.zeros(max(nt, 1), dtype=torch.int64, device=torch.device("cuda", local))
-        for w in range(2):
+        for w in range(warmups):
             plan.run_device(out.data_ptr(), S, seed=0xB200, sample_begin=w * S, device=local, stream=stream)
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -336,6 +355,7 @@ def side_line(name, local, stream, sampler, steps=2, bits=32, samples=None):
         st = plan.stats
     return {"workload": config_block(name, g, S, S_full)["workload"], "threshold_bits": bits, "samples_per_s": S / (ms * 1e-3), "ms_per_step": ms, "steps": steps,
             "gate_evals_per_s": S / (ms * 1e-3) * st["n_gates_live"], "tallies": nt, "G_live": st["n_gates_live"],
+            "spec_version": st["spec_version"], "samples_per_step": S, "warmup_steps": warmups,
             "alg_bytes_per_sample": (st["n_edges_live"] + st["n_gates_stored"] + st["n_basic_live"]) / 8.0}
 
 
@@ -373,6 +393,7 @@ def main():
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    host_group = dist.new_group(backend="gloo") if world > 1 else None   # host-side barrier only (tally_check iii)
     dev = torch.device("cuda", local)
 
     g, S, S_full = workload(args.workload)
@@ -389,8 +410,9 @@ def main():
     # ---- parity evidence before anything is timed ------------------------------------------------------
     check = None
     if not args.no_check:
-        check = tally_check(g, world, rank, local, dev, stream, args.sampler, bits=args.threshold_bits)
-        if not (check["n_way_equals_1_way"] and check["pieces_equal_whole"] and check["prefix_equals_oracle"]):
+        check = tally_check(g, world, rank, local, dev, stream, args.sampler, bits=args.threshold_bits, host_group=host_group)
+        if not (check["n_way_equals_1_way"] and check["pieces_equal_whole"] and check["prefix_equals_oracle"]
+                and check.get("run_multi_equals_1_way", True)):
             if rank == 0:
                 print(json.dumps({"metric": METRIC, "error": "tally_check failed", "tally_check": check}), flush=True)
             if world > 1:
@@ -403,12 +425,18 @@ def main():
     nt = plan.n_tallies
     tallies = torch.zeros(max(nt, 1), dtype=torch.int64, device=dev)
 
+    # One row of tallies per step; ONE collective over the rows of a run after its last step (north_star: "a single NCCL
+    # allreduce of int64 tallies").  Round 2 reduced after every step, which re-synchronised the ranks K times per run.
+    K, W = args.steps, args.warmup
+    rows = torch.zeros((W + K, max(nt, 1)), dtype=torch.int64, device=dev)
+
     def step(k, want_report=False):
-        rep = plan.run_device(tallies.data_ptr(), S, seed=0xB200, sample_begin=(k * world + rank) * S, device=local,
-                              stream=stream, want_report=want_report)
+        return plan.run_device(rows[k].data_ptr(), S, seed=0xB200, sample_begin=(k * world + rank) * S, device=local,
+                               stream=stream, want_report=want_report)
+
+    def reduce_rows(a, b):
         if world > 1:
-            dist.all_reduce(tallies)  # the single collective: int64 tally sum over NVLink
-        return rep
+            dist.all_reduce(rows[a:b])  # the single collective: int64 tally sum over NVLink
 
     def barrier():
         if world > 1:
@@ -417,30 +445,45 @@ def main():
 
     clocks = ClockSampler(local); clocks.start()
     rep0 = step(0, want_report=True)
-    for w in range(1, args.warmup):
+    for w in range(1, W):
         step(w)
-    launches_per_step = rep0.launches + (1 if world > 1 else 0)
+    reduce_rows(0, W)
     barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0, e_own, e1 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
     barrier()
     clocks.mark_begin()
     e0.record()
-    for k in range(args.steps):
-        step(args.warmup + k)
+    for k in range(K):
+        step(W + k)
+    e_own.record()     # this rank's own K steps end here; what follows is the collective (and the wait for the slowest rank)
+    reduce_rows(W, W + K)
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
+    own_ms = e0.elapsed_time(e_own)
     clk = clocks.stop()
     t_ms = torch.tensor([ms], dtype=torch.float64, device=dev)
+    rank_ms = None
     if world > 1:
         dist.all_reduce(t_ms, op=dist.ReduceOp.MAX)
+        mine = torch.tensor([own_ms / K], dtype=torch.float64, device=dev)
+        every = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(every, mine)
+        per_rank = [float(x.item()) for x in every]
+        rank_ms = {"per_rank_ms_per_step": per_rank, "min": min(per_rank), "median": statistics.median(per_rank), "max": max(per_rank),
+                   "allreduce_and_wait_ms_rank0": ms - own_ms,
+                   "what": "device ms per step of each rank's own K steps (CUDA events before the collective); the job's step time is the max"}
     ms = float(t_ms.item())
-    value = world * S * args.steps / (ms * 1e-3)
-    top_tally = int(tallies[0].item()) if nt else 0
+    value = world * S * K / (ms * 1e-3)
+    top_tally = int(rows[W + K - 1][0].item()) if nt else 0
+    launches_total = int(rep0.launches * K + (1 if world > 1 else 0))
 
     # ---- per-kernel roofline pass (every rank, to keep them in step) --------------------------------------
     prof = plan.run_device(tallies.data_ptr(), S, seed=0xB200, sample_begin=0, device=local, stream=stream,
                            profile=True, want_report=True)
+    # the same pass with every walk launched in the shape the timed steps give it (one CTA per SM), still alone
+    prof_shape = plan.run_device(tallies.data_ptr(), S, seed=0xB200, sample_begin=0, device=local, stream=stream,
+                                 profile=True, want_report=True, profile_walk_shape=1)
     alg_ops_per_bit, sampler_mix = sampler_algorithmic_ops(plan, spec)
     plan.close()   # its value buffers (c4: 2 x 48 GB) go to the library's pool: the e2e plans below reuse them
 
@@ -480,6 +523,25 @@ def main():
         dist.all_reduce(t_e, op=dist.ReduceOp.MAX)
     e2e_value = world * S * e2e_steps / float(t_e.item())
 
+    # ---- cold first call (N = 1): what a one-shot user of quantify() pays -- no plan cache, no pooled buffers ------
+    e2e_cold = None
+    if world == 1:
+        from canopy_b200.engine import plan_cache_clear, trim_device_cache
+        torch.cuda.synchronize()
+        trim_device_cache(-1); plan_cache_clear()
+        t0 = time.perf_counter()
+        p3 = Plan(g, tally_all, threshold_bits=args.threshold_bits, sampler=args.sampler, plan_cache=False)
+        t1 = time.perf_counter()
+        p3.run_device(tallies.data_ptr(), S, seed=0xB200, sample_begin=0, device=local, stream=stream, want_report=True)
+        host_out.copy_(tallies, non_blocking=False)
+        t2 = time.perf_counter()
+        p3.close()
+        t3 = time.perf_counter()
+        e2e_cold = {"value": S / (t3 - t0), "unit": UNIT, "steps": 1, "plan_create_ms": (t1 - t0) * 1e3, "run_ms": (t2 - t1) * 1e3,
+                    "plan_destroy_ms": (t3 - t2) * 1e3,
+                    "what": "one step after canopy_trim_device_cache + canopy_plan_cache_clear with no_plan_cache = 1: lowering from "
+                            "scratch, cudaMalloc of the plan arena and both value buffers, run, tallies to host, destroy"}
+
     peaks, peaks_src = load_peaks()
     gate_bytes_per_sample = (stats["n_edges_live"] + stats["n_gates_stored"]) / 8.0
     sampler_bytes_per_sample = stats["n_basic_live"] / 8.0
@@ -510,14 +572,25 @@ def main():
                     "d2h_bytes_per_step": int(nt * 8), "steps": e2e_steps,
                     "host_ms_per_step": {k2: v / e2e_steps for k2, v in e2e_parts.items()},
                     "what": "canopy_plan_create from host arrays + upload + run + allreduce + tallies to host, wall clock"},
-            "gpu_launches": int(launches_per_step * args.steps),
+            "e2e_cold": e2e_cold,
+            "gpu_launches": launches_total,
+            "collective": ("one all_reduce of the [steps, n_tallies] int64 tallies after the K timed steps, inside the timed region"
+                           if world > 1 else "none (N = 1)"),
+            "rank_ms": rank_ms,
             "roofline": {"kernel": "gate_ring_kernel" if prof.sampler_launches else "small_model_kernel (sampler + walk fused over shared-memory rows: the HBM figure is nominal, nothing but tallies leaves the SM)", "bound": "hbm", "achieved": gate_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                          "frac": gate_gbs / peaks["hbm_gbs"], "traffic": traffic,
                          "traffic_note": "DRAM read+write bytes of one full launch, " + cap_note + "; "
                                          "frac can read a little above 1: the peak is a 1:1 read:write copy, this kernel's traffic is about 5:1 reads",
                          "alg_bytes_per_launch": gate_bytes_per_launch, "nominal_hbm_gbs": 7700.0, "frac_of_nominal": gate_gbs / 7700.0,
                          "peak_source": peaks_src, "alg_bytes_per_sample": gate_bytes_per_sample, "avg_launch_ms": gate_launch_ms,
-                         "share_of_step": prof.gate_ms / max(prof.total_ms, 1e-9), "timed": "profile pass, kernels serialised"},
+                         "share_of_step": prof.gate_ms / max(prof.total_ms, 1e-9),
+                         "timed": "profile pass, kernels serialised; `frac` = frac_alone: the walk launched as a kernel that owns the GPU",
+                         "frac_alone": gate_gbs / peaks["hbm_gbs"],
+                         "frac_step_shape": (gate_bytes_per_sample * S / (prof_shape.gate_ms * 1e-3) / 1e9 / peaks["hbm_gbs"]) if prof_shape.gate_ms > 0 else None,
+                         "avg_launch_ms_step_shape": prof_shape.gate_ms / max(1, prof_shape.gate_launches),
+                         "step_shape": "one walk CTA per SM, as every timed step launches it beside the next batch's sampler (here: alone)",
+                         "alg_bytes_full_launch": gate_bytes_per_sample * prof.batch_slabs * prof.slab_samples,
+                         "traffic_over_alg_full_launch": (traffic / (gate_bytes_per_sample * prof.batch_slabs * prof.slab_samples)) if traffic else None},
             "roofline_sampler": {"kernel": kernel_name,
                                  "bound": "int (LOP3 + IMAD.WIDE share one issue rate of 64 lanes/clk/SM)",
                                  "achieved": sampler_rate * alg_ops_per_bit / 1e9, "peak": int_peak / 1e9, "unit": "G int lane-instr/s",
@@ -550,6 +623,12 @@ def main():
             # the same workload under the other threshold width (64-bit thresholds are what p below 1e-8 needs), a quarter step
             ob = 96 - args.threshold_bits
             line["other_configs"][f"{args.workload}_u{ob}"] = side_line(args.workload, local, stream, args.sampler, steps=2, bits=ob, samples=max(S // 4, 1 << 20))
+            if args.workload != "c1":   # config 1: the MEF example through the fused engine
+                line["other_configs"]["c1"] = side_line("c1", local, stream, args.sampler, bits=args.threshold_bits)
+            if spec != 2:   # the literal per-sample compare north_star words (spec 2, "sliced"), a quarter step
+                line["other_configs"][f"{args.workload}_spec2"] = side_line(args.workload, local, stream, 2, steps=2, bits=args.threshold_bits, samples=max(S // 4, 1 << 20))
+            if S_full != S and not args.samples:   # the configuration at its stated sample count, as ONE step on the driver's clock
+                line["other_configs"][f"{args.workload}_full"] = side_line(args.workload, local, stream, args.sampler, steps=1, bits=args.threshold_bits, samples=S_full, warmups=0)
     if rank == 0:
         if args.samples:
             line["config"]["reduced"] = f"--samples {args.samples}: side study, NOT the workload's sample count"

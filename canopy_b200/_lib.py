@@ -54,7 +54,7 @@ class CPlanView(C.Structure):
 class CMcOpts(C.Structure):
     _fields_ = [("seed", C.c_uint64), ("sample_begin", C.c_uint64), ("n_samples", C.c_uint64),
                 ("device", C.c_int32), ("batch_slabs", C.c_int32), ("stream", C.c_void_p),
-                ("overlap", C.c_int32), ("profile", C.c_int32), ("reserved", C.c_int32 * 4)]
+                ("overlap", C.c_int32), ("profile", C.c_int32), ("profile_walk_shape", C.c_int32), ("reserved", C.c_int32 * 3)]
 
 
 class CMcReport(C.Structure):

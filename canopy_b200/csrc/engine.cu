@@ -626,7 +626,7 @@ void mc_run(canopy_plan* plan, const canopy_mc_opts& o, uint64_t* tallies_host, 
             if (profile) { cudaEvent_t e[3]; for (auto& x : e) { CUDA_CHECK(cudaEventCreate(&x)); pe.push_back(x); } CUDA_CHECK(cudaEventRecord(e[0], user)); }
             launch_sampler(s, L, s->vals[0], fs, ns, K, user);
             if (profile) CUDA_CHECK(cudaEventRecord(pe[pe.size() - 2], user));
-            launch_gates(s, L, s->vals[0], fs, ns, begin, end, user, false, 0, 0, (uint32_t)(b & 1));
+            launch_gates(s, L, s->vals[0], fs, ns, begin, end, user, profile && o.profile_walk_shape == 1, 0, 0, (uint32_t)(b & 1));
             if (profile) CUDA_CHECK(cudaEventRecord(pe[pe.size() - 1], user));
             R.sampler_launches += L.n_events() ? 1 : 0; R.gate_launches += 1;
         }

@@ -157,10 +157,12 @@ class Plan:
         return out[: self.n_tallies], _report(rep)
 
     def run_device(self, tallies_ptr: int, n_samples: int, seed: int = 0, sample_begin: int = 0, device: int = 0,
-                   batch_slabs: int = 0, stream=None, overlap: bool = True, profile: bool = False, want_report: bool = False):
+                   batch_slabs: int = 0, stream=None, overlap: bool = True, profile: bool = False, want_report: bool = False,
+                   profile_walk_shape: int = 0):
         """Tallies left in DEVICE memory at `tallies_ptr` (uint64[n_tallies]), ordered on `stream`.
         With want_report=False nothing synchronises the host."""
         o = self._opts(seed, sample_begin, n_samples, device, batch_slabs, stream, overlap, profile)
+        o.profile_walk_shape = int(profile_walk_shape)   # canopy_mc_opts.profile_walk_shape: 1 = the pipeline's one CTA per SM
         rep = _lib.CMcReport()
         _lib.check(_lib.lib().canopy_mc_run_device(self._h, C.byref(o), C.c_void_p(tallies_ptr),
                                                    C.byref(rep) if want_report else None))

@@ -223,7 +223,11 @@ typedef struct canopy_mc_opts {
     int32_t  overlap;         /* 1 (set by canopy_mc_opts_default): the sampler of batch i+1 runs beside the gate walk of
                                  batch i (programmatic dependent launch on the run's stream) */
     int32_t  profile;         /* 1: time sampler / gate kernels separately with CUDA events (serialises the two) */
-    int32_t  reserved[4];
+    int32_t  profile_walk_shape; /* profile = 1 only.  0: each gate walk is launched as a walk that has the GPU to itself
+                                 (several CTAs per SM); 1: in the shape the overlapped pipeline gives it (one CTA per SM,
+                                 the rest of the SM left to the sampler of the next batch), but still alone -- what the
+                                 timed steps actually launch, for the roofline */
+    int32_t  reserved[3];
 } canopy_mc_opts;
 CANOPY_API void canopy_mc_opts_default(canopy_mc_opts* opts);
 

@@ -54,3 +54,18 @@ def test_reference_arm_with_64_bit_thresholds():
                                    "--steps", "1", "--warmup", "0", "--threshold-bits", "64"], env=env, text=True, timeout=300)
     d = json.loads([l for l in out.splitlines() if l.startswith("{")][0])
     assert d["dtype"] == "u64" and d["config"]["threshold_bits"] == 64 and d["value"] > 0
+
+
+def test_recorded_cross_spec_law_check_on_config_c5():
+    """Two recorded 2^36-sample runs of config c5 on 8 GPUs sampled the SAME graph under different specs -- spec 2 (one
+    compare per sample, round 1) and spec 4 (classed sparse, round 2) -- with disjoint random streams.  If both obey the
+    same Bernoulli law per sample, the two top-event estimates differ by less than 3 sigma of their difference."""
+    import json
+    import math
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    a, b = (json.loads(open(os.path.join(root, "profiles", f)).read().strip().splitlines()[-1])
+            for f in ("r01f_c5_full_n8.json", "r02g_c5_full_n8.json"))
+    assert a["samples"] == b["samples"] == 1 << 36 and a["B_live"] == b["B_live"] and a["G_live"] == b["G_live"]
+    sigma_diff = math.hypot(a["sigma"], b["sigma"])
+    assert a["top_event_tally"] != b["top_event_tally"]                  # different streams, not a replay
+    assert abs(a["p_hat"] - b["p_hat"]) < 3.0 * sigma_diff, (a["p_hat"], b["p_hat"], sigma_diff)
