@@ -12,8 +12,10 @@ sample, are the full configuration's (a step is 55 full batches of the pipeline,
 tools/run_c5.py runs the 2^36-sample configuration in one go.
 
 A "step" is one pass of the hot path over the workload's S samples on every rank: rank r evaluates the disjoint
-Philox counter range [(k*N + r)*S, +S) (weak scaling), then ONE all-reduce of the int64 tallies over NCCL.
-`value` = N*S*K / max-over-ranks device time.  Before the timed region `tally_check` runs a FIXED range cut over the
+Philox counter range [(k*N + r)*S, +S) (weak scaling) into row k of a [steps, n_tallies] int64 tensor; after the K timed
+steps ONE all-reduce over NCCL sums those rows across the ranks, inside the timed region (north_star: "a single NCCL
+allreduce of int64 tallies"; until round 2 every step had its own all-reduce, which re-synchronised the ranks K times).
+`value` = N*S*K / max-over-ranks device time; `rank_ms` lists each rank's own device time per step.  Before the timed region `tally_check` runs a FIXED range cut over the
 N ranks by canopy_shard_range with every gate tallied, all-reduces it, and compares it on rank 0 with the same range on
 one GPU and (a prefix) with the CPU oracle; a mismatch exits non-zero.
 `e2e` goes through the public host API every step: lower the graph from HOST arrays (canopy_plan_create),
